@@ -1,0 +1,227 @@
+/*
+ * avdiff_b200.h -- C ABI of libavdiff_b200.so: the B200 (sm_100a) implementation of avdiff's
+ * DDIM + classifier-free-guidance sampling hot path.
+ *
+ * The reference (mauruszach/multimodal_diffusion, "avdiff") is pure Python/PyTorch and has no FFI
+ * layer; its "plugin surface" for this path is a set of Python callables.  Each entry point below
+ * names the reference callable it stands in for (file:line relative to the reference root).  The
+ * Python package `multimodal_diffusion_b200.avdiff` binds these with ctypes and re-exposes them
+ * under the reference's own module/function names.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless the name ends in `_host`;
+ *   - the caller owns and allocates every buffer, including workspaces; the library keeps no state
+ *     besides a cache of TMA descriptors keyed by (pointer, shape) and the last error string;
+ *   - `stream` is a `cudaStream_t` passed as `void*`; all work is enqueued on it, nothing
+ *     synchronises, everything is CUDA-graph capturable;
+ *   - return value 0 = success, negative = error (message via avd_last_error());
+ *   - no CPU fallback exists anywhere in this library.
+ *
+ * Precision modes for the tensor-core GEMMs (bf16 operands, fp32 accumulation in TMEM):
+ *   AVD_PREC_BF16   (1)  plain bf16 operands;
+ *   AVD_PREC_BF16X3 (3)  operands split hi+lo, 3 partial products  (~16 mantissa bits);
+ *   AVD_PREC_FP32   (6)  operands split hi+mid+lo, 6 partial products (~fp32 products).
+ * An activation or weight matrix for mode p is stored as avd_nseg(p) bf16 matrices back to back
+ * ("segments": hi[,mid],lo).
+ */
+#ifndef AVDIFF_B200_H_
+#define AVDIFF_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define AVD_PREC_BF16 1
+#define AVD_PREC_BF16X3 3
+#define AVD_PREC_FP32 6
+
+#define AVD_TARGET_VIDEO 0 /* A2V: audio prompt, video generated (sample_clip.py:354-393) */
+#define AVD_TARGET_AUDIO 1 /* V2A: video prompt, audio generated (sample_clip.py:312-352) */
+
+#define AVD_MAX_LAYERS 64
+#define AVD_MAX_SHARED 8
+
+/* ---------------------------------------------------------------- housekeeping */
+const char* avd_last_error(void);
+int avd_version(void);
+int avd_nseg(int precision);                 /* 1 -> 1, 3 -> 2, 6 -> 3, else -1 */
+int avd_device_check(void);                  /* 0 iff the current device is sm_100 */
+
+/* Per-launch profiler (CUDA events on `stream` around every kernel this library launches).
+ * Used by bench.py for the roofline object; must be off during graph capture. */
+int avd_prof_enable(int on);
+int avd_prof_reset(void);
+int avd_prof_num_kinds(void);
+const char* avd_prof_kind_name(int kind);
+/* synchronises the recorded events; returns total ms and launch count of `kind` */
+int avd_prof_collect(int kind, double* total_ms, int64_t* launches);
+int64_t avd_launch_count(void);              /* kernels launched by this library so far */
+
+/* ---------------------------------------------------------------- K1: tokenisers (bit-exact fp32 moves) */
+/* ops.tube_patch_video (avdiff/utils/ops.py:100-119): z[B,C,T,H,W] -> tok[B,(T/t)(H/h)(W/w),C*t*h*w] */
+int avd_tube_patch(const float* z, float* tok, int B, int C, int T, int H, int W, int t, int h, int w, void* stream);
+/* ops.tube_unpatch_video (ops.py:122-144) */
+int avd_tube_unpatch(const float* tok, float* z, int B, int C, int T, int H, int W, int t, int h, int w, void* stream);
+/* ops.chunk_1d + permute (ops.py:17-45, sample_clip.py:184-188, tokenizers.py:83-88):
+ * z[B,C,L] -> tok[B,N,C*length], N = (L-length)/stride+1 */
+int avd_chunk1d(const float* z, float* tok, int B, int C, int L, int length, int stride, void* stream);
+/* ops.overlap_add_1d + crop/zero-pad (ops.py:48-93, sample_clip.py:191-215, tokenizers.py:90-114):
+ * tok[B,N,C*length] -> z[B,C,L_out]; windows summed in order i=0..N-1, divided by max(count,1e-8) */
+int avd_unchunk1d(const float* tok, float* z, int B, int C, int N, int length, int stride, int L_out, void* stream);
+
+/* ---------------------------------------------------------------- schedules */
+/* su.timestep_embedding (avdiff/utils/schedule_utils.py:64-86): t[B] (float) -> emb[B,dim] = [cos | sin] (+0 pad if odd) */
+int avd_timestep_embedding(const float* t, float* emb, int B, int dim, float max_period, void* stream);
+/* su.ddim_step (schedule_utils.py:146-200) / ModalitySchedule.ddim_step (models/schedules.py:65-74).
+ * x_t, eps_hat, x_prev: [B, per_batch] fp32; t_now/t_prev: int64 [B]; alpha_bar: fp32 [T_train];
+ * noise: the z ~ N(0,1) tensor of the eta>0 branch (may be NULL when eta == 0). */
+int avd_ddim_step(const float* x_t, const float* eps_hat, const float* noise, float* x_prev, const int64_t* t_now,
+                  const int64_t* t_prev, const float* alpha_bar, int T_train, int B, int64_t per_batch, float eta,
+                  void* stream);
+
+/* ---------------------------------------------------------------- K7: fused CFG + un-tokenise + DDIM */
+/* sample_clip.py:342-348 (audio) / 381-389 (video): eps = eps_n + g (eps_c - eps_n) -> latent layout -> ddim_step(eta=0).
+ * eps_cond/eps_null: token layout [B, Nt, Dt]; z_t/z_prev latent layout (may alias).
+ * video: C,T,H,W + tube (t,h,w); audio: C, L=Fa + chunk (length, stride), Nt windows. */
+typedef struct {
+  int target;                 /* AVD_TARGET_* */
+  int B;
+  int C, T, H, W, tt, th, tw; /* video latent + tube (target == video) */
+  int L, length, stride, Nt;  /* audio latent length Fa, chunk, window count (target == audio) */
+  float guidance;
+  int t_now, t_prev;          /* integer timesteps (t_prev may be -1) */
+  int T_train;
+} avd_cfg_ddim_args;
+int avd_cfg_untok_ddim(const avd_cfg_ddim_args* a, const float* eps_cond, const float* eps_null, const float* z_t,
+                       float* z_prev, const float* alpha_bar, void* stream);
+
+/* ---------------------------------------------------------------- operand preparation */
+/* nn.Linear weight [N,K] fp32 (optionally scaled per input column, used to fold a norm's `scale`)
+ * -> avd_nseg(precision) bf16 segments [nseg][N][K]. */
+int avd_pack_weight(const float* W, const float* col_scale, void* out_bf16, int N, int K, int precision, void* stream);
+/* transpose W[N,K] -> Wt[K,N] fp32 (adapter weights for the fused input builder) */
+int avd_transpose_f32(const float* W, float* Wt, int N, int K, void* stream);
+/* x[M,d] fp32 -> bf16 segments [nseg][M][d] + per-row partial sums of squares ssq[M][d/64] */
+int avd_rows_prepare(const float* x, void* xa_bf16, float* ssq, int M, int d, int precision, void* stream);
+/* RMSNorm (mmdt.py:39-42) of rows [row_off, row_off+n_rows) of each of n_seq sequences of N rows:
+ * y = scale * x / (||x||/sqrt(d) + eps).  Output compact [n_seq*n_rows, d] as fp32 and/or bf16 segments. */
+int avd_rmsnorm_rows(const float* x, const float* scale, int n_seq, int N, int row_off, int n_rows, int d, float eps,
+                     float* out_f32, void* out_bf16, int precision, void* stream);
+/* nn.LayerNorm(d, eps) + GELU(erf) (noise_heads.py:139-146): y[M,d] fp32 -> bf16 segments and/or fp32.
+ * apply_gelu = 0 gives a plain LayerNorm. */
+int avd_layernorm_act(const float* y, const float* w, const float* b, int M, int d, float eps, int apply_gelu,
+                      float* out_f32, void* out_bf16, int precision, void* stream);
+
+/* ---------------------------------------------------------------- K4: tcgen05 GEMM with fused prologue/epilogue */
+/* out = epilogue( A[M,K] * W[N,K]^T ).  Stands in for nn.Linear.forward (mmdt.py:54-60,70-71,
+ * noise_heads.py:131-177, sample_clip.py:52) plus the elementwise ops around it:
+ *   v = acc * rinv(row) + bias[col] (+ resid[row,col]);  v = gelu_erf(v) if act;
+ *   rinv(row) = 1/(sqrt(sum_p ssq_in[row,p]) / sqrt(rms_dim) + rms_eps)   -- the RMSNorm prologue of the
+ *   reference, applied after the MMA (its `scale` is folded into W's columns by avd_pack_weight). */
+typedef struct {
+  int M, N, K;
+  int precision;
+  const void* A;            /* bf16 [nseg][M][K] */
+  const void* W;            /* bf16 [nseg][N][K] */
+  const float* bias;        /* [N] or NULL */
+  const float* ssq_in;      /* [M][ssq_parts] or NULL (no row scaling) */
+  int ssq_parts;
+  int rms_dim;
+  float rms_eps;
+  const float* resid;       /* fp32 [M][N] or NULL */
+  int act;                  /* 0 none, 1 GELU(erf) */
+  float* out_f32;           /* fp32 [M][N] or NULL */
+  void* out_bf16;           /* bf16 [out_nseg][M][N] or NULL */
+  int out_precision;        /* precision of the consumer of out_bf16 (selects the segment count) */
+  float* ssq_out;           /* [M][N/64] partial sums of squares of v, or NULL */
+} avd_gemm_args;
+int avd_gemm(const avd_gemm_args* g, void* stream);
+
+/* ---------------------------------------------------------------- K5: joint video+audio self-attention */
+/* nn.MultiheadAttention core (mmdt.py:58-61): per sequence and head softmax(q k^T / sqrt(hd)) v, full
+ * bidirectional, no mask.  qkv: [n_seq*N, 3*d] (columns q | k | v, head j = columns 64j..64j+63 of each),
+ * bf16 when qkv_is_f32 == 0 (tcgen05 flash kernel), fp32 otherwise (fp32 CUDA-core kernel for fp32 mode).
+ * out: bf16 segments [nseg(out_precision)][n_seq*N][d]. */
+int avd_attention(const void* qkv, int qkv_is_f32, void* out_bf16, int out_precision, int n_seq, int N, int n_heads,
+                  int head_dim, void* stream);
+
+/* ---------------------------------------------------------------- K6: MMDT core + noise head */
+typedef struct {
+  const void* w_qkv;  const float* b_qkv;   /* [3d,d] with norm1.scale folded */
+  const void* w_o;    const float* b_o;     /* [d,d] */
+  const void* w_fc1;  const float* b_fc1;   /* [d_mlp,d] with norm2.scale folded */
+  const void* w_fc2;  const float* b_fc2;   /* [d,d_mlp] */
+} avd_block_weights;
+
+typedef struct {
+  int d_model, n_heads, n_layers, d_mlp;
+  int precision;
+  float rms_eps;
+  avd_block_weights blocks[AVD_MAX_LAYERS];
+  const float* final_scale;                 /* final_norm.scale [d] */
+} avd_core_weights;
+
+/* Caller-allocated work buffers for M = n_seq*N rows (S = avd_nseg(precision)):
+ *   x fp32 [M,d]; xa bf16 [S][M,d]; ssq fp32 [M, d/64]; qkv bf16 [M,3d] (fp32 in AVD_PREC_FP32 mode);
+ *   att bf16 [S][M,d]; hmid bf16 [S][M,d_mlp]. */
+typedef struct {
+  float* x; void* xa; float* ssq; void* qkv; void* att; void* hmid;
+} avd_core_workspace;
+
+/* MMDiT.forward minus the final norm (mmdt.py:146-147): runs n_layers blocks.  Reads the input residual
+ * stream from (x_in, xa_in, ssq_in) -- which it never writes -- and leaves the result in ws->x/xa/ssq. */
+int avd_mmdt_blocks(const avd_core_weights* w, const float* x_in, const void* xa_in, const float* ssq_in,
+                    const avd_core_workspace* ws, int n_seq, int N, void* stream);
+
+typedef struct {
+  int d_in, hidden, d_out, n_shared;
+  int precision;
+  float ln_eps;
+  const void* w_in;  const float* b_in;                      /* input_proj[m]  */
+  const void* w_s[AVD_MAX_SHARED]; const float* b_s[AVD_MAX_SHARED];    /* shared[i][0]   */
+  const float* ln_w[AVD_MAX_SHARED]; const float* ln_b[AVD_MAX_SHARED]; /* shared[i][1]   */
+  const void* w_out; const float* b_out;                     /* out_proj[m]    */
+} avd_head_weights;
+
+/* MultiModalNoiseHead.forward for one modality (noise_heads.py:201-220).  h: bf16 segments [S][M][d_in];
+ * act_a/act_b: bf16 [S][M][hidden] scratch; y: fp32 [M][hidden] scratch; eps: fp32 [M][d_out]. */
+int avd_head_forward(const avd_head_weights* w, const void* h, int M, void* act_a, void* act_b, float* y, float* eps,
+                     void* stream);
+
+/* ---------------------------------------------------------------- K8: the sampling loop */
+typedef struct {
+  int target;                       /* AVD_TARGET_* */
+  int B;                            /* clips in this batch; cond+null are co-batched as 2B sequences */
+  int Cv, T, H, W, tt, th, tw;      /* video latent [B,Cv,T,H,W], tube (sampler uses tube.h for h and w) */
+  int Ca, Fa, chunk_len, chunk_stride;
+  int tstep_dim;                    /* width of the concatenated timestep embedding */
+  int steps;                        /* sampler steps S */
+  int T_train;
+  float guidance;
+  const int64_t* timesteps_host;    /* HOST int64 [S+1] (su.make_sampling_schedule) */
+  const float* temb_steps;          /* [S][tstep_dim]: su.timestep_embedding(t_now(step)) */
+  const float* temb_zero;           /* [tstep_dim]: embedding of t = 0 (prompt rows) */
+  const float* alpha_bar;           /* [T_train] */
+  const float* wv_t; const float* bv;   /* video adapter, transposed [Dv][d-tstep_dim], bias */
+  const float* wa_t; const float* ba;   /* audio adapter, transposed [Da][d-tstep_dim], bias */
+  avd_core_weights core;
+  avd_head_weights head;            /* the TARGET modality's head */
+  void* workspace;                  /* >= avd_sampler_workspace_bytes() */
+  int64_t workspace_bytes;
+} avd_sampler;
+
+int64_t avd_sampler_workspace_bytes(const avd_sampler* s);
+/* loop-invariant part (F10): tokenise + adapt the prompt latent, t=0 embedding, zeroed null-branch prompt rows */
+int avd_sample_prepare(const avd_sampler* s, const float* z_prompt, void* stream);
+/* one DDIM+CFG step `step` in [0,S): z (target latent) is updated in place.  Optional taps (may be NULL):
+ * eps_tap [2B,Nt,Dt] receives the per-branch head output (cond rows first, then null). */
+int avd_sample_step(const avd_sampler* s, int step, float* z, float* eps_tap, void* stream);
+/* sample_one_direction's loop (sample_clip.py:317-348 / 359-389) for a batch: prepare + S steps. */
+int avd_sample_loop(const avd_sampler* s, const float* z_prompt, float* z, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* AVDIFF_B200_H_ */

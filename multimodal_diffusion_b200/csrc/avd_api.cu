@@ -1,0 +1,529 @@
+// avd_api.cu -- the C ABI of libavdiff_b200.so (include/avdiff_b200.h): argument validation, launch
+// accounting / event profiler, TMA descriptor cache, and the host-side sequencing of the MMDT blocks, the
+// noise head and the DDIM + CFG sampling loop.  Nothing here allocates device memory or synchronises.
+#include "avd_internal.h"
+
+#include <cmath>
+#include <cstring>
+#include <mutex>
+#include <unordered_map>
+#include <vector>
+
+namespace avd {
+
+// ---------------------------------------------------------------------------------------------------
+// errors
+// ---------------------------------------------------------------------------------------------------
+static thread_local std::string g_last_error;
+
+void set_error(const std::string& msg) { g_last_error = msg; }
+
+int fail(const char* file, int line, const std::string& msg) {
+  const char* base = std::strrchr(file, '/');
+  g_last_error = std::string(base ? base + 1 : file) + ":" + std::to_string(line) + ": " + msg;
+  return -1;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// launch accounting + optional CUDA-event profiler
+// ---------------------------------------------------------------------------------------------------
+static const char* kKindNames[KIND_COUNT] = {"tokenize", "build_x",  "gemm_tcgen05", "attn_tcgen05", "attn_f32",
+                                             "norm",     "ln_act",   "cfg_untok_ddim", "pack",       "misc"};
+struct ProfRecord {
+  int kind;
+  cudaEvent_t beg, end;
+};
+static std::mutex g_prof_mu;
+static bool g_prof_on = false;
+static std::vector<ProfRecord> g_prof;
+static std::vector<cudaEvent_t> g_event_pool;
+static int64_t g_launches = 0;
+
+static cudaEvent_t take_event() {
+  if (!g_event_pool.empty()) {
+    cudaEvent_t e = g_event_pool.back();
+    g_event_pool.pop_back();
+    return e;
+  }
+  cudaEvent_t e = nullptr;
+  cudaEventCreate(&e);
+  return e;
+}
+
+LaunchScope::LaunchScope(Kind k, cudaStream_t s) : kind(k), stream(s), slot(-1) {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  ++g_launches;
+  if (g_prof_on) {
+    ProfRecord r{(int)k, take_event(), take_event()};
+    cudaEventRecord(r.beg, s);
+    g_prof.push_back(r);
+    slot = (int)g_prof.size() - 1;
+  }
+}
+
+LaunchScope::~LaunchScope() {
+  if (slot >= 0) {
+    std::lock_guard<std::mutex> lk(g_prof_mu);
+    cudaEventRecord(g_prof[slot].end, stream);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// TMA descriptor cache
+// ---------------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn g_encode = nullptr;
+
+struct MapKey {
+  const void* base;
+  uint64_t d0, d1, d2, s1, s2;
+  uint32_t b0, b1;
+  bool operator==(const MapKey& o) const {
+    return base == o.base && d0 == o.d0 && d1 == o.d1 && d2 == o.d2 && s1 == o.s1 && s2 == o.s2 && b0 == o.b0 &&
+           b1 == o.b1;
+  }
+};
+struct MapKeyHash {
+  size_t operator()(const MapKey& k) const {
+    uint64_t h = reinterpret_cast<uint64_t>(k.base);
+    auto mix = [&](uint64_t v) { h ^= v + 0x9e3779b97f4a7c15ull + (h << 6) + (h >> 2); };
+    mix(k.d0); mix(k.d1); mix(k.d2); mix(k.s1); mix(k.s2); mix(k.b0); mix(k.b1);
+    return (size_t)h;
+  }
+};
+static std::mutex g_map_mu;
+static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> g_maps;
+
+int get_tensor_map_bf16_3d(const void* base, uint64_t d0, uint64_t d1, uint64_t d2, uint64_t stride1_bytes,
+                           uint64_t stride2_bytes, uint32_t box0, uint32_t box1, CUtensorMap* out) {
+  std::lock_guard<std::mutex> lk(g_map_mu);
+  if (g_encode == nullptr) {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+    if (e != cudaSuccess || fn == nullptr || qres != cudaDriverEntryPointSuccess)
+      AVD_FAIL("cuTensorMapEncodeTiled not available from the CUDA driver");
+    g_encode = reinterpret_cast<EncodeTiledFn>(fn);
+  }
+  MapKey key{base, d0, d1, d2, stride1_bytes, stride2_bytes, box0, box1};
+  auto it = g_maps.find(key);
+  if (it != g_maps.end()) {
+    *out = it->second;
+    return 0;
+  }
+  AVD_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "TMA base must be 16-byte aligned");
+  AVD_REQUIRE(stride1_bytes % 16 == 0 && stride2_bytes % 16 == 0, "TMA strides must be multiples of 16 bytes");
+  AVD_REQUIRE(box0 * 2 == 128, "inner box must span one 128-byte swizzle row");
+  AVD_REQUIRE(box1 >= 1 && box1 <= 256, "box rows out of range");
+  cuuint64_t dims[3] = {d0, d1, d2};
+  cuuint64_t strides[2] = {stride1_bytes, stride2_bytes};
+  cuuint32_t box[3] = {box0, box1, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUtensorMap m;
+  CUresult r = g_encode(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) AVD_FAIL("cuTensorMapEncodeTiled failed with CUresult " + std::to_string((int)r));
+  if (g_maps.size() > 8192) g_maps.clear();
+  g_maps.emplace(key, m);
+  *out = m;
+  return 0;
+}
+
+static inline int64_t align_up(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
+
+// ---------------------------------------------------------------------------------------------------
+// sampler workspace carving (shared by avd_sampler_workspace_bytes and the step functions)
+// ---------------------------------------------------------------------------------------------------
+struct SamplerLayout {
+  int Nv, Na, N, Nt, Dt, Dv, Da, d, d_adapt, n_seq, Mt, parts, S_core, S_head;
+  int row_off_v, row_off_a;
+  int64_t M;
+  // offsets in bytes
+  int64_t x_init, xa_init, ssq_init, x, xa, ssq, qkv, att, hmid, h, act_a, act_b, y, eps, total;
+};
+
+static int sampler_layout(const avd_sampler* s, SamplerLayout* L) {
+  AVD_REQUIRE(s != nullptr, "null sampler");
+  AVD_REQUIRE(s->target == AVD_TARGET_VIDEO || s->target == AVD_TARGET_AUDIO, "bad target");
+  AVD_REQUIRE(s->B > 0, "B must be positive");
+  AVD_REQUIRE(s->tt > 0 && s->th > 0 && s->tw > 0 && s->T % s->tt == 0 && s->H % s->th == 0 && s->W % s->tw == 0,
+              "tube sizes must divide latent dims");
+  AVD_REQUIRE(s->chunk_len > 0 && s->chunk_stride > 0 && s->Fa >= s->chunk_len, "bad audio chunking");
+  AVD_REQUIRE(s->core.n_layers > 0 && s->core.n_layers <= AVD_MAX_LAYERS, "bad layer count");
+  AVD_REQUIRE(s->head.n_shared >= 0 && s->head.n_shared <= AVD_MAX_SHARED, "bad shared-layer count");
+  L->S_core = nseg_of(s->core.precision);
+  L->S_head = nseg_of(s->head.precision);
+  AVD_REQUIRE(L->S_core > 0 && L->S_head > 0, "bad precision");
+  L->Nv = (s->T / s->tt) * (s->H / s->th) * (s->W / s->tw);
+  L->Na = (s->Fa - s->chunk_len) / s->chunk_stride + 1;
+  L->N = L->Nv + L->Na;
+  L->Dv = s->Cv * s->tt * s->th * s->tw;
+  L->Da = s->Ca * s->chunk_len;
+  L->d = s->core.d_model;
+  L->d_adapt = L->d - s->tstep_dim;
+  AVD_REQUIRE(L->d_adapt > 0, "tstep_dim must be smaller than d_model");
+  AVD_REQUIRE(L->d % 64 == 0, "d_model must be a multiple of 64");
+  AVD_REQUIRE(s->head.d_in == L->d, "head input width must equal d_model");
+  L->row_off_v = 0;
+  L->row_off_a = L->Nv;
+  L->Nt = s->target == AVD_TARGET_VIDEO ? L->Nv : L->Na;
+  L->Dt = s->target == AVD_TARGET_VIDEO ? L->Dv : L->Da;
+  AVD_REQUIRE(s->head.d_out == L->Dt, "head output width must equal the target token width");
+  L->n_seq = 2 * s->B;
+  L->M = (int64_t)L->n_seq * L->N;
+  L->Mt = L->n_seq * L->Nt;
+  L->parts = L->d / 64;
+  const int64_t d = L->d, M = L->M, Mt = L->Mt, dm = s->core.d_mlp, hid = s->head.hidden;
+  int64_t off = 0;
+  auto take = [&](int64_t bytes) { int64_t o = off; off = align_up(off + bytes, 1024); return o; };
+  L->x_init = take(M * d * 4);
+  L->xa_init = take((int64_t)L->S_core * M * d * 2);
+  L->ssq_init = take(M * L->parts * 4);
+  L->x = take(M * d * 4);
+  L->xa = take((int64_t)L->S_core * M * d * 2);
+  L->ssq = take(M * L->parts * 4);
+  L->qkv = take(M * 3 * d * (s->core.precision == AVD_PREC_BF16 ? 2 : 4));
+  L->att = take((int64_t)L->S_core * M * d * 2);
+  L->hmid = take((int64_t)L->S_core * M * dm * 2);
+  L->h = take((int64_t)L->S_head * Mt * d * 2);
+  L->act_a = take((int64_t)L->S_head * Mt * hid * 2);
+  L->act_b = take((int64_t)L->S_head * Mt * hid * 2);
+  L->y = take(Mt * hid * 4);
+  L->eps = take(Mt * (int64_t)L->Dt * 4);
+  L->total = off;
+  return 0;
+}
+
+static int core_blocks(const avd_core_weights* w, const float* x_in, const void* xa_in, const float* ssq_in,
+                       const avd_core_workspace* ws, int n_seq, int N, cudaStream_t st) {
+  AVD_REQUIRE(w != nullptr && ws != nullptr, "null argument");
+  const int d = w->d_model, S = nseg_of(w->precision);
+  AVD_REQUIRE(S > 0, "bad precision");
+  AVD_REQUIRE(d % 64 == 0 && w->n_heads > 0 && d % w->n_heads == 0, "bad d_model / n_heads");
+  AVD_REQUIRE(w->n_layers > 0 && w->n_layers <= AVD_MAX_LAYERS, "bad layer count");
+  const int M = n_seq * N, parts = d / 64, hd = d / w->n_heads;
+  const bool tc_attn = (w->precision == AVD_PREC_BF16);
+  for (int l = 0; l < w->n_layers; ++l) {
+    const avd_block_weights& b = w->blocks[l];
+    const void* a_in = (l == 0) ? xa_in : ws->xa;
+    const float* s_in = (l == 0) ? ssq_in : ws->ssq;
+    const float* r_in = (l == 0) ? x_in : ws->x;
+    // qkv = RMS1(x) W_in^T + b_in        (mmdt.py:97 -> :60)
+    avd_gemm_args g{};
+    g.M = M; g.N = 3 * d; g.K = d; g.precision = w->precision;
+    g.A = a_in; g.W = b.w_qkv; g.bias = b.b_qkv;
+    g.ssq_in = s_in; g.ssq_parts = parts; g.rms_dim = d; g.rms_eps = w->rms_eps;
+    if (tc_attn) { g.out_bf16 = ws->qkv; g.out_precision = AVD_PREC_BF16; }
+    else g.out_f32 = static_cast<float*>(ws->qkv);
+    AVD_TRY(launch_gemm(g, st));
+    // a = softmax(q k^T / sqrt(hd)) v
+    if (tc_attn) AVD_TRY(launch_attention_tc(ws->qkv, ws->att, S, n_seq, N, w->n_heads, hd, st));
+    else AVD_TRY(launch_attention_f32(static_cast<const float*>(ws->qkv), ws->att, S, n_seq, N, w->n_heads, hd, st));
+    // x = x + a W_o^T + b_o               (mmdt.py:97)
+    g = avd_gemm_args{};
+    g.M = M; g.N = d; g.K = d; g.precision = w->precision;
+    g.A = ws->att; g.W = b.w_o; g.bias = b.b_o; g.resid = r_in;
+    g.out_f32 = ws->x; g.out_bf16 = ws->xa; g.out_precision = w->precision; g.ssq_out = ws->ssq;
+    AVD_TRY(launch_gemm(g, st));
+    // u = gelu(RMS2(x) W_1^T + b_1)       (mmdt.py:98 -> :78-79)
+    g = avd_gemm_args{};
+    g.M = M; g.N = w->d_mlp; g.K = d; g.precision = w->precision;
+    g.A = ws->xa; g.W = b.w_fc1; g.bias = b.b_fc1;
+    g.ssq_in = ws->ssq; g.ssq_parts = parts; g.rms_dim = d; g.rms_eps = w->rms_eps; g.act = 1;
+    g.out_bf16 = ws->hmid; g.out_precision = w->precision;
+    AVD_TRY(launch_gemm(g, st));
+    // x = x + u W_2^T + b_2               (mmdt.py:98 -> :81)
+    g = avd_gemm_args{};
+    g.M = M; g.N = d; g.K = w->d_mlp; g.precision = w->precision;
+    g.A = ws->hmid; g.W = b.w_fc2; g.bias = b.b_fc2; g.resid = ws->x;
+    g.out_f32 = ws->x; g.out_bf16 = ws->xa; g.out_precision = w->precision; g.ssq_out = ws->ssq;
+    AVD_TRY(launch_gemm(g, st));
+  }
+  return 0;
+}
+
+static int head_forward(const avd_head_weights* w, const void* h, int M, void* act_a, void* act_b, float* y,
+                        float* eps, cudaStream_t st) {
+  AVD_REQUIRE(w != nullptr, "null head");
+  AVD_REQUIRE(w->n_shared >= 0 && w->n_shared <= AVD_MAX_SHARED, "bad shared-layer count");
+  const int S = nseg_of(w->precision);
+  AVD_REQUIRE(S > 0, "bad precision");
+  avd_gemm_args g{};
+  // x = input_proj[m](h)                  (noise_heads.py:205)
+  g.M = M; g.N = w->hidden; g.K = w->d_in; g.precision = w->precision;
+  g.A = h; g.W = w->w_in; g.bias = w->b_in; g.out_bf16 = act_a; g.out_precision = w->precision;
+  AVD_TRY(launch_gemm(g, st));
+  void* cur = act_a;
+  void* nxt = act_b;
+  for (int i = 0; i < w->n_shared; ++i) {   // x = gelu(LN(Linear(x)))   (noise_heads.py:139-146, :208)
+    g = avd_gemm_args{};
+    g.M = M; g.N = w->hidden; g.K = w->hidden; g.precision = w->precision;
+    g.A = cur; g.W = w->w_s[i]; g.bias = w->b_s[i]; g.out_f32 = y;
+    AVD_TRY(launch_gemm(g, st));
+    AVD_TRY(launch_layernorm_act(y, w->ln_w[i], w->ln_b[i], M, w->hidden, w->ln_eps, 1, nullptr, nxt, S, st));
+    void* t = cur; cur = nxt; nxt = t;
+  }
+  g = avd_gemm_args{};                       // eps = out_proj[m](x)   (noise_heads.py:219)
+  g.M = M; g.N = w->d_out; g.K = w->hidden; g.precision = w->precision;
+  g.A = cur; g.W = w->w_out; g.bias = w->b_out; g.out_f32 = eps;
+  AVD_TRY(launch_gemm(g, st));
+  return 0;
+}
+
+static BuildXArgs make_build_args(const avd_sampler* s, const SamplerLayout& L, int modality, bool cond, bool null) {
+  BuildXArgs a{};
+  a.modality = modality;
+  a.B = s->B;
+  a.C = modality == 0 ? s->Cv : s->Ca;
+  a.T = s->T; a.H = s->H; a.W = s->W; a.tt = s->tt; a.th = s->th; a.tw = s->tw;
+  a.L = s->Fa; a.length = s->chunk_len; a.stride = s->chunk_stride;
+  a.n_tok = modality == 0 ? L.Nv : L.Na;
+  a.d_tok = modality == 0 ? L.Dv : L.Da;
+  a.d_adapt = L.d_adapt;
+  a.tstep_dim = s->tstep_dim;
+  a.d = L.d;
+  a.N = L.N;
+  a.row_off = modality == 0 ? L.row_off_v : L.row_off_a;
+  a.n_seq_total = L.n_seq;
+  a.write_cond = cond; a.write_null = null;
+  a.nseg = L.S_core;
+  a.ssq_parts = L.parts;
+  a.M = L.M;
+  return a;
+}
+
+}  // namespace avd
+
+using namespace avd;
+
+#define AVD_STREAM(s) static_cast<cudaStream_t>(s)
+
+extern "C" {
+
+const char* avd_last_error(void) { return g_last_error.c_str(); }
+int avd_version(void) { return 100; }
+int avd_nseg(int precision) { return nseg_of(precision); }
+
+int avd_device_check(void) {
+  int dev = 0;
+  AVD_CUDA(cudaGetDevice(&dev));
+  cudaDeviceProp prop;
+  AVD_CUDA(cudaGetDeviceProperties(&prop, dev));
+  if (prop.major != 10) AVD_FAIL(std::string("device is sm_") + std::to_string(prop.major * 10 + prop.minor) +
+                                 ", this library is built for sm_100a only");
+  return 0;
+}
+
+int avd_prof_enable(int on) {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  g_prof_on = on != 0;
+  return 0;
+}
+int avd_prof_reset(void) {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  for (auto& r : g_prof) { g_event_pool.push_back(r.beg); g_event_pool.push_back(r.end); }
+  g_prof.clear();
+  return 0;
+}
+int avd_prof_num_kinds(void) { return KIND_COUNT; }
+const char* avd_prof_kind_name(int kind) { return (kind >= 0 && kind < KIND_COUNT) ? kKindNames[kind] : ""; }
+int avd_prof_collect(int kind, double* total_ms, int64_t* launches) {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  double tot = 0.0;
+  int64_t n = 0;
+  for (auto& r : g_prof) {
+    if (r.kind != kind) continue;
+    AVD_CUDA(cudaEventSynchronize(r.end));
+    float ms = 0.0f;
+    AVD_CUDA(cudaEventElapsedTime(&ms, r.beg, r.end));
+    tot += ms;
+    ++n;
+  }
+  if (total_ms) *total_ms = tot;
+  if (launches) *launches = n;
+  return 0;
+}
+int64_t avd_launch_count(void) { return g_launches; }
+
+// ---- tokenisers
+int avd_tube_patch(const float* z, float* tok, int B, int C, int T, int H, int W, int t, int h, int w, void* stream) {
+  AVD_REQUIRE(B >= 0 && C > 0 && T > 0 && H > 0 && W > 0, "bad latent shape");
+  AVD_REQUIRE(t > 0 && h > 0 && w > 0 && T % t == 0 && H % h == 0 && W % w == 0, "tube sizes must divide latent dims");
+  return launch_tube_patch(z, tok, B, C, T, H, W, t, h, w, false, AVD_STREAM(stream));
+}
+int avd_tube_unpatch(const float* tok, float* z, int B, int C, int T, int H, int W, int t, int h, int w, void* stream) {
+  AVD_REQUIRE(B >= 0 && C > 0 && T > 0 && H > 0 && W > 0, "bad latent shape");
+  AVD_REQUIRE(t > 0 && h > 0 && w > 0 && T % t == 0 && H % h == 0 && W % w == 0, "tube sizes must divide latent dims");
+  return launch_tube_patch(tok, z, B, C, T, H, W, t, h, w, true, AVD_STREAM(stream));
+}
+int avd_chunk1d(const float* z, float* tok, int B, int C, int L, int length, int stride, void* stream) {
+  AVD_REQUIRE(length > 0 && stride > 0 && L >= length, "chunk_1d needs 0 < length <= L and stride > 0");
+  return launch_chunk1d(z, tok, B, C, L, length, stride, AVD_STREAM(stream));
+}
+int avd_unchunk1d(const float* tok, float* z, int B, int C, int N, int length, int stride, int L_out, void* stream) {
+  AVD_REQUIRE(length > 0 && stride > 0 && N > 0 && L_out >= 0, "bad overlap-add shape");
+  return launch_unchunk1d(tok, z, B, C, N, length, stride, L_out, AVD_STREAM(stream));
+}
+
+// ---- schedules
+int avd_timestep_embedding(const float* t, float* emb, int B, int dim, float max_period, void* stream) {
+  AVD_REQUIRE(dim > 0 && max_period > 0, "bad embedding shape");
+  return launch_timestep_embedding(t, emb, B, dim, max_period, AVD_STREAM(stream));
+}
+int avd_ddim_step(const float* x_t, const float* eps_hat, const float* noise, float* x_prev, const int64_t* t_now,
+                  const int64_t* t_prev, const float* alpha_bar, int T_train, int B, int64_t per_batch, float eta,
+                  void* stream) {
+  AVD_REQUIRE(eta == 0.0f || noise != nullptr, "eta > 0 needs the noise tensor");
+  AVD_REQUIRE(B <= 65535, "batch too large for one launch");
+  return launch_ddim_step(x_t, eps_hat, noise, x_prev, t_now, t_prev, alpha_bar, T_train, B, per_batch, eta,
+                          AVD_STREAM(stream));
+}
+int avd_cfg_untok_ddim(const avd_cfg_ddim_args* a, const float* eps_cond, const float* eps_null, const float* z_t,
+                       float* z_prev, const float* alpha_bar, void* stream) {
+  AVD_REQUIRE(a != nullptr, "null args");
+  AVD_REQUIRE(a->t_now < a->T_train && a->t_prev < a->T_train, "timestep out of range");
+  if (a->target == AVD_TARGET_VIDEO) {
+    AVD_REQUIRE(a->tt > 0 && a->th > 0 && a->tw > 0 && a->T % a->tt == 0 && a->H % a->th == 0 && a->W % a->tw == 0,
+                "tube sizes must divide latent dims");
+  } else {
+    AVD_REQUIRE(a->target == AVD_TARGET_AUDIO && a->length > 0 && a->stride > 0 && a->Nt > 0, "bad audio args");
+  }
+  return launch_cfg_untok_ddim(*a, eps_cond, eps_null, z_t, z_prev, alpha_bar, AVD_STREAM(stream));
+}
+
+// ---- operand preparation
+int avd_pack_weight(const float* W, const float* col_scale, void* out_bf16, int N, int K, int precision, void* stream) {
+  AVD_REQUIRE(nseg_of(precision) > 0, "bad precision");
+  return launch_pack_weight(W, col_scale, out_bf16, N, K, nseg_of(precision), AVD_STREAM(stream));
+}
+int avd_transpose_f32(const float* W, float* Wt, int N, int K, void* stream) {
+  return launch_transpose(W, Wt, N, K, AVD_STREAM(stream));
+}
+int avd_rows_prepare(const float* x, void* xa_bf16, float* ssq, int M, int d, int precision, void* stream) {
+  AVD_REQUIRE(nseg_of(precision) > 0, "bad precision");
+  AVD_REQUIRE(d % 64 == 0, "d must be a multiple of 64");
+  return launch_rows_prepare(x, xa_bf16, ssq, M, d, nseg_of(precision), AVD_STREAM(stream));
+}
+int avd_rmsnorm_rows(const float* x, const float* scale, int n_seq, int N, int row_off, int n_rows, int d, float eps,
+                     float* out_f32, void* out_bf16, int precision, void* stream) {
+  AVD_REQUIRE(d % 4 == 0, "d must be a multiple of 4");
+  AVD_REQUIRE(row_off >= 0 && n_rows >= 0 && row_off + n_rows <= N, "row window outside the sequence");
+  AVD_REQUIRE(out_bf16 == nullptr || nseg_of(precision) > 0, "bad precision");
+  return launch_rmsnorm_rows(x, scale, n_seq, N, row_off, n_rows, d, eps, out_f32, out_bf16,
+                             out_bf16 ? nseg_of(precision) : 0, AVD_STREAM(stream));
+}
+int avd_layernorm_act(const float* y, const float* w, const float* b, int M, int d, float eps, int apply_gelu,
+                      float* out_f32, void* out_bf16, int precision, void* stream) {
+  AVD_REQUIRE(d % 4 == 0, "d must be a multiple of 4");
+  AVD_REQUIRE(out_bf16 == nullptr || nseg_of(precision) > 0, "bad precision");
+  return launch_layernorm_act(y, w, b, M, d, eps, apply_gelu, out_f32, out_bf16, out_bf16 ? nseg_of(precision) : 0,
+                              AVD_STREAM(stream));
+}
+
+// ---- GEMM / attention
+int avd_gemm(const avd_gemm_args* g, void* stream) {
+  AVD_REQUIRE(g != nullptr, "null args");
+  return launch_gemm(*g, AVD_STREAM(stream));
+}
+int avd_attention(const void* qkv, int qkv_is_f32, void* out_bf16, int out_precision, int n_seq, int N, int n_heads,
+                  int head_dim, void* stream) {
+  AVD_REQUIRE(nseg_of(out_precision) > 0, "bad precision");
+  if (qkv_is_f32)
+    return launch_attention_f32(static_cast<const float*>(qkv), out_bf16, nseg_of(out_precision), n_seq, N, n_heads,
+                                head_dim, AVD_STREAM(stream));
+  return launch_attention_tc(qkv, out_bf16, nseg_of(out_precision), n_seq, N, n_heads, head_dim, AVD_STREAM(stream));
+}
+
+// ---- core / head
+int avd_mmdt_blocks(const avd_core_weights* w, const float* x_in, const void* xa_in, const float* ssq_in,
+                    const avd_core_workspace* ws, int n_seq, int N, void* stream) {
+  return core_blocks(w, x_in, xa_in, ssq_in, ws, n_seq, N, AVD_STREAM(stream));
+}
+int avd_head_forward(const avd_head_weights* w, const void* h, int M, void* act_a, void* act_b, float* y, float* eps,
+                     void* stream) {
+  return head_forward(w, h, M, act_a, act_b, y, eps, AVD_STREAM(stream));
+}
+
+// ---- sampler
+int64_t avd_sampler_workspace_bytes(const avd_sampler* s) {
+  SamplerLayout L;
+  if (sampler_layout(s, &L) != 0) return -1;
+  return L.total;
+}
+
+int avd_sample_prepare(const avd_sampler* s, const float* z_prompt, void* stream) {
+  SamplerLayout L;
+  AVD_TRY(sampler_layout(s, &L));
+  AVD_REQUIRE(s->workspace != nullptr && s->workspace_bytes >= L.total, "workspace too small");
+  cudaStream_t st = AVD_STREAM(stream);
+  uint8_t* ws = static_cast<uint8_t*>(s->workspace);
+  // null-branch prompt rows are all-zero rows that stay in the sequence (sample_clip.py:338 / 377)
+  AVD_CUDA(cudaMemsetAsync(ws + L.x_init, 0, (size_t)(L.xa_init - L.x_init), st));
+  AVD_CUDA(cudaMemsetAsync(ws + L.xa_init, 0, (size_t)(L.ssq_init - L.xa_init), st));
+  AVD_CUDA(cudaMemsetAsync(ws + L.ssq_init, 0, (size_t)(L.x - L.ssq_init), st));
+  const int prompt_mod = s->target == AVD_TARGET_VIDEO ? 1 : 0;   // A2V: audio prompt; V2A: video prompt
+  BuildXArgs a = make_build_args(s, L, prompt_mod, /*cond=*/true, /*null=*/false);
+  const float* wt = prompt_mod == 0 ? s->wv_t : s->wa_t;
+  const float* bias = prompt_mod == 0 ? s->bv : s->ba;
+  return launch_build_x(a, z_prompt, wt, bias, s->temb_zero, reinterpret_cast<float*>(ws + L.x_init),
+                        ws + L.xa_init, reinterpret_cast<float*>(ws + L.ssq_init), st);
+}
+
+int avd_sample_step(const avd_sampler* s, int step, float* z, float* eps_tap, void* stream) {
+  SamplerLayout L;
+  AVD_TRY(sampler_layout(s, &L));
+  AVD_REQUIRE(s->workspace != nullptr && s->workspace_bytes >= L.total, "workspace too small");
+  AVD_REQUIRE(step >= 0 && step < s->steps, "step out of range");
+  cudaStream_t st = AVD_STREAM(stream);
+  uint8_t* ws = static_cast<uint8_t*>(s->workspace);
+  float* x_init = reinterpret_cast<float*>(ws + L.x_init);
+  float* ssq_init = reinterpret_cast<float*>(ws + L.ssq_init);
+  // (1) target rows of the joint sequence, identical in the cond and null sequences
+  const int tgt_mod = s->target == AVD_TARGET_VIDEO ? 0 : 1;
+  BuildXArgs a = make_build_args(s, L, tgt_mod, true, true);
+  AVD_TRY(launch_build_x(a, z, tgt_mod == 0 ? s->wv_t : s->wa_t, tgt_mod == 0 ? s->bv : s->ba,
+                         s->temb_steps + (int64_t)step * s->tstep_dim, x_init, ws + L.xa_init, ssq_init, st));
+  // (2) 2B co-batched sequences through the blocks
+  avd_core_workspace cw;
+  cw.x = reinterpret_cast<float*>(ws + L.x);
+  cw.xa = ws + L.xa;
+  cw.ssq = reinterpret_cast<float*>(ws + L.ssq);
+  cw.qkv = ws + L.qkv;
+  cw.att = ws + L.att;
+  cw.hmid = ws + L.hmid;
+  AVD_TRY(core_blocks(&s->core, x_init, ws + L.xa_init, ssq_init, &cw, L.n_seq, L.N, st));
+  // (3) final_norm on the target rows only, compacted for the head (F9)
+  const int row_off = s->target == AVD_TARGET_VIDEO ? L.row_off_v : L.row_off_a;
+  AVD_TRY(launch_rmsnorm_rows(cw.x, s->core.final_scale, L.n_seq, L.N, row_off, L.Nt, L.d, s->core.rms_eps, nullptr,
+                              ws + L.h, L.S_head, st));
+  // (4) noise head of the target modality
+  float* eps = reinterpret_cast<float*>(ws + L.eps);
+  AVD_TRY(head_forward(&s->head, ws + L.h, L.Mt, ws + L.act_a, ws + L.act_b, reinterpret_cast<float*>(ws + L.y), eps,
+                       st));
+  if (eps_tap != nullptr)
+    AVD_CUDA(cudaMemcpyAsync(eps_tap, eps, (size_t)L.Mt * L.Dt * 4, cudaMemcpyDeviceToDevice, st));
+  // (5) CFG + un-tokenise + DDIM
+  avd_cfg_ddim_args c{};
+  c.target = s->target; c.B = s->B;
+  c.C = s->target == AVD_TARGET_VIDEO ? s->Cv : s->Ca;
+  c.T = s->T; c.H = s->H; c.W = s->W; c.tt = s->tt; c.th = s->th; c.tw = s->tw;
+  c.L = s->Fa; c.length = s->chunk_len; c.stride = s->chunk_stride; c.Nt = L.Na;
+  c.guidance = s->guidance;
+  c.t_now = (int)s->timesteps_host[step];
+  c.t_prev = (int)s->timesteps_host[step + 1];
+  c.T_train = s->T_train;
+  AVD_REQUIRE(c.t_now >= 0 && c.t_now < s->T_train && c.t_prev < s->T_train, "timestep out of range");
+  const int64_t half = (int64_t)s->B * L.Nt * L.Dt;
+  return launch_cfg_untok_ddim(c, eps, eps + half, z, z, s->alpha_bar, st);
+}
+
+int avd_sample_loop(const avd_sampler* s, const float* z_prompt, float* z, void* stream) {
+  AVD_TRY(avd_sample_prepare(s, z_prompt, stream));
+  for (int i = 0; i < s->steps; ++i) AVD_TRY(avd_sample_step(s, i, z, nullptr, stream));
+  return 0;
+}
+
+}  // extern "C"

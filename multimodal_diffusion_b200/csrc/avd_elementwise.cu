@@ -1,0 +1,668 @@
+// avd_elementwise.cu -- the HBM-bound kernels of the hot path: tokenisers (bit-exact gathers),
+// timestep embedding, DDIM update, fused CFG + un-tokenise + DDIM, operand preparation
+// (bf16 segment splitting, row sums of squares), RMSNorm / LayerNorm+GELU rows, and the fused
+// input builder (tokenise -> adapter -> concat timestep embedding).
+//
+// Every arithmetic expression that the reference evaluates in fp32 elementwise torch ops is written
+// with __f*_rn intrinsics in the reference's operation order so that nvcc cannot contract it into
+// FMAs: those kernels are bit-exact against the CPU reference (see tests/test_gpu_elementwise.py).
+#include "avd_internal.h"
+#include "avd_ptx.cuh"
+
+namespace avd {
+
+static inline int cdiv(int64_t a, int64_t b) { return static_cast<int>((a + b - 1) / b); }
+
+// =====================================================================================================
+// K1: tube patch / unpatch   (ops.py:100-119, 122-144)
+//   token flat index o = (((((((b*Tt+ti)*Hh+hj)*Ww+wk)*C+c)*t+dt)*h+dh)*w+dw
+//   latent flat index i = (((b*C+c)*T + ti*t+dt)*H + hj*h+dh)*W + wk*w+dw
+// One thread moves VEC consecutive dw elements (contiguous in both layouts when w % VEC == 0).
+// =====================================================================================================
+struct TubeDims {
+  int B, C, T, H, W, t, h, w, Tt, Hh, Ww;
+};
+
+__device__ __forceinline__ int64_t tube_latent_index_from_token(const TubeDims& d, int64_t o) {
+  int dw = o % d.w; o /= d.w;
+  int dh = o % d.h; o /= d.h;
+  int dt = o % d.t; o /= d.t;
+  int c = o % d.C;  o /= d.C;
+  int wk = o % d.Ww; o /= d.Ww;
+  int hj = o % d.Hh; o /= d.Hh;
+  int ti = o % d.Tt; o /= d.Tt;
+  int64_t b = o;
+  return (((b * d.C + c) * d.T + (ti * d.t + dt)) * d.H + (hj * d.h + dh)) * (int64_t)d.W + (wk * d.w + dw);
+}
+
+__device__ __forceinline__ int64_t tube_token_index_from_latent(const TubeDims& d, int64_t i) {
+  int x = i % d.W; i /= d.W;
+  int y = i % d.H; i /= d.H;
+  int tt = i % d.T; i /= d.T;
+  int c = i % d.C;  i /= d.C;
+  int64_t b = i;
+  int wk = x / d.w, dw = x % d.w;
+  int hj = y / d.h, dh = y % d.h;
+  int ti = tt / d.t, dt = tt % d.t;
+  return ((((((b * d.Tt + ti) * d.Hh + hj) * d.Ww + wk) * d.C + c) * d.t + dt) * d.h + dh) * (int64_t)d.w + dw;
+}
+
+template <int VEC, bool INVERSE>
+__global__ void tube_kernel(const float* __restrict__ src, float* __restrict__ dst, TubeDims d, int64_t n_vec) {
+  int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (v >= n_vec) return;
+  int64_t o = v * VEC;  // index in the DESTINATION layout
+  int64_t s = INVERSE ? tube_token_index_from_latent(d, o) : tube_latent_index_from_token(d, o);
+  if (VEC == 4) {
+    *reinterpret_cast<float4*>(dst + o) = __ldg(reinterpret_cast<const float4*>(src + s));
+  } else if (VEC == 2) {
+    *reinterpret_cast<float2*>(dst + o) = __ldg(reinterpret_cast<const float2*>(src + s));
+  } else {
+    dst[o] = __ldg(src + s);
+  }
+}
+
+int launch_tube_patch(const float* src, float* dst, int B, int C, int T, int H, int W, int t, int h, int w, bool inverse,
+                      cudaStream_t s) {
+  TubeDims d{B, C, T, H, W, t, h, w, T / t, H / h, W / w};
+  int64_t total = (int64_t)B * C * T * H * W;
+  if (total == 0) return 0;
+  bool al16 = ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15) == 0;
+  bool al8 = ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 7) == 0;
+  int vec = (w % 4 == 0 && al16) ? 4 : (w % 2 == 0 && al8) ? 2 : 1;
+  int64_t n_vec = total / vec;
+  int threads = 256;
+  int blocks = cdiv(n_vec, threads);
+  LaunchScope ls(KIND_TOKENIZE, s);
+  if (!inverse) {
+    if (vec == 4) tube_kernel<4, false><<<blocks, threads, 0, s>>>(src, dst, d, n_vec);
+    else if (vec == 2) tube_kernel<2, false><<<blocks, threads, 0, s>>>(src, dst, d, n_vec);
+    else tube_kernel<1, false><<<blocks, threads, 0, s>>>(src, dst, d, n_vec);
+  } else {
+    if (vec == 4) tube_kernel<4, true><<<blocks, threads, 0, s>>>(src, dst, d, n_vec);
+    else if (vec == 2) tube_kernel<2, true><<<blocks, threads, 0, s>>>(src, dst, d, n_vec);
+    else tube_kernel<1, true><<<blocks, threads, 0, s>>>(src, dst, d, n_vec);
+  }
+  AVD_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// =====================================================================================================
+// K1: audio chunk / un-chunk   (ops.py:17-45, 48-93; sample_clip.py:184-215)
+//   tok[b,n,c*l+j] = z[b,c,n*s+j]
+// =====================================================================================================
+template <int VEC>
+__global__ void chunk1d_kernel(const float* __restrict__ z, float* __restrict__ tok, int C, int L, int N, int length,
+                               int stride, int64_t n_vec) {
+  int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (v >= n_vec) return;
+  int64_t o = v * VEC;
+  int64_t r = o;
+  int j = r % length; r /= length;
+  int c = r % C; r /= C;
+  int n = r % N; r /= N;
+  int64_t b = r;
+  int64_t s = (b * C + c) * (int64_t)L + (int64_t)n * stride + j;
+  if (VEC == 2) {
+    *reinterpret_cast<float2*>(tok + o) = __ldg(reinterpret_cast<const float2*>(z + s));
+  } else {
+    tok[o] = __ldg(z + s);
+  }
+}
+
+int launch_chunk1d(const float* z, float* tok, int B, int C, int L, int length, int stride, cudaStream_t s) {
+  int N = (L - length) / stride + 1;
+  int64_t total = (int64_t)B * N * C * length;
+  if (total <= 0) return 0;
+  bool al8 = ((reinterpret_cast<uintptr_t>(z) | reinterpret_cast<uintptr_t>(tok)) & 7) == 0;
+  int vec = (length % 2 == 0 && stride % 2 == 0 && L % 2 == 0 && al8) ? 2 : 1;
+  int64_t n_vec = total / vec;
+  LaunchScope ls(KIND_TOKENIZE, s);
+  if (vec == 2) chunk1d_kernel<2><<<cdiv(n_vec, 256), 256, 0, s>>>(z, tok, C, L, N, length, stride, n_vec);
+  else chunk1d_kernel<1><<<cdiv(n_vec, 256), 256, 0, s>>>(z, tok, C, L, N, length, stride, n_vec);
+  AVD_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// Gather form of the reference's sequential overlap-add: position p receives windows i with
+// i*stride <= p < i*stride + length, summed in increasing i (the order of the reference's `+=` loop,
+// starting from 0.0f), then divided by max(count, 1e-8); positions past the last window are zero padding.
+__device__ __forceinline__ float overlap_add_gather(const float* __restrict__ tok_b, int c, int p, int N, int C,
+                                                    int length, int stride) {
+  int L_ola = (N - 1) * stride + length;
+  if (p >= L_ola) return 0.0f;
+  int i_hi = p / stride;
+  if (i_hi > N - 1) i_hi = N - 1;
+  int i_lo = (p - length + stride) / stride;  // ceil((p-length+1)/stride)
+  if (p - length + 1 <= 0) i_lo = 0;
+  float acc = 0.0f, cnt = 0.0f;
+  for (int i = i_lo; i <= i_hi; ++i) {
+    int j = p - i * stride;
+    if (j >= 0 && j < length) {
+      acc = __fadd_rn(acc, __ldg(tok_b + ((int64_t)i * C + c) * length + j));
+      cnt = __fadd_rn(cnt, 1.0f);
+    }
+  }
+  return __fdiv_rn(acc, fmaxf(cnt, 1e-8f));
+}
+
+__global__ void unchunk1d_kernel(const float* __restrict__ tok, float* __restrict__ z, int C, int N, int length,
+                                 int stride, int L_out, int64_t total) {
+  int64_t o = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (o >= total) return;
+  int p = o % L_out;
+  int64_t r = o / L_out;
+  int c = r % C;
+  int64_t b = r / C;
+  z[o] = overlap_add_gather(tok + b * (int64_t)N * C * length, c, p, N, C, length, stride);
+}
+
+int launch_unchunk1d(const float* tok, float* z, int B, int C, int N, int length, int stride, int L_out,
+                     cudaStream_t s) {
+  int64_t total = (int64_t)B * C * L_out;
+  if (total <= 0) return 0;
+  LaunchScope ls(KIND_TOKENIZE, s);
+  unchunk1d_kernel<<<cdiv(total, 256), 256, 0, s>>>(tok, z, C, N, length, stride, L_out, total);
+  AVD_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// =====================================================================================================
+// timestep embedding   (schedule_utils.py:64-86)
+// =====================================================================================================
+__global__ void temb_kernel(const float* __restrict__ t, float* __restrict__ emb, int B, int dim, float neg_log_mp) {
+  int half = dim / 2;
+  int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= B * dim) return;
+  int b = idx / dim, k = idx % dim;
+  if (k >= 2 * half) { emb[idx] = 0.0f; return; }  // odd dim: one zero pad column
+  int kk = k < half ? k : k - half;
+  float f = expf(__fdiv_rn(__fmul_rn(neg_log_mp, (float)kk), (float)half));
+  float a = __fmul_rn(t[b], f);
+  emb[idx] = k < half ? cosf(a) : sinf(a);
+}
+
+int launch_timestep_embedding(const float* t, float* emb, int B, int dim, float max_period, cudaStream_t s) {
+  if (B * dim <= 0) return 0;
+  float neg_log_mp = (float)(-log((double)max_period));
+  LaunchScope ls(KIND_MISC, s);
+  temb_kernel<<<cdiv((int64_t)B * dim, 256), 256, 0, s>>>(t, emb, B, dim, neg_log_mp);
+  AVD_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// =====================================================================================================
+// DDIM   (schedule_utils.py:146-200)
+// =====================================================================================================
+struct DdimCoef {
+  float sqrt_omb_t, denom, sqrt_a_prev, coeff_eps, sigma;
+};
+
+__device__ __forceinline__ DdimCoef ddim_coef(const float* __restrict__ alpha_bar, int64_t t_now, int64_t t_prev,
+                                              float eta) {
+  DdimCoef c;
+  float a_t = alpha_bar[t_now > 0 ? t_now : 0];
+  float a_prev = t_prev >= 0 ? alpha_bar[t_prev] : 1.0f;
+  c.sqrt_omb_t = __fsqrt_rn(fmaxf(__fsub_rn(1.0f, a_t), 0.0f));
+  c.denom = fmaxf(__fsqrt_rn(a_t), 1e-8f);
+  c.sqrt_a_prev = __fsqrt_rn(a_prev);
+  if (eta > 0.0f) {
+    float frac = fmaxf(__fdiv_rn(__fsub_rn(1.0f, a_prev), fmaxf(__fsub_rn(1.0f, a_t), 1e-8f)), 0.0f);
+    float omr = fmaxf(__fsub_rn(1.0f, __fdiv_rn(a_t, fmaxf(a_prev, 1e-8f))), 0.0f);
+    c.sigma = __fmul_rn(eta, __fsqrt_rn(__fmul_rn(frac, omr)));
+  } else {
+    c.sigma = 0.0f;
+  }
+  c.coeff_eps = __fsqrt_rn(fmaxf(__fsub_rn(__fsub_rn(1.0f, a_prev), __fmul_rn(c.sigma, c.sigma)), 0.0f));
+  return c;
+}
+
+__device__ __forceinline__ float ddim_update(const DdimCoef& c, float x, float e, float zn) {
+  float x0 = __fdiv_rn(__fsub_rn(x, __fmul_rn(c.sqrt_omb_t, e)), c.denom);
+  float r = __fadd_rn(__fmul_rn(c.sqrt_a_prev, x0), __fmul_rn(c.coeff_eps, e));
+  return __fadd_rn(r, __fmul_rn(c.sigma, zn));
+}
+
+__global__ void ddim_step_kernel(const float* __restrict__ x_t, const float* __restrict__ eps,
+                                 const float* __restrict__ noise, float* __restrict__ x_prev,
+                                 const int64_t* __restrict__ t_now, const int64_t* __restrict__ t_prev,
+                                 const float* __restrict__ alpha_bar, int64_t per_batch, float eta) {
+  int b = blockIdx.y;
+  DdimCoef c = ddim_coef(alpha_bar, t_now[b], t_prev[b], eta);
+  int64_t base = (int64_t)b * per_batch;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < per_batch; i += (int64_t)gridDim.x * blockDim.x) {
+    float zn = (noise != nullptr) ? noise[base + i] : 0.0f;
+    x_prev[base + i] = ddim_update(c, x_t[base + i], eps[base + i], zn);
+  }
+}
+
+int launch_ddim_step(const float* x_t, const float* eps, const float* noise, float* x_prev, const int64_t* t_now,
+                     const int64_t* t_prev, const float* alpha_bar, int T_train, int B, int64_t per_batch, float eta,
+                     cudaStream_t s) {
+  (void)T_train;
+  if (B <= 0 || per_batch <= 0) return 0;
+  dim3 grid(std::min<int64_t>(cdiv(per_batch, 256), 1024), B);
+  LaunchScope ls(KIND_CFG_DDIM, s);
+  ddim_step_kernel<<<grid, 256, 0, s>>>(x_t, eps, noise, x_prev, t_now, t_prev, alpha_bar, per_batch, eta);
+  AVD_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// =====================================================================================================
+// K7: fused CFG combine + un-tokenise + DDIM(eta=0)   (sample_clip.py:342-348 / 381-389)
+//   16 B per target-latent element: reads eps_cond, eps_null (token layout) and z_t, writes z_prev.
+// =====================================================================================================
+__device__ __forceinline__ float cfg_mix(float ec, float en, float g) {
+  return __fadd_rn(en, __fmul_rn(g, __fsub_rn(ec, en)));
+}
+
+template <int VEC>
+__global__ void cfg_ddim_video_kernel(const float* __restrict__ eps_c, const float* __restrict__ eps_n,
+                                      const float* __restrict__ z_t, float* __restrict__ z_prev, TubeDims d, float g,
+                                      int t_now, int t_prev, const float* __restrict__ alpha_bar, int64_t n_vec) {
+  int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (v >= n_vec) return;
+  DdimCoef c = ddim_coef(alpha_bar, t_now, t_prev, 0.0f);
+  int64_t i = v * VEC;                              // latent index
+  int64_t o = tube_token_index_from_latent(d, i);   // token index of the same element
+  if (VEC == 4) {
+    float4 ec = __ldg(reinterpret_cast<const float4*>(eps_c + o));
+    float4 en = __ldg(reinterpret_cast<const float4*>(eps_n + o));
+    float4 x = *reinterpret_cast<const float4*>(z_t + i);
+    float4 r;
+    r.x = ddim_update(c, x.x, cfg_mix(ec.x, en.x, g), 0.0f);
+    r.y = ddim_update(c, x.y, cfg_mix(ec.y, en.y, g), 0.0f);
+    r.z = ddim_update(c, x.z, cfg_mix(ec.z, en.z, g), 0.0f);
+    r.w = ddim_update(c, x.w, cfg_mix(ec.w, en.w, g), 0.0f);
+    *reinterpret_cast<float4*>(z_prev + i) = r;
+  } else {
+    z_prev[i] = ddim_update(c, z_t[i], cfg_mix(__ldg(eps_c + o), __ldg(eps_n + o), g), 0.0f);
+  }
+}
+
+// Audio: CFG per token element first, then the overlap-add gather (sum order i ascending), then DDIM.
+__global__ void cfg_ddim_audio_kernel(const float* __restrict__ eps_c, const float* __restrict__ eps_n,
+                                      const float* __restrict__ z_t, float* __restrict__ z_prev, int C, int L, int N,
+                                      int length, int stride, float g, int t_now, int t_prev,
+                                      const float* __restrict__ alpha_bar, int64_t total) {
+  int64_t o = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (o >= total) return;
+  DdimCoef cf = ddim_coef(alpha_bar, t_now, t_prev, 0.0f);
+  int p = o % L;
+  int64_t r = o / L;
+  int c = r % C;
+  int64_t b = r / C;
+  const float* ec_b = eps_c + b * (int64_t)N * C * length;
+  const float* en_b = eps_n + b * (int64_t)N * C * length;
+  float e = 0.0f;
+  int L_ola = (N - 1) * stride + length;
+  if (p < L_ola) {
+    int i_hi = min(p / stride, N - 1);
+    int i_lo = (p - length + 1 <= 0) ? 0 : (p - length + stride) / stride;
+    float acc = 0.0f, cnt = 0.0f;
+    for (int i = i_lo; i <= i_hi; ++i) {
+      int j = p - i * stride;
+      if (j >= 0 && j < length) {
+        int64_t k = ((int64_t)i * C + c) * length + j;
+        acc = __fadd_rn(acc, cfg_mix(__ldg(ec_b + k), __ldg(en_b + k), g));
+        cnt = __fadd_rn(cnt, 1.0f);
+      }
+    }
+    e = __fdiv_rn(acc, fmaxf(cnt, 1e-8f));
+  }
+  z_prev[o] = ddim_update(cf, z_t[o], e, 0.0f);
+}
+
+int launch_cfg_untok_ddim(const avd_cfg_ddim_args& a, const float* eps_c, const float* eps_n, const float* z_t,
+                          float* z_prev, const float* alpha_bar, cudaStream_t s) {
+  if (a.target == AVD_TARGET_VIDEO) {
+    TubeDims d{a.B, a.C, a.T, a.H, a.W, a.tt, a.th, a.tw, a.T / a.tt, a.H / a.th, a.W / a.tw};
+    int64_t total = (int64_t)a.B * a.C * a.T * a.H * a.W;
+    if (total <= 0) return 0;
+    uintptr_t al = reinterpret_cast<uintptr_t>(eps_c) | reinterpret_cast<uintptr_t>(eps_n) |
+                   reinterpret_cast<uintptr_t>(z_t) | reinterpret_cast<uintptr_t>(z_prev);
+    bool v4 = (a.tw % 4 == 0) && ((al & 15) == 0);
+    LaunchScope ls(KIND_CFG_DDIM, s);
+    if (v4) {
+      int64_t n_vec = total / 4;
+      cfg_ddim_video_kernel<4><<<cdiv(n_vec, 256), 256, 0, s>>>(eps_c, eps_n, z_t, z_prev, d, a.guidance, a.t_now,
+                                                                  a.t_prev, alpha_bar, n_vec);
+    } else {
+      cfg_ddim_video_kernel<1><<<cdiv(total, 256), 256, 0, s>>>(eps_c, eps_n, z_t, z_prev, d, a.guidance, a.t_now,
+                                                                  a.t_prev, alpha_bar, total);
+    }
+    AVD_CUDA(cudaGetLastError());
+  } else {
+    int64_t total = (int64_t)a.B * a.C * a.L;
+    if (total <= 0) return 0;
+    LaunchScope ls(KIND_CFG_DDIM, s);
+    cfg_ddim_audio_kernel<<<cdiv(total, 256), 256, 0, s>>>(eps_c, eps_n, z_t, z_prev, a.C, a.L, a.Nt, a.length,
+                                                            a.stride, a.guidance, a.t_now, a.t_prev, alpha_bar, total);
+    AVD_CUDA(cudaGetLastError());
+  }
+  return 0;
+}
+
+// =====================================================================================================
+// operand preparation
+// =====================================================================================================
+__device__ __forceinline__ void store_split(__nv_bfloat16* base, int64_t seg_stride, int64_t idx, int nseg, float v) {
+  __nv_bfloat16 hi, mid, lo;
+  split_bf16(v, hi, mid, lo);
+  base[idx] = hi;
+  if (nseg == 2) {
+    // two segments: lo absorbs the whole remainder (round once)
+    base[seg_stride + idx] = __float2bfloat16_rn(v - __bfloat162float(hi));
+  } else if (nseg == 3) {
+    base[seg_stride + idx] = mid;
+    base[2 * seg_stride + idx] = lo;
+  }
+}
+
+__global__ void pack_weight_kernel(const float* __restrict__ W, const float* __restrict__ col_scale,
+                                   __nv_bfloat16* __restrict__ out, int N, int K, int nseg) {
+  int64_t total = (int64_t)N * K;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    float v = W[i];
+    if (col_scale != nullptr) v = __fmul_rn(v, col_scale[i % K]);
+    store_split(out, total, i, nseg, v);
+  }
+}
+
+int launch_pack_weight(const float* W, const float* col_scale, void* out, int N, int K, int nseg, cudaStream_t s) {
+  int64_t total = (int64_t)N * K;
+  if (total <= 0) return 0;
+  LaunchScope ls(KIND_PACK, s);
+  pack_weight_kernel<<<std::min(cdiv(total, 256), 4096), 256, 0, s>>>(W, col_scale, static_cast<__nv_bfloat16*>(out),
+                                                                      N, K, nseg);
+  AVD_CUDA(cudaGetLastError());
+  return 0;
+}
+
+__global__ void transpose_kernel(const float* __restrict__ W, float* __restrict__ Wt, int N, int K) {
+  __shared__ float tile[32][33];
+  int k0 = blockIdx.x * 32, n0 = blockIdx.y * 32;
+  for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+    int n = n0 + r, k = k0 + threadIdx.x;
+    tile[r][threadIdx.x] = (n < N && k < K) ? W[(int64_t)n * K + k] : 0.0f;
+  }
+  __syncthreads();
+  for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+    int k = k0 + r, n = n0 + threadIdx.x;
+    if (k < K && n < N) Wt[(int64_t)k * N + n] = tile[threadIdx.x][r];
+  }
+}
+
+int launch_transpose(const float* W, float* Wt, int N, int K, cudaStream_t s) {
+  if (N <= 0 || K <= 0) return 0;
+  dim3 grid(cdiv(K, 32), cdiv(N, 32)), block(32, 8);
+  LaunchScope ls(KIND_PACK, s);
+  transpose_kernel<<<grid, block, 0, s>>>(W, Wt, N, K);
+  AVD_CUDA(cudaGetLastError());
+  return 0;
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// one warp per row; each 64-column part: lane handles 2 consecutive columns
+__global__ void rows_prepare_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ xa,
+                                    float* __restrict__ ssq, int M, int d, int nseg) {
+  int row = blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32;
+  int lane = threadIdx.x % 32;
+  if (row >= M) return;
+  int parts = d / 64;
+  int64_t seg_stride = (int64_t)M * d;
+  for (int p = 0; p < parts; ++p) {
+    int col = p * 64 + lane * 2;
+    float2 v = *reinterpret_cast<const float2*>(x + (int64_t)row * d + col);
+    store_split(xa, seg_stride, (int64_t)row * d + col, nseg, v.x);
+    store_split(xa, seg_stride, (int64_t)row * d + col + 1, nseg, v.y);
+    float s = warp_sum(v.x * v.x + v.y * v.y);
+    if (lane == 0) ssq[(int64_t)row * parts + p] = s;
+  }
+}
+
+int launch_rows_prepare(const float* x, void* xa, float* ssq, int M, int d, int nseg, cudaStream_t s) {
+  if (M <= 0) return 0;
+  LaunchScope ls(KIND_NORM, s);
+  rows_prepare_kernel<<<cdiv(M, 8), 256, 0, s>>>(x, static_cast<__nv_bfloat16*>(xa), ssq, M, d, nseg);
+  AVD_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// RMSNorm of selected rows (mmdt.py:39-42): y = scale * x / (||x|| / sqrt(d) + eps); one warp per output row.
+__global__ void rmsnorm_rows_kernel(const float* __restrict__ x, const float* __restrict__ scale, int n_seq, int N,
+                                    int row_off, int n_rows, int d, float eps, float* __restrict__ out_f32,
+                                    __nv_bfloat16* __restrict__ out_bf16, int nseg) {
+  int orow = blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32;
+  int lane = threadIdx.x % 32;
+  int Mo = n_seq * n_rows;
+  if (orow >= Mo) return;
+  int sq = orow / n_rows, r = orow % n_rows;
+  const float* xr = x + ((int64_t)sq * N + row_off + r) * d;
+  float ss = 0.0f;
+  for (int c = lane * 4; c < d; c += 128) {
+    float4 v = *reinterpret_cast<const float4*>(xr + c);
+    ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+  }
+  ss = warp_sum(ss);
+  float den = __fadd_rn(__fdiv_rn(__fsqrt_rn(ss), __fsqrt_rn((float)d)), eps);
+  int64_t seg_stride = (int64_t)Mo * d;
+  for (int c = lane * 4; c < d; c += 128) {
+    float4 v = *reinterpret_cast<const float4*>(xr + c);
+    float4 sc = *reinterpret_cast<const float4*>(scale + c);
+    float y[4] = {__fdiv_rn(__fmul_rn(sc.x, v.x), den), __fdiv_rn(__fmul_rn(sc.y, v.y), den),
+                  __fdiv_rn(__fmul_rn(sc.z, v.z), den), __fdiv_rn(__fmul_rn(sc.w, v.w), den)};
+    int64_t o = (int64_t)orow * d + c;
+    if (out_f32 != nullptr) *reinterpret_cast<float4*>(out_f32 + o) = make_float4(y[0], y[1], y[2], y[3]);
+    if (out_bf16 != nullptr) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) store_split(out_bf16, seg_stride, o + k, nseg, y[k]);
+    }
+  }
+}
+
+int launch_rmsnorm_rows(const float* x, const float* scale, int n_seq, int N, int row_off, int n_rows, int d, float eps,
+                        float* out_f32, void* out_bf16, int nseg, cudaStream_t s) {
+  int Mo = n_seq * n_rows;
+  if (Mo <= 0) return 0;
+  LaunchScope ls(KIND_NORM, s);
+  rmsnorm_rows_kernel<<<cdiv(Mo, 8), 256, 0, s>>>(x, scale, n_seq, N, row_off, n_rows, d, eps, out_f32,
+                                                  static_cast<__nv_bfloat16*>(out_bf16), nseg);
+  AVD_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// LayerNorm (+ GELU erf) rows; one warp per row, two-pass statistics in fp32.
+__global__ void layernorm_act_kernel(const float* __restrict__ y, const float* __restrict__ w,
+                                     const float* __restrict__ b, int M, int d, float eps, int gelu,
+                                     float* __restrict__ out_f32, __nv_bfloat16* __restrict__ out_bf16, int nseg) {
+  int row = blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32;
+  int lane = threadIdx.x % 32;
+  if (row >= M) return;
+  const float* yr = y + (int64_t)row * d;
+  float sum = 0.0f;
+  for (int c = lane * 4; c < d; c += 128) {
+    float4 v = *reinterpret_cast<const float4*>(yr + c);
+    sum += (v.x + v.y) + (v.z + v.w);
+  }
+  float mu = warp_sum(sum) / (float)d;
+  float sq = 0.0f;
+  for (int c = lane * 4; c < d; c += 128) {
+    float4 v = *reinterpret_cast<const float4*>(yr + c);
+    float a0 = v.x - mu, a1 = v.y - mu, a2 = v.z - mu, a3 = v.w - mu;
+    sq += a0 * a0 + a1 * a1 + a2 * a2 + a3 * a3;
+  }
+  float var = warp_sum(sq) / (float)d;
+  float rstd = 1.0f / sqrtf(var + eps);
+  int64_t seg_stride = (int64_t)M * d;
+  for (int c = lane * 4; c < d; c += 128) {
+    float4 v = *reinterpret_cast<const float4*>(yr + c);
+    float4 ww = *reinterpret_cast<const float4*>(w + c);
+    float4 bb = *reinterpret_cast<const float4*>(b + c);
+    float o[4] = {(v.x - mu) * rstd * ww.x + bb.x, (v.y - mu) * rstd * ww.y + bb.y, (v.z - mu) * rstd * ww.z + bb.z,
+                  (v.w - mu) * rstd * ww.w + bb.w};
+    if (gelu) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) o[k] = gelu_erf(o[k]);
+    }
+    int64_t idx = (int64_t)row * d + c;
+    if (out_f32 != nullptr) *reinterpret_cast<float4*>(out_f32 + idx) = make_float4(o[0], o[1], o[2], o[3]);
+    if (out_bf16 != nullptr) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) store_split(out_bf16, seg_stride, idx + k, nseg, o[k]);
+    }
+  }
+}
+
+int launch_layernorm_act(const float* y, const float* w, const float* b, int M, int d, float eps, int gelu,
+                         float* out_f32, void* out_bf16, int nseg, cudaStream_t s) {
+  if (M <= 0) return 0;
+  LaunchScope ls(KIND_LN_ACT, s);
+  layernorm_act_kernel<<<cdiv(M, 8), 256, 0, s>>>(y, w, b, M, d, eps, gelu, out_f32,
+                                                  static_cast<__nv_bfloat16*>(out_bf16), nseg);
+  AVD_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// =====================================================================================================
+// Fused input builder (sample_clip.py:322-330 / 363-371): for R consecutive tokens of one clip
+//   tok = gather(latent)           (tube patch or 1-D chunk index map)
+//   X[:, 0:d_adapt]   = tok @ W^T + b      (fp32 FMA; adapter weights pre-transposed [d_tok][d_adapt])
+//   X[:, d_adapt:d]   = timestep embedding row (host table computed with the reference formula)
+// and writes the joint-sequence row into x (fp32), xa (bf16 segments) and ssq (row sum of squares in
+// part 0, zeros elsewhere) for the cond sequence b and/or the null sequence B+b.
+// =====================================================================================================
+constexpr int BX_R = 8;      // tokens per CTA
+constexpr int BX_J = 4;      // adapter columns per thread (d_adapt <= 256 * BX_J)
+constexpr int BX_THREADS = 256;
+
+__global__ void __launch_bounds__(BX_THREADS) build_x_kernel(BuildXArgs a, const float* __restrict__ z,
+                                                            const float* __restrict__ wt,
+                                                            const float* __restrict__ bias,
+                                                            const float* __restrict__ temb, float* __restrict__ x,
+                                                            __nv_bfloat16* __restrict__ xa, float* __restrict__ ssq) {
+  extern __shared__ float bx_smem[];
+  float* tok = bx_smem;                       // [BX_R][d_tok]
+  __shared__ float red[BX_R][BX_THREADS / 32];
+  __shared__ float row_ss[BX_R];
+
+  int groups = (a.n_tok + BX_R - 1) / BX_R;
+  int b = blockIdx.x / groups;
+  int n0 = (blockIdx.x % groups) * BX_R;
+  int tid = threadIdx.x;
+
+  // ---- gather R tokens
+  for (int idx = tid; idx < BX_R * a.d_tok; idx += BX_THREADS) {
+    int r = idx / a.d_tok, k = idx % a.d_tok;
+    int n = n0 + r;
+    float v = 0.0f;
+    if (n < a.n_tok) {
+      int64_t src;
+      if (a.modality == 0) {
+        int Hh = a.H / a.th, Ww = a.W / a.tw;
+        int wk = n % Ww, hj = (n / Ww) % Hh, ti = n / (Ww * Hh);
+        int dw = k % a.tw, dh = (k / a.tw) % a.th, dt = (k / (a.tw * a.th)) % a.tt, c = k / (a.tw * a.th * a.tt);
+        src = ((((int64_t)b * a.C + c) * a.T + (ti * a.tt + dt)) * a.H + (hj * a.th + dh)) * a.W + (wk * a.tw + dw);
+      } else {
+        int j = k % a.length, c = k / a.length;
+        src = ((int64_t)b * a.C + c) * a.L + (int64_t)n * a.stride + j;
+      }
+      v = __ldg(z + src);
+    }
+    tok[idx] = v;
+  }
+  __syncthreads();
+
+  // ---- adapter GEMV for R rows, BX_J columns per thread
+  float acc[BX_R][BX_J];
+#pragma unroll
+  for (int r = 0; r < BX_R; ++r)
+#pragma unroll
+    for (int j = 0; j < BX_J; ++j) acc[r][j] = 0.0f;
+  for (int k = 0; k < a.d_tok; ++k) {
+    float wv[BX_J];
+#pragma unroll
+    for (int j = 0; j < BX_J; ++j) {
+      int c = tid + j * BX_THREADS;
+      wv[j] = (c < a.d_adapt) ? __ldg(wt + (int64_t)k * a.d_adapt + c) : 0.0f;
+    }
+#pragma unroll
+    for (int r = 0; r < BX_R; ++r) {
+      float t = tok[r * a.d_tok + k];
+#pragma unroll
+      for (int j = 0; j < BX_J; ++j) acc[r][j] = fmaf(t, wv[j], acc[r][j]);
+    }
+  }
+
+  // ---- write rows + sums of squares
+  int64_t seg_stride = a.M * (int64_t)a.d;
+#pragma unroll
+  for (int r = 0; r < BX_R; ++r) {
+    int n = n0 + r;
+    bool live = n < a.n_tok;
+    float part = 0.0f;
+    int64_t row_c = ((int64_t)b * a.N + a.row_off + n) * a.d;
+    int64_t row_n = ((int64_t)(a.B + b) * a.N + a.row_off + n) * a.d;
+#pragma unroll
+    for (int j = 0; j < BX_J; ++j) {
+      int c = tid + j * BX_THREADS;
+      if (live && c < a.d_adapt) {
+        float v = acc[r][j] + __ldg(bias + c);
+        part += v * v;
+        if (a.write_cond) { x[row_c + c] = v; store_split(xa, seg_stride, row_c + c, a.nseg, v); }
+        if (a.write_null) { x[row_n + c] = v; store_split(xa, seg_stride, row_n + c, a.nseg, v); }
+      }
+    }
+    for (int c2 = tid; c2 < a.tstep_dim; c2 += BX_THREADS) {
+      if (live) {
+        float v = __ldg(temb + c2);
+        int c = a.d_adapt + c2;
+        part += v * v;
+        if (a.write_cond) { x[row_c + c] = v; store_split(xa, seg_stride, row_c + c, a.nseg, v); }
+        if (a.write_null) { x[row_n + c] = v; store_split(xa, seg_stride, row_n + c, a.nseg, v); }
+      }
+    }
+    part = warp_sum(part);
+    if ((tid & 31) == 0) red[r][tid >> 5] = part;
+  }
+  __syncthreads();
+  if (tid < BX_R) {
+    float s = 0.0f;
+#pragma unroll
+    for (int wv = 0; wv < BX_THREADS / 32; ++wv) s += red[tid][wv];
+    row_ss[tid] = s;
+  }
+  __syncthreads();
+  for (int idx = tid; idx < BX_R * a.ssq_parts; idx += BX_THREADS) {
+    int r = idx / a.ssq_parts, p = idx % a.ssq_parts;
+    int n = n0 + r;
+    if (n < a.n_tok) {
+      float v = (p == 0) ? row_ss[r] : 0.0f;
+      if (a.write_cond) ssq[((int64_t)b * a.N + a.row_off + n) * a.ssq_parts + p] = v;
+      if (a.write_null) ssq[((int64_t)(a.B + b) * a.N + a.row_off + n) * a.ssq_parts + p] = v;
+    }
+  }
+}
+
+int launch_build_x(const BuildXArgs& a, const float* z, const float* wt, const float* bias, const float* temb,
+                   float* x, void* xa, float* ssq, cudaStream_t s) {
+  AVD_REQUIRE(a.d_adapt <= BX_THREADS * BX_J, "adapter width too large for build_x");
+  AVD_REQUIRE(a.d_tok * BX_R * 4 <= 160 * 1024, "token width too large for build_x");
+  if (a.B <= 0 || a.n_tok <= 0) return 0;
+  int groups = (a.n_tok + BX_R - 1) / BX_R;
+  size_t smem = (size_t)BX_R * a.d_tok * sizeof(float);
+  if (smem > 48 * 1024) {
+    AVD_CUDA(cudaFuncSetAttribute(build_x_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  }
+  LaunchScope ls(KIND_BUILD_X, s);
+  build_x_kernel<<<a.B * groups, BX_THREADS, smem, s>>>(a, z, wt, bias, temb, x, static_cast<__nv_bfloat16*>(xa), ssq);
+  AVD_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace avd

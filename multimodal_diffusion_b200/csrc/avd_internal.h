@@ -1,0 +1,115 @@
+// avd_internal.h -- declarations shared by the translation units of libavdiff_b200.so.
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda.h>
+#include <stdint.h>
+#include <string>
+
+#include "../../include/avdiff_b200.h"
+
+namespace avd {
+
+// ---- error plumbing -----------------------------------------------------------------------------
+void set_error(const std::string& msg);
+int fail(const char* file, int line, const std::string& msg);
+
+#define AVD_FAIL(msg) return ::avd::fail(__FILE__, __LINE__, (msg))
+#define AVD_REQUIRE(cond, msg) \
+  do {                         \
+    if (!(cond)) AVD_FAIL(std::string("requirement failed: " #cond " -- ") + (msg)); \
+  } while (0)
+#define AVD_CUDA(expr)                                                                        \
+  do {                                                                                        \
+    cudaError_t _e = (expr);                                                                  \
+    if (_e != cudaSuccess) AVD_FAIL(std::string(#expr " -> ") + cudaGetErrorString(_e));      \
+  } while (0)
+#define AVD_TRY(expr)          \
+  do {                         \
+    int _rc = (expr);          \
+    if (_rc != 0) return _rc;  \
+  } while (0)
+
+// ---- launch accounting / profiler ---------------------------------------------------------------
+enum Kind : int {
+  KIND_TOKENIZE = 0,
+  KIND_BUILD_X,
+  KIND_GEMM,
+  KIND_ATTN_TC,
+  KIND_ATTN_F32,
+  KIND_NORM,
+  KIND_LN_ACT,
+  KIND_CFG_DDIM,
+  KIND_PACK,
+  KIND_MISC,
+  KIND_COUNT
+};
+
+struct LaunchScope {  // brackets one kernel launch; counts it and (optionally) times it with CUDA events
+  LaunchScope(Kind k, cudaStream_t s);
+  ~LaunchScope();
+  Kind kind;
+  cudaStream_t stream;
+  int slot;
+};
+
+inline int nseg_of(int precision) { return precision == 1 ? 1 : precision == 3 ? 2 : precision == 6 ? 3 : -1; }
+
+// ---- kernels (launchers) ------------------------------------------------------------------------
+// elementwise / data movement (avd_elementwise.cu)
+int launch_tube_patch(const float* src, float* dst, int B, int C, int T, int H, int W, int t, int h, int w, bool inverse,
+                      cudaStream_t s);
+int launch_chunk1d(const float* z, float* tok, int B, int C, int L, int length, int stride, cudaStream_t s);
+int launch_unchunk1d(const float* tok, float* z, int B, int C, int N, int length, int stride, int L_out,
+                     cudaStream_t s);
+int launch_timestep_embedding(const float* t, float* emb, int B, int dim, float max_period, cudaStream_t s);
+int launch_ddim_step(const float* x_t, const float* eps, const float* noise, float* x_prev, const int64_t* t_now,
+                     const int64_t* t_prev, const float* alpha_bar, int T_train, int B, int64_t per_batch, float eta,
+                     cudaStream_t s);
+int launch_cfg_untok_ddim(const avd_cfg_ddim_args& a, const float* eps_c, const float* eps_n, const float* z_t,
+                          float* z_prev, const float* alpha_bar, cudaStream_t s);
+int launch_pack_weight(const float* W, const float* col_scale, void* out, int N, int K, int nseg, cudaStream_t s);
+int launch_transpose(const float* W, float* Wt, int N, int K, cudaStream_t s);
+int launch_rows_prepare(const float* x, void* xa, float* ssq, int M, int d, int nseg, cudaStream_t s);
+int launch_rmsnorm_rows(const float* x, const float* scale, int n_seq, int N, int row_off, int n_rows, int d, float eps,
+                        float* out_f32, void* out_bf16, int nseg, cudaStream_t s);
+int launch_layernorm_act(const float* y, const float* w, const float* b, int M, int d, float eps, int gelu,
+                         float* out_f32, void* out_bf16, int nseg, cudaStream_t s);
+
+// Fused input builder: tokenise a latent, adapter GEMV, concat timestep embedding; writes rows of the joint
+// sequence into x (fp32), xa (bf16 segments) and ssq.  See avd_elementwise.cu.
+struct BuildXArgs {
+  int modality;            // 0 video latent [B,C,T,H,W] with tube, 1 audio latent [B,C,L] with chunk
+  int B;
+  int C, T, H, W, tt, th, tw;
+  int L, length, stride;
+  int n_tok;               // tokens per clip of this modality
+  int d_tok;               // raw token width (C*t*h*w or C*length)
+  int d_adapt;             // adapter output width (d - tstep_dim)
+  int tstep_dim;
+  int d;                   // d_adapt + tstep_dim
+  int N;                   // joint sequence length
+  int row_off;             // first row of this modality inside a sequence
+  int n_seq_total;         // 2B
+  int write_cond, write_null;  // write rows of sequence b (cond) and/or B+b (null)
+  int nseg;
+  int ssq_parts;
+  int64_t M;               // n_seq_total * N
+};
+int launch_build_x(const BuildXArgs& a, const float* z, const float* wt, const float* bias, const float* temb,
+                   float* x, void* xa, float* ssq, cudaStream_t s);
+
+// tcgen05 GEMM (avd_gemm.cu)
+int launch_gemm(const avd_gemm_args& g, cudaStream_t s);
+
+// attention (avd_attn.cu)
+int launch_attention_tc(const void* qkv_bf16, void* out, int out_nseg, int n_seq, int N, int n_heads, int hd,
+                        cudaStream_t s);
+int launch_attention_f32(const float* qkv, void* out, int out_nseg, int n_seq, int N, int n_heads, int hd,
+                         cudaStream_t s);
+
+// ---- TMA descriptor cache (avd_api.cu) ----------------------------------------------------------
+// bf16 tensor [d2][d1][d0] (d0 contiguous), box [1][box1][box0], SWIZZLE_128B (box0 * 2 bytes must be 128).
+int get_tensor_map_bf16_3d(const void* base, uint64_t d0, uint64_t d1, uint64_t d2, uint64_t stride1_bytes,
+                           uint64_t stride2_bytes, uint32_t box0, uint32_t box1, CUtensorMap* out);
+
+}  // namespace avd
