@@ -80,11 +80,11 @@ __global__ void __launch_bounds__(128) attn_tc_kernel(const __grid_constant__ CU
 
   if (tid == 0) {
     mbar_expect_tx(q_full, ATT_TILE_BYTES);
-    tma_load_2d(sQ, &tmQKV, q_full, colQ, row_base + q0);
+    tma_load_3d(sQ, &tmQKV, q_full, colQ, row_base + q0, 0);
     mbar_expect_tx(&k_full[0], ATT_TILE_BYTES);
-    tma_load_2d(sK, &tmQKV, &k_full[0], colK, row_base);
+    tma_load_3d(sK, &tmQKV, &k_full[0], colK, row_base, 0);
     mbar_expect_tx(&v_full[0], ATT_TILE_BYTES);
-    tma_load_2d(sV, &tmQKV, &v_full[0], colV, row_base);
+    tma_load_3d(sV, &tmQKV, &v_full[0], colV, row_base, 0);
   }
 
   float o_acc[ATT_HD];
@@ -113,9 +113,9 @@ __global__ void __launch_bounds__(128) attn_tc_kernel(const __grid_constant__ CU
       if (j + 1 < nkv) {  // stage st^1 was last read by block j-1's MMAs, which completed before o_done(j-1)
         const int nst = st ^ 1;
         mbar_expect_tx(&k_full[nst], ATT_TILE_BYTES);
-        tma_load_2d(sK + nst * ATT_TILE_BYTES, &tmQKV, &k_full[nst], colK, row_base + (j + 1) * ATT_BKV);
+        tma_load_3d(sK + nst * ATT_TILE_BYTES, &tmQKV, &k_full[nst], colK, row_base + (j + 1) * ATT_BKV, 0);
         mbar_expect_tx(&v_full[nst], ATT_TILE_BYTES);
-        tma_load_2d(sV + nst * ATT_TILE_BYTES, &tmQKV, &v_full[nst], colV, row_base + (j + 1) * ATT_BKV);
+        tma_load_3d(sV + nst * ATT_TILE_BYTES, &tmQKV, &v_full[nst], colV, row_base + (j + 1) * ATT_BKV, 0);
       }
     }
     __syncwarp();

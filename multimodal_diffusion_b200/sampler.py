@@ -1,0 +1,252 @@
+"""The fused DDIM + CFG sampling loop (K8): host-side owner of the buffers that avd_sample_* work on.
+
+One ``FusedSampler`` = one direction (target modality), one clip-batch size B, one set of packed weights.
+Per DDIM step the C ABI enqueues:
+    build_x (tokenise target latent + adapter + concat timestep embedding, cond and null sequences at once)
+    -> 8 x [QKV GEMM, joint attention, out-proj GEMM(+residual,+row ssq), fc1 GEMM(+GELU), fc2 GEMM(+residual,+row ssq)]
+    -> final RMSNorm on the target rows -> head (4 GEMMs + 2 LayerNorm/GELU) -> fused CFG + un-tokenise + DDIM.
+The cond / null CFG branches are co-batched as 2B sequences, the prompt side is built once
+(F10), the non-target head is skipped (F9).  The whole S-step loop is captured into one CUDA graph.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+from typing import Dict, Optional, Tuple
+
+import numpy as np
+import torch
+
+from . import _lib, packing
+from .avdiff.utils import schedule_utils as su
+
+
+@dataclass
+class HotPathConfig:
+    """The scalars sample_one_direction reads from the merged YAML (sample_clip.py:241-265); defaults = mvp.yaml
+    merged with a2v.yaml / v2a.yaml, with the benchmark's 50 sampler steps."""
+    d_model: int = 512
+    n_layers: int = 8
+    n_heads: int = 8
+    mlp_ratio: float = 4.0
+    tstep_dim: int = 256
+    head_hidden: int = 512
+    Cv: int = 8
+    tube: Tuple[int, int, int] = (2, 4, 4)      # the sampler uses tube.h for both h and w (sample_clip.py:252,181)
+    Ca: int = 8
+    chunk: Tuple[int, int] = (4, 4)             # (length, stride)
+    Fa: int = 150
+    video_latent: Tuple[int, int, int] = (12, 16, 16)   # T', H', W' (48 frames / 4, 128 / 8)
+    T_train: int = 1000
+    schedule: str = "cosine"
+    min_beta: float = 1e-4
+    max_beta: float = 0.02
+    sampler_steps: int = 50
+    guidance: float = 3.5
+    eta: float = 0.0
+
+    @classmethod
+    def from_yaml_dict(cls, cfg: Dict, target: str, sampler_steps: Optional[int] = None) -> "HotPathConfig":
+        """Same keys as sample_clip.py:78-106,241-265 on the deep-merged config dict."""
+        core = cfg["model"]["core"]
+        dif = cfg["diffusion"][target]
+        p = int(cfg["tokenizer"]["video"]["tube"]["h"])
+        fps = int(cfg["video"]["fps"])
+        T_in = int(round(cfg["data"]["clip_seconds"] * fps)) if "data" in cfg and "clip_seconds" in cfg["data"] else 48
+        H, W = int(cfg["video"]["size"][0]), int(cfg["video"]["size"][1])
+        t_down, s_down = int(cfg["video"]["latent"]["t_down"]), int(cfg["video"]["latent"]["s_down"])
+        return cls(
+            d_model=int(core["d_model"]), n_layers=int(core["n_layers"]), n_heads=int(core["n_heads"]),
+            mlp_ratio=float(core.get("mlp_ratio", 4.0)),
+            tstep_dim=int(cfg["embeddings"].get("timestep_dim", 256)),
+            head_hidden=int(cfg["model"]["heads"]["video"]["hidden_dim"]),
+            Cv=int(cfg["video"]["latent"]["channels"]),
+            tube=(int(cfg["tokenizer"]["video"]["tube"]["t"]), p, p),
+            Ca=int(cfg["audio"]["latent"]["channels"]),
+            chunk=(int(cfg["tokenizer"]["audio"]["chunk"]["length"]), int(cfg["tokenizer"]["audio"]["chunk"]["stride"])),
+            Fa=int(cfg["audio"]["latent"]["frames_per_clip"]),
+            video_latent=(max(1, T_in // t_down), H // s_down, W // s_down),
+            T_train=int(dif["steps"]), schedule=dif["schedule"], min_beta=float(dif["min_beta"]),
+            max_beta=float(dif["max_beta"]),
+            sampler_steps=int(sampler_steps if sampler_steps is not None else dif["sampler_steps"]),
+            guidance=float(cfg["sampling"]["guidance_scale"].get(target, 3.0)),
+            eta=float(cfg["sampling"].get("ddim_eta", 0.0)))
+
+    # derived shapes
+    @property
+    def Nv(self) -> int:
+        T, H, W = self.video_latent
+        return (T // self.tube[0]) * (H // self.tube[1]) * (W // self.tube[2])
+
+    @property
+    def Na(self) -> int:
+        return (self.Fa - self.chunk[0]) // self.chunk[1] + 1
+
+    @property
+    def Dv(self) -> int:
+        return self.Cv * self.tube[0] * self.tube[1] * self.tube[2]
+
+    @property
+    def Da(self) -> int:
+        return self.Ca * self.chunk[0]
+
+    def flops_per_clip(self, target: str) -> float:
+        """Algorithmic FLOPs of one clip's S-step sampling: 2 core forwards + 2 head passes over
+        the target tokens + 1 target adapter per step."""
+        d, L, N = self.d_model, self.n_layers, self.Nv + self.Na
+        core = L * N * (24 * d * d + 4 * N * d) if self.mlp_ratio == 4.0 else \
+            L * N * ((8 + 4 * self.mlp_ratio) * d * d + 4 * N * d)
+        Nt, Dt = (self.Nv, self.Dv) if target == "video" else (self.Na, self.Da)
+        hid = self.head_hidden
+        head_tok = 2 * (d * hid + 2 * hid * hid + hid * Dt)
+        adapt_tok = 2 * Dt * (d - self.tstep_dim)
+        return self.sampler_steps * (2 * core + 2 * Nt * head_tok + Nt * adapt_tok)
+
+
+def _state_dict_of(obj) -> Dict[str, torch.Tensor]:
+    return obj if isinstance(obj, dict) else obj.state_dict()
+
+
+class FusedSampler:
+    """sample_one_direction's loop (sample_clip.py:317-348 / 359-389) for a batch of B clips on one GPU.
+
+    adapt_v / adapt_a / core / head: reference (or mirror) modules or their ``state_dict``s.
+    target: "audio" (V2A: z_prompt = video latent [B,Cv,T',H',W'], z = audio latent [B,Ca,Fa]) or
+            "video" (A2V: z_prompt = audio latent, z = video latent).
+    """
+
+    def __init__(self, cfg: HotPathConfig, adapt_v, adapt_a, core, head, target: str, batch: int,
+                 device="cuda", core_precision="bf16", head_precision="bf16x3"):
+        if target not in ("audio", "video"):
+            raise ValueError("target must be 'audio' or 'video'")
+        if cfg.eta != 0.0:
+            raise NotImplementedError("the fused loop implements eta = 0 (every shipped config); use "
+                                      "avdiff.utils.schedule_utils.ddim_step for eta > 0")
+        lib = _lib.load()
+        self.cfg, self.target, self.B = cfg, target, int(batch)
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise _lib.AvdError("FusedSampler needs a CUDA device (no CPU path)")
+        with torch.cuda.device(self.device):
+            _lib.check(lib.avd_device_check())
+        self.core = packing.PackedCore(_state_dict_of(core), cfg.n_layers, cfg.n_heads, core_precision, self.device)
+        self.head = packing.PackedHead(_state_dict_of(head), target, head_precision, self.device)
+        self.av = packing.PackedAdapter(_state_dict_of(adapt_v), self.device)
+        self.aa = packing.PackedAdapter(_state_dict_of(adapt_a), self.device)
+        if self.av.d_in != cfg.Dv or self.aa.d_in != cfg.Da or self.av.d_out != cfg.d_model - cfg.tstep_dim:
+            raise ValueError("adapter shapes do not match the config")
+
+        # host tables (reference functions' fp32 results)
+        alpha_bar = su.alphas_cumprod_from_betas(
+            su.make_beta_schedule(cfg.T_train, cfg.schedule, cfg.min_beta, cfg.max_beta))[1]
+        self.timesteps = su.make_sampling_schedule(cfg.T_train, cfg.sampler_steps)        # int64 [S+1], host
+        self._ts_host = np.ascontiguousarray(self.timesteps.numpy().astype(np.int64))
+        self.alpha_bar = alpha_bar.to(self.device)
+        self.temb_steps = su.timestep_embedding_host(self.timesteps[:-1], cfg.tstep_dim).to(self.device).contiguous()
+        self.temb_zero = su.timestep_embedding_host(torch.zeros(1, dtype=torch.long), cfg.tstep_dim)[0] \
+            .to(self.device).contiguous()
+
+        s = _lib.SamplerArgs()
+        s.target = _lib.AVD_TARGET_AUDIO if target == "audio" else _lib.AVD_TARGET_VIDEO
+        s.B = self.B
+        s.Cv = cfg.Cv
+        s.T, s.H, s.W = cfg.video_latent
+        s.tt, s.th, s.tw = cfg.tube
+        s.Ca, s.Fa, s.chunk_len, s.chunk_stride = cfg.Ca, cfg.Fa, cfg.chunk[0], cfg.chunk[1]
+        s.tstep_dim, s.steps, s.T_train, s.guidance = cfg.tstep_dim, cfg.sampler_steps, cfg.T_train, cfg.guidance
+        s.timesteps_host = self._ts_host.ctypes.data
+        s.temb_steps, s.temb_zero = self.temb_steps.data_ptr(), self.temb_zero.data_ptr()
+        s.alpha_bar = self.alpha_bar.data_ptr()
+        s.wv_t, s.bv = self.av.wt.data_ptr(), self.av.bias.data_ptr()
+        s.wa_t, s.ba = self.aa.wt.data_ptr(), self.aa.bias.data_ptr()
+        s.core, s.head = self.core.struct, self.head.struct
+        s.workspace, s.workspace_bytes = None, 0
+        nbytes = lib.avd_sampler_workspace_bytes(C.byref(s))
+        if nbytes < 0:
+            raise _lib.AvdError(lib.avd_last_error().decode())
+        self.workspace = torch.empty(int(nbytes), device=self.device, dtype=torch.uint8)
+        s.workspace, s.workspace_bytes = self.workspace.data_ptr(), int(nbytes)
+        self.args = s
+        self.Nt, self.Dt = (cfg.Na, cfg.Da) if target == "audio" else (cfg.Nv, cfg.Dv)
+        self.prompt_shape = (self.B, cfg.Cv, *cfg.video_latent) if target == "audio" else (self.B, cfg.Ca, cfg.Fa)
+        self.latent_shape = (self.B, cfg.Ca, cfg.Fa) if target == "audio" else (self.B, cfg.Cv, *cfg.video_latent)
+        self._graph: Optional[torch.cuda.CUDAGraph] = None
+        self._g_prompt: Optional[torch.Tensor] = None
+        self._g_z: Optional[torch.Tensor] = None
+
+    # ---- per-call API (eager launches on the current stream) ---------------------------------------
+    def _chk(self, t: torch.Tensor, shape, name: str) -> torch.Tensor:
+        t = _lib.require_cuda_f32(t, name)
+        if tuple(t.shape) != tuple(shape):
+            raise ValueError(f"{name} must have shape {tuple(shape)}, got {tuple(t.shape)}")
+        return t
+
+    def prepare(self, z_prompt: torch.Tensor) -> None:
+        zp = self._chk(z_prompt, self.prompt_shape, "z_prompt")
+        _lib.check(_lib.load().avd_sample_prepare(C.byref(self.args), zp.data_ptr(), _lib.stream_ptr()))
+
+    def step(self, i: int, z: torch.Tensor, eps_tap: Optional[torch.Tensor] = None) -> None:
+        """One DDIM+CFG step, z updated IN PLACE.  eps_tap [2B,Nt,Dt] receives (eps_cond ; eps_null)."""
+        z = self._chk(z, self.latent_shape, "z")
+        if eps_tap is not None:
+            eps_tap = self._chk(eps_tap, (2 * self.B, self.Nt, self.Dt), "eps_tap")
+        _lib.check(_lib.load().avd_sample_step(C.byref(self.args), int(i), z.data_ptr(), _lib.ptr(eps_tap),
+                                               _lib.stream_ptr()))
+
+    def sample_eager(self, z_prompt: torch.Tensor, z_init: torch.Tensor) -> torch.Tensor:
+        zp = self._chk(z_prompt, self.prompt_shape, "z_prompt")
+        z = self._chk(z_init, self.latent_shape, "z_init").clone()
+        _lib.check(_lib.load().avd_sample_loop(C.byref(self.args), zp.data_ptr(), z.data_ptr(), _lib.stream_ptr()))
+        return z
+
+    # ---- CUDA-graph path -------------------------------------------------------------------------
+    def capture(self) -> None:
+        """Capture prepare + S steps into one CUDA graph over static prompt / latent buffers."""
+        if self._graph is not None:
+            return
+        self._g_prompt = torch.zeros(self.prompt_shape, device=self.device, dtype=torch.float32)
+        self._g_z = torch.zeros(self.latent_shape, device=self.device, dtype=torch.float32)
+        lib = _lib.load()
+        # warm-up launch outside capture (sets kernel attributes, builds the TMA descriptor cache)
+        side = torch.cuda.Stream(device=self.device)
+        side.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(side):
+            _lib.check(lib.avd_sample_prepare(C.byref(self.args), self._g_prompt.data_ptr(), _lib.stream_ptr()))
+            _lib.check(lib.avd_sample_step(C.byref(self.args), 0, self._g_z.data_ptr(), None, _lib.stream_ptr()))
+        torch.cuda.current_stream(self.device).wait_stream(side)
+        torch.cuda.synchronize(self.device)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            _lib.check(lib.avd_sample_loop(C.byref(self.args), self._g_prompt.data_ptr(), self._g_z.data_ptr(),
+                                           _lib.stream_ptr()))
+        self._graph = g
+
+    def sample(self, z_prompt: torch.Tensor, z_init: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """z_final for a batch (graph replay).  Inputs may be CUDA tensors or pinned host tensors."""
+        self.capture()
+        self._g_prompt.copy_(z_prompt.reshape(self.prompt_shape), non_blocking=True)
+        self._g_z.copy_(z_init.reshape(self.latent_shape), non_blocking=True)
+        self._graph.replay()
+        if out is None:
+            return self._g_z.clone()
+        out.copy_(self._g_z, non_blocking=True)
+        return out
+
+    def kernels_per_sample(self) -> int:
+        """Kernel launches of one S-step sampling call (the claim behind bench.py's gpu_launches)."""
+        L, ns = self.cfg.n_layers, self.head.struct.n_shared
+        per_step = 1 + 5 * L + 1 + (2 + 2 * ns) + 1
+        return 1 + self.cfg.sampler_steps * per_step     # + prompt-side build_x (memsets are not kernels of ours)
+
+
+def shard_range(n_items: int, rank: int, world: int) -> Tuple[int, int]:
+    """Contiguous block partition of clip indices over ranks: rank r owns [lo, hi)."""
+    base, rem = divmod(n_items, world)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def clip_noise(shape_per_clip, clip_index: int, base_seed: int) -> torch.Tensor:
+    """Per-clip seeded N(0,1) latent (host generator) so results are invariant to how clips are sharded."""
+    g = torch.Generator().manual_seed(int(base_seed) + int(clip_index))
+    return torch.randn(*shape_per_clip, generator=g, dtype=torch.float32)
