@@ -37,6 +37,7 @@ struct AttnParams {
   int out_nseg;
   float scale_log2e;  // (1/sqrt(hd)) * log2(e)
   uint32_t v_lbo, v_sbo;  // MN-major V descriptor strides (bytes)
+  int dbg_stop;           // debug: leave the main loop early at a given stage (0 = run normally)
 };
 
 __global__ void __launch_bounds__(128) attn_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnParams p) {
@@ -69,6 +70,7 @@ __global__ void __launch_bounds__(128) attn_tc_kernel(const __grid_constant__ CU
     for (int i = 0; i < 7; ++i) mbar_init(&bars[i], 1);
     fence_barrier_init();
   }
+  __syncwarp();
   if (warp == 0) tmem_alloc<ATT_TMEM_COLS>(tmem_slot);
   tc_fence_before();
   __syncthreads();
@@ -92,7 +94,7 @@ __global__ void __launch_bounds__(128) attn_tc_kernel(const __grid_constant__ CU
   for (int c = 0; c < ATT_HD; ++c) o_acc[c] = 0.0f;
   float m_run = -INFINITY, l_run = 0.0f;
 
-  for (int j = 0; j < nkv; ++j) {
+  for (int j = 0; j < nkv && p.dbg_stop != 1; ++j) {
     const int st = j & 1;
     const uint32_t ph = (j >> 1) & 1;
     const int kv_valid = min(ATT_BKV, p.N - j * ATT_BKV);
@@ -121,6 +123,7 @@ __global__ void __launch_bounds__(128) attn_tc_kernel(const __grid_constant__ CU
     __syncwarp();
     mbar_wait(s_done, j & 1);
     tc_fence_after();
+    if (p.dbg_stop == 2) break;
 
     // ---- pass 1: row max over the valid keys
     const int nch = (kv_n + 31) >> 5;
@@ -166,6 +169,7 @@ __global__ void __launch_bounds__(128) attn_tc_kernel(const __grid_constant__ CU
     fence_async_smem();   // P (generic-proxy stores) -> visible to the tensor core's async-proxy reads
     tc_fence_before();
     __syncthreads();
+    if (p.dbg_stop == 3) break;
 
     if (tid == 0) {
       tc_fence_after();
@@ -196,6 +200,13 @@ __global__ void __launch_bounds__(128) attn_tc_kernel(const __grid_constant__ CU
       for (int c = 0; c < 32; ++c) o_acc[ch * 32 + c] = fmaf(o_acc[ch * 32 + c], alpha, __uint_as_float(r[c]));
     }
     tc_fence_before();
+  }
+
+  if (p.dbg_stop != 0 && tid == 0) {   // debug exits: drain the TMA loads that are still in flight
+    mbar_wait(q_full, 0);
+    mbar_wait(&k_full[0], 0);
+    mbar_wait(&v_full[0], 0);
+    if (nkv > 1 && p.dbg_stop >= 2) { mbar_wait(&k_full[1], 0); mbar_wait(&v_full[1], 0); }
   }
 
   // ---- normalise and store this thread's query row
@@ -260,6 +271,7 @@ int launch_attention_tc(const void* qkv_bf16, void* out, int out_nseg, int n_seq
   p.scale_log2e = (1.0f / sqrtf((float)hd)) * 1.4426950408889634f;
   p.v_lbo = env_u32("AVD_DBG_V_LBO", 16);      // debug overrides for the MN-major descriptor
   p.v_sbo = env_u32("AVD_DBG_V_SBO", 1024);
+  p.dbg_stop = (int)env_u32("AVD_DBG_ATT_STOP", 0);
   dim3 grid((N + ATT_BQ - 1) / ATT_BQ, n_heads, n_seq);
   LaunchScope ls(KIND_ATTN_TC, s);
   attn_tc_kernel<<<grid, 128, ATT_SMEM, s>>>(tm, p);

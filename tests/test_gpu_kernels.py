@@ -1,0 +1,266 @@
+"""GPU: each kernel of libavdiff_b200.so through the C ABI / the mirror ops, against the CPU oracle
+(bit-exact for data movement and the fp32 elementwise chains; stated tolerances for the GEMM / attention)."""
+import ctypes as C
+import math
+
+import numpy as np
+import pytest
+import torch
+
+from _common import golden, orc, randn, rel_l2
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def dev(lib):
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    from multimodal_diffusion_b200 import _lib
+    _lib.check(lib.avd_device_check())
+    return torch.device("cuda:0")
+
+
+def T(a):
+    return torch.from_numpy(np.asarray(a))
+
+
+# ------------------------------------------------------------------------------------------ tokenisers
+@pytest.mark.parametrize("shape,tube", [((2, 8, 12, 16, 16), (2, 4, 4)), ((1, 3, 4, 6, 8), (2, 3, 2)),
+                                        ((1, 3, 4, 6, 8), (1, 2, 1)), ((3, 8, 40, 16, 16), (2, 4, 4)),
+                                        ((0, 8, 12, 16, 16), (2, 4, 4))])
+def test_tube_patch_unpatch_bit_exact(dev, shape, tube):
+    from multimodal_diffusion_b200.avdiff.utils import ops
+    z = randn(1, *shape)
+    t, h, w = tube
+    want = orc.tube_patch_video(z, t, h, w)
+    got = ops.tube_patch_video(z.to(dev), t, h, w)
+    assert got.shape == want.shape and torch.equal(got.cpu(), want)
+    back = ops.tube_unpatch_video(got, shape[1], shape[2], shape[3], shape[4], t, h, w)
+    assert torch.equal(back.cpu(), z)                      # the reference's own round-trip pin (test_shapes.py:26-36)
+
+
+def test_tube_golden_and_errors(dev):
+    from multimodal_diffusion_b200.avdiff.utils import ops
+    g = golden("tokenizers")
+    zs = T(g["tube_small_z"]).to(dev)
+    assert np.array_equal(ops.tube_patch_video(zs, 2, 3, 2).cpu().numpy(), g["tube_small_tok_t2h3w2"])
+    assert np.array_equal(ops.tube_patch_video(zs, 1, 2, 1).cpu().numpy(), g["tube_small_tok_t1h2w1"])
+    with pytest.raises(AssertionError):
+        ops.tube_patch_video(zs, 3, 3, 2)                  # ops.py:113
+    with pytest.raises(AssertionError):
+        ops.tube_unpatch_video(torch.zeros(1, 5, 7, device=dev), 3, 4, 6, 8, 2, 3, 2)   # ops.py:137
+
+
+def test_audio_chunk_unchunk_bit_exact(dev):
+    from multimodal_diffusion_b200.avdiff.utils import ops
+    from multimodal_diffusion_b200.avdiff.models.tokenizers import AudioTokenizer, AudioTokenizerCfg
+    g = golden("tokenizers")
+    za = T(g["aud_z"]).to(dev)
+    assert np.array_equal(ops.chunk_1d(za, 4, 4).cpu().numpy(), g["aud_windows_l4s4"])
+    assert np.array_equal(ops.chunk_1d(za, 6, 2).cpu().numpy(), g["aud_windows_l6s2"])
+    assert np.array_equal(ops.latents_to_tokens_audio(za, 4, 4).cpu().numpy(), g["aud_tok_l4s4"])
+    assert np.array_equal(ops.latents_to_tokens_audio(za, 6, 2).cpu().numpy(), g["aud_tok_l6s2"])
+    assert np.array_equal(AudioTokenizer().encode(za).cpu().numpy(), g["aud_tok_l4s4"])
+    tk = T(g["aud_untok_in"]).to(dev)
+    u = ops.tokens_to_latents_audio(tk, 8, 4, 150, 4)
+    assert np.array_equal(u.cpu().numpy(), g["aud_untok_l4s4_F150"])
+    assert float(u[..., 148:].abs().max()) == 0.0
+    assert np.array_equal(ops.tokens_to_latents_audio(tk, 8, 4, 140, 4).cpu().numpy(), g["aud_untok_l4s4_F140"])
+    tk2 = T(g["aud_untok2_in"]).to(dev)
+    assert np.array_equal(AudioTokenizer(AudioTokenizerCfg(6, 2)).decode(tk2, 8, 150).cpu().numpy(),
+                          g["aud_untok_l6s2_F150"])
+    w = T(g["ola_in"]).to(dev)
+    for s in (3, 5, 7):
+        assert np.array_equal(ops.overlap_add_1d(w, stride=s).cpu().numpy(), g[f"ola_s{s}"])
+    short = ops.chunk_1d(randn(6, 2, 3).to(dev), 4, 4)
+    assert np.array_equal(short.cpu().numpy(), g["chunk_short"])
+    # transposed dim + long clip (10 s config: Fa = 500)
+    x = randn(9, 2, 500, 8)
+    assert torch.equal(ops.chunk_1d(x.to(dev), 4, 4, dim=1).cpu(), orc.chunk_1d(x, 4, 4, dim=1))
+
+
+# ------------------------------------------------------------------------------------------ schedules
+def test_ddim_step_bit_exact(dev):
+    from multimodal_diffusion_b200.avdiff.utils import schedule_utils as su
+    from multimodal_diffusion_b200.avdiff.models.schedules import ModalitySchedule
+    g = golden("schedules")
+    ab = T(g["alpha_bar_cosine"])
+    assert np.array_equal(su.alphas_cumprod_from_betas(su.make_beta_schedule(1000, "cosine"))[1].numpy(),
+                          g["alpha_bar_cosine"])
+    x, e = T(g["ddim_x"]).to(dev), T(g["ddim_eps"]).to(dev)
+    for name, (tn, tp) in {"first": (999, 979), "mid": (499, 479), "last": (19, -1)}.items():
+        out = su.ddim_step(x, torch.full((3,), tn), torch.full((3,), tp), e, ab)
+        assert np.array_equal(out.cpu().numpy(), g[f"ddim_{name}"]), name
+    out = su.ddim_step(x, torch.tensor([999, 499, 19]), torch.tensor([979, 479, -1]), e, ab.to(dev))
+    assert np.array_equal(out.cpu().numpy(), g["ddim_mixed_t"])
+    sch = ModalitySchedule.make(kind="cosine", steps=1000).to(dev)
+    out2 = sch.ddim_step(x, torch.tensor([999, 499, 19], device=dev), torch.tensor([979, 479, -1], device=dev), e)
+    assert np.array_equal(out2.cpu().numpy(), g["ddim_mixed_t"])
+    # eta > 0: same formula with an injected noise tensor (statistical check of the sigma * z term)
+    xs, es = randn(3, 4, 8, 150).to(dev), randn(4, 4, 8, 150).to(dev)
+    o = su.ddim_step(xs, torch.full((4,), 499), torch.full((4,), 479), es, ab, eta=1.0)
+    base = orc.ddim_step(xs.cpu(), torch.full((4,), 499), torch.full((4,), 479), es.cpu(), ab, eta=1.0,
+                         noise=torch.zeros(4, 8, 150))
+    a_t, a_p = float(ab[499]), float(ab[479])
+    sigma = math.sqrt((1 - a_p) / (1 - a_t) * (1 - a_t / a_p))
+    resid = (o.cpu() - base) / sigma
+    assert abs(float(resid.mean())) < 0.06 and abs(float(resid.std()) - 1.0) < 0.06
+
+
+def test_timestep_embedding(dev):
+    from multimodal_diffusion_b200.avdiff.utils import schedule_utils as su
+    g = golden("schedules")
+    ts = su.make_sampling_schedule(1000, 50)
+    assert np.array_equal(ts.numpy(), g["sched_50"])
+    assert np.array_equal(su.timestep_embedding_host(ts[:-1], 256).numpy(), g["temb_steps_256"])   # host table: exact
+    emb = su.timestep_embedding(ts[:-1].to(dev), 256).cpu().numpy()
+    assert np.abs(emb - g["temb_steps_256"]).max() < 2e-4       # device sin/cos of arguments up to 999 rad
+    odd = su.timestep_embedding(torch.tensor([0, 3, 999], device=dev), 7).cpu().numpy()
+    assert odd.shape == (3, 7) and np.abs(odd - g["temb_odd_7"]).max() < 2e-4
+
+
+# ------------------------------------------------------------------------------------------ fused CFG + untokenise + DDIM
+@pytest.mark.parametrize("B", [1, 8])
+@pytest.mark.parametrize("tn,tp", [(999, 979), (19, -1)])
+def test_cfg_untok_ddim_video_bit_exact(dev, lib, B, tn, tp):
+    from multimodal_diffusion_b200 import _lib
+    cfg = orc.HotPathConfig()
+    ab = cfg.alpha_bar()
+    ec, en, z = randn(1, B, 96, 256) * 50, randn(2, B, 96, 256) * 50, randn(3, B, 8, 12, 16, 16) * 30
+    e_hat = en + 3.5 * (ec - en)
+    want = orc.ddim_step(z, torch.full((B,), tn), torch.full((B,), tp),
+                         orc.tube_unpatch_video(e_hat, 8, 12, 16, 16, 2, 4, 4), ab)
+    a = _lib.CfgDdimArgs(target=_lib.AVD_TARGET_VIDEO, B=B, C=8, T=12, H=16, W=16, tt=2, th=4, tw=4, guidance=3.5,
+                         t_now=tn, t_prev=tp, T_train=1000)
+    zd, out = z.to(dev), torch.empty(B, 8, 12, 16, 16, device=dev)
+    ecd, end, abd = ec.to(dev), en.to(dev), ab.to(dev)      # keep the device tensors alive across the launch
+    _lib.check(lib.avd_cfg_untok_ddim(C.byref(a), ecd.data_ptr(), end.data_ptr(), zd.data_ptr(), out.data_ptr(),
+                                      abd.data_ptr(), _lib.stream_ptr()))
+    assert torch.equal(out.cpu(), want)
+
+
+@pytest.mark.parametrize("length,stride,Fa", [(4, 4, 150), (6, 2, 150), (4, 4, 500)])
+def test_cfg_untok_ddim_audio_bit_exact(dev, lib, length, stride, Fa):
+    from multimodal_diffusion_b200 import _lib
+    B, Ca = 3, 8
+    Na = (Fa - length) // stride + 1
+    ab = orc.HotPathConfig().alpha_bar()
+    ec, en, z = randn(1, B, Na, Ca * length), randn(2, B, Na, Ca * length), randn(3, B, Ca, Fa)
+    e_hat = en + 3.5 * (ec - en)
+    want = orc.ddim_step(z, torch.full((B,), 979), torch.full((B,), 959),
+                         orc.tokens_to_latents_audio(e_hat, Ca, length, Fa, stride), ab)
+    a = _lib.CfgDdimArgs(target=_lib.AVD_TARGET_AUDIO, B=B, C=Ca, L=Fa, length=length, stride=stride, Nt=Na,
+                         guidance=3.5, t_now=979, t_prev=959, T_train=1000)
+    zd, ecd, end, abd = z.to(dev), ec.to(dev), en.to(dev), ab.to(dev)
+    _lib.check(lib.avd_cfg_untok_ddim(C.byref(a), ecd.data_ptr(), end.data_ptr(), zd.data_ptr(), zd.data_ptr(),
+                                      abd.data_ptr(), _lib.stream_ptr()))   # in place
+    assert torch.equal(zd.cpu(), want)
+
+
+# ------------------------------------------------------------------------------------------ norms
+def test_rmsnorm_and_layernorm_rows(dev, lib):
+    from multimodal_diffusion_b200.avdiff.models.mmdt import RMSNorm
+    x = randn(5, 2, 133, 512) * 7
+    x[0, 3] = 0.0                                         # a null-branch prompt row: must give exactly 0, not NaN
+    scale = 1.0 + 0.1 * randn(6, 512)
+    m = RMSNorm(512).to(dev)
+    with torch.no_grad():
+        m.scale.copy_(scale)
+        got = m(x.to(dev)).cpu()
+    want = orc.rmsnorm(x, scale)
+    assert rel_l2(got, want) < 1e-6 and float(got[0, 3].abs().max()) == 0.0
+    from multimodal_diffusion_b200 import _lib
+    y, w, b = randn(7, 300, 512) * 3, 1 + 0.1 * randn(8, 512), 0.1 * randn(9, 512)
+    out = torch.empty(300, 512, device=dev)
+    yd, wd, bd = y.to(dev), w.to(dev), b.to(dev)
+    _lib.check(lib.avd_layernorm_act(yd.data_ptr(), wd.data_ptr(), bd.data_ptr(), 300, 512, 1e-5, 1, out.data_ptr(),
+                                     None, 0, _lib.stream_ptr()))
+    assert rel_l2(out.cpu(), orc.gelu_erf(orc.layernorm(y, w, b))) < 2e-6
+
+
+# ------------------------------------------------------------------------------------------ GEMM
+def _gemm_case(dev, M, N, K, precision, **kw):
+    from multimodal_diffusion_b200 import _lib, packing
+    prec = _lib.precision_code(precision)
+    A, W, bias = randn(1, M, K), randn(2, N, K) / math.sqrt(K), randn(3, N)
+    Ad, Wd = A.to(dev), W.to(dev)
+    xa, ssq = packing.rows_prepare(Ad, prec)
+    Wp = packing.pack_linear_weight(Wd, prec)
+    out = torch.zeros(M, N, device=dev)
+    packing.gemm(xa, Wp, M, N, K, prec, bias=bias.to(dev), out_f32=out, **kw)
+    torch.cuda.synchronize()
+    if precision == "bf16":
+        Ar, Wr = A.bfloat16().double(), W.bfloat16().double()
+    else:
+        Ar, Wr = A.double(), W.double()
+    return out.cpu(), Ar @ Wr.t() + bias.double(), ssq.cpu(), A
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (300, 512, 512), (2128, 1536, 512), (266, 512, 2048),
+                                   (74, 32, 512), (133, 256, 64)])
+def test_gemm_bf16_exact_products(dev, M, N, K):
+    got, want, ssq, A = _gemm_case(dev, M, N, K, "bf16")
+    assert rel_l2(got, want) < 2e-6          # bf16 x bf16 products are exact in fp32; only accumulation order differs
+    assert rel_l2(ssq.sum(-1), (A.double() ** 2).sum(-1)) < 1e-6
+
+
+@pytest.mark.parametrize("precision,tol", [("bf16x3", 3e-5), ("fp32", 2e-6)])
+@pytest.mark.parametrize("M,N,K", [(300, 512, 512), (266, 512, 2048)])
+def test_gemm_split_precision(dev, M, N, K, precision, tol):
+    got, want, _, _ = _gemm_case(dev, M, N, K, precision)
+    assert rel_l2(got, want) < tol
+
+
+def test_gemm_fused_epilogue(dev):
+    """RMSNorm-as-row-scale prologue, bias, residual, GELU(erf), bf16-segment output and row ssq of the result."""
+    from multimodal_diffusion_b200 import _lib, packing
+    M, N, K = 266, 512, 512
+    prec = _lib.AVD_PREC_FP32
+    x, W, bias, resid = randn(1, M, K) * 4, randn(2, N, K) / math.sqrt(K), randn(3, N), randn(4, M, N)
+    x[5] = 0.0
+    scale = 1 + 0.1 * randn(5, K)
+    xd = x.to(dev)
+    xa, ssq = packing.rows_prepare(xd, prec)
+    Wp = packing.pack_linear_weight(W.to(dev), prec, scale.to(dev))
+    out = torch.empty(M, N, device=dev)
+    out_b = torch.empty(3, M, N, device=dev, dtype=torch.bfloat16)
+    ssq_o = torch.empty(M, N // 64, device=dev)
+    packing.gemm(xa, Wp, M, N, K, prec, bias=bias.to(dev), ssq_in=ssq, rms_dim=K, rms_eps=1e-6, resid=resid.to(dev),
+                 act=1, out_f32=out, out_bf16=out_b, out_precision=prec, ssq_out=ssq_o)
+    want = orc.gelu_erf((orc.rmsnorm(x, scale).double() @ W.double().t() + bias.double() + resid.double()).float())
+    assert rel_l2(out.cpu(), want) < 3e-6
+    assert rel_l2(out_b.float().sum(0).cpu(), out.cpu()) < 1e-6           # hi + mid + lo reassembles the fp32 value
+    assert rel_l2(ssq_o.sum(-1).cpu(), (out.cpu().double() ** 2).sum(-1)) < 1e-5
+
+
+# ------------------------------------------------------------------------------------------ attention
+def _attn_ref(qkv, n_seq, N, H, hd):
+    d = H * hd
+    q, k, v = qkv.double().view(n_seq, N, 3, H, hd).permute(2, 0, 3, 1, 4)
+    p = torch.softmax(q @ k.transpose(-1, -2) / math.sqrt(hd), dim=-1)
+    return (p @ v).permute(0, 2, 1, 3).reshape(n_seq * N, d)
+
+
+@pytest.mark.parametrize("n_seq,N", [(2, 133), (1, 128), (3, 445), (2, 16), (1, 300)])
+def test_attention_tcgen05(dev, lib, n_seq, N):
+    from multimodal_diffusion_b200 import _lib
+    H, hd = 8, 64
+    qkv = (randn(1, n_seq * N, 3 * H * hd) * 1.5).bfloat16()
+    out = torch.zeros(1, n_seq * N, H * hd, device=dev, dtype=torch.bfloat16)
+    qd = qkv.to(dev)
+    _lib.check(lib.avd_attention(qd.data_ptr(), 0, out.data_ptr(), _lib.AVD_PREC_BF16, n_seq, N, H, hd,
+                                 _lib.stream_ptr()))
+    torch.cuda.synchronize()
+    assert rel_l2(out[0].float().cpu(), _attn_ref(qkv.float(), n_seq, N, H, hd)) < 8e-3   # P and O rounded to bf16
+
+
+@pytest.mark.parametrize("n_seq,N", [(2, 133), (1, 445)])
+def test_attention_fp32(dev, lib, n_seq, N):
+    from multimodal_diffusion_b200 import _lib
+    H, hd = 8, 64
+    qkv = randn(1, n_seq * N, 3 * H * hd) * 1.5
+    out = torch.zeros(3, n_seq * N, H * hd, device=dev, dtype=torch.bfloat16)
+    qd = qkv.to(dev)
+    _lib.check(lib.avd_attention(qd.data_ptr(), 1, out.data_ptr(), _lib.AVD_PREC_FP32, n_seq, N, H, hd,
+                                 _lib.stream_ptr()))
+    assert rel_l2(out.float().sum(0).cpu(), _attn_ref(qkv, n_seq, N, H, hd)) < 2e-6
