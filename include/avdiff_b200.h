@@ -48,6 +48,10 @@ const char* avd_last_error(void);
 int avd_version(void);
 int avd_nseg(int precision);                 /* 1 -> 1, 3 -> 2, 6 -> 3, else -1 */
 int avd_device_check(void);                  /* 0 iff the current device is sm_100 */
+/* sizeof() of the ABI structs as this library was compiled (binding self-check):
+ * 0 avd_cfg_ddim_args, 1 avd_gemm_args, 2 avd_block_weights, 3 avd_core_weights, 4 avd_core_workspace,
+ * 5 avd_head_weights, 6 avd_sampler; -1 for any other id */
+int avd_struct_size(int which);
 
 /* Per-launch profiler (CUDA events on `stream` around every kernel this library launches).
  * Used by bench.py for the roofline object; must be off during graph capture. */

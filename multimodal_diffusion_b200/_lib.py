@@ -97,6 +97,7 @@ _SIGNATURES = {
     "avd_version": (_I, []),
     "avd_nseg": (_I, [_I]),
     "avd_device_check": (_I, []),
+    "avd_struct_size": (_I, [_I]),
     "avd_prof_enable": (_I, [_I]),
     "avd_prof_reset": (_I, []),
     "avd_prof_num_kinds": (_I, []),
@@ -125,6 +126,7 @@ _SIGNATURES = {
     "avd_sample_loop": (_I, [C.POINTER(SamplerArgs), fp, fp, vp]),
 }
 EXPORTED_SYMBOLS = tuple(_SIGNATURES)
+ABI_STRUCTS = (CfgDdimArgs, GemmArgs, BlockWeights, CoreWeights, CoreWorkspace, HeadWeights, SamplerArgs)
 
 _lib: Optional[C.CDLL] = None
 
@@ -149,6 +151,10 @@ def load() -> C.CDLL:
             raise AvdLibraryError(f"{LIB_PATH} does not export {name}") from e
         fn.restype = res
         fn.argtypes = args
+    for i, st in enumerate(ABI_STRUCTS):          # the ctypes mirrors must match the compiled structs byte for byte
+        if lib.avd_struct_size(i) != C.sizeof(st):
+            raise AvdLibraryError(f"ABI mismatch: sizeof({st.__name__}) is {C.sizeof(st)} in the binding but "
+                                  f"{lib.avd_struct_size(i)} in {LIB_PATH.name}; rebuild the library")
     _lib = lib
     return lib
 

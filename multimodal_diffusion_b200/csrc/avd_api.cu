@@ -307,6 +307,19 @@ const char* avd_last_error(void) { return g_last_error.c_str(); }
 int avd_version(void) { return 100; }
 int avd_nseg(int precision) { return nseg_of(precision); }
 
+int avd_struct_size(int which) {
+  switch (which) {
+    case 0: return (int)sizeof(avd_cfg_ddim_args);
+    case 1: return (int)sizeof(avd_gemm_args);
+    case 2: return (int)sizeof(avd_block_weights);
+    case 3: return (int)sizeof(avd_core_weights);
+    case 4: return (int)sizeof(avd_core_workspace);
+    case 5: return (int)sizeof(avd_head_weights);
+    case 6: return (int)sizeof(avd_sampler);
+    default: return -1;
+  }
+}
+
 int avd_device_check(void) {
   int dev = 0;
   AVD_CUDA(cudaGetDevice(&dev));
