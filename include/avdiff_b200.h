@@ -62,6 +62,9 @@ const char* avd_prof_kind_name(int kind);
 /* synchronises the recorded events; returns total ms and launch count of `kind` */
 int avd_prof_collect(int kind, double* total_ms, int64_t* launches);
 int64_t avd_launch_count(void);              /* kernels launched by this library so far */
+/* Debug only: GEMM CTAs write 8 x (globaltimer ns, clock64) phase stamps into dev_u64[cta*16 ..] when the
+ * grid fits n_u64; NULL switches it off (the default). */
+int avd_debug_trace(void* dev_u64, int64_t n_u64);
 
 /* ---------------------------------------------------------------- K1: tokenisers (bit-exact fp32 moves) */
 /* ops.tube_patch_video (avdiff/utils/ops.py:100-119): z[B,C,T,H,W] -> tok[B,(T/t)(H/h)(W/w),C*t*h*w] */

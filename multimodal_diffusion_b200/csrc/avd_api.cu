@@ -4,6 +4,7 @@
 #include "avd_internal.h"
 
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <unordered_map>
@@ -79,25 +80,27 @@ static EncodeTiledFn g_encode = nullptr;
 struct MapKey {
   const void* base;
   uint64_t d0, d1, d2, s1, s2;
-  uint32_t b0, b1;
+  uint32_t b0, b1, dt;
   bool operator==(const MapKey& o) const {
     return base == o.base && d0 == o.d0 && d1 == o.d1 && d2 == o.d2 && s1 == o.s1 && s2 == o.s2 && b0 == o.b0 &&
-           b1 == o.b1;
+           b1 == o.b1 && dt == o.dt;
   }
 };
 struct MapKeyHash {
   size_t operator()(const MapKey& k) const {
     uint64_t h = reinterpret_cast<uint64_t>(k.base);
     auto mix = [&](uint64_t v) { h ^= v + 0x9e3779b97f4a7c15ull + (h << 6) + (h >> 2); };
-    mix(k.d0); mix(k.d1); mix(k.d2); mix(k.s1); mix(k.s2); mix(k.b0); mix(k.b1);
+    mix(k.d0); mix(k.d1); mix(k.d2); mix(k.s1); mix(k.s2); mix(k.b0); mix(k.b1); mix(k.dt);
     return (size_t)h;
   }
 };
 static std::mutex g_map_mu;
 static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> g_maps;
 
-int get_tensor_map_bf16_3d(const void* base, uint64_t d0, uint64_t d1, uint64_t d2, uint64_t stride1_bytes,
-                           uint64_t stride2_bytes, uint32_t box0, uint32_t box1, CUtensorMap* out) {
+// [d2][d1][d0] tensor (d0 contiguous) of bf16 (elem_bytes 2) or fp32 (4); box [1][box1][box0] with
+// box0 * elem_bytes == 128 (one 128-byte swizzle row).
+int get_tensor_map_3d(const void* base, int elem_bytes, uint64_t d0, uint64_t d1, uint64_t d2, uint64_t stride1_bytes,
+                      uint64_t stride2_bytes, uint32_t box0, uint32_t box1, CUtensorMap* out) {
   std::lock_guard<std::mutex> lk(g_map_mu);
   if (g_encode == nullptr) {
     void* fn = nullptr;
@@ -107,7 +110,8 @@ int get_tensor_map_bf16_3d(const void* base, uint64_t d0, uint64_t d1, uint64_t 
       AVD_FAIL("cuTensorMapEncodeTiled not available from the CUDA driver");
     g_encode = reinterpret_cast<EncodeTiledFn>(fn);
   }
-  MapKey key{base, d0, d1, d2, stride1_bytes, stride2_bytes, box0, box1};
+  AVD_REQUIRE(elem_bytes == 2 || elem_bytes == 4, "tensor maps are built for bf16 or fp32");
+  MapKey key{base, d0, d1, d2, stride1_bytes, stride2_bytes, box0, box1, (uint32_t)elem_bytes};
   auto it = g_maps.find(key);
   if (it != g_maps.end()) {
     *out = it->second;
@@ -115,21 +119,36 @@ int get_tensor_map_bf16_3d(const void* base, uint64_t d0, uint64_t d1, uint64_t 
   }
   AVD_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "TMA base must be 16-byte aligned");
   AVD_REQUIRE(stride1_bytes % 16 == 0 && stride2_bytes % 16 == 0, "TMA strides must be multiples of 16 bytes");
-  AVD_REQUIRE(box0 * 2 == 128, "inner box must span one 128-byte swizzle row");
+  AVD_REQUIRE(box0 * (uint32_t)elem_bytes == 128, "inner box must span one 128-byte swizzle row");
   AVD_REQUIRE(box1 >= 1 && box1 <= 256, "box rows out of range");
   cuuint64_t dims[3] = {d0, d1, d2};
   cuuint64_t strides[2] = {stride1_bytes, stride2_bytes};
   cuuint32_t box[3] = {box0, box1, 1};
   cuuint32_t estr[3] = {1, 1, 1};
   CUtensorMap m;
-  CUresult r = g_encode(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
-                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+  CUresult r = g_encode(&m, elem_bytes == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3,
+                        const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) AVD_FAIL("cuTensorMapEncodeTiled failed with CUresult " + std::to_string((int)r));
   if (g_maps.size() > 8192) g_maps.clear();
   g_maps.emplace(key, m);
   *out = m;
   return 0;
+}
+
+int get_tensor_map_bf16_3d(const void* base, uint64_t d0, uint64_t d1, uint64_t d2, uint64_t stride1_bytes,
+                           uint64_t stride2_bytes, uint32_t box0, uint32_t box1, CUtensorMap* out) {
+  return get_tensor_map_3d(base, 2, d0, d1, d2, stride1_bytes, stride2_bytes, box0, box1, out);
+}
+
+bool pdl_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = std::getenv("AVD_PDL");
+    v = (e == nullptr || std::atoi(e) != 0) ? 1 : 0;
+  }
+  return v == 1;
 }
 
 static inline int64_t align_up(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
@@ -360,6 +379,11 @@ int avd_prof_collect(int kind, double* total_ms, int64_t* launches) {
   return 0;
 }
 int64_t avd_launch_count(void) { return g_launches; }
+int avd_debug_trace(void* dev_u64, int64_t n_u64) {
+  g_dbg_trace = static_cast<unsigned long long*>(dev_u64);
+  g_dbg_trace_slots = dev_u64 ? n_u64 : 0;
+  return 0;
+}
 
 // ---- tokenisers
 int avd_tube_patch(const float* z, float* tok, int B, int C, int T, int H, int W, int t, int h, int w, void* stream) {

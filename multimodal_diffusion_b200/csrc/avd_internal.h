@@ -101,6 +101,10 @@ int launch_build_x(const BuildXArgs& a, const float* z, const float* wt, const f
 // tcgen05 GEMM (avd_gemm.cu)
 int launch_gemm(const avd_gemm_args& g, cudaStream_t s);
 
+bool pdl_enabled();     // programmatic dependent launch between the kernels of a step (AVD_PDL=0 switches it off)
+extern unsigned long long* g_dbg_trace;   // debug phase trace of the GEMM kernel (avd_debug_trace)
+extern int64_t g_dbg_trace_slots;
+
 // attention (avd_attn.cu)
 int launch_attention_tc(const void* qkv_bf16, void* out, int out_nseg, int n_seq, int N, int n_heads, int hd,
                         cudaStream_t s);
@@ -109,6 +113,8 @@ int launch_attention_f32(const float* qkv, void* out, int out_nseg, int n_seq, i
 
 // ---- TMA descriptor cache (avd_api.cu) ----------------------------------------------------------
 // bf16 tensor [d2][d1][d0] (d0 contiguous), box [1][box1][box0], SWIZZLE_128B (box0 * 2 bytes must be 128).
+int get_tensor_map_3d(const void* base, int elem_bytes, uint64_t d0, uint64_t d1, uint64_t d2, uint64_t stride1_bytes,
+                      uint64_t stride2_bytes, uint32_t box0, uint32_t box1, CUtensorMap* out);
 int get_tensor_map_bf16_3d(const void* base, uint64_t d0, uint64_t d1, uint64_t d2, uint64_t stride1_bytes,
                            uint64_t stride2_bytes, uint32_t box0, uint32_t box1, CUtensorMap* out);
 
