@@ -138,7 +138,7 @@ typedef struct {
   int rms_dim;
   float rms_eps;
   const float* resid;       /* fp32 [M][N] or NULL */
-  int act;                  /* 0 none, 1 GELU(erf) */
+  int act;                  /* 0 none, 1 GELU(erff), 2 GELU with a 1.5e-7-accurate erf (bf16 mode) */
   float* out_f32;           /* fp32 [M][N] or NULL */
   void* out_bf16;           /* bf16 [out_nseg][M][N] or NULL */
   int out_precision;        /* precision of the consumer of out_bf16 (selects the segment count) */

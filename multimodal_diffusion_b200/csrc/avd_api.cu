@@ -251,7 +251,8 @@ static int core_blocks(const avd_core_weights* w, const float* x_in, const void*
     g = avd_gemm_args{};
     g.M = M; g.N = w->d_mlp; g.K = d; g.precision = w->precision;
     g.A = ws->xa; g.W = b.w_fc1; g.bias = b.b_fc1;
-    g.ssq_in = ws->ssq; g.ssq_parts = parts; g.rms_dim = d; g.rms_eps = w->rms_eps; g.act = 1;
+    g.ssq_in = ws->ssq; g.ssq_parts = parts; g.rms_dim = d; g.rms_eps = w->rms_eps;
+    g.act = tc_attn ? 2 : 1;   // bf16 mode: fast erf (|err| < 2e-7, far below the bf16 rounding of the result)
     g.out_bf16 = ws->hmid; g.out_precision = w->precision;
     AVD_TRY(launch_gemm(g, st));
     // x = x + u W_2^T + b_2               (mmdt.py:98 -> :81)

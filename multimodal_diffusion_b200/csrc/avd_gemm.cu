@@ -3,19 +3,28 @@
 //
 //   out = epilogue( A[M,K] x W[N,K]^T ),   A, W bf16 K-major, fp32 accumulation in TMEM.
 //
-// Warp roles (192 threads, one 128 x BN output tile per CTA):
-//   warp 0      TMA producer: cp.async.bulk.tensor (3-D maps {K, rows, segment}) into a STAGES-deep ring of
-//               128B-swizzled smem tiles, mbarrier complete_tx
-//   warp 1      TMEM allocator + MMA issuer: one elected lane issues tcgen05.mma.cta_group::1.kind::f16
-//               (M=128, N=BN, K=16) x 4 per 64-wide k-block; tcgen05.commit releases the smem slot / signals
-//               the epilogue
-//   warps 2..5  epilogue: tcgen05.ld 32 lanes x 32 columns -> registers; thread == output row
-//               v = acc * rinv(row) + bias (+ resid) [gelu]; stores fp32 and/or bf16 segments, and the
-//               per-row partial sums of squares that the NEXT GEMM turns into its RMSNorm row scale.
+// One CTA = one 128 x BN output tile, 256 threads, TWO independent load/MMA pipelines that split the k-blocks
+// (pipeline h takes k-block iterations h, h+2, ...) and accumulate into two TMEM tiles that the epilogue adds.
+// Why two: on B200 a single thread can only push one {mbarrier wait, 4 x tcgen05.mma, commit} round per ~500
+// cycles and one {wait, expect_tx, 2 x TMA} round per ~300 cycles (tools/mma_probe.cu, tools/tma_probe.cu), while a
+// 128x64x64 block of MMAs executes in ~220 cycles; two issuing warps hide each other's barrier latency and bring
+// the tensor pipe to its floor (64 cycles per M128 N128 K16 MMA, 48 at N64).
+//
+// Warp roles:
+//   warps 0,1   TMA producers of pipeline 0 / 1: cp.async.bulk.tensor (3-D maps {K, rows, segment}) into a ring of
+//               128B-swizzled smem stages, mbarrier complete_tx.  Weight tiles of the first ring pass are issued
+//               BEFORE griddepcontrol.wait (they do not depend on the previous kernel), activations after it.
+//   warps 2,3   MMA issuers of pipeline 0 / 1 (warp 2 also owns the TMEM allocation): one lane issues
+//               tcgen05.mma.cta_group::1.kind::f16 (M=128, N=BN, K=16) x 4 per 64-wide k-block; tcgen05.commit
+//               releases the smem stage / signals the epilogue
+//   warps 4..7  epilogue: tcgen05.ld 32 lanes x 32 columns of both accumulators -> registers; thread == output row
+//               v = (acc0+acc1) * rinv(row) + bias (+ resid) [gelu]; results are staged in 128B-swizzled smem boxes
+//               and leave through TMA stores (fp32 and/or bf16 segments); per-row partial sums of squares feed the
+//               NEXT GEMM's RMSNorm row scale.
 //
 // Precision modes are realised by the k-loop: for mode p the operands are stored as hi/(mid/)lo bf16
 // segments and the loop runs over a list of (A segment, W segment) pairs, smallest products first, all
-// accumulating into the same TMEM tile (1, 3 or 6 passes over K).
+// accumulating into the same TMEM tiles (1, 3 or 6 passes over K).
 #include "avd_internal.h"
 #include "avd_ptx.cuh"
 
@@ -25,7 +34,7 @@ namespace avd {
 
 constexpr int GEMM_BM = 128;
 constexpr int GEMM_BK = 64;            // 64 bf16 = 128 B = one swizzle atom row
-constexpr int GEMM_THREADS = 192;
+constexpr int GEMM_THREADS = 256;
 constexpr int GEMM_BOX = 4096;         // one epilogue staging box: 32 rows x 128 B (32 fp32 or 64 bf16 columns)
 
 struct GemmParams {
@@ -38,36 +47,35 @@ struct GemmParams {
   float inv_sqrt_rms_dim;    // 1/sqrt(rms_dim)
   float rms_eps;
   int has_resid;             // residual tile comes in through tmR (and the fp32 result is written over it in smem)
-  int act;
-  int has_f32;               // fp32 result leaves through tmF
-  int out_nseg;              // bf16 segments leaving through tmO (0 = none)
+  int act;                   // 0 none, 1 GELU (erff), 2 GELU (fast erf, |err| < 2e-7)
+  float* out_f32;            // fp32 result [M,N] (may alias the residual) or nullptr
+  __nv_bfloat16* out_bf16;   // bf16 result segments [out_nseg][M][N] or nullptr
+  int out_nseg;
   float* ssq_out;
-  int cx, cy;                // cluster dims: A tiles are multicast across x (N tiles), W tiles across y (M tiles)
-  int dbg;                   // debug: 1 = MMA loop only (loads stop after the first fill), 2 = loads only (no MMA)
   unsigned long long* trace; // debug: per-CTA phase timestamps (avd_debug_trace), nullptr in production
 };
 
-__device__ __forceinline__ void trace_mark(const GemmParams& p, int slot) {
-  if (p.trace != nullptr) {
+__device__ __forceinline__ void trace_mark(unsigned long long* trace, int slot) {
+  if (trace != nullptr) {
     const int cta = blockIdx.y * gridDim.x + blockIdx.x;
     unsigned long long g, c;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g));
     asm volatile("mov.u64 %0, %%clock64;" : "=l"(c));
-    p.trace[(cta * 16 + slot) * 2] = g;
-    p.trace[(cta * 16 + slot) * 2 + 1] = c;
+    trace[(cta * 16 + slot) * 2] = g;
+    trace[(cta * 16 + slot) * 2 + 1] = c;
   }
 }
 
-template <int BN, int STAGES>
+template <int BN, int STAGES>   // STAGES = ring depth of EACH of the two pipelines
 struct GemmSmem {
   static constexpr int A_BYTES = GEMM_BM * GEMM_BK * 2;
   static constexpr int B_BYTES = BN * GEMM_BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int PIPE_BYTES = STAGES * STAGE_BYTES;
+  static constexpr int PIPE_BYTES = 2 * STAGES * STAGE_BYTES;
   static constexpr int F32_TILE = GEMM_BM * BN * 4;
   static constexpr int BF16_TILE = GEMM_BM * BN * 2;
-  static constexpr int TAIL_BYTES = 256 + BN * 4;          // mbarriers + TMEM slot, bias tile
-  static int total(bool resid) { return PIPE_BYTES + (resid ? F32_TILE : 0) + TAIL_BYTES; }
+  static constexpr int TAIL_BYTES = 256 + BN * 4 + 1024 + 512;   // mbarriers + TMEM slot, bias tile, ssq exchange, rinv
+  static constexpr int total(bool resid) { return PIPE_BYTES + (resid ? F32_TILE : 0) + TAIL_BYTES; }
 };
 
 __device__ __forceinline__ float4 lds128(const uint8_t* p) {
@@ -82,29 +90,46 @@ __device__ __forceinline__ void sts128u(uint8_t* p, uint32_t a, uint32_t b, uint
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(smem_u32(p)), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
 
-// smem map:  [ STAGES x (A 128x64 | W BNx64) ]  [ residual / fp32 result tile, only with has_resid ]  [ barriers | bias ]
+// GELU with erf from Abramowitz-Stegun 7.1.26 (|erf error| <= 1.5e-7): 2 MUFU + ~12 FMA-pipe instructions instead
+// of erff's ~40.  Used in bf16 mode only, where the result is rounded to bf16 (2^-9) anyway.
+__device__ __forceinline__ float gelu_fast(float x) {
+  const float y = fabsf(x) * 0.70710678118654752440f;
+  float t;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, y, 1.0f)));
+  float pl = fmaf(t, 1.061405429f, -1.453152027f);
+  pl = fmaf(pl, t, 1.421413741f);
+  pl = fmaf(pl, t, -0.284496736f);
+  pl = fmaf(pl, t, 0.254829592f);
+  pl *= t;
+  float e;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(-y * y * 1.4426950408889634f));
+  const float erf_abs = fmaf(-pl, e, 1.0f);
+  const float h = 0.5f * x;
+  return fmaf(fabsf(h), erf_abs, h);          // 0.5 x (1 + sign(x) erf|.|) = h + |h| erf_abs
+}
+
+// smem map:  [ 2 pipelines x STAGES x (A 128x64 | W BNx64) ]  [ residual / fp32 result tile, only with has_resid ]
+//            [ barriers | bias ]
 // After the last MMA has retired the pipeline region is reused as epilogue staging: fp32 result boxes first (when
 // there is no residual tile to overwrite), then out_nseg bf16 tiles.  Every staging box is 32 rows x 128 B with the
 // 128-byte swizzle the TMA store expects, written by the warp that owns those 32 TMEM lanes.
 template <int BN, int STAGES>
-__global__ void __launch_bounds__(GEMM_THREADS) gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA,
-                                                               const __grid_constant__ CUtensorMap tmB,
-                                                               const __grid_constant__ CUtensorMap tmR,
-                                                               const __grid_constant__ CUtensorMap tmF,
-                                                               const __grid_constant__ CUtensorMap tmO,
-                                                               const GemmParams p) {
+__global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                                  const __grid_constant__ CUtensorMap tmB,
+                                                                  const __grid_constant__ CUtensorMap tmR,
+                                                                  const GemmParams p) {
   using S = GemmSmem<BN, STAGES>;
-  constexpr uint32_t TMEM_COLS = BN < 32 ? 32 : BN;
+  constexpr uint32_t TMEM_COLS = BN <= 32 ? 64 : BN <= 64 ? 128 : BN <= 128 ? 256 : 512;   // two accumulators
   extern __shared__ __align__(1024) uint8_t gemm_smem[];
   uint8_t* smem = gemm_smem;
   if ((smem_u32(smem) & 1023u) != 0) __trap();   // 128B-swizzle tiles need 1024-B aligned bases
   uint8_t* res_tile = smem + S::PIPE_BYTES;
   uint8_t* tail = res_tile + (p.has_resid ? S::F32_TILE : 0);
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(tail);
-  uint64_t* empty_bar = full_bar + STAGES;
-  uint64_t* acc_bar = empty_bar + STAGES;
-  uint64_t* res_bar = acc_bar + 1;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tail + 192);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(tail);
+  // per pipeline h: full[h*STAGES + s], empty[(2 + h)*STAGES + s]; then acc[2], res
+  uint64_t* acc_bar = bars + 4 * STAGES;
+  uint64_t* res_bar = acc_bar + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tail + 240);
   float* bias_s = reinterpret_cast<float*>(tail + 256);
 
   const int warp = threadIdx.x >> 5;
@@ -113,170 +138,206 @@ __global__ void __launch_bounds__(GEMM_THREADS) gemm_tc_kernel(const __grid_cons
   const int n0 = blockIdx.x * BN;
   const int kblocks = p.K / GEMM_BK;
   const int iters = kblocks * p.n_pairs;
-  const int csize = p.cx * p.cy;
-  const int rx = blockIdx.x % p.cx, ry = blockIdx.y % p.cy;      // position inside the cluster
-  const uint16_t a_mask = (uint16_t)(((1u << p.cx) - 1u) << (ry * p.cx));
-  uint16_t w_mask = 0;
-  for (int y = 0; y < p.cy; ++y) w_mask |= (uint16_t)(1u << (rx + y * p.cx));
+  unsigned long long* const trace = p.trace;
 
-  if (threadIdx.x == 0) trace_mark(p, 0);
+  if (threadIdx.x == 0) trace_mark(trace, 0);
   if (warp == 0 && lane == 0) {
-    if (csize > 1 && (int)cluster_ctarank() != ry * p.cx + rx) __trap();
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
     if (p.has_resid) tma_prefetch_desc(&tmR);
-    if (p.has_f32) tma_prefetch_desc(&tmF);
-    if (p.out_nseg) tma_prefetch_desc(&tmO);
-    for (int i = 0; i < STAGES; ++i) {
-      mbar_init(&full_bar[i], 1);
-      mbar_init(&empty_bar[i], p.cx + p.cy - 1);   // every CTA that reads a slice of this slot's multicasts
-    }
-    mbar_init(acc_bar, 1);
-    mbar_init(res_bar, 1);
+    for (int i = 0; i < 4 * STAGES + 3; ++i) mbar_init(&bars[i], 1);
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc<TMEM_COLS>(tmem_slot);
-  if (warp >= 2) {
-    const int t = threadIdx.x - 64;
-    if (t < BN) bias_s[t] = p.bias != nullptr ? p.bias[n0 + t] : 0.0f;   // weights: not produced by the previous kernel
+  if (warp == 2) tmem_alloc<TMEM_COLS>(tmem_slot);
+  if (warp >= 4) {
+    for (int t = threadIdx.x - 128; t < BN; t += 128)
+      bias_s[t] = p.bias != nullptr ? p.bias[n0 + t] : 0.0f;   // weights: not produced by the previous kernel
   }
   tc_fence_before();
-  if (csize > 1) cluster_sync_all(); else __syncthreads();
+  __syncthreads();
   tc_fence_after();
   const uint32_t tmem_acc = *tmem_slot;
   pdl_launch_dependents();
-  if (threadIdx.x == 0) trace_mark(p, 1);
+  if (threadIdx.x == 0) trace_mark(trace, 1);
 
-  if (warp == 0) {
-    // ------------------------------------------------------------------ TMA producer
+  if (warp < 2) {
+    // ------------------------------------------------------------------ TMA producer of pipeline h
     if (lane == 0) {
-      const int a_rows = GEMM_BM / p.cx, w_rows = BN / p.cy;    // this CTA's slice of the A / W tile
-      auto load_w = [&](int it) {
-        const int st = it % STAGES;
-        const int pi = it / kblocks, kb = it - pi * kblocks;
-        const int sw = (p.pairs >> (4 * pi)) & 3;
-        uint8_t* b_dst = smem + st * S::STAGE_BYTES + S::A_BYTES + ry * w_rows * 128;
-        if (p.cy > 1) tma_load_3d_mc(b_dst, &tmB, &full_bar[st], kb * GEMM_BK, n0 + ry * w_rows, sw, w_mask);
-        else tma_load_3d(b_dst, &tmB, &full_bar[st], kb * GEMM_BK, n0, sw);
-      };
-      auto load_a = [&](int it) {
-        const int st = it % STAGES;
-        const int pi = it / kblocks, kb = it - pi * kblocks;
-        const int sa = ((p.pairs >> (4 * pi)) & 0xF) >> 2;
-        uint8_t* a_dst = smem + st * S::STAGE_BYTES + rx * a_rows * 128;
-        if (p.cx > 1) tma_load_3d_mc(a_dst, &tmA, &full_bar[st], kb * GEMM_BK, m0 + rx * a_rows, sa, a_mask);
-        else tma_load_3d(a_dst, &tmA, &full_bar[st], kb * GEMM_BK, m0, sa);
-      };
-      const int pre = iters < STAGES ? iters : STAGES;
-      for (int it = 0; it < pre; ++it) {          // weights first: they do not depend on the previous kernel
-        mbar_expect_tx(&full_bar[it], S::STAGE_BYTES);
-        load_w(it);
+      const int h = warp;
+      const int count = (iters - h + 1) >> 1;            // iterations h, h+2, ...
+      uint64_t* full = bars + h * STAGES;
+      uint64_t* empty = bars + (2 + h) * STAGES;
+      uint8_t* ring = smem + h * STAGES * S::STAGE_BYTES;
+      const uint32_t pairs = p.pairs;
+      int kb = h, pi = 0;
+      while (kb >= kblocks) { kb -= kblocks; ++pi; }
+      int kb_w = kb, pi_w = pi;                          // the weight loads of the first ring pass run ahead
+      const int pre = count < STAGES ? count : STAGES;
+      for (int j = 0; j < pre; ++j) {
+        mbar_expect_tx(&full[j], S::STAGE_BYTES);
+        tma_load_3d(ring + j * S::STAGE_BYTES + S::A_BYTES, &tmB, &full[j], kb_w * GEMM_BK, n0, (pairs >> (4 * pi_w)) & 3);
+        kb_w += 2;
+        while (kb_w >= kblocks) { kb_w -= kblocks; ++pi_w; }
       }
       pdl_wait();
-      for (int it = 0; it < pre; ++it) load_a(it);
-      if (p.has_resid) {
+      for (int j = 0; j < pre; ++j) {
+        tma_load_3d(ring + j * S::STAGE_BYTES, &tmA, &full[j], kb * GEMM_BK, m0, (pairs >> (4 * pi + 2)) & 3);
+        kb += 2;
+        while (kb >= kblocks) { kb -= kblocks; ++pi; }
+      }
+      if (h == 0 && p.has_resid) {
         mbar_expect_tx(res_bar, S::F32_TILE);
         for (int ch = 0; ch < BN / 32; ++ch)
           for (int q = 0; q < 4; ++q)
             tma_load_3d(res_tile + (ch * 4 + q) * GEMM_BOX, &tmR, res_bar, n0 + ch * 32, m0 + q * 32, 0);
       }
-      for (int it = pre; it < iters && p.dbg != 1 && p.dbg != 3; ++it) {
-        const int st = it % STAGES;
-        mbar_wait(&empty_bar[st], ((it / STAGES) & 1) ^ 1);
-        mbar_expect_tx(&full_bar[st], S::STAGE_BYTES);
-        load_w(it);
-        load_a(it);
-      }
-    }
-  } else if (warp == 1) {
-    // ------------------------------------------------------------------ MMA issuer
-    if (lane == 0) {
-      const uint32_t idesc = make_idesc_bf16(GEMM_BM, BN, 0, 0);
-      const uint16_t c_mask = a_mask | w_mask;
-      const uint32_t desc_hi = smem_desc_hi_sw128(1024);
-      const uint32_t a_lo0 = smem_desc_lo_sw128(smem_u32(smem), 16);
       int st = 0;
-      uint32_t ph = 0;
-      for (int it = 0; it < iters; ++it) {
-        if ((p.dbg != 1 && p.dbg != 3) || it < STAGES) mbar_wait(&full_bar[st], ph);
-        tc_fence_after();
-        if (it == 0) trace_mark(p, 2);
-        const uint32_t a_lo = a_lo0 + st * (S::STAGE_BYTES >> 4);
-        const uint32_t b_lo = a_lo + (S::A_BYTES >> 4);
-        if (p.dbg != 2) {
-#pragma unroll
-          for (int k = 0; k < GEMM_BK / 16; ++k)     // +32 bytes (2 x 16-byte units) per 16-wide k step
-            umma_bf16_lh(tmem_acc, a_lo + 2 * k, b_lo + 2 * k, desc_hi, idesc, (it > 0 || k > 0) ? 1u : 0u);
-        }
-        // smem slot reusable (cluster-wide, for the multicast writers) once these MMAs have read it
-        if (it + STAGES < iters) {
-          if (csize > 1) umma_commit_mc(&empty_bar[st], c_mask); else umma_commit(&empty_bar[st]);
-        }
+      uint32_t ph = 0;                                   // parity of the ring pass being REFILLED
+      for (int j = pre; j < count; ++j) {
+        mbar_wait(&empty[st], ph);
+        uint8_t* dst = ring + st * S::STAGE_BYTES;
+        const uint32_t pr = pairs >> (4 * pi);
+        mbar_expect_tx(&full[st], S::STAGE_BYTES);
+        tma_load_3d(dst, &tmA, &full[st], kb * GEMM_BK, m0, (pr >> 2) & 3);
+        tma_load_3d(dst + S::A_BYTES, &tmB, &full[st], kb * GEMM_BK, n0, pr & 3);
+        kb += 2;
+        while (kb >= kblocks) { kb -= kblocks; ++pi; }
         if (++st == STAGES) { st = 0; ph ^= 1; }
       }
-      umma_commit(acc_bar);            // accumulator complete
-      trace_mark(p, 3);
     }
-  } else {
-    // ------------------------------------------------------------------ epilogue (warps 2..5)
+  } else if (warp < 4) {
+    // ------------------------------------------------------------------ MMA issuer of pipeline h
+    if (lane == 0) {
+      const int h = warp - 2;
+      const int count = (iters - h + 1) >> 1;
+      uint64_t* full = bars + h * STAGES;
+      uint64_t* empty = bars + (2 + h) * STAGES;
+      const uint32_t idesc = make_idesc_bf16(GEMM_BM, BN, 0, 0);
+      const uint32_t desc_hi = smem_desc_hi_sw128(1024);
+      const uint32_t a_lo0 = smem_desc_lo_sw128(smem_u32(smem + h * STAGES * S::STAGE_BYTES), 16);
+      const uint32_t acc = tmem_acc + h * BN;
+      int st = 0;
+      uint32_t ph = 0;
+      uint32_t a_lo = a_lo0;
+      for (int j = 0; j < count; ++j) {
+        mbar_wait(&full[st], ph);
+        tc_fence_after();
+        const uint32_t b_lo = a_lo + (S::A_BYTES >> 4);
+#pragma unroll
+        for (int k = 0; k < GEMM_BK / 16; ++k)     // +32 bytes (2 x 16-byte units) per 16-wide k step
+          umma_bf16_lh(acc, a_lo + 2 * k, b_lo + 2 * k, desc_hi, idesc, (j > 0 || k > 0) ? 1u : 0u);
+        if (j + STAGES < count) umma_commit(&empty[st]);   // stage reusable once these MMAs have read it
+        a_lo += S::STAGE_BYTES >> 4;
+        if (++st == STAGES) { st = 0; ph ^= 1; a_lo = a_lo0; }
+      }
+      if (count > 0) umma_commit(&acc_bar[h]);     // accumulator h complete
+      else mbar_arrive(&acc_bar[h]);               // nothing to do for this pipeline (a single k-block)
+      if (h == 0) trace_mark(trace, 3);
+    }
+  }
+  __syncwarp();   // lanes 1..31 of the role warps sleep here (no polling next to the issuing lane) until lane 0 is done
+
+  {
+    // ------------------------------------------------------------------ epilogue (all 8 warps)
+    // warp w and warp w+4 share TMEM lane quadrant w%4; within each 64-column pair of chunks, warp w takes the
+    // even 32-column chunk and warp w+4 the odd one.
     const int quad = warp & 3;                 // TMEM lane quadrant this warp may access
+    const int hf = warp >> 2;
     const int row = m0 + quad * 32 + lane;
     const bool live = row < p.M;
-    const bool box_live = m0 + quad * 32 < p.M;
+    const bool two_acc = iters > 1;
+    const int act = p.act, out_nseg = p.out_nseg;
+    const bool has_resid = p.has_resid != 0, has_f32 = p.out_f32 != nullptr;
+    float* const ssq_out = p.ssq_out;
+    float* ssq_x = bias_s + BN;                // [2][128] partial row sums handed from warp w+4 to warp w
+    float* rinv_s = ssq_x + 256;               // [128] RMSNorm row scales, computed by warps 4..7 during the mainloop
     pdl_wait();
     float rinv = 1.0f;
-    if (p.ssq_in != nullptr && live) {
-      float ss = 0.0f;
-      for (int q = 0; q < p.ssq_parts; ++q) ss += p.ssq_in[(int64_t)row * p.ssq_parts + q];
-      rinv = 1.0f / (sqrtf(ss) * p.inv_sqrt_rms_dim + p.rms_eps);
+    if (hf == 1) {
+      if (p.ssq_in != nullptr && live) {
+        float ss = 0.0f;
+        for (int q = 0; q < p.ssq_parts; ++q) ss += p.ssq_in[(int64_t)row * p.ssq_parts + q];
+        rinv = 1.0f / (sqrtf(ss) * p.inv_sqrt_rms_dim + p.rms_eps);
+      }
+      rinv_s[quad * 32 + lane] = rinv;
+      asm volatile("bar.arrive 1, 256;" ::: "memory");
+    } else {
+      named_bar_sync(1, 256);
+      rinv = rinv_s[quad * 32 + lane];
     }
-    named_bar_sync(1, 128);                    // bias tile visible to all four epilogue warps
-    if (p.has_resid) mbar_wait(res_bar, 0);
-    if (threadIdx.x == 64) trace_mark(p, 4);
-    mbar_wait(acc_bar, 0);
+    if (has_resid) mbar_wait(res_bar, 0);
+    if (threadIdx.x == 128) trace_mark(trace, 4);
+    mbar_wait(&acc_bar[0], 0);
+    mbar_wait(&acc_bar[1], 0);
     tc_fence_after();
-    if (threadIdx.x == 64) trace_mark(p, 5);
+    if (threadIdx.x == 128) trace_mark(trace, 5);
     // staging: the fp32 result overwrites the residual tile in place, or (no residual) starts the reused pipeline smem
-    uint8_t* f32_stage = p.has_resid ? res_tile : smem;
-    uint8_t* bf_stage = smem + ((p.has_f32 && !p.has_resid) ? S::F32_TILE : 0);
+    uint8_t* f32_stage = has_resid ? res_tile : smem;
+    uint8_t* bf_stage = smem + ((has_f32 && !has_resid) ? S::F32_TILE : 0);
     const int sw = lane & 7;
-    float ssq_acc = 0.0f;
+    const uint32_t t_row = tmem_acc + ((uint32_t)(quad * 32) << 16);
+    uint32_t r[32], r1[32];
+    if (hf < BN / 32) {                        // prefetch this warp's first chunk
+      tmem_ld_32x32(t_row + hf * 32, r);
+      if (two_acc) tmem_ld_32x32(t_row + BN + hf * 32, r1);
+    }
 #pragma unroll 1
-    for (int ch = 0; ch < BN / 32; ++ch) {
-      uint32_t r[32];
-      tmem_ld_32x32(tmem_acc + ((uint32_t)(quad * 32) << 16) + ch * 32, r);
-      tmem_ld_wait();
-      if (threadIdx.x == 64 && ch == 0) trace_mark(p, 8);
+    for (int ch = hf; ch < BN / 32; ch += 2) {
       float v[32];
+      tmem_ld_wait();
+      if (two_acc) {
 #pragma unroll
-      for (int j = 0; j < 32; ++j) v[j] = fmaf(__uint_as_float(r[j]), rinv, bias_s[ch * 32 + j]);
+        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) + __uint_as_float(r1[j]);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+      }
+      if (ch + 2 < BN / 32) {                  // next chunk's TMEM loads fly while this one is processed
+        tmem_ld_32x32(t_row + (ch + 2) * 32, r);
+        if (two_acc) tmem_ld_32x32(t_row + BN + (ch + 2) * 32, r1);
+      }
+      if (threadIdx.x == 128 && ch == hf) trace_mark(trace, 8);
+#pragma unroll
+      for (int j = 0; j < 32; j += 4) {
+        const float4 b4 = *reinterpret_cast<const float4*>(bias_s + ch * 32 + j);
+        v[j] = fmaf(v[j], rinv, b4.x); v[j + 1] = fmaf(v[j + 1], rinv, b4.y);
+        v[j + 2] = fmaf(v[j + 2], rinv, b4.z); v[j + 3] = fmaf(v[j + 3], rinv, b4.w);
+      }
       uint8_t* fbox = f32_stage + (ch * 4 + quad) * GEMM_BOX + lane * 128;
-      if (p.has_resid) {
+      if (has_resid) {
 #pragma unroll
         for (int c = 0; c < 8; ++c) {
           const float4 x4 = lds128(fbox + ((c ^ sw) << 4));
           v[4 * c] += x4.x; v[4 * c + 1] += x4.y; v[4 * c + 2] += x4.z; v[4 * c + 3] += x4.w;
         }
       }
-      if (p.act == 1) {
+      if (act == 1) {
 #pragma unroll
         for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
+      } else if (act == 2) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = gelu_fast(v[j]);
       }
-      if (threadIdx.x == 64 && ch == 0) trace_mark(p, 9);
-      if (p.has_f32) {
+      if (threadIdx.x == 128 && ch == hf) trace_mark(trace, 9);
+      if (has_f32) {
 #pragma unroll
         for (int c = 0; c < 8; ++c) sts128(fbox + ((c ^ sw) << 4), v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
       }
-      if (p.ssq_out != nullptr) {
+      float ssq_acc = 0.0f;
+      if (ssq_out != nullptr) {
 #pragma unroll
         for (int j = 0; j < 32; ++j) ssq_acc = fmaf(v[j], v[j], ssq_acc);
-        if (ch & 1) {  // a 64-column part is complete
-          if (live) p.ssq_out[(int64_t)row * (p.N / 64) + ((n0 + ch * 32) >> 6)] = ssq_acc;
-          ssq_acc = 0.0f;
-        }
+        if (hf == 1) ssq_x[((ch >> 1) & 1) * 128 + quad * 32 + lane] = ssq_acc;
       }
-      if (p.out_nseg > 0) {
-        for (int sg = 0; sg < p.out_nseg; ++sg) {
+      const int c0 = (ch & 1) * 4;
+      if (out_nseg == 1) {
+        uint8_t* bbox = bf_stage + ((ch >> 1) * 4 + quad) * GEMM_BOX + lane * 128;
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+          sts128u(bbox + (((c0 + c) ^ sw) << 4), pack_bf16x2(v[8 * c], v[8 * c + 1]), pack_bf16x2(v[8 * c + 2], v[8 * c + 3]),
+                  pack_bf16x2(v[8 * c + 4], v[8 * c + 5]), pack_bf16x2(v[8 * c + 6], v[8 * c + 7]));
+      } else if (out_nseg > 1) {
+        for (int sg = 0; sg < out_nseg; ++sg) {
           uint32_t w[16];
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
@@ -287,39 +348,53 @@ __global__ void __launch_bounds__(GEMM_THREADS) gemm_tc_kernel(const __grid_cons
             w[j] = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
           }
           uint8_t* bbox = bf_stage + ((sg * (BN / 64) + (ch >> 1)) * 4 + quad) * GEMM_BOX + lane * 128;
-          const int c0 = (ch & 1) * 4;
 #pragma unroll
           for (int c = 0; c < 4; ++c)
             sts128u(bbox + (((c0 + c) ^ sw) << 4), w[4 * c], w[4 * c + 1], w[4 * c + 2], w[4 * c + 3]);
         }
       }
-      if (threadIdx.x == 64 && ch == 0) trace_mark(p, 10);
-      fence_async_smem();      // staging writes (generic proxy) -> visible to the TMA store (async proxy)
-      __syncwarp();
-      if (threadIdx.x == 64 && ch == 0) trace_mark(p, 11);
-      if (lane == 0 && box_live) {
-        if (p.has_f32) tma_store_3d(&tmF, f32_stage + (ch * 4 + quad) * GEMM_BOX, n0 + ch * 32, m0 + quad * 32, 0);
-        if (p.out_nseg > 0 && (ch & 1)) {
-          for (int sg = 0; sg < p.out_nseg; ++sg)
-            tma_store_3d(&tmO, bf_stage + ((sg * (BN / 64) + (ch >> 1)) * 4 + quad) * GEMM_BOX, n0 + (ch >> 1) * 64,
-                         m0 + quad * 32, sg);
+      if (threadIdx.x == 128 && ch == hf) trace_mark(trace, 10);
+      const bool paired = (out_nseg > 0 || ssq_out != nullptr);   // the two warps of a quadrant share 64-column units
+      if (paired) named_bar_sync(2 + quad, 64); else __syncwarp();
+      if (threadIdx.x == 128 && ch == hf) trace_mark(trace, 11);
+      if (hf == 0 && ssq_out != nullptr && live)
+        ssq_out[(int64_t)row * (p.N / 64) + ((n0 + ch * 32) >> 6)] = ssq_acc + ssq_x[((ch >> 1) & 1) * 128 + quad * 32 + lane];
+      // staged boxes -> global, coalesced: 8 lanes cover one 128-byte row, one warp instruction covers 4 rows
+      const int rr = lane >> 3, cc = lane & 7;
+      if (has_f32) {
+        const uint8_t* box = f32_stage + (ch * 4 + quad) * GEMM_BOX;
+        float* gp = p.out_f32 + (int64_t)(m0 + quad * 32) * p.N + n0 + ch * 32 + cc * 4;
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+          const int rw = it * 4 + rr;
+          const float4 x4 = lds128(box + rw * 128 + ((cc ^ (rw & 7)) << 4));
+          if (m0 + quad * 32 + rw < p.M) *reinterpret_cast<float4*>(gp + (int64_t)rw * p.N) = x4;
         }
-        tma_store_commit();
       }
-      if (threadIdx.x == 64 && ch == 0) trace_mark(p, 12);
-      if (threadIdx.x == 64 && ch == BN / 32 - 1) trace_mark(p, 13);
+      if (out_nseg > 0) {      // the pair's 64-column bf16 box: this warp stores rows [16 hf, 16 hf + 16)
+        for (int sg = 0; sg < out_nseg; ++sg) {
+          const uint8_t* box = bf_stage + ((sg * (BN / 64) + (ch >> 1)) * 4 + quad) * GEMM_BOX;
+          __nv_bfloat16* gp = p.out_bf16 + (int64_t)sg * p.M * p.N + (int64_t)(m0 + quad * 32) * p.N + n0 + (ch >> 1) * 64 + cc * 8;
+#pragma unroll
+          for (int it = 0; it < 4; ++it) {
+            const int rw = hf * 16 + it * 4 + rr;
+            const float4 x4 = lds128(box + rw * 128 + ((cc ^ (rw & 7)) << 4));
+            if (m0 + quad * 32 + rw < p.M) *reinterpret_cast<float4*>(gp + (int64_t)rw * p.N) = x4;
+          }
+        }
+      }
+      if (threadIdx.x == 128 && ch == hf) trace_mark(trace, 12);
     }
-    if (lane == 0) tma_store_wait_read();      // smem must stay alive until the bulk stores have read it
-    if (threadIdx.x == 64) trace_mark(p, 6);
+    if (threadIdx.x == 128) trace_mark(trace, 6);
   }
 
   tc_fence_before();
-  if (csize > 1) cluster_sync_all(); else __syncthreads();   // peers may still multicast into / arrive on this CTA
-  if (warp == 1) {
+  __syncthreads();
+  if (warp == 2) {
     tc_fence_after();
     tmem_dealloc<TMEM_COLS>(tmem_acc);
   }
-  if (threadIdx.x == 0) trace_mark(p, 7);
+  if (threadIdx.x == 0) trace_mark(trace, 7);
 }
 
 unsigned long long* g_dbg_trace = nullptr;
@@ -331,30 +406,22 @@ static int env_int(const char* name, int dflt) {
 }
 
 template <int BN, int STAGES>
-static int launch_gemm_bn(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmR, const CUtensorMap& tmF,
-                          const CUtensorMap& tmO, const GemmParams& p, cudaStream_t s) {
+static int launch_gemm_bn(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmR, const GemmParams& p,
+                          cudaStream_t s) {
   using S = GemmSmem<BN, STAGES>;
   static bool attr_set = false;
   if (!attr_set) {
     AVD_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  S::total(true)));
+                                  S::total(BN <= 64)));
     attr_set = true;
   }
-  const int mt = (p.M + GEMM_BM - 1) / GEMM_BM;
   cudaLaunchConfig_t cfg{};
-  cfg.gridDim = dim3(p.N / BN, (mt + p.cy - 1) / p.cy * p.cy);
+  cfg.gridDim = dim3(p.N / BN, (p.M + GEMM_BM - 1) / GEMM_BM);
   cfg.blockDim = dim3(GEMM_THREADS);
   cfg.dynamicSmemBytes = S::total(p.has_resid != 0);
   cfg.stream = s;
-  cudaLaunchAttribute attrs[2];
+  cudaLaunchAttribute attrs[1];
   int na = 0;
-  if (p.cx * p.cy > 1) {
-    attrs[na].id = cudaLaunchAttributeClusterDimension;
-    attrs[na].val.clusterDim.x = p.cx;
-    attrs[na].val.clusterDim.y = p.cy;
-    attrs[na].val.clusterDim.z = 1;
-    ++na;
-  }
   if (pdl_enabled()) {
     attrs[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attrs[na].val.programmaticStreamSerializationAllowed = 1;
@@ -363,8 +430,18 @@ static int launch_gemm_bn(const CUtensorMap& tmA, const CUtensorMap& tmB, const 
   cfg.attrs = attrs;
   cfg.numAttrs = na;
   LaunchScope ls(KIND_GEMM, s);
-  AVD_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<BN, STAGES>, tmA, tmB, tmR, tmF, tmO, p));
+  AVD_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<BN, STAGES>, tmA, tmB, tmR, p));
   return 0;
+}
+
+static int pipe_bytes_of(int bn) {
+  switch (bn) {
+    case 256: return GemmSmem<256, 2>::PIPE_BYTES;
+    case 192: return GemmSmem<192, 2>::PIPE_BYTES;
+    case 128: return GemmSmem<128, 3>::PIPE_BYTES;
+    case 64: return GemmSmem<64, 3>::PIPE_BYTES;
+    default: return GemmSmem<32, 3>::PIPE_BYTES;
+  }
 }
 
 int launch_gemm(const avd_gemm_args& g, cudaStream_t s) {
@@ -378,25 +455,34 @@ int launch_gemm(const avd_gemm_args& g, cudaStream_t s) {
   AVD_REQUIRE(g.out_f32 != nullptr || g.out_bf16 != nullptr, "no output");
   AVD_REQUIRE(g.out_bf16 == nullptr || g.N % 64 == 0, "bf16 output needs N % 64 == 0");
   AVD_REQUIRE(g.resid == nullptr || g.out_f32 != nullptr, "a residual needs the fp32 output");
+  AVD_REQUIRE(g.act >= 0 && g.act <= 2, "act must be 0 (none), 1 (GELU erf) or 2 (GELU fast erf)");
   const int out_nseg = g.out_bf16 != nullptr ? nseg_of(g.out_precision) : 0;
   AVD_REQUIRE(g.out_bf16 == nullptr || out_nseg > 0, "out_precision must be 1, 3 or 6");
 
-  // tile width: widest BN that divides N, still gives >= ~1 wave of CTAs on 148 SMs, and whose epilogue staging
-  // (fp32 tile unless it overwrites the residual tile, plus out_nseg bf16 tiles) fits the reused pipeline smem
+  // Tile width: the widest BN that divides N, still gives >= ~0.8 waves of CTAs on 148 SMs, and whose epilogue staging
+  // (fp32 tile unless it overwrites the residual tile, plus out_nseg bf16 tiles) fits the reused pipeline smem.
+  // A residual tile needs dedicated smem, which only the narrow tiles can spare.
   const int mt = (g.M + GEMM_BM - 1) / GEMM_BM;
   auto staging = [&](int bn) {
     return ((g.out_f32 != nullptr && g.resid == nullptr) ? GEMM_BM * bn * 4 : 0) + out_nseg * GEMM_BM * bn * 2;
   };
-  int bn = 32;
-  if (g.N % 128 == 0 && (int64_t)mt * (g.N / 128) >= 120 && staging(128) <= GemmSmem<128, 3>::PIPE_BYTES) bn = 128;
-  else if (g.N % 64 == 0 && staging(64) <= GemmSmem<64, 4>::PIPE_BYTES) bn = 64;
-  if ((g.ssq_out != nullptr || g.out_bf16 != nullptr) && bn < 64) bn = 64;
+  auto usable = [&](int bn) {
+    if (g.N % bn != 0) return false;
+    if (g.resid != nullptr && bn > 64) return false;
+    if ((g.ssq_out != nullptr || g.out_bf16 != nullptr) && bn < 64) return false;
+    return staging(bn) <= pipe_bytes_of(bn);
+  };
+  const int cands[5] = {256, 192, 128, 64, 32};
+  int bn = 0;
   const int force_bn = env_int("AVD_GEMM_BN", 0);
-  if (force_bn == 128 && g.N % 128 == 0 && staging(128) <= GemmSmem<128, 3>::PIPE_BYTES) bn = 128;
-  if (force_bn == 64 && g.N % 64 == 0) bn = 64;
-  AVD_REQUIRE(staging(bn) <= (bn == 128 ? GemmSmem<128, 3>::PIPE_BYTES
-                                        : bn == 64 ? GemmSmem<64, 4>::PIPE_BYTES : GemmSmem<32, 4>::PIPE_BYTES),
-              "epilogue staging does not fit: use fewer outputs per GEMM");
+  if (force_bn > 0 && usable(force_bn)) bn = force_bn;
+  for (int i = 0; i < 5 && bn == 0; ++i)
+    if (usable(cands[i]) && (int64_t)mt * (g.N / cands[i]) >= 120) bn = cands[i];
+  for (int i = 3; i < 5 && bn == 0; ++i)            // small problems: narrow tiles, more CTAs
+    if (usable(cands[i])) bn = cands[i];
+  for (int i = 0; i < 5 && bn == 0; ++i)
+    if (usable(cands[i])) bn = cands[i];
+  AVD_REQUIRE(bn > 0, "no tile shape fits this combination of outputs: use fewer outputs per GEMM");
 
   GemmParams p{};
   p.M = g.M; p.N = g.N; p.K = g.K;
@@ -415,43 +501,26 @@ int launch_gemm(const avd_gemm_args& g, cudaStream_t s) {
   p.rms_eps = g.rms_eps;
   p.has_resid = g.resid != nullptr;
   p.act = g.act;
-  p.has_f32 = g.out_f32 != nullptr;
+  p.out_f32 = g.out_f32;
+  p.out_bf16 = static_cast<__nv_bfloat16*>(g.out_bf16);
   p.out_nseg = out_nseg;
   p.ssq_out = g.ssq_out;
-  p.dbg = env_int("AVD_GEMM_DBG", 0);
-
-  // cluster shape: A tiles multicast across cx N-tiles, W tiles across cy M-tiles (cx * cy <= 8)
-  const int nt = g.N / bn;
-  int cx = env_int("AVD_GEMM_CX", 1), cy = env_int("AVD_GEMM_CY", 1);
-  while (cx > 1 && (nt % cx != 0 || GEMM_BM / cx % 8 != 0)) cx >>= 1;
-  while (cy > 1 && (cy > mt || bn / cy % 8 != 0)) cy >>= 1;
-  while (cx * cy > 8) { if (cx >= cy) cx >>= 1; else cy >>= 1; }
-  p.cx = cx < 1 ? 1 : cx;
-  p.cy = cy < 1 ? 1 : cy;
-  const int64_t n_ctas = (int64_t)nt * ((mt + p.cy - 1) / p.cy * p.cy);
+  const int64_t n_ctas = (int64_t)(g.N / bn) * mt;
   p.trace = (g_dbg_trace != nullptr && n_ctas * 32 <= g_dbg_trace_slots) ? g_dbg_trace : nullptr;
 
-  CUtensorMap tmA, tmB, tmR, tmF, tmO;
-  AVD_TRY(get_tensor_map_3d(g.A, 2, g.K, g.M, nseg, (uint64_t)g.K * 2, (uint64_t)g.M * g.K * 2, GEMM_BK,
-                            GEMM_BM / p.cx, &tmA));
-  AVD_TRY(get_tensor_map_3d(g.W, 2, g.K, g.N, nseg, (uint64_t)g.K * 2, (uint64_t)g.N * g.K * 2, GEMM_BK, bn / p.cy,
-                            &tmB));
-  tmR = tmA; tmF = tmA; tmO = tmA;   // placeholders when unused (never dereferenced)
+  CUtensorMap tmA, tmB, tmR;
+  AVD_TRY(get_tensor_map_3d(g.A, 2, g.K, g.M, nseg, (uint64_t)g.K * 2, (uint64_t)g.M * g.K * 2, GEMM_BK, GEMM_BM, &tmA));
+  AVD_TRY(get_tensor_map_3d(g.W, 2, g.K, g.N, nseg, (uint64_t)g.K * 2, (uint64_t)g.N * g.K * 2, GEMM_BK, bn, &tmB));
+  tmR = tmA;   // placeholder when unused (never dereferenced)
   if (g.resid != nullptr)
     AVD_TRY(get_tensor_map_3d(g.resid, 4, g.N, g.M, 1, (uint64_t)g.N * 4, (uint64_t)g.M * g.N * 4, 32, 32, &tmR));
-  if (g.out_f32 != nullptr)
-    AVD_TRY(get_tensor_map_3d(g.out_f32, 4, g.N, g.M, 1, (uint64_t)g.N * 4, (uint64_t)g.M * g.N * 4, 32, 32, &tmF));
-  if (g.out_bf16 != nullptr)
-    AVD_TRY(get_tensor_map_3d(g.out_bf16, 2, g.N, g.M, out_nseg, (uint64_t)g.N * 2, (uint64_t)g.M * g.N * 2, 64, 32,
-                              &tmO));
-
-  const int deep = env_int("AVD_GEMM_DEEP", 0);
-  if (bn == 128 && deep) return launch_gemm_bn<128, 5>(tmA, tmB, tmR, tmF, tmO, p, s);
-  if (bn == 64 && deep == 1) return launch_gemm_bn<64, 6>(tmA, tmB, tmR, tmF, tmO, p, s);
-  if (bn == 64 && deep == 2) return launch_gemm_bn<64, 7>(tmA, tmB, tmR, tmF, tmO, p, s);
-  if (bn == 128) return launch_gemm_bn<128, 3>(tmA, tmB, tmR, tmF, tmO, p, s);
-  if (bn == 64) return launch_gemm_bn<64, 4>(tmA, tmB, tmR, tmF, tmO, p, s);
-  return launch_gemm_bn<32, 4>(tmA, tmB, tmR, tmF, tmO, p, s);
+  switch (bn) {
+    case 256: return launch_gemm_bn<256, 2>(tmA, tmB, tmR, p, s);
+    case 192: return launch_gemm_bn<192, 2>(tmA, tmB, tmR, p, s);
+    case 128: return launch_gemm_bn<128, 3>(tmA, tmB, tmR, p, s);
+    case 64: return launch_gemm_bn<64, 3>(tmA, tmB, tmR, p, s);
+    default: return launch_gemm_bn<32, 3>(tmA, tmB, tmR, p, s);
+  }
 }
 
 }  // namespace avd

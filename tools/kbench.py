@@ -81,7 +81,7 @@ def main() -> None:
         packing.gemm(A512, Wo, M, d, d, P, bias=bo, resid=x, out_f32=xo, out_bf16=xa, out_precision=P, ssq_out=ssq_o)
 
     def g_fc1():
-        packing.gemm(A512, W1, M, dm, d, P, bias=b1, ssq_in=ssq, rms_dim=d, rms_eps=1e-6, act=1, out_bf16=hm,
+        packing.gemm(A512, W1, M, dm, d, P, bias=b1, ssq_in=ssq, rms_dim=d, rms_eps=1e-6, act=2, out_bf16=hm,
                      out_precision=P)
 
     def g_fc2():
@@ -141,12 +141,14 @@ def main() -> None:
             g0 = t[:, 0, 0].min()
             gt = (t[:, :, 0] - g0).float()      # ns since the first CTA started
             ck = (t[:, :, 1] - t[:, 0:1, 1]).float()   # cycles since CTA start
-            names = ["start", "setup done", "first tile landed", "last mma issued", "epi: rinv ready",
+            names = ["start", "setup done", "-", "pipe0: last mma issued", "epi: rinv+resid ready",
                      "epi: acc ready", "epi: stores read", "exit", "ch0: tmem ld done", "ch0: math done",
                      "ch0: sts done", "ch0: fence+syncwarp", "ch0: tma store issued", "last chunk issued"]
             print(f"--- trace {name}: {t.shape[0]} CTAs; kernel span {gt[:, 7].max():.0f} ns "
                   f"(CTA start spread {gt[:, 0].max():.0f} ns)")
             for i, nm in enumerate(names):
+                if nm == "-":
+                    continue
                 print(f"   {nm:20s} cycles since CTA start: median {ck[:, i].median():8.0f}  max {ck[:, i].max():8.0f}"
                       f"   | ns since kernel start: median {gt[:, i].median():8.0f} max {gt[:, i].max():8.0f}")
 
