@@ -1,17 +1,23 @@
 // avd_attn.cu -- K5: joint video+audio self-attention (nn.MultiheadAttention core, mmdt.py:58-61).
 //
-// attn_tc_kernel (bf16 mode): flash-style, one CTA = one (sequence, head, 128-query tile), 128 threads,
-// thread t owns query row t (TMEM lane t).
-//   per 128-key block j:   S = Q K_j^T        tcgen05.mma  M=128, N=round16(keys), K=64   -> TMEM cols [0,128)
-//                          online softmax     tcgen05.ld rows of S, fp32 max / exp2 / sum in registers,
-//                                             P (bf16) written to 128B-swizzled smem
-//                          O_j = P V_j        tcgen05.mma  M=128, N=64, K=round16(keys)   -> TMEM cols [128,192)
-//                                             (V consumed MN-major straight from the [keys, 64] TMA tile)
-//                          O = O*alpha + O_j  in registers
-// K/V tiles are double-buffered: the TMA for block j+1 is issued as soon as block j's S-MMA is queued.
-// The key count of the last block is rounded to 16 only (instruction-descriptor N / k-steps are runtime
-// values), so N = 133 costs 128 + 16 key columns, not 256.  No mask: the reference's sampler passes none,
-// and null-branch prompt rows stay in the sequence as keys/values.
+// attn_tc_kernel (bf16 mode): flash-style.  One CTA = one (sequence, head, PAIR of 128-query tiles), 512 threads:
+//   warps 0..7   softmax / output of query tile 0: warp w works on TMEM lanes (= query rows) 32 (w%4) .. +31, and the
+//                two warps that share a lane quadrant split the key columns (and the 64 output columns) in halves
+//   warps 8..15  the same for query tile 1
+//   lane 0 of the first warp of each tile is the tile's "leader": between the softmax phases (when its warp would
+//   only wait) it issues the tile's tcgen05.mma; the leader of tile 0 also issues every TMA load.  (A 17th issuer
+//   warp would cap the kernel at 96 registers per thread: 5 warps on one SM sub-partition.)
+// so the sequence's K/V tiles are loaded once for both query tiles and the two tiles' softmax phases run in
+// parallel.  Per key block j (up to 192 keys; N = 133 is ONE block of 144 key columns):
+//     S_t = Q_t K_j^T     tcgen05.mma  M=128, N=round16(keys), K=64     -> TMEM cols [256 t, 256 t + 192)
+//     online softmax      tcgen05.ld rows of S, fp32 max / exp2 / sum in registers, P (bf16) -> 128B-swizzled smem
+//     O_t,j = P_t V_j     tcgen05.mma  M=128, N=64, K=round16(keys)     -> TMEM cols [256 t + 192, 256 t + 256)
+//                         (V consumed MN-major straight from the [keys, 64] TMA tile)
+//     O_t = O_t * alpha + O_t,j   in registers
+// K_{j+1} is fetched as soon as the S MMAs of block j have retired, V_{j+1} once the PV MMAs have.
+// No mask: the reference's sampler passes none, and null-branch prompt rows stay in the sequence as keys/values
+// (SURVEY F8).  Key columns past the sequence end are given probability 0; the rows TMA fetched for them belong to
+// the next sequence (or are zero fill) and never reach the result.
 //
 // attn_f32_kernel (fp32-parity mode): CUDA-core fp32, one warp per query row, scores staged in smem.
 #include "avd_internal.h"
@@ -22,11 +28,15 @@
 namespace avd {
 
 constexpr int ATT_BQ = 128;
-constexpr int ATT_BKV = 128;
+constexpr int ATT_BKV = 192;                         // key block: S_t needs ATT_BKV TMEM columns per query tile
 constexpr int ATT_HD = 64;
-constexpr int ATT_TILE_BYTES = ATT_BQ * ATT_HD * 2;  // 16 KB: [128 rows][64 bf16], 128B swizzle
-constexpr int ATT_SMEM = ATT_TILE_BYTES * (1 + 2 + 2 + 2) + 128;  // Q, K[2], V[2], P (2 atoms), barriers (2 CTAs/SM fit)
-constexpr uint32_t ATT_TMEM_COLS = 256;  // S: 128 cols, O: 64 cols
+constexpr int ATT_THREADS = 512;
+constexpr int ATT_Q_BYTES = ATT_BQ * ATT_HD * 2;     // 16 KB: [128 rows][64 bf16], 128B swizzle
+constexpr int ATT_KV_BYTES = ATT_BKV * ATT_HD * 2;   // 24 KB
+constexpr int ATT_P_BYTES = 3 * ATT_Q_BYTES;         // three 64-key swizzle atoms of [128 rows][128 B]
+constexpr int ATT_XCHG_BYTES = (8 + 4) * 128 * 4;    // row-max exchange [2 bufs][2 tiles][2 halves][128], row-sum [2][2][128]
+constexpr int ATT_SMEM = 2 * ATT_Q_BYTES + 2 * ATT_KV_BYTES + 2 * ATT_P_BYTES + ATT_XCHG_BYTES + 256;
+constexpr uint32_t ATT_TMEM_COLS = 512;
 
 struct AttnParams {
   int N;            // tokens per sequence
@@ -36,232 +46,356 @@ struct AttnParams {
   __nv_bfloat16* out;
   int out_nseg;
   float scale_log2e;  // (1/sqrt(hd)) * log2(e)
-  uint32_t v_lbo, v_sbo;  // MN-major V descriptor strides (bytes)
-  int dbg_stop;           // debug: leave the main loop early at a given stage (0 = run normally)
+  unsigned long long* trace;   // debug phase stamps (avd_debug_trace)
 };
 
-__global__ void __launch_bounds__(128) attn_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnParams p) {
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+__device__ __forceinline__ void att_mark(unsigned long long* trace, int slot) {
+  if (trace != nullptr) {
+    const int cta = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+    unsigned long long g, c;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g));
+    asm volatile("mov.u64 %0, %%clock64;" : "=l"(c));
+    trace[(cta * 16 + slot) * 2] = g;
+    trace[(cta * 16 + slot) * 2 + 1] = c;
+  }
+}
+
+// barrier slots
+enum { AB_Q = 0, AB_K = 1, AB_V = 2, AB_S = 3 /*+t*/, AB_P = 5 /*+t*/, AB_O = 7 /*+t*/, AB_R = 9 /*+t*/, AB_COUNT = 11 };
+
+template <bool ONE_BLOCK>   // ONE_BLOCK: N <= 192 keys, the whole score row stays in registers (single softmax pass)
+__global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ,
+                                                                 const __grid_constant__ CUtensorMap tmKV,
+                                                                 const AttnParams p) {
   extern __shared__ __align__(1024) uint8_t att_smem[];
   uint8_t* smem = att_smem;
   if ((smem_u32(smem) & 1023u) != 0) __trap();   // 128B-swizzle tiles need 1024-B aligned bases
-  uint8_t* sQ = smem;
-  uint8_t* sK = sQ + ATT_TILE_BYTES;       // 2 stages
-  uint8_t* sV = sK + 2 * ATT_TILE_BYTES;   // 2 stages
-  uint8_t* sP = sV + 2 * ATT_TILE_BYTES;   // 2 swizzle atoms of [128][64]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 2 * ATT_TILE_BYTES);
-  uint64_t* q_full = bars;
-  uint64_t* k_full = bars + 1;   // [2]
-  uint64_t* v_full = bars + 3;   // [2]
-  uint64_t* s_done = bars + 5;
-  uint64_t* o_done = bars + 6;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 7);
+  uint8_t* sQ = smem;                            // 2 query tiles (later: output staging)
+  uint8_t* sK = sQ + 2 * ATT_Q_BYTES;
+  uint8_t* sV = sK + ATT_KV_BYTES;
+  uint8_t* sP = sV + ATT_KV_BYTES;               // 2 tiles x 3 atoms
+  float* xmax = reinterpret_cast<float*>(sP + 2 * ATT_P_BYTES);      // [2][2 tiles][2 halves][128]
+  float* xsum = xmax + 8 * 128;                                      // [2 tiles][2 halves][128]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 2 * ATT_P_BYTES + ATT_XCHG_BYTES);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + AB_COUNT);
 
   const int tid = threadIdx.x;
-  const int warp = tid >> 5;
-  const int q0 = blockIdx.x * ATT_BQ;
+  const int warp = tid >> 5, lane = tid & 31;
+  unsigned long long* const trace = p.trace;
+  if (tid == 0) att_mark(trace, 0);
   const int head = blockIdx.y;
   const int seq = blockIdx.z;
   const int row_base = seq * p.N;           // first row of this sequence in the [M, 3d] matrix
+  const int q_first = blockIdx.x * 2 * ATT_BQ;
+  const int n_tiles = (p.N - q_first > ATT_BQ) ? 2 : 1;          // active query tiles of this CTA
   const int colQ = head * ATT_HD, colK = p.d + head * ATT_HD, colV = 2 * p.d + head * ATT_HD;
   const int nkv = (p.N + ATT_BKV - 1) / ATT_BKV;
 
   if (tid == 0) {
-    tma_prefetch_desc(&tmQKV);
-    for (int i = 0; i < 7; ++i) mbar_init(&bars[i], 1);
+    for (int i = 0; i < AB_COUNT; ++i) {
+      uint32_t count = 1;
+      if ((i >= AB_P && i < AB_O) || i >= AB_R) {       // arrivals: the warp pairs of the tile that own valid query rows
+        const int rows = min(ATT_BQ, p.N - q_first - ((i - AB_P) & 1) * ATT_BQ);
+        count = rows > 0 ? 64 * ((rows + 31) >> 5) : 1;
+      }
+      mbar_init(&bars[i], count);
+    }
     fence_barrier_init();
   }
-  __syncwarp();
-  if (warp == 0) tmem_alloc<ATT_TMEM_COLS>(tmem_slot);
+  if (warp == 0) {
+    if (lane == 0) { tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmKV); }
+    __syncwarp();
+    tmem_alloc<ATT_TMEM_COLS>(tmem_slot);
+  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const uint32_t tmem_S = tmem_base;
-  const uint32_t tmem_O = tmem_base + 128;
-  const uint32_t lane_sel = (uint32_t)(warp * 32) << 16;
+  pdl_launch_dependents();
+  if (tid == 0) att_mark(trace, 1);
 
-  if (tid == 0) {
-    mbar_expect_tx(q_full, ATT_TILE_BYTES);
-    tma_load_3d(sQ, &tmQKV, q_full, colQ, row_base + q0, 0);
-    mbar_expect_tx(&k_full[0], ATT_TILE_BYTES);
-    tma_load_3d(sK, &tmQKV, &k_full[0], colK, row_base, 0);
-    mbar_expect_tx(&v_full[0], ATT_TILE_BYTES);
-    tma_load_3d(sV, &tmQKV, &v_full[0], colV, row_base, 0);
-  }
-
-  float o_acc[ATT_HD];
+  if ((warp >> 3) < n_tiles && q_first + (warp >> 3) * ATT_BQ + (warp & 3) * 32 < p.N) {
+    // ------------------------------------------------------------------ softmax + output of query tile t
+    const int t = warp >> 3, sp = (warp >> 2) & 1, quad = warp & 3;
+    const int r = quad * 32 + lane;                 // row inside the tile == TMEM lane
+    const uint32_t tmem_S = tmem_base + t * 256 + ((uint32_t)(quad * 32) << 16);
+    const uint32_t tmem_O = tmem_S + ATT_BKV + sp * 32;       // this thread's 32 of the 64 output columns
+    const uint32_t pair_bar = 1 + t * 4 + quad;     // named barrier of the two warps that share these rows
+    uint8_t* sPt = sP + t * ATT_P_BYTES;
+    float o_acc[32];
+    if constexpr (!ONE_BLOCK) {
 #pragma unroll
-  for (int c = 0; c < ATT_HD; ++c) o_acc[c] = 0.0f;
-  float m_run = -INFINITY, l_run = 0.0f;
+      for (int c = 0; c < 32; ++c) o_acc[c] = 0.0f;
+    }
+    float m_run = -INFINITY, l_run = 0.0f;
+    const float sc = p.scale_log2e;
+    const bool mark = (tid == 0);
+    const bool leader = (warp & 7) == 0 && lane == 0;      // issues this tile's MMAs
+    const uint32_t hi = smem_desc_hi_sw128(1024);
+    const uint32_t q_lo = smem_desc_lo_sw128(smem_u32(sQ + t * ATT_Q_BYTES), 16);
+    const uint32_t k_lo = smem_desc_lo_sw128(smem_u32(sK), 16);
+    const uint32_t v_lo = smem_desc_lo_sw128(smem_u32(sV), 16);
+    const uint32_t p_lo = smem_desc_lo_sw128(smem_u32(sPt), 16);
+    if (tid == 0) {                                         // the leader of tile 0 owns the TMA loads
+      pdl_wait();                                           // qkv comes from the previous kernel
+      mbar_expect_tx(&bars[AB_Q], n_tiles * ATT_Q_BYTES);
+      for (int tt = 0; tt < n_tiles; ++tt)
+        tma_load_3d(sQ + tt * ATT_Q_BYTES, &tmQ, &bars[AB_Q], colQ, row_base + q_first + tt * ATT_BQ, 0);
+      mbar_expect_tx(&bars[AB_K], ATT_KV_BYTES);
+      tma_load_3d(sK, &tmKV, &bars[AB_K], colK, row_base, 0);
+      mbar_expect_tx(&bars[AB_V], ATT_KV_BYTES);
+      tma_load_3d(sV, &tmKV, &bars[AB_V], colV, row_base, 0);
+    }
 
-  for (int j = 0; j < nkv && p.dbg_stop != 1; ++j) {
-    const int st = j & 1;
-    const uint32_t ph = (j >> 1) & 1;
-    const int kv_valid = min(ATT_BKV, p.N - j * ATT_BKV);
-    const int kv_n = (kv_valid + 15) & ~15;
-
-    if (tid == 0) {
-      if (j == 0) mbar_wait(q_full, 0);
-      mbar_wait(&k_full[st], ph);
+    for (int j = 0; j < nkv; ++j) {
+      const uint32_t ph = j & 1;
+      const int kv_valid = min(ATT_BKV, p.N - j * ATT_BKV);
+      const int nch = (kv_valid + 31) >> 5;         // 32-column chunks holding valid keys (<= 6)
+      const int ch0 = sp * 3;                       // this thread's chunks: [ch0, ch1)
+      const int ch1 = min(nch, ch0 + 3);
+      float* xm = xmax + ((ph * 2 + t) * 2) * 128;
+      const int kv_n = (kv_valid + 15) & ~15;
+      if (leader) {                                 // S_t = Q_t K_j^T (S columns were drained before p_ready of j-1)
+        if (j == 0) mbar_wait(&bars[AB_Q], 0);
+        mbar_wait(&bars[AB_K], ph);
+        tc_fence_after();
+        if (mark && j == 0) att_mark(trace, 2);
+        const uint32_t idesc_s = make_idesc_bf16(ATT_BQ, kv_n, 0, 0);
+#pragma unroll
+        for (int k = 0; k < ATT_HD / 16; ++k)
+          umma_bf16_lh(tmem_base + t * 256, q_lo + 2 * k, k_lo + 2 * k, hi, idesc_s, k > 0 ? 1u : 0u);
+        umma_commit(&bars[AB_S + t]);
+        if (mark && j == 0) att_mark(trace, 3);
+      }
+      __syncwarp();
+      mbar_wait(&bars[AB_S + t], ph);
       tc_fence_after();
-      const uint32_t idesc_s = make_idesc_bf16(ATT_BQ, kv_n, 0, 0);
-      const uint32_t q_addr = smem_u32(sQ), k_addr = smem_u32(sK + st * ATT_TILE_BYTES);
-#pragma unroll
-      for (int k = 0; k < ATT_HD / 16; ++k) {
-        umma_bf16(tmem_S, make_smem_desc_sw128(q_addr + k * 32, 16, 1024),
-                  make_smem_desc_sw128(k_addr + k * 32, 16, 1024), idesc_s, k > 0 ? 1u : 0u);
+      if (tid == 0 && j + 1 < nkv) {                // K_{j+1} may land as soon as every tile's S MMAs have read K_j
+        for (int tt = 1; tt < n_tiles; ++tt) mbar_wait(&bars[AB_S + tt], ph);
+        mbar_expect_tx(&bars[AB_K], ATT_KV_BYTES);
+        tma_load_3d(sK, &tmKV, &bars[AB_K], colK, row_base + (j + 1) * ATT_BKV, 0);
       }
-      umma_commit(s_done);
-      if (j + 1 < nkv) {  // stage st^1 was last read by block j-1's MMAs, which completed before o_done(j-1)
-        const int nst = st ^ 1;
-        mbar_expect_tx(&k_full[nst], ATT_TILE_BYTES);
-        tma_load_3d(sK + nst * ATT_TILE_BYTES, &tmQKV, &k_full[nst], colK, row_base + (j + 1) * ATT_BKV, 0);
-        mbar_expect_tx(&v_full[nst], ATT_TILE_BYTES);
-        tma_load_3d(sV + nst * ATT_TILE_BYTES, &tmQKV, &v_full[nst], colV, row_base + (j + 1) * ATT_BKV, 0);
-      }
-    }
-    __syncwarp();
-    mbar_wait(s_done, j & 1);
-    tc_fence_after();
-    if (p.dbg_stop == 2) break;
-
-    // ---- pass 1: row max over the valid keys
-    const int nch = (kv_n + 31) >> 5;
-    float m_blk = -INFINITY;
-    for (int ch = 0; ch < nch; ++ch) {
-      uint32_t r[32];
-      tmem_ld_32x32(tmem_S + lane_sel + ch * 32, r);
-      tmem_ld_wait();
+      if (mark && j == 0) att_mark(trace, 5);
+      float l_blk = 0.0f, alpha;
+      if constexpr (ONE_BLOCK) {
+        // ---- single pass: up to 3 chunks (96 scores) of this row live in registers
+        uint32_t x[3][32];
 #pragma unroll
-      for (int c = 0; c < 32; ++c) {
-        if (ch * 32 + c < kv_valid) m_blk = fmaxf(m_blk, __uint_as_float(r[c]));
-      }
-    }
-    const float m_new = fmaxf(m_run, m_blk);
-    const float alpha = exp2f((m_run - m_new) * p.scale_log2e);   // m_run = -inf on the first block -> 0
-    const float m_sc = m_new * p.scale_log2e;
-
-    // ---- pass 2: p = exp2(s*c - m*c), row sum, P -> smem (K-major, 128B swizzle, two 64-key atoms)
-    float l_blk = 0.0f;
-    for (int ch = 0; ch < nch; ++ch) {
-      uint32_t r[32];
-      tmem_ld_32x32(tmem_S + lane_sel + ch * 32, r);
-      tmem_ld_wait();
-      uint32_t w[16];
+        for (int i = 0; i < 3; ++i)
+          if (i == 0 || ch0 + i < nch) tmem_ld_32x32(tmem_S + (ch0 + i) * 32, x[i]);   // columns past the keys are masked
+        tmem_ld_wait();
+        float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
-      for (int c = 0; c < 32; c += 2) {
-        float p0 = (ch * 32 + c < kv_valid) ? exp2f(fmaf(__uint_as_float(r[c]), p.scale_log2e, -m_sc)) : 0.0f;
-        float p1 = (ch * 32 + c + 1 < kv_valid) ? exp2f(fmaf(__uint_as_float(r[c + 1]), p.scale_log2e, -m_sc)) : 0.0f;
-        l_blk += p0 + p1;
-        w[c >> 1] = pack_bf16x2(p0, p1);
-      }
-      uint8_t* atom = sP + (ch >> 1) * ATT_TILE_BYTES + tid * 128;
-      const int q_base = (ch & 1) * 4;  // 16-byte chunk index of this 32-column group inside the 128-byte row
+        for (int i = 0; i < 3; ++i) {
+          const int lim = kv_valid - (ch0 + i) * 32;
+          if (lim > 0) {
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const int q = (q_base + i) ^ (tid & 7);
-        *reinterpret_cast<uint4*>(atom + q * 16) = make_uint4(w[4 * i], w[4 * i + 1], w[4 * i + 2], w[4 * i + 3]);
-      }
-    }
-    l_run = l_run * alpha + l_blk;
-    m_run = m_new;
-
-    fence_async_smem();   // P (generic-proxy stores) -> visible to the tensor core's async-proxy reads
-    tc_fence_before();
-    __syncthreads();
-    if (p.dbg_stop == 3) break;
-
-    if (tid == 0) {
-      tc_fence_after();
-      mbar_wait(&v_full[st], ph);
-      tc_fence_after();
-      const uint32_t idesc_o = make_idesc_bf16(ATT_BQ, ATT_HD, 0, 1);   // B = V is MN-major
-      const uint32_t p_addr = smem_u32(sP), v_addr = smem_u32(sV + st * ATT_TILE_BYTES);
-      const int ksteps = kv_n >> 4;
-      for (int ks = 0; ks < ksteps; ++ks) {
-        const uint32_t pa = p_addr + (ks >> 2) * ATT_TILE_BYTES + (ks & 3) * 32;
-        const uint32_t va = v_addr + ks * 16 * 128;   // 16 keys = 16 rows of 128 B
-        umma_bf16(tmem_O, make_smem_desc_sw128(pa, 16, 1024), make_smem_desc_sw128(va, p.v_lbo, p.v_sbo), idesc_o,
-                  ks > 0 ? 1u : 0u);
-      }
-      umma_commit(o_done);
-    }
-    __syncwarp();
-    mbar_wait(o_done, j & 1);
-    tc_fence_after();
-
-    // ---- O = O * alpha + O_j
-#pragma unroll
-    for (int ch = 0; ch < ATT_HD / 32; ++ch) {
-      uint32_t r[32];
-      tmem_ld_32x32(tmem_O + lane_sel + ch * 32, r);
-      tmem_ld_wait();
-#pragma unroll
-      for (int c = 0; c < 32; ++c) o_acc[ch * 32 + c] = fmaf(o_acc[ch * 32 + c], alpha, __uint_as_float(r[c]));
-    }
-    tc_fence_before();
-  }
-
-  if (p.dbg_stop != 0 && tid == 0) {   // debug exits: drain the TMA loads that are still in flight
-    mbar_wait(q_full, 0);
-    mbar_wait(&k_full[0], 0);
-    mbar_wait(&v_full[0], 0);
-    if (nkv > 1 && p.dbg_stop >= 2) { mbar_wait(&k_full[1], 0); mbar_wait(&v_full[1], 0); }
-  }
-
-  // ---- normalise and store this thread's query row
-  const int q = q0 + tid;
-  if (q < p.N) {
-    const float inv_l = 1.0f / l_run;
-    const int64_t seg_stride = p.M * (int64_t)p.d;
-    __nv_bfloat16* op = p.out + ((int64_t)row_base + q) * p.d + head * ATT_HD;
-    float rem[ATT_HD];
-#pragma unroll
-    for (int c = 0; c < ATT_HD; ++c) rem[c] = o_acc[c] * inv_l;
-    for (int sg = 0; sg < p.out_nseg; ++sg) {
-      uint4* o4 = reinterpret_cast<uint4*>(op + sg * seg_stride);
-#pragma unroll
-      for (int v4 = 0; v4 < ATT_HD / 8; ++v4) {
-        uint32_t w[4];
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          const int c = v4 * 8 + k * 2;
-          __nv_bfloat16 h0 = __float2bfloat16_rn(rem[c]);
-          __nv_bfloat16 h1 = __float2bfloat16_rn(rem[c + 1]);
-          rem[c] -= __bfloat162float(h0);
-          rem[c + 1] -= __bfloat162float(h1);
-          w[k] = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
+            for (int c = 0; c < 32; ++c) mx[c & 3] = fmaxf(mx[c & 3], c < lim ? __uint_as_float(x[i][c]) : -INFINITY);
+          }
         }
-        o4[v4] = make_uint4(w[0], w[1], w[2], w[3]);
+        const float m_part = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
+        xm[sp * 128 + r] = m_part;
+        named_bar_sync(pair_bar, 64);
+        const float m_new = fmaxf(m_part, xm[(sp ^ 1) * 128 + r]);
+        if (mark && j == 0) att_mark(trace, 6);
+        alpha = 0.0f;
+        const float m_sc = m_new * sc;
+        m_run = m_new;
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+          const int ch = ch0 + i;
+          const int lim = kv_valid - ch * 32;
+          if (lim > -16) {                           // chunks wholly past round16(keys) are never read by the PV MMA
+            float l0 = 0.0f, l1 = 0.0f;
+            uint32_t w[16];
+#pragma unroll
+            for (int c = 0; c < 32; c += 2) {
+              float p0 = ex2_approx(fmaf(__uint_as_float(x[i][c]), sc, -m_sc));
+              float p1 = ex2_approx(fmaf(__uint_as_float(x[i][c + 1]), sc, -m_sc));
+              p0 = c < lim ? p0 : 0.0f;
+              p1 = c + 1 < lim ? p1 : 0.0f;
+              l0 += p0;
+              l1 += p1;
+              w[c >> 1] = pack_bf16x2(p0, p1);
+            }
+            l_blk += l0 + l1;
+            uint8_t* atom = sPt + (ch >> 1) * ATT_Q_BYTES + r * 128;
+            const int q_base = (ch & 1) * 4;  // 16-byte chunk index of this 32-column group inside the 128-byte row
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+              *reinterpret_cast<uint4*>(atom + (((q_base + q) ^ (r & 7)) << 4)) =
+                  make_uint4(w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
+          }
+        }
+      } else {
+        // ---- pass 1: row max over this thread's valid keys
+        float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+        for (int ch = ch0; ch < ch1; ++ch) {
+          uint32_t x[32];
+          tmem_ld_32x32(tmem_S + ch * 32, x);
+          tmem_ld_wait();
+          const int lim = kv_valid - ch * 32;
+#pragma unroll
+          for (int c = 0; c < 32; ++c) mx[c & 3] = fmaxf(mx[c & 3], c < lim ? __uint_as_float(x[c]) : -INFINITY);
+        }
+        const float m_part = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
+        xm[sp * 128 + r] = m_part;
+        named_bar_sync(pair_bar, 64);
+        const float m_new = fmaxf(m_run, fmaxf(m_part, xm[(sp ^ 1) * 128 + r]));
+        alpha = ex2_approx((m_run - m_new) * sc);   // m_run = -inf on the first block -> 0
+        const float m_sc = m_new * sc;
+        m_run = m_new;
+        // ---- pass 2: p = exp2(s*c - m*c), row sum, P -> smem (K-major, 128B swizzle, 64-key atoms)
+        for (int ch = ch0; ch < ch1; ++ch) {
+          uint32_t x[32];
+          tmem_ld_32x32(tmem_S + ch * 32, x);
+          tmem_ld_wait();
+          const int lim = kv_valid - ch * 32;
+          float l0 = 0.0f, l1 = 0.0f;
+          uint32_t w[16];
+#pragma unroll
+          for (int c = 0; c < 32; c += 2) {
+            float p0 = ex2_approx(fmaf(__uint_as_float(x[c]), sc, -m_sc));
+            float p1 = ex2_approx(fmaf(__uint_as_float(x[c + 1]), sc, -m_sc));
+            p0 = c < lim ? p0 : 0.0f;
+            p1 = c + 1 < lim ? p1 : 0.0f;
+            l0 += p0;
+            l1 += p1;
+            w[c >> 1] = pack_bf16x2(p0, p1);
+          }
+          l_blk += l0 + l1;
+          uint8_t* atom = sPt + (ch >> 1) * ATT_Q_BYTES + r * 128;
+          const int q_base = (ch & 1) * 4;
+#pragma unroll
+          for (int q = 0; q < 4; ++q)
+            *reinterpret_cast<uint4*>(atom + (((q_base + q) ^ (r & 7)) << 4)) =
+                make_uint4(w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
+        }
+      }
+      l_run = l_run * alpha + l_blk;                // partial row sum over this thread's key columns
+      fence_async_smem();   // P (generic-proxy stores) -> visible to the tensor core's async-proxy reads
+      tc_fence_before();    // the S columns have been read: the next S MMA may overwrite them
+      mbar_arrive(&bars[AB_P + t]);
+      if (mark && j == 0) att_mark(trace, 7);
+      if (leader) {                                 // O_t,j = P_t V_j
+        mbar_wait(&bars[AB_P + t], ph);
+        mbar_wait(&bars[AB_V], ph);
+        if (j > 0) mbar_wait(&bars[AB_R + t], ph ^ 1);     // O_t,j-1 has been read out of TMEM
+        tc_fence_after();
+        const uint32_t idesc_o = make_idesc_bf16(ATT_BQ, ATT_HD, 0, 1);   // B = V is MN-major
+        const int ksteps = kv_n >> 4;
+        for (int ks = 0; ks < ksteps; ++ks) {
+          const uint32_t pa = p_lo + (((ks >> 2) * ATT_Q_BYTES + (ks & 3) * 32) >> 4);
+          const uint32_t va = v_lo + ((ks * 16 * 128) >> 4);            // 16 keys = 16 rows of 128 B
+          umma_bf16_lh(tmem_base + t * 256 + ATT_BKV, pa, va, hi, idesc_o, ks > 0 ? 1u : 0u);
+        }
+        umma_commit(&bars[AB_O + t]);
+        if (mark && j == 0) att_mark(trace, 4);
+      }
+      __syncwarp();
+      mbar_wait(&bars[AB_O + t], ph);
+      tc_fence_after();
+      if (mark && j == 0) att_mark(trace, 8);
+      {   // ---- O = O * alpha + O_j on this thread's 32 output columns
+        uint32_t x[32];
+        tmem_ld_32x32(tmem_O, x);
+        tmem_ld_wait();
+#pragma unroll
+        for (int c = 0; c < 32; ++c) {
+          if constexpr (ONE_BLOCK) o_acc[c] = __uint_as_float(x[c]);
+          else o_acc[c] = fmaf(o_acc[c], alpha, __uint_as_float(x[c]));
+        }
+      }
+      if (j + 1 < nkv) {
+        tc_fence_before();
+        mbar_arrive(&bars[AB_R + t]);
+        if (tid == 0) {                             // V_{j+1} once every tile's PV MMAs have read V_j
+          for (int tt = 1; tt < n_tiles; ++tt) mbar_wait(&bars[AB_O + tt], ph);
+          mbar_expect_tx(&bars[AB_V], ATT_KV_BYTES);
+          tma_load_3d(sV, &tmKV, &bars[AB_V], colV, row_base + (j + 1) * ATT_BKV, 0);
+        }
       }
     }
+    if (mark) att_mark(trace, 9);
+
+    // ---- total row sum = the two halves' partial sums; normalise this thread's 32 output columns
+    float* xs = xsum + (t * 2) * 128;
+    xs[sp * 128 + r] = l_run;
+    named_bar_sync(pair_bar, 64);
+    const float inv_l = 1.0f / (l_run + xs[(sp ^ 1) * 128 + r]);
+    // ---- stage the 32 rows x 128 B of this warp pair in the retired Q tile; coalesced 128-byte row stores
+    const int64_t seg_stride = p.M * (int64_t)p.d;
+    uint8_t* stage = sQ + t * ATT_Q_BYTES + quad * 32 * 128;
+    const int q_tile0 = q_first + t * ATT_BQ + quad * 32;        // first query row of this warp pair
+    float rem[32];
+#pragma unroll
+    for (int c = 0; c < 32; ++c) rem[c] = o_acc[c] * inv_l;
+    for (int sg = 0; sg < p.out_nseg; ++sg) {
+#pragma unroll
+      for (int v4 = 0; v4 < 4; ++v4) {
+        uint32_t w[4];
+        if (p.out_nseg == 1) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) w[k] = pack_bf16x2(rem[v4 * 8 + k * 2], rem[v4 * 8 + k * 2 + 1]);
+        } else {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const int c = v4 * 8 + k * 2;
+            const __nv_bfloat16 h0 = __float2bfloat16_rn(rem[c]);
+            const __nv_bfloat16 h1 = __float2bfloat16_rn(rem[c + 1]);
+            rem[c] -= __bfloat162float(h0);
+            rem[c + 1] -= __bfloat162float(h1);
+            w[k] = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
+          }
+        }
+        *reinterpret_cast<uint4*>(stage + lane * 128 + (((sp * 4 + v4) ^ (lane & 7)) << 4)) =
+            make_uint4(w[0], w[1], w[2], w[3]);
+      }
+      named_bar_sync(pair_bar, 64);
+      const int rr = lane >> 3, cc = lane & 7;
+      __nv_bfloat16* gp = p.out + sg * seg_stride + ((int64_t)row_base + q_tile0) * p.d + head * ATT_HD + cc * 8;
+#pragma unroll
+      for (int it = 0; it < 4; ++it) {               // this warp stores rows [16 sp, 16 sp + 16) of the pair's 32
+        const int rw = sp * 16 + it * 4 + rr;
+        const uint4 x4 = *reinterpret_cast<const uint4*>(stage + rw * 128 + ((cc ^ (rw & 7)) << 4));
+        if (q_tile0 + rw < p.N) *reinterpret_cast<uint4*>(gp + (int64_t)rw * p.d) = x4;
+      }
+      if (sg + 1 < p.out_nseg) named_bar_sync(pair_bar, 64);
+    }
+    if (mark) att_mark(trace, 10);
   }
 
   tc_fence_before();
   __syncthreads();
+  if (tid == 0) att_mark(trace, 11);
   if (warp == 0) {
     tc_fence_after();
     tmem_dealloc<ATT_TMEM_COLS>(tmem_base);
   }
 }
 
-static uint32_t env_u32(const char* name, uint32_t dflt) {
-  const char* v = std::getenv(name);
-  return v ? (uint32_t)std::strtoul(v, nullptr, 0) : dflt;
-}
-
 int launch_attention_tc(const void* qkv_bf16, void* out, int out_nseg, int n_seq, int N, int n_heads, int hd,
                         cudaStream_t s) {
   AVD_REQUIRE(hd == ATT_HD, "tcgen05 attention kernel is built for head_dim 64");
   AVD_REQUIRE(n_seq > 0 && N > 0 && n_heads > 0, "empty attention");
+  AVD_REQUIRE(out_nseg >= 1 && out_nseg <= 3, "bad output precision");
   const int d = n_heads * hd;
   const int64_t M = (int64_t)n_seq * N;
-  CUtensorMap tm;
-  AVD_TRY(get_tensor_map_bf16_3d(qkv_bf16, (uint64_t)3 * d, (uint64_t)M, 1, (uint64_t)3 * d * 2,
-                                 (uint64_t)M * 3 * d * 2, ATT_HD, ATT_BQ, &tm));
+  CUtensorMap tmQ, tmKV;
+  AVD_TRY(get_tensor_map_3d(qkv_bf16, 2, (uint64_t)3 * d, (uint64_t)M, 1, (uint64_t)3 * d * 2, (uint64_t)M * 3 * d * 2,
+                            ATT_HD, ATT_BQ, &tmQ));
+  AVD_TRY(get_tensor_map_3d(qkv_bf16, 2, (uint64_t)3 * d, (uint64_t)M, 1, (uint64_t)3 * d * 2, (uint64_t)M * 3 * d * 2,
+                            ATT_HD, ATT_BKV, &tmKV));
   static bool attr_set = false;
   if (!attr_set) {
-    AVD_CUDA(cudaFuncSetAttribute(attn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM));
+    AVD_CUDA(cudaFuncSetAttribute(attn_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM));
+    AVD_CUDA(cudaFuncSetAttribute(attn_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM));
     attr_set = true;
   }
   AttnParams p{};
@@ -269,15 +403,30 @@ int launch_attention_tc(const void* qkv_bf16, void* out, int out_nseg, int n_seq
   p.out = static_cast<__nv_bfloat16*>(out);
   p.out_nseg = out_nseg;
   p.scale_log2e = (1.0f / sqrtf((float)hd)) * 1.4426950408889634f;
-  p.v_lbo = env_u32("AVD_DBG_V_LBO", 16);      // debug overrides for the MN-major descriptor
-  p.v_sbo = env_u32("AVD_DBG_V_SBO", 1024);
-  p.dbg_stop = (int)env_u32("AVD_DBG_ATT_STOP", 0);
-  dim3 grid((N + ATT_BQ - 1) / ATT_BQ, n_heads, n_seq);
+  {
+    const int64_t n_ctas = (int64_t)((N + 2 * ATT_BQ - 1) / (2 * ATT_BQ)) * n_heads * n_seq;
+    p.trace = (g_dbg_trace != nullptr && n_ctas * 32 <= g_dbg_trace_slots) ? g_dbg_trace : nullptr;
+  }
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3((N + 2 * ATT_BQ - 1) / (2 * ATT_BQ), n_heads, n_seq);
+  cfg.blockDim = dim3(ATT_THREADS);
+  cfg.dynamicSmemBytes = ATT_SMEM;
+  cfg.stream = s;
+  cudaLaunchAttribute attrs[1];
+  int na = 0;
+  if (pdl_enabled()) {
+    attrs[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attrs[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  cfg.attrs = attrs;
+  cfg.numAttrs = na;
   LaunchScope ls(KIND_ATTN_TC, s);
-  attn_tc_kernel<<<grid, 128, ATT_SMEM, s>>>(tm, p);
-  AVD_CUDA(cudaGetLastError());
+  if (N <= ATT_BKV) AVD_CUDA(cudaLaunchKernelEx(&cfg, attn_tc_kernel<true>, tmQ, tmKV, p));
+  else AVD_CUDA(cudaLaunchKernelEx(&cfg, attn_tc_kernel<false>, tmQ, tmKV, p));
   return 0;
 }
+
 
 // =====================================================================================================
 // fp32 CUDA-core attention (parity mode): one warp per query row.

@@ -127,6 +127,23 @@ def main() -> None:
     print(f"{'one block (5 kernels)':40s} {us:8.2f} us", flush=True)
 
     if args.trace:
+        buf = torch.zeros(32 * 512, device=dev, dtype=torch.int64)
+        g_att()
+        torch.cuda.synchronize()
+        _lib.check(lib.avd_debug_trace(buf.data_ptr(), buf.numel()))
+        g_att()
+        torch.cuda.synchronize()
+        _lib.check(lib.avd_debug_trace(None, 0))
+        t = buf.view(-1, 16, 2).cpu()
+        t = t[t[:, 0, 0] > 0]
+        gt = (t[:, :, 0] - t[:, 0, 0].min()).float()
+        ck = (t[:, :, 1] - t[:, 0:1, 1]).float()
+        an = ["start", "setup done", "iss: Q,K landed", "iss: S issued, K prefetch", "iss: PV0 issued", "sm: S ready",
+              "sm: pass1 done", "sm: P written", "sm: O ready", "sm: O accumulated", "sm: stored", "exit"]
+        print(f"--- trace attention: {t.shape[0]} CTAs; kernel span {gt[:, 11].max():.0f} ns")
+        for i, nm in enumerate(an):
+            print(f"   {nm:26s} cycles: median {ck[:, i].median():8.0f} max {ck[:, i].max():8.0f} | ns since kernel start: "
+                  f"median {gt[:, i].median():8.0f} max {gt[:, i].max():8.0f}")
         for name, fn in (("qkv", g_qkv), ("oproj", g_o), ("fc2", g_fc2), ("head", g_head)):
             buf = torch.zeros(32 * 512, device=dev, dtype=torch.int64)
             fn()
