@@ -207,17 +207,22 @@ static int sampler_layout(const avd_sampler* s, SamplerLayout* L) {
   L->qkv = take(M * 3 * d * (s->core.precision == AVD_PREC_BF16 ? 2 : 4));
   L->att = take((int64_t)L->S_core * M * d * 2);
   L->hmid = take((int64_t)L->S_core * M * dm * 2);
-  L->h = take((int64_t)L->S_head * Mt * d * 2);
-  L->act_a = take((int64_t)L->S_head * Mt * hid * 2);
-  L->act_b = take((int64_t)L->S_head * Mt * hid * 2);
-  L->y = take(Mt * hid * 4);
-  L->eps = take(Mt * (int64_t)L->Dt * 4);
+  // the head runs over ALL rows of the joint sequences (the target rows are picked by the CFG/DDIM kernel): with one
+  // 128-row tile per CTA the extra prompt rows cost no time, and the final RMSNorm folds into the input projection
+  L->h = take((int64_t)L->S_head * M * d * 2);
+  L->act_a = take((int64_t)L->S_head * M * hid * 2);
+  L->act_b = take((int64_t)L->S_head * M * hid * 2);
+  L->y = take(M * hid * 4);
+  L->eps = take(M * (int64_t)L->Dt * 4);
+  (void)Mt;
   L->total = off;
   return 0;
 }
 
+// last_out / last_prec: when given, the last block's residual stream leaves as bf16 segments of that precision in
+// last_out (the noise head's operand) instead of ws->xa.
 static int core_blocks(const avd_core_weights* w, const float* x_in, const void* xa_in, const float* ssq_in,
-                       const avd_core_workspace* ws, int n_seq, int N, cudaStream_t st) {
+                       const avd_core_workspace* ws, int n_seq, int N, void* last_out, int last_prec, cudaStream_t st) {
   AVD_REQUIRE(w != nullptr && ws != nullptr, "null argument");
   const int d = w->d_model, S = nseg_of(w->precision);
   AVD_REQUIRE(S > 0, "bad precision");
@@ -260,13 +265,16 @@ static int core_blocks(const avd_core_weights* w, const float* x_in, const void*
     g.M = M; g.N = d; g.K = w->d_mlp; g.precision = w->precision;
     g.A = ws->hmid; g.W = b.w_fc2; g.bias = b.b_fc2; g.resid = ws->x;
     g.out_f32 = ws->x; g.out_bf16 = ws->xa; g.out_precision = w->precision; g.ssq_out = ws->ssq;
+    if (l == w->n_layers - 1 && last_out != nullptr) { g.out_bf16 = last_out; g.out_precision = last_prec; }
     AVD_TRY(launch_gemm(g, st));
   }
   return 0;
 }
 
+// ssq_in (optional): row sums of squares of h; then the input projection applies the RMSNorm row scale
+// 1/(sqrt(ssq/rms_dim) + rms_eps) in its epilogue (the norm's `scale` vector is folded into w_in by the packer).
 static int head_forward(const avd_head_weights* w, const void* h, int M, void* act_a, void* act_b, float* y,
-                        float* eps, cudaStream_t st) {
+                        float* eps, const float* ssq_in, int ssq_parts, int rms_dim, float rms_eps, cudaStream_t st) {
   AVD_REQUIRE(w != nullptr, "null head");
   AVD_REQUIRE(w->n_shared >= 0 && w->n_shared <= AVD_MAX_SHARED, "bad shared-layer count");
   const int S = nseg_of(w->precision);
@@ -275,6 +283,7 @@ static int head_forward(const avd_head_weights* w, const void* h, int M, void* a
   // x = input_proj[m](h)                  (noise_heads.py:205)
   g.M = M; g.N = w->hidden; g.K = w->d_in; g.precision = w->precision;
   g.A = h; g.W = w->w_in; g.bias = w->b_in; g.out_bf16 = act_a; g.out_precision = w->precision;
+  g.ssq_in = ssq_in; g.ssq_parts = ssq_parts; g.rms_dim = rms_dim; g.rms_eps = rms_eps;
   AVD_TRY(launch_gemm(g, st));
   void* cur = act_a;
   void* nxt = act_b;
@@ -429,7 +438,7 @@ int avd_cfg_untok_ddim(const avd_cfg_ddim_args* a, const float* eps_cond, const 
   } else {
     AVD_REQUIRE(a->target == AVD_TARGET_AUDIO && a->length > 0 && a->stride > 0 && a->Nt > 0, "bad audio args");
   }
-  return launch_cfg_untok_ddim(*a, eps_cond, eps_null, z_t, z_prev, alpha_bar, AVD_STREAM(stream));
+  return launch_cfg_untok_ddim(*a, eps_cond, eps_null, z_t, z_prev, alpha_bar, 0, AVD_STREAM(stream));
 }
 
 // ---- operand preparation
@@ -478,11 +487,11 @@ int avd_attention(const void* qkv, int qkv_is_f32, void* out_bf16, int out_preci
 // ---- core / head
 int avd_mmdt_blocks(const avd_core_weights* w, const float* x_in, const void* xa_in, const float* ssq_in,
                     const avd_core_workspace* ws, int n_seq, int N, void* stream) {
-  return core_blocks(w, x_in, xa_in, ssq_in, ws, n_seq, N, AVD_STREAM(stream));
+  return core_blocks(w, x_in, xa_in, ssq_in, ws, n_seq, N, nullptr, 0, AVD_STREAM(stream));
 }
 int avd_head_forward(const avd_head_weights* w, const void* h, int M, void* act_a, void* act_b, float* y, float* eps,
                      void* stream) {
-  return head_forward(w, h, M, act_a, act_b, y, eps, AVD_STREAM(stream));
+  return head_forward(w, h, M, act_a, act_b, y, eps, nullptr, 0, 0, 0.0f, AVD_STREAM(stream));
 }
 
 // ---- sampler
@@ -519,9 +528,11 @@ int avd_sample_step(const avd_sampler* s, int step, float* z, float* eps_tap, vo
   uint8_t* ws = static_cast<uint8_t*>(s->workspace);
   float* x_init = reinterpret_cast<float*>(ws + L.x_init);
   float* ssq_init = reinterpret_cast<float*>(ws + L.ssq_init);
+  static const int dbg_skip = std::getenv("AVD_DBG_STEP_SKIP") ? std::atoi(std::getenv("AVD_DBG_STEP_SKIP")) : 0;  // timing aid
   // (1) target rows of the joint sequence, identical in the cond and null sequences
   const int tgt_mod = s->target == AVD_TARGET_VIDEO ? 0 : 1;
   BuildXArgs a = make_build_args(s, L, tgt_mod, true, true);
+  if (!(dbg_skip & 1))
   AVD_TRY(launch_build_x(a, z, tgt_mod == 0 ? s->wv_t : s->wa_t, tgt_mod == 0 ? s->bv : s->ba,
                          s->temb_steps + (int64_t)step * s->tstep_dim, x_init, ws + L.xa_init, ssq_init, st));
   // (2) 2B co-batched sequences through the blocks
@@ -532,17 +543,20 @@ int avd_sample_step(const avd_sampler* s, int step, float* z, float* eps_tap, vo
   cw.qkv = ws + L.qkv;
   cw.att = ws + L.att;
   cw.hmid = ws + L.hmid;
-  AVD_TRY(core_blocks(&s->core, x_init, ws + L.xa_init, ssq_init, &cw, L.n_seq, L.N, st));
-  // (3) final_norm on the target rows only, compacted for the head (F9)
-  const int row_off = s->target == AVD_TARGET_VIDEO ? L.row_off_v : L.row_off_a;
-  AVD_TRY(launch_rmsnorm_rows(cw.x, s->core.final_scale, L.n_seq, L.N, row_off, L.Nt, L.d, s->core.rms_eps, nullptr,
-                              ws + L.h, L.S_head, st));
-  // (4) noise head of the target modality
+  if (!(dbg_skip & 2))
+  AVD_TRY(core_blocks(&s->core, x_init, ws + L.xa_init, ssq_init, &cw, L.n_seq, L.N, ws + L.h, s->head.precision, st));
+  // (3)+(4) final_norm folded into the input projection of the target modality's noise head, over all rows (F9: the
+  // non-target head is never evaluated; the target rows are selected by the CFG/DDIM kernel below)
   float* eps = reinterpret_cast<float*>(ws + L.eps);
-  AVD_TRY(head_forward(&s->head, ws + L.h, L.Mt, ws + L.act_a, ws + L.act_b, reinterpret_cast<float*>(ws + L.y), eps,
-                       st));
-  if (eps_tap != nullptr)
-    AVD_CUDA(cudaMemcpyAsync(eps_tap, eps, (size_t)L.Mt * L.Dt * 4, cudaMemcpyDeviceToDevice, st));
+  if (!(dbg_skip & 8))
+  AVD_TRY(head_forward(&s->head, ws + L.h, (int)L.M, ws + L.act_a, ws + L.act_b, reinterpret_cast<float*>(ws + L.y), eps,
+                       cw.ssq, L.parts, L.d, s->core.rms_eps, st));
+  const int row_off = s->target == AVD_TARGET_VIDEO ? L.row_off_v : L.row_off_a;
+  const float* eps_c = eps + (int64_t)row_off * L.Dt;                          // rows of clip b: sequence b
+  const float* eps_n = eps + ((int64_t)s->B * L.N + row_off) * L.Dt;           //                 sequence B + b
+  if (eps_tap != nullptr)      // compact (eps_cond ; eps_null) [2B, Nt, Dt]
+    AVD_CUDA(cudaMemcpy2DAsync(eps_tap, (size_t)L.Nt * L.Dt * 4, eps_c, (size_t)L.N * L.Dt * 4, (size_t)L.Nt * L.Dt * 4,
+                               (size_t)L.n_seq, cudaMemcpyDeviceToDevice, st));
   // (5) CFG + un-tokenise + DDIM
   avd_cfg_ddim_args c{};
   c.target = s->target; c.B = s->B;
@@ -554,8 +568,8 @@ int avd_sample_step(const avd_sampler* s, int step, float* z, float* eps_tap, vo
   c.t_prev = (int)s->timesteps_host[step + 1];
   c.T_train = s->T_train;
   AVD_REQUIRE(c.t_now >= 0 && c.t_now < s->T_train && c.t_prev < s->T_train, "timestep out of range");
-  const int64_t half = (int64_t)s->B * L.Nt * L.Dt;
-  return launch_cfg_untok_ddim(c, eps, eps + half, z, z, s->alpha_bar, st);
+  if (dbg_skip & 16) return 0;
+  return launch_cfg_untok_ddim(c, eps_c, eps_n, z, z, s->alpha_bar, (int64_t)L.N * L.Dt, st);
 }
 
 int avd_sample_loop(const avd_sampler* s, const float* z_prompt, float* z, void* stream) {

@@ -13,6 +13,23 @@ namespace avd {
 
 static inline int cdiv(int64_t a, int64_t b) { return static_cast<int>((a + b - 1) / b); }
 
+// Launch with the programmatic-dependent-launch attribute: the kernel may start while its predecessor drains; every
+// kernel launched this way calls pdl_wait() before it touches memory (and so also orders the chain transitively).
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 // =====================================================================================================
 // K1: tube patch / unpatch   (ops.py:100-119, 122-144)
 //   token flat index o = (((((((b*Tt+ti)*Hh+hj)*Ww+wk)*C+c)*t+dt)*h+dh)*w+dw
@@ -259,12 +276,16 @@ __device__ __forceinline__ float cfg_mix(float ec, float en, float g) {
 template <int VEC>
 __global__ void cfg_ddim_video_kernel(const float* __restrict__ eps_c, const float* __restrict__ eps_n,
                                       const float* __restrict__ z_t, float* __restrict__ z_prev, TubeDims d, float g,
-                                      int t_now, int t_prev, const float* __restrict__ alpha_bar, int64_t n_vec) {
+                                      int t_now, int t_prev, const float* __restrict__ alpha_bar, int64_t n_vec,
+                                      int64_t clip_elems, int64_t clip_stride) {
+  pdl_wait();
+  pdl_launch_dependents();
   int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (v >= n_vec) return;
   DdimCoef c = ddim_coef(alpha_bar, t_now, t_prev, 0.0f);
   int64_t i = v * VEC;                              // latent index
   int64_t o = tube_token_index_from_latent(d, i);   // token index of the same element
+  o += (i / clip_elems) * (clip_stride - clip_elems);   // eps rows of one clip may sit clip_stride elements apart
   if (VEC == 4) {
     float4 ec = __ldg(reinterpret_cast<const float4*>(eps_c + o));
     float4 en = __ldg(reinterpret_cast<const float4*>(eps_n + o));
@@ -284,7 +305,9 @@ __global__ void cfg_ddim_video_kernel(const float* __restrict__ eps_c, const flo
 __global__ void cfg_ddim_audio_kernel(const float* __restrict__ eps_c, const float* __restrict__ eps_n,
                                       const float* __restrict__ z_t, float* __restrict__ z_prev, int C, int L, int N,
                                       int length, int stride, float g, int t_now, int t_prev,
-                                      const float* __restrict__ alpha_bar, int64_t total) {
+                                      const float* __restrict__ alpha_bar, int64_t total, int64_t clip_stride) {
+  pdl_wait();
+  pdl_launch_dependents();
   int64_t o = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (o >= total) return;
   DdimCoef cf = ddim_coef(alpha_bar, t_now, t_prev, 0.0f);
@@ -292,8 +315,8 @@ __global__ void cfg_ddim_audio_kernel(const float* __restrict__ eps_c, const flo
   int64_t r = o / L;
   int c = r % C;
   int64_t b = r / C;
-  const float* ec_b = eps_c + b * (int64_t)N * C * length;
-  const float* en_b = eps_n + b * (int64_t)N * C * length;
+  const float* ec_b = eps_c + b * clip_stride;
+  const float* en_b = eps_n + b * clip_stride;
   float e = 0.0f;
   int L_ola = (N - 1) * stride + length;
   if (p < L_ola) {
@@ -314,8 +337,10 @@ __global__ void cfg_ddim_audio_kernel(const float* __restrict__ eps_c, const flo
 }
 
 int launch_cfg_untok_ddim(const avd_cfg_ddim_args& a, const float* eps_c, const float* eps_n, const float* z_t,
-                          float* z_prev, const float* alpha_bar, cudaStream_t s) {
+                          float* z_prev, const float* alpha_bar, int64_t eps_clip_stride, cudaStream_t s) {
   if (a.target == AVD_TARGET_VIDEO) {
+    const int64_t clip_elems = (int64_t)a.C * a.T * a.H * a.W;
+    const int64_t clip_stride = eps_clip_stride > 0 ? eps_clip_stride : clip_elems;
     TubeDims d{a.B, a.C, a.T, a.H, a.W, a.tt, a.th, a.tw, a.T / a.tt, a.H / a.th, a.W / a.tw};
     int64_t total = (int64_t)a.B * a.C * a.T * a.H * a.W;
     if (total <= 0) return 0;
@@ -325,19 +350,20 @@ int launch_cfg_untok_ddim(const avd_cfg_ddim_args& a, const float* eps_c, const 
     LaunchScope ls(KIND_CFG_DDIM, s);
     if (v4) {
       int64_t n_vec = total / 4;
-      cfg_ddim_video_kernel<4><<<cdiv(n_vec, 256), 256, 0, s>>>(eps_c, eps_n, z_t, z_prev, d, a.guidance, a.t_now,
-                                                                  a.t_prev, alpha_bar, n_vec);
+      AVD_CUDA(launch_pdl(cfg_ddim_video_kernel<4>, dim3(cdiv(n_vec, 256)), dim3(256), 0, s, eps_c, eps_n, z_t, z_prev, d,
+                          a.guidance, a.t_now, a.t_prev, alpha_bar, n_vec, clip_elems, clip_stride));
     } else {
-      cfg_ddim_video_kernel<1><<<cdiv(total, 256), 256, 0, s>>>(eps_c, eps_n, z_t, z_prev, d, a.guidance, a.t_now,
-                                                                  a.t_prev, alpha_bar, total);
+      AVD_CUDA(launch_pdl(cfg_ddim_video_kernel<1>, dim3(cdiv(total, 256)), dim3(256), 0, s, eps_c, eps_n, z_t, z_prev, d,
+                          a.guidance, a.t_now, a.t_prev, alpha_bar, total, clip_elems, clip_stride));
     }
     AVD_CUDA(cudaGetLastError());
   } else {
     int64_t total = (int64_t)a.B * a.C * a.L;
     if (total <= 0) return 0;
     LaunchScope ls(KIND_CFG_DDIM, s);
-    cfg_ddim_audio_kernel<<<cdiv(total, 256), 256, 0, s>>>(eps_c, eps_n, z_t, z_prev, a.C, a.L, a.Nt, a.length,
-                                                            a.stride, a.guidance, a.t_now, a.t_prev, alpha_bar, total);
+    const int64_t clip_stride = eps_clip_stride > 0 ? eps_clip_stride : (int64_t)a.Nt * a.C * a.length;
+    AVD_CUDA(launch_pdl(cfg_ddim_audio_kernel, dim3(cdiv(total, 256)), dim3(256), 0, s, eps_c, eps_n, z_t, z_prev, a.C, a.L,
+                        a.Nt, a.length, a.stride, a.guidance, a.t_now, a.t_prev, alpha_bar, total, clip_stride));
     AVD_CUDA(cudaGetLastError());
   }
   return 0;
@@ -477,44 +503,67 @@ int launch_rmsnorm_rows(const float* x, const float* scale, int n_seq, int N, in
   return 0;
 }
 
-// LayerNorm (+ GELU erf) rows; one warp per row, two-pass statistics in fp32.
-__global__ void layernorm_act_kernel(const float* __restrict__ y, const float* __restrict__ w,
-                                     const float* __restrict__ b, int M, int d, float eps, int gelu,
-                                     float* __restrict__ out_f32, __nv_bfloat16* __restrict__ out_bf16, int nseg) {
+// LayerNorm (+ GELU erf) rows; one warp per row held in registers (d <= 1024), two-pass statistics in fp32.
+constexpr int LN_MAX_V4 = 8;   // float4 per lane
+__global__ void __launch_bounds__(256) layernorm_act_kernel(const float* __restrict__ y, const float* __restrict__ w,
+                                                            const float* __restrict__ b, int M, int d, float eps, int gelu,
+                                                            float* __restrict__ out_f32,
+                                                            __nv_bfloat16* __restrict__ out_bf16, int nseg) {
+  pdl_wait();
+  pdl_launch_dependents();
   int row = blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32;
   int lane = threadIdx.x % 32;
   if (row >= M) return;
   const float* yr = y + (int64_t)row * d;
+  const int nv = d / 128;                         // float4 per lane (d % 128 == 0 checked by the launcher)
+  float4 v[LN_MAX_V4];
   float sum = 0.0f;
-  for (int c = lane * 4; c < d; c += 128) {
-    float4 v = *reinterpret_cast<const float4*>(yr + c);
-    sum += (v.x + v.y) + (v.z + v.w);
+#pragma unroll
+  for (int i = 0; i < LN_MAX_V4; ++i) {
+    if (i < nv) {
+      v[i] = *reinterpret_cast<const float4*>(yr + i * 128 + lane * 4);
+      sum += (v[i].x + v[i].y) + (v[i].z + v[i].w);
+    }
   }
   float mu = warp_sum(sum) / (float)d;
   float sq = 0.0f;
-  for (int c = lane * 4; c < d; c += 128) {
-    float4 v = *reinterpret_cast<const float4*>(yr + c);
-    float a0 = v.x - mu, a1 = v.y - mu, a2 = v.z - mu, a3 = v.w - mu;
-    sq += a0 * a0 + a1 * a1 + a2 * a2 + a3 * a3;
+#pragma unroll
+  for (int i = 0; i < LN_MAX_V4; ++i) {
+    if (i < nv) {
+      float a0 = v[i].x - mu, a1 = v[i].y - mu, a2 = v[i].z - mu, a3 = v[i].w - mu;
+      sq += a0 * a0 + a1 * a1 + a2 * a2 + a3 * a3;
+    }
   }
   float var = warp_sum(sq) / (float)d;
   float rstd = 1.0f / sqrtf(var + eps);
   int64_t seg_stride = (int64_t)M * d;
-  for (int c = lane * 4; c < d; c += 128) {
-    float4 v = *reinterpret_cast<const float4*>(yr + c);
-    float4 ww = *reinterpret_cast<const float4*>(w + c);
-    float4 bb = *reinterpret_cast<const float4*>(b + c);
-    float o[4] = {(v.x - mu) * rstd * ww.x + bb.x, (v.y - mu) * rstd * ww.y + bb.y, (v.z - mu) * rstd * ww.z + bb.z,
-                  (v.w - mu) * rstd * ww.w + bb.w};
-    if (gelu) {
 #pragma unroll
-      for (int k = 0; k < 4; ++k) o[k] = gelu_erf(o[k]);
-    }
-    int64_t idx = (int64_t)row * d + c;
-    if (out_f32 != nullptr) *reinterpret_cast<float4*>(out_f32 + idx) = make_float4(o[0], o[1], o[2], o[3]);
-    if (out_bf16 != nullptr) {
+  for (int i = 0; i < LN_MAX_V4; ++i) {
+    if (i < nv) {
+      const int c = i * 128 + lane * 4;
+      float4 ww = *reinterpret_cast<const float4*>(w + c);
+      float4 bb = *reinterpret_cast<const float4*>(b + c);
+      float o[4] = {(v[i].x - mu) * rstd * ww.x + bb.x, (v[i].y - mu) * rstd * ww.y + bb.y,
+                    (v[i].z - mu) * rstd * ww.z + bb.z, (v[i].w - mu) * rstd * ww.w + bb.w};
+      if (gelu) {
 #pragma unroll
-      for (int k = 0; k < 4; ++k) store_split(out_bf16, seg_stride, idx + k, nseg, o[k]);
+        for (int k = 0; k < 4; ++k) o[k] = gelu_erf(o[k]);
+      }
+      int64_t idx = (int64_t)row * d + c;
+      if (out_f32 != nullptr) *reinterpret_cast<float4*>(out_f32 + idx) = make_float4(o[0], o[1], o[2], o[3]);
+      if (out_bf16 != nullptr) {
+        for (int sg = 0; sg < nseg; ++sg) {        // hi / mid / lo bf16 terms, 4 columns = one 8-byte store
+          uint32_t pk[2];
+#pragma unroll
+          for (int k = 0; k < 2; ++k) {
+            __nv_bfloat16 h0 = __float2bfloat16_rn(o[2 * k]), h1 = __float2bfloat16_rn(o[2 * k + 1]);
+            o[2 * k] -= __bfloat162float(h0);
+            o[2 * k + 1] -= __bfloat162float(h1);
+            pk[k] = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
+          }
+          *reinterpret_cast<uint2*>(out_bf16 + sg * seg_stride + idx) = make_uint2(pk[0], pk[1]);
+        }
+      }
     }
   }
 }
@@ -522,10 +571,10 @@ __global__ void layernorm_act_kernel(const float* __restrict__ y, const float* _
 int launch_layernorm_act(const float* y, const float* w, const float* b, int M, int d, float eps, int gelu,
                          float* out_f32, void* out_bf16, int nseg, cudaStream_t s) {
   if (M <= 0) return 0;
+  AVD_REQUIRE(d % 128 == 0 && d <= 128 * LN_MAX_V4, "LayerNorm rows must be a multiple of 128 wide, at most 1024");
   LaunchScope ls(KIND_LN_ACT, s);
-  layernorm_act_kernel<<<cdiv(M, 8), 256, 0, s>>>(y, w, b, M, d, eps, gelu, out_f32,
-                                                  static_cast<__nv_bfloat16*>(out_bf16), nseg);
-  AVD_CUDA(cudaGetLastError());
+  AVD_CUDA(launch_pdl(layernorm_act_kernel, dim3(cdiv(M, 8)), dim3(256), 0, s, y, w, b, M, d, eps, gelu, out_f32,
+                      static_cast<__nv_bfloat16*>(out_bf16), nseg));
   return 0;
 }
 
@@ -537,9 +586,10 @@ int launch_layernorm_act(const float* y, const float* w, const float* b, int M, 
 // and writes the joint-sequence row into x (fp32), xa (bf16 segments) and ssq (row sum of squares in
 // part 0, zeros elsewhere) for the cond sequence b and/or the null sequence B+b.
 // =====================================================================================================
-constexpr int BX_R = 8;      // tokens per CTA
+constexpr int BX_R = 4;      // tokens per CTA
 constexpr int BX_J = 4;      // adapter columns per thread (d_adapt <= 256 * BX_J)
 constexpr int BX_THREADS = 256;
+constexpr int BX_KU = 8;     // weight rows fetched per batch (independent loads in flight)
 
 __global__ void __launch_bounds__(BX_THREADS) build_x_kernel(BuildXArgs a, const float* __restrict__ z,
                                                             const float* __restrict__ wt,
@@ -551,10 +601,21 @@ __global__ void __launch_bounds__(BX_THREADS) build_x_kernel(BuildXArgs a, const
   __shared__ float red[BX_R][BX_THREADS / 32];
   __shared__ float row_ss[BX_R];
 
-  int groups = (a.n_tok + BX_R - 1) / BX_R;
-  int b = blockIdx.x / groups;
-  int n0 = (blockIdx.x % groups) * BX_R;
-  int tid = threadIdx.x;
+  const int groups = (a.n_tok + BX_R - 1) / BX_R;
+  const int b = blockIdx.x / groups;
+  const int n0 = (blockIdx.x % groups) * BX_R;
+  const int tid = threadIdx.x;
+  const int ncol = (a.d_adapt + BX_THREADS - 1) / BX_THREADS;   // live adapter columns of this thread (<= BX_J)
+
+  // adapter bias / first weight rows do not depend on the previous kernel
+  float bv[BX_J];
+#pragma unroll
+  for (int j = 0; j < BX_J; ++j) {
+    const int c = tid + j * BX_THREADS;
+    bv[j] = (c < a.d_adapt) ? __ldg(bias + c) : 0.0f;
+  }
+  pdl_wait();
+  pdl_launch_dependents();
 
   // ---- gather R tokens
   for (int idx = tid; idx < BX_R * a.d_tok; idx += BX_THREADS) {
@@ -572,30 +633,37 @@ __global__ void __launch_bounds__(BX_THREADS) build_x_kernel(BuildXArgs a, const
         int j = k % a.length, c = k / a.length;
         src = ((int64_t)b * a.C + c) * a.L + (int64_t)n * a.stride + j;
       }
-      v = __ldg(z + src);
+      v = z[src];
     }
     tok[idx] = v;
   }
   __syncthreads();
 
-  // ---- adapter GEMV for R rows, BX_J columns per thread
+  // ---- adapter GEMV for R rows: BX_KU weight rows in flight per batch, k ascending (fixed summation order)
   float acc[BX_R][BX_J];
 #pragma unroll
   for (int r = 0; r < BX_R; ++r)
 #pragma unroll
     for (int j = 0; j < BX_J; ++j) acc[r][j] = 0.0f;
-  for (int k = 0; k < a.d_tok; ++k) {
-    float wv[BX_J];
+  for (int k0 = 0; k0 < a.d_tok; k0 += BX_KU) {
+    float wv[BX_KU][BX_J];
 #pragma unroll
-    for (int j = 0; j < BX_J; ++j) {
-      int c = tid + j * BX_THREADS;
-      wv[j] = (c < a.d_adapt) ? __ldg(wt + (int64_t)k * a.d_adapt + c) : 0.0f;
-    }
+    for (int u = 0; u < BX_KU; ++u)
 #pragma unroll
-    for (int r = 0; r < BX_R; ++r) {
-      float t = tok[r * a.d_tok + k];
+      for (int j = 0; j < BX_J; ++j) {
+        const int c = tid + j * BX_THREADS;
+        wv[u][j] = (j < ncol && c < a.d_adapt && k0 + u < a.d_tok) ? __ldg(wt + (int64_t)(k0 + u) * a.d_adapt + c) : 0.0f;
+      }
 #pragma unroll
-      for (int j = 0; j < BX_J; ++j) acc[r][j] = fmaf(t, wv[j], acc[r][j]);
+    for (int u = 0; u < BX_KU; ++u) {
+      if (k0 + u < a.d_tok) {
+#pragma unroll
+        for (int r = 0; r < BX_R; ++r) {
+          const float t = tok[r * a.d_tok + k0 + u];
+#pragma unroll
+          for (int j = 0; j < BX_J; ++j) acc[r][j] = fmaf(t, wv[u][j], acc[r][j]);
+        }
+      }
     }
   }
 
@@ -612,7 +680,7 @@ __global__ void __launch_bounds__(BX_THREADS) build_x_kernel(BuildXArgs a, const
     for (int j = 0; j < BX_J; ++j) {
       int c = tid + j * BX_THREADS;
       if (live && c < a.d_adapt) {
-        float v = acc[r][j] + __ldg(bias + c);
+        float v = acc[r][j] + bv[j];
         part += v * v;
         if (a.write_cond) { x[row_c + c] = v; store_split(xa, seg_stride, row_c + c, a.nseg, v); }
         if (a.write_null) { x[row_n + c] = v; store_split(xa, seg_stride, row_n + c, a.nseg, v); }
@@ -660,8 +728,8 @@ int launch_build_x(const BuildXArgs& a, const float* z, const float* wt, const f
     AVD_CUDA(cudaFuncSetAttribute(build_x_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   }
   LaunchScope ls(KIND_BUILD_X, s);
-  build_x_kernel<<<a.B * groups, BX_THREADS, smem, s>>>(a, z, wt, bias, temb, x, static_cast<__nv_bfloat16*>(xa), ssq);
-  AVD_CUDA(cudaGetLastError());
+  AVD_CUDA(launch_pdl(build_x_kernel, dim3(a.B * groups), dim3(BX_THREADS), smem, s, a, z, wt, bias, temb, x,
+                      static_cast<__nv_bfloat16*>(xa), ssq));
   return 0;
 }
 

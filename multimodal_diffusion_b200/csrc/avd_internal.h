@@ -65,8 +65,9 @@ int launch_timestep_embedding(const float* t, float* emb, int B, int dim, float 
 int launch_ddim_step(const float* x_t, const float* eps, const float* noise, float* x_prev, const int64_t* t_now,
                      const int64_t* t_prev, const float* alpha_bar, int T_train, int B, int64_t per_batch, float eta,
                      cudaStream_t s);
+// eps_clip_stride: elements between the eps rows of consecutive clips (0 = compact [B, Nt, Dt])
 int launch_cfg_untok_ddim(const avd_cfg_ddim_args& a, const float* eps_c, const float* eps_n, const float* z_t,
-                          float* z_prev, const float* alpha_bar, cudaStream_t s);
+                          float* z_prev, const float* alpha_bar, int64_t eps_clip_stride, cudaStream_t s);
 int launch_pack_weight(const float* W, const float* col_scale, void* out, int N, int K, int nseg, cudaStream_t s);
 int launch_transpose(const float* W, float* Wt, int N, int K, cudaStream_t s);
 int launch_rows_prepare(const float* x, void* xa, float* ssq, int M, int d, int nseg, cudaStream_t s);

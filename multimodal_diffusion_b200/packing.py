@@ -87,7 +87,10 @@ class PackedCore:
 class PackedHead:
     """One modality's path of MultiModalNoiseHead (noise_heads.py state_dict keys) for avd_head_forward."""
 
-    def __init__(self, sd: Dict[str, torch.Tensor], modality: str, precision, device, ln_eps: float = 1e-5):
+    def __init__(self, sd: Dict[str, torch.Tensor], modality: str, precision, device, ln_eps: float = 1e-5,
+                 in_col_scale: Optional[torch.Tensor] = None):
+        """in_col_scale: RMSNorm ``scale`` of the layer feeding the head (MMDiT.final_norm); when given it is folded
+        into the columns of input_proj so the fused sampler can apply the norm as a row scale in the GEMM epilogue."""
         self.precision = _lib.precision_code(precision)
         self.modality = modality
         n_shared = 0
@@ -105,7 +108,8 @@ class PackedHead:
         w.hidden, w.d_in = int(win.shape[0]), int(win.shape[1])
         w.d_out, w.n_shared = int(wout.shape[0]), n_shared
         w.precision, w.ln_eps = self.precision, float(ln_eps)
-        pin, pout = pack_linear_weight(win, self.precision), pack_linear_weight(wout, self.precision)
+        cs = None if in_col_scale is None else _dev_f32(in_col_scale, device)
+        pin, pout = pack_linear_weight(win, self.precision, cs), pack_linear_weight(wout, self.precision)
         bin_, bout = _dev_f32(sd[f"input_proj.{modality}.bias"], device), _dev_f32(sd[f"out_proj.{modality}.bias"], device)
         self.keep += [pin, pout, bin_, bout]
         w.w_in, w.b_in, w.w_out, w.b_out = pin.data_ptr(), bin_.data_ptr(), pout.data_ptr(), bout.data_ptr()

@@ -130,7 +130,9 @@ class FusedSampler:
         with torch.cuda.device(self.device):
             _lib.check(lib.avd_device_check())
         self.core = packing.PackedCore(_state_dict_of(core), cfg.n_layers, cfg.n_heads, core_precision, self.device)
-        self.head = packing.PackedHead(_state_dict_of(head), target, head_precision, self.device)
+        # final_norm.scale is folded into the head's input projection (the norm itself runs in that GEMM's epilogue)
+        self.head = packing.PackedHead(_state_dict_of(head), target, head_precision, self.device,
+                                       in_col_scale=_state_dict_of(core)["final_norm.scale"])
         self.av = packing.PackedAdapter(_state_dict_of(adapt_v), self.device)
         self.aa = packing.PackedAdapter(_state_dict_of(adapt_a), self.device)
         if self.av.d_in != cfg.Dv or self.aa.d_in != cfg.Da or self.av.d_out != cfg.d_model - cfg.tstep_dim:
@@ -235,7 +237,7 @@ class FusedSampler:
     def kernels_per_sample(self) -> int:
         """Kernel launches of one S-step sampling call (the claim behind bench.py's gpu_launches)."""
         L, ns = self.cfg.n_layers, self.head.struct.n_shared
-        per_step = 1 + 5 * L + 1 + (2 + 2 * ns) + 1
+        per_step = 1 + 5 * L + (2 + 2 * ns) + 1
         return 1 + self.cfg.sampler_steps * per_step     # + prompt-side build_x (memsets are not kernels of ours)
 
 
