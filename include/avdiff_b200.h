@@ -54,7 +54,8 @@ int avd_device_check(void);                  /* 0 iff the current device is sm_1
 int avd_struct_size(int which);
 
 /* Per-launch profiler (CUDA events on `stream` around every kernel this library launches).
- * Used by bench.py for the roofline object; must be off during graph capture. */
+ * Used by bench.py for the roofline object.  When the launches are being captured into a CUDA graph the events
+ * become event-record nodes, so one replay of that graph times every kernel on the device back to back. */
 int avd_prof_enable(int on);
 int avd_prof_reset(void);
 int avd_prof_num_kinds(void);
@@ -65,6 +66,9 @@ int64_t avd_launch_count(void);              /* kernels launched by this library
 /* Debug only: GEMM CTAs write 8 x (globaltimer ns, clock64) phase stamps into dev_u64[cta*16 ..] when the
  * grid fits n_u64; NULL switches it off (the default). */
 int avd_debug_trace(void* dev_u64, int64_t n_u64);
+/* Measurement aid: bit k of mask set -> kernels of profiler kind k are not launched (results are then meaningless).
+ * bench.py uses it to time, with CUDA events, a graph that holds only the GEMM launches of a sampling call. */
+int avd_debug_skip_kinds(int mask);
 
 /* ---------------------------------------------------------------- K1: tokenisers (bit-exact fp32 moves) */
 /* ops.tube_patch_video (avdiff/utils/ops.py:100-119): z[B,C,T,H,W] -> tok[B,(T/t)(H/h)(W/w),C*t*h*w] */

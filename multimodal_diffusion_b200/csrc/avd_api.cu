@@ -51,12 +51,21 @@ static cudaEvent_t take_event() {
   return e;
 }
 
+// Inside a stream capture the events become event-record nodes of the graph (cudaEventRecordExternal), so a replay
+// of the captured step times every kernel on the device without host launch gaps in between.
+static void record_event(cudaEvent_t e, cudaStream_t s) {
+  cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+  cudaStreamIsCapturing(s, &st);
+  if (st == cudaStreamCaptureStatusActive) cudaEventRecordWithFlags(e, s, cudaEventRecordExternal);
+  else cudaEventRecord(e, s);
+}
+
 LaunchScope::LaunchScope(Kind k, cudaStream_t s) : kind(k), stream(s), slot(-1) {
   std::lock_guard<std::mutex> lk(g_prof_mu);
   ++g_launches;
   if (g_prof_on) {
     ProfRecord r{(int)k, take_event(), take_event()};
-    cudaEventRecord(r.beg, s);
+    record_event(r.beg, s);
     g_prof.push_back(r);
     slot = (int)g_prof.size() - 1;
   }
@@ -65,7 +74,7 @@ LaunchScope::LaunchScope(Kind k, cudaStream_t s) : kind(k), stream(s), slot(-1) 
 LaunchScope::~LaunchScope() {
   if (slot >= 0) {
     std::lock_guard<std::mutex> lk(g_prof_mu);
-    cudaEventRecord(g_prof[slot].end, stream);
+    record_event(g_prof[slot].end, stream);
   }
 }
 
@@ -141,6 +150,8 @@ int get_tensor_map_bf16_3d(const void* base, uint64_t d0, uint64_t d1, uint64_t 
                            uint64_t stride2_bytes, uint32_t box0, uint32_t box1, CUtensorMap* out) {
   return get_tensor_map_3d(base, 2, d0, d1, d2, stride1_bytes, stride2_bytes, box0, box1, out);
 }
+
+int g_skip_kinds = 0;
 
 bool pdl_enabled() {
   static int v = -1;
@@ -389,6 +400,10 @@ int avd_prof_collect(int kind, double* total_ms, int64_t* launches) {
   return 0;
 }
 int64_t avd_launch_count(void) { return g_launches; }
+int avd_debug_skip_kinds(int mask) {
+  g_skip_kinds = mask;
+  return 0;
+}
 int avd_debug_trace(void* dev_u64, int64_t n_u64) {
   g_dbg_trace = static_cast<unsigned long long*>(dev_u64);
   g_dbg_trace_slots = dev_u64 ? n_u64 : 0;

@@ -421,6 +421,7 @@ int launch_attention_tc(const void* qkv_bf16, void* out, int out_nseg, int n_seq
   }
   cfg.attrs = attrs;
   cfg.numAttrs = na;
+  if (kind_skipped(KIND_ATTN_TC)) return 0;
   LaunchScope ls(KIND_ATTN_TC, s);
   if (N <= ATT_BKV) AVD_CUDA(cudaLaunchKernelEx(&cfg, attn_tc_kernel<true>, tmQ, tmKV, p));
   else AVD_CUDA(cudaLaunchKernelEx(&cfg, attn_tc_kernel<false>, tmQ, tmKV, p));
@@ -508,6 +509,7 @@ int launch_attention_f32(const float* qkv, void* out, int out_nseg, int n_seq, i
     AVD_CUDA(cudaFuncSetAttribute(attn_f32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   }
   dim3 grid((N + AF_ROWS - 1) / AF_ROWS, n_heads, n_seq);
+  if (kind_skipped(KIND_ATTN_F32)) return 0;
   LaunchScope ls(KIND_ATTN_F32, s);
   attn_f32_kernel<<<grid, AF_WARPS * 32, smem, s>>>(qkv, static_cast<__nv_bfloat16*>(out), out_nseg, N, d, hd,
                                                     (int64_t)n_seq * N, 1.0f / sqrtf((float)hd));

@@ -347,6 +347,7 @@ int launch_cfg_untok_ddim(const avd_cfg_ddim_args& a, const float* eps_c, const 
     uintptr_t al = reinterpret_cast<uintptr_t>(eps_c) | reinterpret_cast<uintptr_t>(eps_n) |
                    reinterpret_cast<uintptr_t>(z_t) | reinterpret_cast<uintptr_t>(z_prev);
     bool v4 = (a.tw % 4 == 0) && ((al & 15) == 0);
+    if (kind_skipped(KIND_CFG_DDIM)) return 0;
     LaunchScope ls(KIND_CFG_DDIM, s);
     if (v4) {
       int64_t n_vec = total / 4;
@@ -360,6 +361,7 @@ int launch_cfg_untok_ddim(const avd_cfg_ddim_args& a, const float* eps_c, const 
   } else {
     int64_t total = (int64_t)a.B * a.C * a.L;
     if (total <= 0) return 0;
+    if (kind_skipped(KIND_CFG_DDIM)) return 0;
     LaunchScope ls(KIND_CFG_DDIM, s);
     const int64_t clip_stride = eps_clip_stride > 0 ? eps_clip_stride : (int64_t)a.Nt * a.C * a.length;
     AVD_CUDA(launch_pdl(cfg_ddim_audio_kernel, dim3(cdiv(total, 256)), dim3(256), 0, s, eps_c, eps_n, z_t, z_prev, a.C, a.L,
@@ -572,6 +574,7 @@ int launch_layernorm_act(const float* y, const float* w, const float* b, int M, 
                          float* out_f32, void* out_bf16, int nseg, cudaStream_t s) {
   if (M <= 0) return 0;
   AVD_REQUIRE(d % 128 == 0 && d <= 128 * LN_MAX_V4, "LayerNorm rows must be a multiple of 128 wide, at most 1024");
+  if (kind_skipped(KIND_LN_ACT)) return 0;
   LaunchScope ls(KIND_LN_ACT, s);
   AVD_CUDA(launch_pdl(layernorm_act_kernel, dim3(cdiv(M, 8)), dim3(256), 0, s, y, w, b, M, d, eps, gelu, out_f32,
                       static_cast<__nv_bfloat16*>(out_bf16), nseg));
@@ -727,6 +730,7 @@ int launch_build_x(const BuildXArgs& a, const float* z, const float* wt, const f
   if (smem > 48 * 1024) {
     AVD_CUDA(cudaFuncSetAttribute(build_x_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   }
+  if (kind_skipped(KIND_BUILD_X)) return 0;
   LaunchScope ls(KIND_BUILD_X, s);
   AVD_CUDA(launch_pdl(build_x_kernel, dim3(a.B * groups), dim3(BX_THREADS), smem, s, a, z, wt, bias, temb, x,
                       static_cast<__nv_bfloat16*>(xa), ssq));

@@ -429,6 +429,7 @@ static int launch_gemm_bn(const CUtensorMap& tmA, const CUtensorMap& tmB, const 
   }
   cfg.attrs = attrs;
   cfg.numAttrs = na;
+  if (kind_skipped(KIND_GEMM)) return 0;
   LaunchScope ls(KIND_GEMM, s);
   AVD_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<BN, STAGES>, tmA, tmB, tmR, p));
   return 0;

@@ -102,6 +102,8 @@ int launch_build_x(const BuildXArgs& a, const float* z, const float* wt, const f
 // tcgen05 GEMM (avd_gemm.cu)
 int launch_gemm(const avd_gemm_args& g, cudaStream_t s);
 
+extern int g_skip_kinds;   // debug / measurement: bit k set -> launches of Kind k are skipped (avd_debug_skip_kinds)
+inline bool kind_skipped(int k) { return (g_skip_kinds >> k) & 1; }
 bool pdl_enabled();     // programmatic dependent launch between the kernels of a step (AVD_PDL=0 switches it off)
 extern unsigned long long* g_dbg_trace;   // debug phase trace of the GEMM kernel (avd_debug_trace)
 extern int64_t g_dbg_trace_slots;
