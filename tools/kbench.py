@@ -109,7 +109,15 @@ def main() -> None:
     def g_tiny():
         _lib.check(lib.avd_timestep_embedding(tt.data_ptr(), temb.data_ptr(), 1, 256, 10000.0, _lib.stream_ptr()))
 
+    yl = torch.randn(8, 512, device=dev)
+    wl, bl, ol = torch.ones(512, device=dev), torch.zeros(512, device=dev), torch.empty(8, 512, device=dev)
+
+    def g_tiny_pdl():
+        _lib.check(lib.avd_layernorm_act(yl.data_ptr(), wl.data_ptr(), bl.data_ptr(), 8, 512, 1e-5, 0, ol.data_ptr(), None, 0,
+                                         _lib.stream_ptr()))
+
     cases = [("tiny elementwise (launch floor)", g_tiny, 0.0),
+             ("tiny elementwise with PDL", g_tiny_pdl, 0.0),
              (f"qkv   {M}x1536x512", g_qkv, 2.0 * M * 1536 * 512),
              (f"attn  16 seq x {N} x 8 heads", g_att, 4.0 * 16 * N * N * 512),
              (f"oproj {M}x512x512", g_o, 2.0 * M * 512 * 512),

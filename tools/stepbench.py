@@ -36,6 +36,8 @@ def main() -> None:
 
     us = time_graph(step, 10)
     print(f"one DDIM+CFG step ({target}, B={B}): {us:9.2f} us  -> {B / (us * 50e-6):8.1f} clips/s")
+    if "--kinds" not in sys.argv:
+        return
     # per-kind breakdown with the event profiler (eager; includes launch gaps, use for shares only)
     lib.avd_prof_reset(); lib.avd_prof_enable(1)
     for _ in range(5):
