@@ -64,7 +64,7 @@ int main() {
   cudaFuncSetAttribute(probe, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   printf("%6s %6s %6s %6s | %10s %12s %10s\n", "ctas", "nprod", "depth", "share", "cyc/box", "B/cyc/SM", "KB/cyc chip");
   for (int ctas : {40, 148})
-    for (int share : {3, 4})
+    for (int share : {0, 3, 4})
       for (int nprod : {1, 2, 4})
         for (int depth : {1, 2, 3}) {
           Args a{256, depth, nprod, share, K, d};     // share = log2 of the CTAs reading the same rows
