@@ -69,6 +69,9 @@ int avd_debug_trace(void* dev_u64, int64_t n_u64);
 /* Measurement aid: bit k of mask set -> kernels of profiler kind k are not launched (results are then meaningless).
  * bench.py uses it to time, with CUDA events, a graph that holds only the GEMM launches of a sampling call. */
 int avd_debug_skip_kinds(int mask);
+/* Debug only: out256[0] = number of barrier waits of the persistent GEMM that timed out since the last call, then
+ * from out256[8] up to 30 records {tag, cta, thread, counter, parity, N, K, grid*1000+BN}; the call clears them. */
+int avd_debug_gemm_timeout(unsigned int* out256);
 
 /* ---------------------------------------------------------------- K1: tokenisers (bit-exact fp32 moves) */
 /* ops.tube_patch_video (avdiff/utils/ops.py:100-119): z[B,C,T,H,W] -> tok[B,(T/t)(H/h)(W/w),C*t*h*w] */

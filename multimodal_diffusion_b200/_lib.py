@@ -106,6 +106,7 @@ _SIGNATURES = {
     "avd_launch_count": (C.c_int64, []),
     "avd_debug_trace": (_I, [vp, C.c_int64]),
     "avd_debug_skip_kinds": (_I, [_I]),
+    "avd_debug_gemm_timeout": (_I, [C.POINTER(C.c_uint)]),
     "avd_tube_patch": (_I, [fp, fp, _I, _I, _I, _I, _I, _I, _I, _I, vp]),
     "avd_tube_unpatch": (_I, [fp, fp, _I, _I, _I, _I, _I, _I, _I, _I, vp]),
     "avd_chunk1d": (_I, [fp, fp, _I, _I, _I, _I, _I, vp]),

@@ -2,6 +2,7 @@
 // accounting / event profiler, TMA descriptor cache, and the host-side sequencing of the MMDT blocks, the
 // noise head and the DDIM + CFG sampling loop.  Nothing here allocates device memory or synchronises.
 #include "avd_internal.h"
+namespace avd { int ps_debug_read(unsigned int* out8); }
 
 #include <cmath>
 #include <cstdlib>
@@ -400,6 +401,11 @@ int avd_prof_collect(int kind, double* total_ms, int64_t* launches) {
   return 0;
 }
 int64_t avd_launch_count(void) { return g_launches; }
+int avd_debug_gemm_timeout(unsigned int* out8) {
+  AVD_REQUIRE(out8 != nullptr, "null output");
+  return ps_debug_read(out8);
+}
+
 int avd_debug_skip_kinds(int mask) {
   g_skip_kinds = mask;
   return 0;

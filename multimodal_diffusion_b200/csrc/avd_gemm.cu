@@ -25,47 +25,11 @@
 // Precision modes are realised by the k-loop: for mode p the operands are stored as hi/(mid/)lo bf16
 // segments and the loop runs over a list of (A segment, W segment) pairs, smallest products first, all
 // accumulating into the same TMEM tiles (1, 3 or 6 passes over K).
-#include "avd_internal.h"
-#include "avd_ptx.cuh"
+#include "avd_gemm_common.cuh"
 
-#include <cuda_fp16.h>
 #include <cstdlib>
 
 namespace avd {
-
-constexpr int GEMM_BM = 128;
-constexpr int GEMM_BK = 64;            // 64 bf16 = 128 B = one swizzle atom row
-constexpr int GEMM_THREADS = 256;
-constexpr int GEMM_BOX = 4096;         // one epilogue staging box: 32 rows x 128 B (32 fp32 or 64 bf16 columns)
-
-struct GemmParams {
-  int M, N, K;
-  int n_pairs;
-  uint32_t pairs;            // 4 bits per pair: (a_seg << 2) | w_seg, pair i in bits [4i, 4i+4)
-  const float* bias;
-  const float* ssq_in;
-  int ssq_parts;
-  float inv_sqrt_rms_dim;    // 1/sqrt(rms_dim)
-  float rms_eps;
-  int has_resid;             // residual tile comes in through tmR (and the fp32 result is written over it in smem)
-  int act;                   // 0 none, 1 GELU (erff), 2 GELU (fast erf, |err| < 2e-7)
-  float* out_f32;            // fp32 result [M,N] (may alias the residual) or nullptr
-  __nv_bfloat16* out_bf16;   // bf16 result segments [out_nseg][M][N] or nullptr
-  int out_nseg;
-  float* ssq_out;
-  unsigned long long* trace; // debug: per-CTA phase timestamps (avd_debug_trace), nullptr in production
-};
-
-__device__ __forceinline__ void trace_mark(unsigned long long* trace, int slot) {
-  if (trace != nullptr) {
-    const int cta = blockIdx.y * gridDim.x + blockIdx.x;
-    unsigned long long g, c;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g));
-    asm volatile("mov.u64 %0, %%clock64;" : "=l"(c));
-    trace[(cta * 16 + slot) * 2] = g;
-    trace[(cta * 16 + slot) * 2 + 1] = c;
-  }
-}
 
 template <int BN, int STAGES>   // STAGES = ring depth of EACH of the two pipelines
 struct GemmSmem {
@@ -78,53 +42,6 @@ struct GemmSmem {
   static constexpr int TAIL_BYTES = 256 + BN * 4 + 1024 + 512;   // mbarriers + TMEM slot, bias tile, ssq exchange, rinv
   static constexpr int total(bool resid) { return PIPE_BYTES + (resid ? F32_TILE : 0) + TAIL_BYTES; }
 };
-
-__device__ __forceinline__ float4 lds128(const uint8_t* p) {
-  float4 v;
-  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(smem_u32(p)));
-  return v;
-}
-__device__ __forceinline__ void sts128(uint8_t* p, float a, float b, float c, float d) {
-  asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(smem_u32(p)), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
-}
-__device__ __forceinline__ void sts128u(uint8_t* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
-  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(smem_u32(p)), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
-}
-
-// GELU with erf from Abramowitz-Stegun 7.1.26 (|erf error| <= 1.5e-7): 2 MUFU + ~12 FMA-pipe instructions instead
-// of erff's ~40.  Used in bf16 mode only, where the result is rounded to bf16 (2^-9) anyway.
-__device__ __forceinline__ float gelu_fast(float x) {
-  const float y = fabsf(x) * 0.70710678118654752440f;
-  float t;
-  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, y, 1.0f)));
-  float pl = fmaf(t, 1.061405429f, -1.453152027f);
-  pl = fmaf(pl, t, 1.421413741f);
-  pl = fmaf(pl, t, -0.284496736f);
-  pl = fmaf(pl, t, 0.254829592f);
-  pl *= t;
-  float e;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(-y * y * 1.4426950408889634f));
-  const float erf_abs = fmaf(-pl, e, 1.0f);
-  const float h = 0.5f * x;
-  return fmaf(fabsf(h), erf_abs, h);          // 0.5 x (1 + sign(x) erf|.|) = h + |h| erf_abs
-}
-
-// GELU of two values in f16x2 arithmetic, tanh form with the hardware tanh.approx.f16x2, packed as bf16x2.  Used only
-// where the result is stored as ONE bf16 segment (fc1 of the bf16 mode): |tanh form - erf form| <= 4.8e-4 and the
-// f16 arithmetic (2^-11) are both below the bf16 quantum (2^-9) of the stored value; rms over N(0,1) inputs 3e-4 vs
-// 1.1e-3 for the bf16 rounding itself.  ~10 instructions + 1 MUFU per PAIR instead of ~16 + 2 MUFU per element.
-__device__ __forceinline__ uint32_t gelu_pair_bf16x2(float a, float b) {
-  const __half2 x = __floats2half2_rn(a, b);
-  const __half2 u = __hmul2(x, x);
-  const __half2 inner = __hfma2(__float2half2_rn(0.0356774081f), u, __float2half2_rn(0.7978845608f));
-  const __half2 w = __hmul2(x, inner);
-  uint32_t wi = *reinterpret_cast<const uint32_t*>(&w), ti;
-  asm("tanh.approx.f16x2 %0, %1;" : "=r"(ti) : "r"(wi));
-  const __half2 t = *reinterpret_cast<const __half2*>(&ti);
-  const __half2 h = __hmul2(x, __float2half2_rn(0.5f));
-  const float2 o = __half22float2(__hfma2(h, t, h));
-  return pack_bf16x2(o.x, o.y);
-}
 
 // smem map:  [ 2 pipelines x STAGES x (A 128x64 | W BNx64) ]  [ residual / fp32 result tile, only with has_resid ]
 //            [ barriers | bias ]
@@ -486,6 +403,32 @@ int launch_gemm(const avd_gemm_args& g, cudaStream_t s) {
   const int out_nseg = g.out_bf16 != nullptr ? nseg_of(g.out_precision) : 0;
   AVD_REQUIRE(g.out_bf16 == nullptr || out_nseg > 0, "out_precision must be 1, 3 or 6");
 
+  GemmParams p{};
+  p.M = g.M; p.N = g.N; p.K = g.K;
+  // smallest partial products first so they are not absorbed by the large ones
+  if (g.precision == 1) { p.n_pairs = 1; p.pairs = 0x0; }
+  else if (g.precision == 3) { p.n_pairs = 3; p.pairs = (0x4u) | (0x1u << 4) | (0x0u << 8); }  // (lo,hi) (hi,lo) (hi,hi)
+  else {
+    // segments 0=hi 1=mid 2=lo: (1,1) (2,0) (0,2) (1,0) (0,1) (0,0)
+    p.n_pairs = 6;
+    p.pairs = (0x5u) | (0x8u << 4) | (0x2u << 8) | (0x4u << 12) | (0x1u << 16) | (0x0u << 20);
+  }
+  p.bias = g.bias;
+  p.ssq_in = g.ssq_in;
+  p.ssq_parts = g.ssq_parts;
+  p.inv_sqrt_rms_dim = g.rms_dim > 0 ? 1.0f / sqrtf((float)g.rms_dim) : 1.0f;
+  p.rms_eps = g.rms_eps;
+  p.has_resid = g.resid != nullptr;
+  p.act = g.act;
+  p.out_f32 = g.out_f32;
+  p.out_bf16 = static_cast<__nv_bfloat16*>(g.out_bf16);
+  p.out_nseg = out_nseg;
+  p.ssq_out = g.ssq_out;
+  // Persistent kernel with the epilogue under the next tile's mainloop (avd_gemm_ps.cu) unless AVD_GEMM_V=3 asks for
+  // the one-tile-per-CTA kernel below.
+  static const int gemm_v = env_int("AVD_GEMM_V", 3);
+  if (gemm_v != 3) return launch_gemm_ps(g, p, nseg, env_int("AVD_GEMM_BN", 0), s);
+
   // Tile width: the widest BN that divides N, still gives >= ~0.8 waves of CTAs on 148 SMs, and whose epilogue staging
   // (fp32 tile unless it overwrites the residual tile, plus out_nseg bf16 tiles) fits the reused pipeline smem.
   // A residual tile needs dedicated smem, which only the narrow tiles can spare.
@@ -511,27 +454,6 @@ int launch_gemm(const avd_gemm_args& g, cudaStream_t s) {
     if (usable(cands[i])) bn = cands[i];
   AVD_REQUIRE(bn > 0, "no tile shape fits this combination of outputs: use fewer outputs per GEMM");
 
-  GemmParams p{};
-  p.M = g.M; p.N = g.N; p.K = g.K;
-  // smallest partial products first so they are not absorbed by the large ones
-  if (g.precision == 1) { p.n_pairs = 1; p.pairs = 0x0; }
-  else if (g.precision == 3) { p.n_pairs = 3; p.pairs = (0x4u) | (0x1u << 4) | (0x0u << 8); }  // (lo,hi) (hi,lo) (hi,hi)
-  else {
-    // segments 0=hi 1=mid 2=lo: (1,1) (2,0) (0,2) (1,0) (0,1) (0,0)
-    p.n_pairs = 6;
-    p.pairs = (0x5u) | (0x8u << 4) | (0x2u << 8) | (0x4u << 12) | (0x1u << 16) | (0x0u << 20);
-  }
-  p.bias = g.bias;
-  p.ssq_in = g.ssq_in;
-  p.ssq_parts = g.ssq_parts;
-  p.inv_sqrt_rms_dim = g.rms_dim > 0 ? 1.0f / sqrtf((float)g.rms_dim) : 1.0f;
-  p.rms_eps = g.rms_eps;
-  p.has_resid = g.resid != nullptr;
-  p.act = g.act;
-  p.out_f32 = g.out_f32;
-  p.out_bf16 = static_cast<__nv_bfloat16*>(g.out_bf16);
-  p.out_nseg = out_nseg;
-  p.ssq_out = g.ssq_out;
   const int64_t n_ctas = (int64_t)(g.N / bn) * mt;
   p.trace = (g_dbg_trace != nullptr && n_ctas * 32 <= g_dbg_trace_slots) ? g_dbg_trace : nullptr;
 

@@ -1,0 +1,97 @@
+// avd_gemm_common.cuh -- pieces shared by the two tcgen05 GEMM kernels (avd_gemm.cu: one tile per CTA;
+// avd_gemm_ps.cu: persistent CTAs with double-buffered TMEM accumulators).
+#pragma once
+#include "avd_internal.h"
+#include "avd_ptx.cuh"
+
+#include <cuda_fp16.h>
+
+namespace avd {
+
+constexpr int GEMM_BM = 128;
+constexpr int GEMM_BK = 64;            // 64 bf16 = 128 B = one swizzle atom row
+constexpr int GEMM_THREADS = 256;
+constexpr int GEMM_BOX = 4096;         // one epilogue staging box: 32 rows x 128 B (32 fp32 or 64 bf16 columns)
+
+struct GemmParams {
+  int M, N, K;
+  int n_pairs;
+  uint32_t pairs;            // 4 bits per pair: (a_seg << 2) | w_seg, pair i in bits [4i, 4i+4)
+  const float* bias;
+  const float* ssq_in;
+  int ssq_parts;
+  float inv_sqrt_rms_dim;    // 1/sqrt(rms_dim)
+  float rms_eps;
+  int has_resid;             // residual tile comes in through tmR (and the fp32 result is written over it in smem)
+  int act;                   // 0 none, 1 GELU (erff), 2 GELU (fast erf, |err| < 2e-7)
+  float* out_f32;            // fp32 result [M,N] (may alias the residual) or nullptr
+  __nv_bfloat16* out_bf16;   // bf16 result segments [out_nseg][M][N] or nullptr
+  int out_nseg;
+  float* ssq_out;
+  unsigned long long* trace; // debug: per-CTA phase timestamps (avd_debug_trace), nullptr in production
+};
+
+__device__ __forceinline__ void trace_mark(unsigned long long* trace, int slot) {
+  if (trace != nullptr) {
+    const int cta = blockIdx.y * gridDim.x + blockIdx.x;
+    unsigned long long g, c;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g));
+    asm volatile("mov.u64 %0, %%clock64;" : "=l"(c));
+    trace[(cta * 16 + slot) * 2] = g;
+    trace[(cta * 16 + slot) * 2 + 1] = c;
+  }
+}
+
+__device__ __forceinline__ float4 lds128(const uint8_t* p) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(smem_u32(p)));
+  return v;
+}
+__device__ __forceinline__ void sts128(uint8_t* p, float a, float b, float c, float d) {
+  asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(smem_u32(p)), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+__device__ __forceinline__ void sts128u(uint8_t* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(smem_u32(p)), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+
+// GELU with erf from Abramowitz-Stegun 7.1.26 (|erf error| <= 1.5e-7): 2 MUFU + ~12 FMA-pipe instructions instead
+// of erff's ~40.  Used in bf16 mode only, where the result is rounded to bf16 (2^-9) anyway.
+__device__ __forceinline__ float gelu_fast(float x) {
+  const float y = fabsf(x) * 0.70710678118654752440f;
+  float t;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, y, 1.0f)));
+  float pl = fmaf(t, 1.061405429f, -1.453152027f);
+  pl = fmaf(pl, t, 1.421413741f);
+  pl = fmaf(pl, t, -0.284496736f);
+  pl = fmaf(pl, t, 0.254829592f);
+  pl *= t;
+  float e;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(-y * y * 1.4426950408889634f));
+  const float erf_abs = fmaf(-pl, e, 1.0f);
+  const float h = 0.5f * x;
+  return fmaf(fabsf(h), erf_abs, h);          // 0.5 x (1 + sign(x) erf|.|) = h + |h| erf_abs
+}
+
+// GELU of two values in f16x2 arithmetic, tanh form with the hardware tanh.approx.f16x2, packed as bf16x2.  Used only
+// where the result is stored as ONE bf16 segment (fc1 of the bf16 mode): |tanh form - erf form| <= 4.8e-4 and the
+// f16 arithmetic (2^-11) are both below the bf16 quantum (2^-9) of the stored value; rms over N(0,1) inputs 3e-4 vs
+// 1.1e-3 for the bf16 rounding itself.  ~10 instructions + 1 MUFU per PAIR instead of ~16 + 2 MUFU per element.
+__device__ __forceinline__ uint32_t gelu_pair_bf16x2(float a, float b) {
+  const __half2 x = __floats2half2_rn(a, b);
+  const __half2 u = __hmul2(x, x);
+  const __half2 inner = __hfma2(__float2half2_rn(0.0356774081f), u, __float2half2_rn(0.7978845608f));
+  const __half2 w = __hmul2(x, inner);
+  uint32_t wi = *reinterpret_cast<const uint32_t*>(&w), ti;
+  asm("tanh.approx.f16x2 %0, %1;" : "=r"(ti) : "r"(wi));
+  const __half2 t = *reinterpret_cast<const __half2*>(&ti);
+  const __half2 h = __hmul2(x, __float2half2_rn(0.5f));
+  const float2 o = __half22float2(__hfma2(h, t, h));
+  return pack_bf16x2(o.x, o.y);
+}
+
+
+// persistent kernel (avd_gemm_ps.cu); bn = 0 lets it choose the tile width
+int launch_gemm_ps(const avd_gemm_args& g, GemmParams p, int nseg, int force_bn, cudaStream_t s);
+int ps_debug_read(unsigned int* out8);
+
+}  // namespace avd

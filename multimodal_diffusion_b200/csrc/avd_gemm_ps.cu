@@ -1,0 +1,516 @@
+// avd_gemm_ps.cu -- K4, persistent form: out = epilogue( A[M,K] x W[N,K]^T ) with the epilogue of one output tile
+// running UNDER the mainloop of the next one.
+//
+// Why: with d_model = 512 every output element carries only 2K = 1024 flops, so at tensor-core speed an SM must
+// retire ~8 epilogue outputs per cycle; in the one-tile-per-CTA kernel (avd_gemm.cu) the tensor pipe idles during the
+// whole epilogue (40 % of the kernel at mvp shapes, and the reason the large-M sweep plateaus near 30 % of peak).
+//
+// One CTA per SM, 384 threads, tiles t = blockIdx.x, +gridDim.x, ... (n fastest):
+//   warps 0,1   TMA producers: k-block iteration `it` (counted over ALL tiles of this CTA) belongs to producer it & 1
+//               and ring slot it % stages (stages is even, so a slot never changes hands: the ring is two interleaved
+//               rings, one per {producer h, issuer h}); two issuing threads because one thread sustains only ~one
+//               {wait, expect_tx, 2 x TMA} round per 300 cycles (tools/tma_probe.cu).  The weight boxes of the first
+//               ring pass are issued before griddepcontrol.wait (they do not depend on the previous kernel).
+//   warps 2,3   MMA issuers (warp 2 also owns TMEM): tcgen05.mma.cta_group::1.kind::f16 M=128 N=BN K=16, 4 per k-block.
+//               Issuer h takes the iterations it = h (mod 2) and accumulates its share of a tile into its own TMEM
+//               tile [buffer tile & 1][h] (4 x BN columns in all; the epilogue adds the two halves): one thread needs
+//               ~400 cycles per {mbarrier wait, 4 MMAs, commit} round whatever N is (tools/mma_probe.cu: any
+//               dependent wait between MMA batches costs ~180 cycles), more than the 220-256 cycles the pipe needs for
+//               the round at N = 64/128, so two threads alternate.  tcgen05.commit frees the ring slot and, after an
+//               issuer's last k-block of the tile, counts one arrival on acc_full.
+//   warps 4..11 epilogue: warp w reads TMEM lanes 32 (w % 4) .. +31; the two warps of a quadrant take the even / odd
+//               32-column chunks.  v = acc * rinv(row) + bias (+ residual) [gelu] -> fp32 and/or bf16 segments,
+//               staged through per-warp 128B-swizzled smem boxes and stored with 16-byte coalesced accesses; row
+//               partial sums of squares for the next RMSNorm.  After its last tcgen05.ld of a tile the warp arrives on
+//               acc_empty, which lets the issuer start tile + 2 in that buffer.
+// Residual tiles come in per 32 x 32 chunk through TMA into the warp's fp32 staging box (the result overwrites it).
+#include "avd_gemm_common.cuh"
+
+#include <cstdlib>
+
+namespace avd {
+
+constexpr int PS_THREADS = 384;
+constexpr int PS_MAX_STAGES = 8;
+constexpr int PS_TAIL_BYTES = 2048;          // barriers + TMEM slot (512 B), ssq exchange (1 KB)
+constexpr int PS_SMEM_MAX = 232448 - 1024;   // 227 KB opt-in limit minus alignment slack
+
+// Debug records of barrier waits that timed out: {tag, cta, thread, counter, parity, N, K, grid * 1000 + BN}.
+// The record lives in mapped pinned host memory so that it survives a device-side trap.
+static unsigned int* g_ps_dbg_host = nullptr;
+static unsigned int* g_ps_dbg_dev = nullptr;
+
+struct PsPlan {
+  unsigned int* dbg;               // host-visible record of barrier waits that timed out (avd_debug_gemm_timeout)
+  int stages;
+  int tiles_n, tiles_total;
+  int f32_off, bf_off, tail_off;   // byte offsets of the staging regions and the barrier block
+};
+
+template <int BN>
+__global__ void __launch_bounds__(PS_THREADS, 1) gemm_ps_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                                const __grid_constant__ CUtensorMap tmB,
+                                                                const __grid_constant__ CUtensorMap tmR,
+                                                                const GemmParams p, const PsPlan plan) {
+  constexpr int A_BYTES = GEMM_BM * GEMM_BK * 2;
+  constexpr int B_BYTES = BN * GEMM_BK * 2;
+  constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  constexpr uint32_t TMEM_COLS = BN <= 32 ? 128 : BN <= 64 ? 256 : 512;   // 2 buffers x 2 issuers x BN columns
+  static_assert(BN <= 128, "four accumulators of BN columns must fit the 512 TMEM columns");
+  constexpr int NCH = BN / 32;
+  extern __shared__ __align__(1024) uint8_t ps_smem[];
+  uint8_t* smem = ps_smem;
+  if ((smem_u32(smem) & 1023u) != 0) __trap();   // 128B-swizzle tiles need 1024-B aligned bases
+  uint8_t* tail = smem + plan.tail_off;
+  uint64_t* full = reinterpret_cast<uint64_t*>(tail);
+  uint64_t* empty = full + PS_MAX_STAGES;
+  uint64_t* acc_full = empty + PS_MAX_STAGES;
+  uint64_t* acc_empty = acc_full + 2;
+  uint64_t* res_bar = acc_empty + 2;           // one per epilogue warp
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_bar + 8);
+  float* ssq_x = reinterpret_cast<float*>(tail + 512);   // [128] partial row sums handed from warp w+4 to warp w
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  // Bounded barrier wait: a protocol bug leaves a record in host-visible memory and traps instead of hanging the GPU.
+  auto wait = [&](uint64_t* bar, uint32_t parity, unsigned tag, int counter) {
+    uint32_t spins = 0;
+    while (!mbar_try_wait(bar, parity)) {
+      if (++spins > (1u << 26)) {
+        unsigned int* dbg = plan.dbg;      // [0] = number of records, then 8-word records from dbg[8]
+        const unsigned idx = atomicAdd_system(&dbg[0], 1u);
+        if (idx < 30) {
+          unsigned int* r = dbg + 8 + idx * 8;
+          r[0] = tag; r[1] = blockIdx.x; r[2] = threadIdx.x; r[3] = (unsigned)counter;
+          r[4] = parity; r[5] = (unsigned)p.N; r[6] = (unsigned)p.K; r[7] = gridDim.x * 1000u + (unsigned)BN;
+          __threadfence_system();
+        }
+        __nanosleep(4000000);              // let the other stuck waiters record themselves before the trap
+        __trap();
+      }
+    }
+  };
+  const int stages = plan.stages;
+  const int G = gridDim.x;
+  const int kblocks = p.K / GEMM_BK;
+  const int ipt = kblocks * p.n_pairs;                                   // k-block iterations per tile
+  const int my_tiles = (plan.tiles_total - (int)blockIdx.x + G - 1) / G;
+  const int total_it = my_tiles * ipt;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    if (p.has_resid) tma_prefetch_desc(&tmR);
+    for (int i = 0; i < 2 * PS_MAX_STAGES; ++i) mbar_init(&full[i], 1);       // full, empty
+    for (int i = 0; i < 2; ++i) mbar_init(&acc_full[i], 2);                   // one arrival per issuer
+    for (int i = 0; i < 2; ++i) mbar_init(&acc_empty[i], 8);                  // one arrival per epilogue warp
+    for (int i = 0; i < 8; ++i) mbar_init(&res_bar[i], 1);
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc<TMEM_COLS>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_launch_dependents();
+
+  if (warp < 2) {
+    // ------------------------------------------------------------------ TMA producer h: iterations it = h (mod 2)
+    if (lane == 0) {
+      const int h = warp;
+      const uint32_t pairs = p.pairs;
+      const int tiles_n = plan.tiles_n;
+      auto coords = [&](int it, int& m0, int& n0, int& kc, uint32_t& pr) {
+        const int tl = it / ipt;
+        const int j = it - tl * ipt;
+        const int pi = j / kblocks;
+        const int t = (int)blockIdx.x + tl * G;
+        const int mt = t / tiles_n;
+        m0 = mt * GEMM_BM;
+        n0 = (t - mt * tiles_n) * BN;
+        kc = (j - pi * kblocks) * GEMM_BK;
+        pr = (pairs >> (4 * pi)) & 15u;
+      };
+      const int pre_end = total_it < stages ? total_it : stages;
+      int m0, n0, kc;
+      uint32_t pr;
+      for (int it = h; it < pre_end; it += 2) {          // weights of the first ring pass run ahead of the dependency
+        coords(it, m0, n0, kc, pr);
+        mbar_expect_tx(&full[it], STAGE_BYTES);
+        tma_load_3d(smem + it * STAGE_BYTES + A_BYTES, &tmB, &full[it], kc, n0, pr & 3);
+      }
+      pdl_wait();
+      for (int it = h; it < pre_end; it += 2) {
+        coords(it, m0, n0, kc, pr);
+        tma_load_3d(smem + it * STAGE_BYTES, &tmA, &full[it], kc, m0, (pr >> 2) & 3);
+      }
+      int it = pre_end + (((pre_end & 1) != h) ? 1 : 0);
+      for (; it < total_it; it += 2) {
+        const int pass = it / stages;
+        const int slot = it - pass * stages;
+        coords(it, m0, n0, kc, pr);
+        wait(&empty[slot], (pass & 1) ^ 1, 1, it);
+        uint8_t* dst = smem + slot * STAGE_BYTES;
+        mbar_expect_tx(&full[slot], STAGE_BYTES);
+        tma_load_3d(dst, &tmA, &full[slot], kc, m0, (pr >> 2) & 3);
+        tma_load_3d(dst + A_BYTES, &tmB, &full[slot], kc, n0, pr & 3);
+      }
+    }
+  } else if (warp < 4) {
+    // ------------------------------------------------------------------ MMA issuer h: iterations j = h (mod 2) of each tile
+    if (lane == 0) {
+      const int h = warp - 2;
+      const uint32_t idesc = make_idesc_bf16(GEMM_BM, BN, 0, 0);
+      const uint32_t desc_hi = smem_desc_hi_sw128(1024);
+      const uint32_t a_lo0 = smem_desc_lo_sw128(smem_u32(smem), 16);
+      for (int i = 0; i < my_tiles; ++i) {
+        const int b = i & 1;
+        const int base = i * ipt;                          // global iteration of this tile's first k-block
+        const int j0 = (h ^ base) & 1;                     // this issuer's first k-block iteration of the tile
+        const int pass0 = (base + j0) / stages;
+        int slot = base + j0 - pass0 * stages;             // ring position of global iteration base + j
+        uint32_t ph = pass0 & 1;
+        wait(&acc_empty[b], ((i >> 1) & 1) ^ 1, 2, i);     // the epilogue has drained this buffer (tile i - 2)
+        tc_fence_after();
+        const uint32_t acc = tmem_base + (b * 2 + h) * BN;
+        for (int j = j0; j < ipt; j += 2) {
+          wait(&full[slot], ph, 3, base + j);
+          tc_fence_after();
+          const uint32_t a_lo = a_lo0 + slot * (STAGE_BYTES >> 4);
+          const uint32_t b_lo = a_lo + (A_BYTES >> 4);
+#pragma unroll
+          for (int k = 0; k < GEMM_BK / 16; ++k)           // +32 bytes (2 x 16-byte units) per 16-wide k step
+            umma_bf16_lh(acc, a_lo + 2 * k, b_lo + 2 * k, desc_hi, idesc, (j > j0 || k > 0) ? 1u : 0u);
+          umma_commit(&empty[slot]);                       // slot reusable once these MMAs have read it
+          slot += 2;
+          if (slot >= stages) { slot -= stages; ph ^= 1; }
+        }
+        if (j0 < ipt) umma_commit(&acc_full[b]);           // this issuer's half of tile i is complete
+        else mbar_arrive(&acc_full[b]);                    // a single k-block: nothing for this issuer
+      }
+    }
+  } else if (warp >= 4) {
+    // ------------------------------------------------------------------ epilogue
+    const int e = warp - 4;
+    const int quad = warp & 3;                 // TMEM lane quadrant this warp may access
+    const int hf = e >> 2;                     // even / odd 32-column chunks
+    const int act = p.act, out_nseg = p.out_nseg;
+    const bool has_resid = p.has_resid != 0, has_f32 = p.out_f32 != nullptr;
+    float* const ssq_out = p.ssq_out;
+    const bool paired = (out_nseg > 0 || ssq_out != nullptr);   // the two warps of a quadrant share 64-column units
+    const bool packed_gelu = (act == 2 && out_nseg == 1 && !has_f32 && ssq_out == nullptr);
+    uint8_t* const fbox = smem + plan.f32_off + e * GEMM_BOX;                   // this warp's fp32 staging box
+    uint8_t* const bf_quad = smem + plan.bf_off + quad * out_nseg * GEMM_BOX;   // [out_nseg] boxes of the pair
+    const int sw = lane & 7;
+    const int rr = lane >> 3, cc = lane & 7;
+    const int tiles_n = plan.tiles_n;
+    uint32_t res_ph = 0;
+    pdl_wait();                                // ssq_in / residual / output buffers belong to earlier kernels until now
+
+    auto issue_resid = [&](int m0, int n0, int ch) {
+      __syncwarp();
+      if (lane == 0) {
+        fence_async_smem();                    // earlier generic reads of the box are ordered before the async write
+        mbar_expect_tx(&res_bar[e], GEMM_BOX);
+        tma_load_3d(fbox, &tmR, &res_bar[e], n0 + ch * 32, m0 + quad * 32, 0);
+      }
+    };
+
+    for (int i = 0; i < my_tiles; ++i) {
+      const int t = (int)blockIdx.x + i * G;
+      const int mt = t / tiles_n;
+      const int m0 = mt * GEMM_BM, n0 = (t - mt * tiles_n) * BN;
+      const int b = i & 1;
+      const int row = m0 + quad * 32 + lane;
+      const bool live = row < p.M;
+      if (has_resid && hf < NCH) issue_resid(m0, n0, hf);
+      float rinv = 1.0f;
+      if (p.ssq_in != nullptr && live) {
+        float ss = 0.0f;
+        for (int q = 0; q < p.ssq_parts; ++q) ss += p.ssq_in[(int64_t)row * p.ssq_parts + q];
+        rinv = 1.0f / (sqrtf(ss) * p.inv_sqrt_rms_dim + p.rms_eps);
+      }
+      wait(&acc_full[b], (i >> 1) & 1, 4, i);
+      tc_fence_after();
+      const bool two_acc = ipt > 1;          // with a single k-block the tile sits in issuer ((i * ipt) & 1)'s accumulator
+      const uint32_t t_row = tmem_base + (b * 2 + (two_acc ? 0 : ((i * ipt) & 1))) * BN + ((uint32_t)(quad * 32) << 16);
+      uint32_t r[32], r1[32];
+      if (hf < NCH) {
+        tmem_ld_32x32(t_row + hf * 32, r);
+        if (two_acc) tmem_ld_32x32(t_row + BN + hf * 32, r1);
+      } else {                                   // BN = 32: the odd-chunk warps have nothing to read
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&acc_empty[b]);
+      }
+#pragma unroll 1
+      for (int ch = hf; ch < NCH; ch += 2) {
+        float v[32];
+        tmem_ld_wait();
+        if (two_acc) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) + __uint_as_float(r1[j]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+        }
+        if (ch + 2 < NCH) {                    // next chunk's TMEM loads fly while this one is processed
+          tmem_ld_32x32(t_row + (ch + 2) * 32, r);
+          if (two_acc) tmem_ld_32x32(t_row + BN + (ch + 2) * 32, r1);
+        } else {
+          tc_fence_before();                   // this warp's last read of the accumulator: hand the buffer back
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&acc_empty[b]);
+        }
+        if (p.bias != nullptr) {
+          const float4* bp = reinterpret_cast<const float4*>(p.bias + n0 + ch * 32);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 b4 = __ldg(bp + j);
+            v[4 * j] = fmaf(v[4 * j], rinv, b4.x); v[4 * j + 1] = fmaf(v[4 * j + 1], rinv, b4.y);
+            v[4 * j + 2] = fmaf(v[4 * j + 2], rinv, b4.z); v[4 * j + 3] = fmaf(v[4 * j + 3], rinv, b4.w);
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] *= rinv;
+        }
+        uint8_t* frow = fbox + lane * 128;
+        if (has_resid) {
+          wait(&res_bar[e], res_ph, 5, i);
+          res_ph ^= 1;
+#pragma unroll
+          for (int c = 0; c < 8; ++c) {
+            const float4 x4 = lds128(frow + ((c ^ sw) << 4));
+            v[4 * c] += x4.x; v[4 * c + 1] += x4.y; v[4 * c + 2] += x4.z; v[4 * c + 3] += x4.w;
+          }
+        }
+        if (act == 1) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
+        } else if (act == 2 && !packed_gelu) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = gelu_fast(v[j]);
+        }
+        if (has_f32) {
+#pragma unroll
+          for (int c = 0; c < 8; ++c) sts128(frow + ((c ^ sw) << 4), v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
+        }
+        float ssq_acc = 0.0f;
+        if (ssq_out != nullptr) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) ssq_acc = fmaf(v[j], v[j], ssq_acc);
+          if (hf == 1) ssq_x[quad * 32 + lane] = ssq_acc;
+        }
+        const int c0 = (ch & 1) * 4;
+        if (packed_gelu) {
+          uint8_t* brow = bf_quad + lane * 128;
+#pragma unroll
+          for (int c = 0; c < 4; ++c)
+            sts128u(brow + (((c0 + c) ^ sw) << 4), gelu_pair_bf16x2(v[8 * c], v[8 * c + 1]),
+                    gelu_pair_bf16x2(v[8 * c + 2], v[8 * c + 3]), gelu_pair_bf16x2(v[8 * c + 4], v[8 * c + 5]),
+                    gelu_pair_bf16x2(v[8 * c + 6], v[8 * c + 7]));
+        } else if (out_nseg == 1) {
+          uint8_t* brow = bf_quad + lane * 128;
+#pragma unroll
+          for (int c = 0; c < 4; ++c)
+            sts128u(brow + (((c0 + c) ^ sw) << 4), pack_bf16x2(v[8 * c], v[8 * c + 1]), pack_bf16x2(v[8 * c + 2], v[8 * c + 3]),
+                    pack_bf16x2(v[8 * c + 4], v[8 * c + 5]), pack_bf16x2(v[8 * c + 6], v[8 * c + 7]));
+        } else if (out_nseg > 1) {
+          for (int sg = 0; sg < out_nseg; ++sg) {
+            uint32_t w[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const __nv_bfloat16 h0 = __float2bfloat16_rn(v[2 * j]);
+              const __nv_bfloat16 h1 = __float2bfloat16_rn(v[2 * j + 1]);
+              v[2 * j] -= __bfloat162float(h0);
+              v[2 * j + 1] -= __bfloat162float(h1);
+              w[j] = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
+            }
+            uint8_t* brow = bf_quad + sg * GEMM_BOX + lane * 128;
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+              sts128u(brow + (((c0 + c) ^ sw) << 4), w[4 * c], w[4 * c + 1], w[4 * c + 2], w[4 * c + 3]);
+          }
+        }
+        if (paired) named_bar_sync(2 + quad, 64); else __syncwarp();
+        if (hf == 0 && ssq_out != nullptr && live)
+          ssq_out[(int64_t)row * (p.N / 64) + ((n0 + ch * 32) >> 6)] = ssq_acc + ssq_x[quad * 32 + lane];
+        // staged boxes -> global, coalesced: 8 lanes cover one 128-byte row, one warp instruction covers 4 rows
+        if (has_f32) {
+          float* gp = p.out_f32 + (int64_t)(m0 + quad * 32) * p.N + n0 + ch * 32 + cc * 4;
+#pragma unroll
+          for (int it = 0; it < 8; ++it) {
+            const int rw = it * 4 + rr;
+            const float4 x4 = lds128(fbox + rw * 128 + ((cc ^ (rw & 7)) << 4));
+            if (m0 + quad * 32 + rw < p.M) *reinterpret_cast<float4*>(gp + (int64_t)rw * p.N) = x4;
+          }
+        }
+        if (out_nseg > 0) {      // the pair's 64-column bf16 box: this warp stores rows [16 hf, 16 hf + 16)
+          for (int sg = 0; sg < out_nseg; ++sg) {
+            const uint8_t* box = bf_quad + sg * GEMM_BOX;
+            __nv_bfloat16* gp = p.out_bf16 + (int64_t)sg * p.M * p.N + (int64_t)(m0 + quad * 32) * p.N + n0 + (ch >> 1) * 64 + cc * 8;
+#pragma unroll
+            for (int it = 0; it < 4; ++it) {
+              const int rw = hf * 16 + it * 4 + rr;
+              const float4 x4 = lds128(box + rw * 128 + ((cc ^ (rw & 7)) << 4));
+              if (m0 + quad * 32 + rw < p.M) *reinterpret_cast<float4*>(gp + (int64_t)rw * p.N) = x4;
+            }
+          }
+        }
+        if (has_resid && ch + 2 < NCH) issue_resid(m0, n0, ch + 2);
+        // the pair's shared boxes (bf16, ssq_x) are rewritten by the next chunk / tile: both warps must be done reading
+        if (paired) named_bar_sync(2 + quad, 64); else __syncwarp();
+      }
+    }
+  }
+
+  __syncwarp();   // lanes 1..31 of the role warps wait here for their lane 0
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc<TMEM_COLS>(tmem_base);
+  }
+}
+
+static int ps_env_int(const char* name, int dflt) {
+  const char* v = std::getenv(name);
+  return v ? std::atoi(v) : dflt;
+}
+
+int ps_debug_read(unsigned int* out8) {       // host copy of the timeout record; clears it
+  for (int i = 0; i < 256; ++i) {
+    out8[i] = g_ps_dbg_host != nullptr ? g_ps_dbg_host[i] : 0u;
+    if (g_ps_dbg_host != nullptr) g_ps_dbg_host[i] = 0u;
+  }
+  return 0;
+}
+
+static int ps_num_sms() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+      n = 148;
+  }
+  return n;
+}
+
+template <int BN>
+static int launch_ps_bn(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmR, const GemmParams& p,
+                        const PsPlan& plan, int smem_bytes, int grid, cudaStream_t s) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    AVD_CUDA(cudaFuncSetAttribute(gemm_ps_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, PS_SMEM_MAX + 1024));
+    attr_set = true;
+  }
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(PS_THREADS);
+  cfg.dynamicSmemBytes = smem_bytes;
+  cfg.stream = s;
+  cudaLaunchAttribute attrs[1];
+  int na = 0;
+  if (pdl_enabled()) {
+    attrs[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attrs[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  cfg.attrs = attrs;
+  cfg.numAttrs = na;
+  if (kind_skipped(KIND_GEMM)) return 0;
+  LaunchScope ls(KIND_GEMM, s);
+  AVD_CUDA(cudaLaunchKernelEx(&cfg, gemm_ps_kernel<BN>, tmA, tmB, tmR, p, plan));
+  return 0;
+}
+
+// smem plan of a tile width; returns false when fewer than 2 ring stages fit
+static bool ps_plan(const avd_gemm_args& g, int out_nseg, int bn, PsPlan* plan, int* smem_bytes) {
+  const int stage = (GEMM_BM + bn) * GEMM_BK * 2;
+  const int f32_bytes = (g.out_f32 != nullptr || g.resid != nullptr) ? 8 * GEMM_BOX : 0;
+  const int bf_bytes = out_nseg * 4 * GEMM_BOX;
+  const int fixed = f32_bytes + bf_bytes + PS_TAIL_BYTES;
+  int stages = (PS_SMEM_MAX - fixed) / stage;
+  if (stages > PS_MAX_STAGES) stages = PS_MAX_STAGES;
+  static const int cap = ps_env_int("AVD_PS_MAX_STAGES", PS_MAX_STAGES);
+  if (stages > cap) stages = cap;
+  stages &= ~1;   // even: global iteration `it` then always lands in a ring slot of its own parity, so every slot (and
+                  // its two barriers) has ONE producer and ONE issuer, who see its uses in order (parity waits are
+                  // only sound when the waiter is never two phases away from the barrier)
+  if (stages < 2) return false;
+  plan->stages = stages;
+  plan->f32_off = stages * stage;
+  plan->bf_off = plan->f32_off + f32_bytes;
+  plan->tail_off = plan->bf_off + bf_bytes;
+  *smem_bytes = plan->tail_off + PS_TAIL_BYTES;
+  return true;
+}
+
+int launch_gemm_ps(const avd_gemm_args& g, GemmParams p, int nseg, int force_bn, cudaStream_t s) {
+  const int out_nseg = p.out_nseg;
+  const int mt = (g.M + GEMM_BM - 1) / GEMM_BM;
+  const int sms = ps_num_sms();
+  const int ipt = (g.K / GEMM_BK) * p.n_pairs;
+  // Tile width by a cycle model of the persistent schedule (constants from the phase traces of tools/kbench.py):
+  //   mainloop of a tile  = k-block iterations x max(TMA ingest at ~110 B/cycle/SM, 4 MMAs of max(BN/2, 48) cycles)
+  //   epilogue of a tile  = (BN / 64) chunk rounds of the 8 epilogue warps
+  //   time = first mainloop + (waves - 1) x max(mainloop, epilogue) + last epilogue
+  static const int c_epi = ps_env_int("AVD_PS_EPI_CYCLES", 1500);
+  auto usable = [&](int bn) {
+    if (g.N % bn != 0) return false;
+    if ((g.ssq_out != nullptr || g.out_bf16 != nullptr) && bn < 64) return false;
+    PsPlan pl; int sm;
+    return ps_plan(g, out_nseg, bn, &pl, &sm) && pl.stages >= 3;
+  };
+  auto cost = [&](int bn) {
+    const int64_t tiles = (int64_t)mt * (g.N / bn);
+    const int64_t waves = (tiles + sms - 1) / sms;
+    const double ingest = (GEMM_BM + bn) * 128.0 / 110.0;
+    const double mma = 4.0 * (bn / 2 > 52 ? bn / 2 : 52);
+    const double ml = ipt * (ingest > mma ? ingest : mma);
+    double epi = (bn >= 64 ? bn / 64 : 1) * (double)c_epi;
+    if (g.act != 0) epi *= 1.3;
+    if (out_nseg > 1) epi *= 1.0 + 0.3 * (out_nseg - 1);
+    return ml + (waves - 1) * (ml > epi ? ml : epi) + epi;
+  };
+  const int cands[3] = {128, 64, 32};
+  int bn = 0;
+  if (force_bn > 0 && usable(force_bn)) bn = force_bn;
+  if (bn == 0) {
+    double best = 0.0;
+    for (int i = 0; i < 3; ++i)
+      if (usable(cands[i])) {
+        const double c = cost(cands[i]);
+        if (bn == 0 || c < best) { bn = cands[i]; best = c; }
+      }
+  }
+  AVD_REQUIRE(bn > 0, "no tile shape fits this combination of outputs: use fewer outputs per GEMM");
+
+  PsPlan plan{};
+  int smem_bytes = 0;
+  ps_plan(g, out_nseg, bn, &plan, &smem_bytes);
+  if (g_ps_dbg_host == nullptr) {
+    AVD_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&g_ps_dbg_host), 1024, cudaHostAllocMapped));
+    for (int i = 0; i < 256; ++i) g_ps_dbg_host[i] = 0u;
+    AVD_CUDA(cudaHostGetDevicePointer(reinterpret_cast<void**>(&g_ps_dbg_dev), g_ps_dbg_host, 0));
+  }
+  plan.dbg = g_ps_dbg_dev;
+  plan.tiles_n = g.N / bn;
+  plan.tiles_total = mt * plan.tiles_n;
+  const int grid = plan.tiles_total < sms ? plan.tiles_total : sms;
+  p.trace = nullptr;
+
+  CUtensorMap tmA, tmB, tmR;
+  AVD_TRY(get_tensor_map_3d(g.A, 2, g.K, g.M, nseg, (uint64_t)g.K * 2, (uint64_t)g.M * g.K * 2, GEMM_BK, GEMM_BM, &tmA));
+  AVD_TRY(get_tensor_map_3d(g.W, 2, g.K, g.N, nseg, (uint64_t)g.K * 2, (uint64_t)g.N * g.K * 2, GEMM_BK, bn, &tmB));
+  tmR = tmA;   // placeholder when unused (never dereferenced)
+  if (g.resid != nullptr)
+    AVD_TRY(get_tensor_map_3d(g.resid, 4, g.N, g.M, 1, (uint64_t)g.N * 4, (uint64_t)g.M * g.N * 4, 32, 32, &tmR));
+  switch (bn) {
+    case 128: return launch_ps_bn<128>(tmA, tmB, tmR, p, plan, smem_bytes, grid, s);
+    case 64: return launch_ps_bn<64>(tmA, tmB, tmR, p, plan, smem_bytes, grid, s);
+    default: return launch_ps_bn<32>(tmA, tmB, tmR, p, plan, smem_bytes, grid, s);
+  }
+}
+
+}  // namespace avd

@@ -16,7 +16,7 @@ __global__ void __launch_bounds__(128) probe(Args a) {
   uint64_t* bar = reinterpret_cast<uint64_t*>(smem + 96 * 1024);
   uint32_t* slot = reinterpret_cast<uint32_t*>(bar + 8);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  if (threadIdx.x == 0) { mbar_init(&bar[0], 1); mbar_init(&bar[1], 1); mbar_init(&bar[2], 1); mbar_init(&bar[3], 1); fence_barrier_init(); mbar_arrive(&bar[2]); }
+  if (threadIdx.x == 0) { mbar_init(&bar[0], 1); mbar_init(&bar[1], 1); mbar_init(&bar[2], 1); mbar_init(&bar[3], 1); bar[6] = 0; fence_barrier_init(); mbar_arrive(&bar[2]); }
   if (warp == 0) tmem_alloc<256>(slot);
   // zero the operand tiles so the MMAs are numerically harmless
   for (int i = threadIdx.x; i < 96 * 1024 / 16; i += blockDim.x) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
@@ -37,6 +37,16 @@ __global__ void __launch_bounds__(128) probe(Args a) {
     for (int i = 0; i < a.n_mma; i += KB) {
       const uint32_t so = ((i / KB) & 1) * 3072;
       if (MODE & 2) { mbar_wait(&bar[2], 0); }          // an already-completed barrier (phase 0 done)
+      if (MODE & 8) {                                    // same with the non-suspending mbarrier.test_wait
+        uint32_t ok = 0;
+        while (!ok)
+          asm volatile("{\n\t.reg .pred P1;\n\tmbarrier.test_wait.parity.shared::cta.b64 P1, [%1], %2;\n\tselp.b32 %0, 1, 0, P1;\n\t}\n"
+                       : "=r"(ok) : "r"(smem_u32(&bar[2])), "r"(0) : "memory");
+      }
+      if (MODE & 16) {                                   // a plain shared-memory load + dependent branch instead
+        volatile uint32_t* f = reinterpret_cast<volatile uint32_t*>(bar + 6);
+        while (*f != 0) {}
+      }
       if (MODE & 4) tc_fence_after();
 #pragma unroll
       for (int k = 0; k < KB; ++k)
@@ -79,6 +89,7 @@ int main() {
   for (int N : {64, 128}) {
     run<0, 4>(N, 148, d); run<1, 4>(N, 148, d); run<2, 4>(N, 148, d); run<4, 4>(N, 148, d); run<7, 4>(N, 148, d);
     run<7, 8>(N, 148, d); run<7, 4>(N, 296, d); run<7, 8>(N, 296, d);
+    run<8, 4>(N, 148, d); run<13, 4>(N, 148, d); run<16, 4>(N, 148, d); run<3, 4>(N, 148, d);
   }
   return 0;
 }
