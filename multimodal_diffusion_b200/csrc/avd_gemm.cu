@@ -424,11 +424,6 @@ int launch_gemm(const avd_gemm_args& g, cudaStream_t s) {
   p.out_bf16 = static_cast<__nv_bfloat16*>(g.out_bf16);
   p.out_nseg = out_nseg;
   p.ssq_out = g.ssq_out;
-  // Persistent kernel with the epilogue under the next tile's mainloop (avd_gemm_ps.cu) unless AVD_GEMM_V=3 asks for
-  // the one-tile-per-CTA kernel below.
-  static const int gemm_v = env_int("AVD_GEMM_V", 3);
-  if (gemm_v != 3) return launch_gemm_ps(g, p, nseg, env_int("AVD_GEMM_BN", 0), s);
-
   // Tile width: the widest BN that divides N, still gives >= ~0.8 waves of CTAs on 148 SMs, and whose epilogue staging
   // (fp32 tile unless it overwrites the residual tile, plus out_nseg bf16 tiles) fits the reused pipeline smem.
   // A residual tile needs dedicated smem, which only the narrow tiles can spare.
@@ -452,6 +447,16 @@ int launch_gemm(const avd_gemm_args& g, cudaStream_t s) {
     if (usable(cands[i])) bn = cands[i];
   for (int i = 0; i < 5 && bn == 0; ++i)
     if (usable(cands[i])) bn = cands[i];
+  // Two kernels.  While the tiles chosen above fit one wave of CTAs the one-tile-per-CTA kernel of this file wins (wide
+  // tiles, every warp on the epilogue); beyond one wave the persistent kernel (avd_gemm_ps.cu) hides the epilogue under
+  // the next tile's mainloop (+45 % at M = 32768, tools/kbench.py --M).  AVD_GEMM_V = 3 / 4 forces one of them.
+  static const int gemm_v = env_int("AVD_GEMM_V", 0);
+  {
+    int dev = 0, sms = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const bool persistent = gemm_v == 4 || (gemm_v != 3 && (bn == 0 || (int64_t)mt * (g.N / bn) > sms));
+    if (persistent) return launch_gemm_ps(g, p, nseg, force_bn, s);
+  }
   AVD_REQUIRE(bn > 0, "no tile shape fits this combination of outputs: use fewer outputs per GEMM");
 
   const int64_t n_ctas = (int64_t)(g.N / bn) * mt;

@@ -66,8 +66,8 @@ __global__ void __launch_bounds__(PS_THREADS, 1) gemm_ps_kernel(const __grid_con
   uint64_t* empty = full + PS_MAX_STAGES;
   uint64_t* acc_full = empty + PS_MAX_STAGES;
   uint64_t* acc_empty = acc_full + 2;
-  uint64_t* res_bar = acc_empty + 2;           // one per epilogue warp
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_bar + 8);
+  uint64_t* res_bar = acc_empty + 2;           // two per epilogue warp (double-buffered residual boxes)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_bar + 16);
   float* ssq_x = reinterpret_cast<float*>(tail + 512);   // [128] partial row sums handed from warp w+4 to warp w
 
   const int warp = threadIdx.x >> 5;
@@ -97,6 +97,8 @@ __global__ void __launch_bounds__(PS_THREADS, 1) gemm_ps_kernel(const __grid_con
   const int my_tiles = (plan.tiles_total - (int)blockIdx.x + G - 1) / G;
   const int total_it = my_tiles * ipt;
 
+  unsigned long long* const trace = p.trace;
+  if (threadIdx.x == 0) trace_mark(trace, 0);
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
@@ -104,7 +106,7 @@ __global__ void __launch_bounds__(PS_THREADS, 1) gemm_ps_kernel(const __grid_con
     for (int i = 0; i < 2 * PS_MAX_STAGES; ++i) mbar_init(&full[i], 1);       // full, empty
     for (int i = 0; i < 2; ++i) mbar_init(&acc_full[i], 2);                   // one arrival per issuer
     for (int i = 0; i < 2; ++i) mbar_init(&acc_empty[i], 8);                  // one arrival per epilogue warp
-    for (int i = 0; i < 8; ++i) mbar_init(&res_bar[i], 1);
+    for (int i = 0; i < 16; ++i) mbar_init(&res_bar[i], 1);
     fence_barrier_init();
   }
   if (warp == 2) tmem_alloc<TMEM_COLS>(tmem_slot);
@@ -113,6 +115,7 @@ __global__ void __launch_bounds__(PS_THREADS, 1) gemm_ps_kernel(const __grid_con
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   pdl_launch_dependents();
+  if (threadIdx.x == 0) trace_mark(trace, 1);
 
   if (warp < 2) {
     // ------------------------------------------------------------------ TMA producer h: iterations it = h (mod 2)
@@ -120,41 +123,52 @@ __global__ void __launch_bounds__(PS_THREADS, 1) gemm_ps_kernel(const __grid_con
       const int h = warp;
       const uint32_t pairs = p.pairs;
       const int tiles_n = plan.tiles_n;
-      auto coords = [&](int it, int& m0, int& n0, int& kc, uint32_t& pr) {
-        const int tl = it / ipt;
-        const int j = it - tl * ipt;
-        const int pi = j / kblocks;
-        const int t = (int)blockIdx.x + tl * G;
+      const int n_pairs = p.n_pairs;
+      // cursor over this CTA's k-block iterations (tile, operand-segment pair, k-block), advanced without divisions
+      struct Cur { int tl, pi, kb, m0, n0; };
+      auto tile_origin = [&](Cur& c) {
+        const int t = (int)blockIdx.x + c.tl * G;
         const int mt = t / tiles_n;
-        m0 = mt * GEMM_BM;
-        n0 = (t - mt * tiles_n) * BN;
-        kc = (j - pi * kblocks) * GEMM_BK;
-        pr = (pairs >> (4 * pi)) & 15u;
+        c.m0 = mt * GEMM_BM;
+        c.n0 = (t - mt * tiles_n) * BN;
       };
+      auto advance = [&](Cur& c) {
+        if (++c.kb == kblocks) {
+          c.kb = 0;
+          if (++c.pi == n_pairs) { c.pi = 0; ++c.tl; tile_origin(c); }
+        }
+      };
+      Cur cb{0, 0, 0, 0, 0};
+      tile_origin(cb);
+      if (h == 1) advance(cb);
+      Cur ca = cb;
       const int pre_end = total_it < stages ? total_it : stages;
-      int m0, n0, kc;
-      uint32_t pr;
       for (int it = h; it < pre_end; it += 2) {          // weights of the first ring pass run ahead of the dependency
-        coords(it, m0, n0, kc, pr);
         mbar_expect_tx(&full[it], STAGE_BYTES);
-        tma_load_3d(smem + it * STAGE_BYTES + A_BYTES, &tmB, &full[it], kc, n0, pr & 3);
+        tma_load_3d(smem + it * STAGE_BYTES + A_BYTES, &tmB, &full[it], cb.kb * GEMM_BK, cb.n0, (pairs >> (4 * cb.pi)) & 3);
+        advance(cb); advance(cb);
       }
       pdl_wait();
-      for (int it = h; it < pre_end; it += 2) {
-        coords(it, m0, n0, kc, pr);
-        tma_load_3d(smem + it * STAGE_BYTES, &tmA, &full[it], kc, m0, (pr >> 2) & 3);
+      int it = h;
+      for (; it < pre_end; it += 2) {
+        tma_load_3d(smem + it * STAGE_BYTES, &tmA, &full[it], ca.kb * GEMM_BK, ca.m0, (pairs >> (4 * ca.pi + 2)) & 3);
+        advance(ca); advance(ca);
       }
-      int it = pre_end + (((pre_end & 1) != h) ? 1 : 0);
+      // steady state: `it` continues from the first ring pass; stages is even, so slot parity == h
+      int slot = it % stages;
+      uint32_t ph = ((it / stages) & 1) ^ 1;             // parity of the consumption this refill waits for
       for (; it < total_it; it += 2) {
-        const int pass = it / stages;
-        const int slot = it - pass * stages;
-        coords(it, m0, n0, kc, pr);
-        wait(&empty[slot], (pass & 1) ^ 1, 1, it);
+        wait(&empty[slot], ph, 1, it);
+        const uint32_t pr = pairs >> (4 * ca.pi);
         uint8_t* dst = smem + slot * STAGE_BYTES;
         mbar_expect_tx(&full[slot], STAGE_BYTES);
-        tma_load_3d(dst, &tmA, &full[slot], kc, m0, (pr >> 2) & 3);
-        tma_load_3d(dst + A_BYTES, &tmB, &full[slot], kc, n0, pr & 3);
+        tma_load_3d(dst, &tmA, &full[slot], ca.kb * GEMM_BK, ca.m0, (pr >> 2) & 3);
+        tma_load_3d(dst + A_BYTES, &tmB, &full[slot], ca.kb * GEMM_BK, ca.n0, pr & 3);
+        advance(ca); advance(ca);
+        slot += 2;
+        if (slot >= stages) { slot -= stages; ph ^= 1; }
       }
+      if (h == 0) trace_mark(trace, 10);
     }
   } else if (warp < 4) {
     // ------------------------------------------------------------------ MMA issuer h: iterations j = h (mod 2) of each tile
@@ -176,6 +190,7 @@ __global__ void __launch_bounds__(PS_THREADS, 1) gemm_ps_kernel(const __grid_con
         for (int j = j0; j < ipt; j += 2) {
           wait(&full[slot], ph, 3, base + j);
           tc_fence_after();
+          if (h == 0 && i == 0 && j == j0) trace_mark(trace, 2);
           const uint32_t a_lo = a_lo0 + slot * (STAGE_BYTES >> 4);
           const uint32_t b_lo = a_lo + (A_BYTES >> 4);
 #pragma unroll
@@ -187,6 +202,7 @@ __global__ void __launch_bounds__(PS_THREADS, 1) gemm_ps_kernel(const __grid_con
         }
         if (j0 < ipt) umma_commit(&acc_full[b]);           // this issuer's half of tile i is complete
         else mbar_arrive(&acc_full[b]);                    // a single k-block: nothing for this issuer
+        if (h == 0 && i == my_tiles - 1) trace_mark(trace, 3);
       }
     }
   } else if (warp >= 4) {
@@ -199,22 +215,34 @@ __global__ void __launch_bounds__(PS_THREADS, 1) gemm_ps_kernel(const __grid_con
     float* const ssq_out = p.ssq_out;
     const bool paired = (out_nseg > 0 || ssq_out != nullptr);   // the two warps of a quadrant share 64-column units
     const bool packed_gelu = (act == 2 && out_nseg == 1 && !has_f32 && ssq_out == nullptr);
-    uint8_t* const fbox = smem + plan.f32_off + e * GEMM_BOX;                   // this warp's fp32 staging box
+    uint8_t* const fbox0 = smem + plan.f32_off + e * 2 * GEMM_BOX;              // this warp's fp32 staging boxes: the
+    // residual chunk q of the warp's chunk sequence lands in box q & 1 (prefetched while chunk q - 1 is processed)
+    // and the fp32 result overwrites it in place; without a residual only box 0 is used
+    constexpr int CPW = NCH >= 2 ? NCH / 2 : 1;                                 // chunks per warp per tile
     uint8_t* const bf_quad = smem + plan.bf_off + quad * out_nseg * GEMM_BOX;   // [out_nseg] boxes of the pair
     const int sw = lane & 7;
     const int rr = lane >> 3, cc = lane & 7;
     const int tiles_n = plan.tiles_n;
-    uint32_t res_ph = 0;
+    const bool warp_has_chunks = hf < NCH;
+    const int n_chunks = warp_has_chunks ? my_tiles * CPW : 0;          // length of this warp's chunk sequence
     pdl_wait();                                // ssq_in / residual / output buffers belong to earlier kernels until now
 
-    auto issue_resid = [&](int m0, int n0, int ch) {
+    auto issue_resid = [&](int q) {            // residual box of chunk q of this warp's sequence
+      if (!has_resid || q >= n_chunks) return;
+      const int ti = q / CPW;
+      const int ch = hf + 2 * (q - ti * CPW);
+      const int t = (int)blockIdx.x + ti * G;
+      const int mt = t / tiles_n;
       __syncwarp();
       if (lane == 0) {
         fence_async_smem();                    // earlier generic reads of the box are ordered before the async write
-        mbar_expect_tx(&res_bar[e], GEMM_BOX);
-        tma_load_3d(fbox, &tmR, &res_bar[e], n0 + ch * 32, m0 + quad * 32, 0);
+        uint64_t* bar = &res_bar[e * 2 + (q & 1)];
+        mbar_expect_tx(bar, GEMM_BOX);
+        tma_load_3d(fbox0 + (q & 1) * GEMM_BOX, &tmR, bar, (t - mt * tiles_n) * BN + ch * 32, mt * GEMM_BM + quad * 32, 0);
       }
     };
+    issue_resid(0);
+    int q = 0;
 
     for (int i = 0; i < my_tiles; ++i) {
       const int t = (int)blockIdx.x + i * G;
@@ -223,15 +251,29 @@ __global__ void __launch_bounds__(PS_THREADS, 1) gemm_ps_kernel(const __grid_con
       const int b = i & 1;
       const int row = m0 + quad * 32 + lane;
       const bool live = row < p.M;
-      if (has_resid && hf < NCH) issue_resid(m0, n0, hf);
+      // lane l keeps bias[n0 + 32 ch + l] of this warp's (at most two) chunks; broadcast by shuffle in the chunk loop
+      float bias_a = 0.0f, bias_b = 0.0f;
+      if (p.bias != nullptr) {
+        if (hf < NCH) bias_a = __ldg(p.bias + n0 + hf * 32 + lane);
+        if (hf + 2 < NCH) bias_b = __ldg(p.bias + n0 + (hf + 2) * 32 + lane);
+      }
       float rinv = 1.0f;
       if (p.ssq_in != nullptr && live) {
         float ss = 0.0f;
         for (int q = 0; q < p.ssq_parts; ++q) ss += p.ssq_in[(int64_t)row * p.ssq_parts + q];
         rinv = 1.0f / (sqrtf(ss) * p.inv_sqrt_rms_dim + p.rms_eps);
       }
-      wait(&acc_full[b], (i >> 1) & 1, 4, i);
+      if (warp == 4 && lane == 0 && i == 0) trace_mark(trace, 4);
+      if (lane == 0) {                           // one polling lane per warp, backing off: the issuing threads on the
+        uint32_t spins = 0;                      // same SM sub-partition need the issue slots during the mainloop
+        while (!mbar_try_wait(&acc_full[b], (i >> 1) & 1)) {
+          __nanosleep(64);
+          if (++spins > (1u << 24)) wait(&acc_full[b], (i >> 1) & 1, 4, i);
+        }
+      }
+      __syncwarp();
       tc_fence_after();
+      if (warp == 4 && lane == 0) trace_mark(trace, i == 0 ? 5 : 8);
       const bool two_acc = ipt > 1;          // with a single k-block the tile sits in issuer ((i * ipt) & 1)'s accumulator
       const uint32_t t_row = tmem_base + (b * 2 + (two_acc ? 0 : ((i * ipt) & 1))) * BN + ((uint32_t)(quad * 32) << 16);
       uint32_t r[32], r1[32];
@@ -262,22 +304,16 @@ __global__ void __launch_bounds__(PS_THREADS, 1) gemm_ps_kernel(const __grid_con
           __syncwarp();
           if (lane == 0) mbar_arrive(&acc_empty[b]);
         }
-        if (p.bias != nullptr) {
-          const float4* bp = reinterpret_cast<const float4*>(p.bias + n0 + ch * 32);
+        {
+          const float bl = (ch == hf) ? bias_a : bias_b;
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const float4 b4 = __ldg(bp + j);
-            v[4 * j] = fmaf(v[4 * j], rinv, b4.x); v[4 * j + 1] = fmaf(v[4 * j + 1], rinv, b4.y);
-            v[4 * j + 2] = fmaf(v[4 * j + 2], rinv, b4.z); v[4 * j + 3] = fmaf(v[4 * j + 3], rinv, b4.w);
-          }
-        } else {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] *= rinv;
+          for (int j = 0; j < 32; ++j) v[j] = fmaf(v[j], rinv, __shfl_sync(0xffffffffu, bl, j));
         }
+        uint8_t* const fbox = fbox0 + (has_resid ? (q & 1) * GEMM_BOX : 0);
         uint8_t* frow = fbox + lane * 128;
         if (has_resid) {
-          wait(&res_bar[e], res_ph, 5, i);
-          res_ph ^= 1;
+          issue_resid(q + 1);                  // the other box: its last readers (chunk q - 1's stores) are done
+          wait(&res_bar[e * 2 + (q & 1)], (q >> 1) & 1, 5, i);
 #pragma unroll
           for (int c = 0; c < 8; ++c) {
             const float4 x4 = lds128(frow + ((c ^ sw) << 4));
@@ -357,10 +393,11 @@ __global__ void __launch_bounds__(PS_THREADS, 1) gemm_ps_kernel(const __grid_con
             }
           }
         }
-        if (has_resid && ch + 2 < NCH) issue_resid(m0, n0, ch + 2);
+        ++q;
         // the pair's shared boxes (bf16, ssq_x) are rewritten by the next chunk / tile: both warps must be done reading
         if (paired) named_bar_sync(2 + quad, 64); else __syncwarp();
       }
+      if (warp == 4 && lane == 0) trace_mark(trace, i == 0 ? 6 : 9);
     }
   }
 
@@ -371,6 +408,7 @@ __global__ void __launch_bounds__(PS_THREADS, 1) gemm_ps_kernel(const __grid_con
     tc_fence_after();
     tmem_dealloc<TMEM_COLS>(tmem_base);
   }
+  if (threadIdx.x == 0) trace_mark(trace, 7);
 }
 
 static int ps_env_int(const char* name, int dflt) {
@@ -427,7 +465,7 @@ static int launch_ps_bn(const CUtensorMap& tmA, const CUtensorMap& tmB, const CU
 // smem plan of a tile width; returns false when fewer than 2 ring stages fit
 static bool ps_plan(const avd_gemm_args& g, int out_nseg, int bn, PsPlan* plan, int* smem_bytes) {
   const int stage = (GEMM_BM + bn) * GEMM_BK * 2;
-  const int f32_bytes = (g.out_f32 != nullptr || g.resid != nullptr) ? 8 * GEMM_BOX : 0;
+  const int f32_bytes = (g.out_f32 != nullptr || g.resid != nullptr) ? 16 * GEMM_BOX : 0;
   const int bf_bytes = out_nseg * 4 * GEMM_BOX;
   const int fixed = f32_bytes + bf_bytes + PS_TAIL_BYTES;
   int stages = (PS_SMEM_MAX - fixed) / stage;
@@ -465,7 +503,7 @@ int launch_gemm_ps(const avd_gemm_args& g, GemmParams p, int nseg, int force_bn,
   auto cost = [&](int bn) {
     const int64_t tiles = (int64_t)mt * (g.N / bn);
     const int64_t waves = (tiles + sms - 1) / sms;
-    const double ingest = (GEMM_BM + bn) * 128.0 / 110.0;
+    const double ingest = 2.0 * (GEMM_BM + bn);   // smem port (128 B/cycle) carries the TMA writes AND the MMA operand reads
     const double mma = 4.0 * (bn / 2 > 52 ? bn / 2 : 52);
     const double ml = ipt * (ingest > mma ? ingest : mma);
     double epi = (bn >= 64 ? bn / 64 : 1) * (double)c_epi;
@@ -498,7 +536,10 @@ int launch_gemm_ps(const avd_gemm_args& g, GemmParams p, int nseg, int force_bn,
   plan.tiles_n = g.N / bn;
   plan.tiles_total = mt * plan.tiles_n;
   const int grid = plan.tiles_total < sms ? plan.tiles_total : sms;
-  p.trace = nullptr;
+  {
+    const int64_t n_ctas = grid;
+    p.trace = (g_dbg_trace != nullptr && n_ctas * 32 <= g_dbg_trace_slots) ? g_dbg_trace : nullptr;
+  }
 
   CUtensorMap tmA, tmB, tmR;
   AVD_TRY(get_tensor_map_3d(g.A, 2, g.K, g.M, nseg, (uint64_t)g.K * 2, (uint64_t)g.M * g.K * 2, GEMM_BK, GEMM_BM, &tmA));

@@ -49,6 +49,7 @@ def main() -> None:
     ap.add_argument("--reps", type=int, default=40)
     ap.add_argument("--trace", action="store_true")
     ap.add_argument("--M", type=int, default=2128)
+    ap.add_argument("--once", action="store_true", help="run one block's kernels 3 times eagerly and exit (ncu target)")
     args = ap.parse_args()
     lib = _lib.load()
     dev = torch.device("cuda:0")
@@ -124,6 +125,11 @@ def main() -> None:
              (f"fc1   {M}x2048x512", g_fc1, 2.0 * M * 2048 * 512),
              (f"fc2   {M}x512x2048", g_fc2, 2.0 * M * 512 * 2048),
              (f"head  {Mt}x512x512 bf16x3", g_head, 2.0 * Mt * 512 * 512)]
+    if args.once:
+        for _ in range(3):
+            g_qkv(); g_att(); g_o(); g_fc1(); g_fc2()
+        torch.cuda.synchronize()
+        return
     for name, fn, flops in cases:
         us = time_graph(fn, args.reps)
         tf = flops / us * 1e-6 if flops else 0.0
@@ -152,7 +158,9 @@ def main() -> None:
         for i, nm in enumerate(an):
             print(f"   {nm:26s} cycles: median {ck[:, i].median():8.0f} max {ck[:, i].max():8.0f} | ns since kernel start: "
                   f"median {gt[:, i].median():8.0f} max {gt[:, i].max():8.0f}")
-        for name, fn in (("qkv", g_qkv), ("oproj", g_o), ("fc2", g_fc2), ("head", g_head)):
+        import os
+        v4 = os.environ.get("AVD_GEMM_V", "3") != "3"
+        for name, fn in (("qkv", g_qkv), ("oproj", g_o), ("fc1", g_fc1), ("fc2", g_fc2), ("head", g_head)):
             buf = torch.zeros(32 * 512, device=dev, dtype=torch.int64)
             fn()
             torch.cuda.synchronize()
@@ -169,6 +177,10 @@ def main() -> None:
             names = ["start", "setup done", "-", "pipe0: last mma issued", "epi: rinv+resid ready",
                      "epi: acc ready", "epi: stores read", "exit", "ch0: tmem ld done", "ch0: math done",
                      "ch0: sts done", "ch0: fence+syncwarp", "ch0: tma store issued", "last chunk issued"]
+            if v4:
+                names = ["start", "setup done", "iss0: first stage landed", "iss0: last mma issued",
+                         "epi: tile0 rinv/resid issued", "epi: tile0 acc ready", "epi: tile0 done", "exit",
+                         "epi: last acc ready", "epi: last tile done", "prod0: last load issued"]
             print(f"--- trace {name}: {t.shape[0]} CTAs; kernel span {gt[:, 7].max():.0f} ns "
                   f"(CTA start spread {gt[:, 0].max():.0f} ns)")
             for i, nm in enumerate(names):
