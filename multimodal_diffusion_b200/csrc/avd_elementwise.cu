@@ -40,7 +40,8 @@ struct TubeDims {
   int B, C, T, H, W, t, h, w, Tt, Hh, Ww;
 };
 
-__device__ __forceinline__ int64_t tube_latent_index_from_token(const TubeDims& d, int64_t o) {
+template <typename I>
+__device__ __forceinline__ I tube_latent_index_from_token(const TubeDims& d, I o) {
   int dw = o % d.w; o /= d.w;
   int dh = o % d.h; o /= d.h;
   int dt = o % d.t; o /= d.t;
@@ -48,35 +49,57 @@ __device__ __forceinline__ int64_t tube_latent_index_from_token(const TubeDims& 
   int wk = o % d.Ww; o /= d.Ww;
   int hj = o % d.Hh; o /= d.Hh;
   int ti = o % d.Tt; o /= d.Tt;
-  int64_t b = o;
-  return (((b * d.C + c) * d.T + (ti * d.t + dt)) * d.H + (hj * d.h + dh)) * (int64_t)d.W + (wk * d.w + dw);
+  I b = o;
+  return (((b * d.C + c) * d.T + (ti * d.t + dt)) * d.H + (hj * d.h + dh)) * (I)d.W + (wk * d.w + dw);
 }
 
-__device__ __forceinline__ int64_t tube_token_index_from_latent(const TubeDims& d, int64_t i) {
+template <typename I>
+__device__ __forceinline__ I tube_token_index_from_latent(const TubeDims& d, I i) {
   int x = i % d.W; i /= d.W;
   int y = i % d.H; i /= d.H;
   int tt = i % d.T; i /= d.T;
   int c = i % d.C;  i /= d.C;
-  int64_t b = i;
+  I b = i;
   int wk = x / d.w, dw = x % d.w;
   int hj = y / d.h, dh = y % d.h;
   int ti = tt / d.t, dt = tt % d.t;
-  return ((((((b * d.Tt + ti) * d.Hh + hj) * d.Ww + wk) * d.C + c) * d.t + dt) * d.h + dh) * (int64_t)d.w + dw;
+  return ((((((b * d.Tt + ti) * d.Hh + hj) * d.Ww + wk) * d.C + c) * d.t + dt) * d.h + dh) * (I)d.w + dw;
+}
+
+template <int VEC> struct VecOf { using type = float; };
+template <> struct VecOf<2> { using type = float2; };
+template <> struct VecOf<4> { using type = float4; };
+constexpr int EW_UNROLL = 4;   // independent vectors in flight per thread (HBM latency needs the memory parallelism)
+
+// I = uint32_t when every element index fits 32 bits (the divisions are then 32-bit), int64_t otherwise.
+template <int VEC, bool INVERSE, typename I>
+__global__ void __launch_bounds__(256) tube_kernel(const float* __restrict__ src, float* __restrict__ dst, TubeDims d,
+                                                   int64_t n_vec) {
+  using V = typename VecOf<VEC>::type;
+  const int64_t v0 = (blockIdx.x * (int64_t)EW_UNROLL) * blockDim.x + threadIdx.x;
+  V val[EW_UNROLL];
+#pragma unroll
+  for (int u = 0; u < EW_UNROLL; ++u) {
+    const int64_t v = v0 + (int64_t)u * blockDim.x;
+    if (v < n_vec) {
+      const I o = (I)(v * VEC);      // index in the DESTINATION layout
+      const I sidx = INVERSE ? tube_token_index_from_latent<I>(d, o) : tube_latent_index_from_token<I>(d, o);
+      val[u] = __ldg(reinterpret_cast<const V*>(src + sidx));
+    }
+  }
+#pragma unroll
+  for (int u = 0; u < EW_UNROLL; ++u) {
+    const int64_t v = v0 + (int64_t)u * blockDim.x;
+    if (v < n_vec) *reinterpret_cast<V*>(dst + v * VEC) = val[u];
+  }
 }
 
 template <int VEC, bool INVERSE>
-__global__ void tube_kernel(const float* __restrict__ src, float* __restrict__ dst, TubeDims d, int64_t n_vec) {
-  int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  if (v >= n_vec) return;
-  int64_t o = v * VEC;  // index in the DESTINATION layout
-  int64_t s = INVERSE ? tube_token_index_from_latent(d, o) : tube_latent_index_from_token(d, o);
-  if (VEC == 4) {
-    *reinterpret_cast<float4*>(dst + o) = __ldg(reinterpret_cast<const float4*>(src + s));
-  } else if (VEC == 2) {
-    *reinterpret_cast<float2*>(dst + o) = __ldg(reinterpret_cast<const float2*>(src + s));
-  } else {
-    dst[o] = __ldg(src + s);
-  }
+static void launch_tube_vec(const float* src, float* dst, const TubeDims& d, int64_t total, cudaStream_t s) {
+  const int64_t n_vec = total / VEC;
+  const int blocks = cdiv(n_vec, 256 * EW_UNROLL);
+  if (total < (int64_t(1) << 31)) tube_kernel<VEC, INVERSE, uint32_t><<<blocks, 256, 0, s>>>(src, dst, d, n_vec);
+  else tube_kernel<VEC, INVERSE, int64_t><<<blocks, 256, 0, s>>>(src, dst, d, n_vec);
 }
 
 int launch_tube_patch(const float* src, float* dst, int B, int C, int T, int H, int W, int t, int h, int w, bool inverse,
@@ -87,18 +110,15 @@ int launch_tube_patch(const float* src, float* dst, int B, int C, int T, int H, 
   bool al16 = ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15) == 0;
   bool al8 = ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 7) == 0;
   int vec = (w % 4 == 0 && al16) ? 4 : (w % 2 == 0 && al8) ? 2 : 1;
-  int64_t n_vec = total / vec;
-  int threads = 256;
-  int blocks = cdiv(n_vec, threads);
   LaunchScope ls(KIND_TOKENIZE, s);
   if (!inverse) {
-    if (vec == 4) tube_kernel<4, false><<<blocks, threads, 0, s>>>(src, dst, d, n_vec);
-    else if (vec == 2) tube_kernel<2, false><<<blocks, threads, 0, s>>>(src, dst, d, n_vec);
-    else tube_kernel<1, false><<<blocks, threads, 0, s>>>(src, dst, d, n_vec);
+    if (vec == 4) launch_tube_vec<4, false>(src, dst, d, total, s);
+    else if (vec == 2) launch_tube_vec<2, false>(src, dst, d, total, s);
+    else launch_tube_vec<1, false>(src, dst, d, total, s);
   } else {
-    if (vec == 4) tube_kernel<4, true><<<blocks, threads, 0, s>>>(src, dst, d, n_vec);
-    else if (vec == 2) tube_kernel<2, true><<<blocks, threads, 0, s>>>(src, dst, d, n_vec);
-    else tube_kernel<1, true><<<blocks, threads, 0, s>>>(src, dst, d, n_vec);
+    if (vec == 4) launch_tube_vec<4, true>(src, dst, d, total, s);
+    else if (vec == 2) launch_tube_vec<2, true>(src, dst, d, total, s);
+    else launch_tube_vec<1, true>(src, dst, d, total, s);
   }
   AVD_CUDA(cudaGetLastError());
   return 0;
@@ -108,22 +128,28 @@ int launch_tube_patch(const float* src, float* dst, int B, int C, int T, int H, 
 // K1: audio chunk / un-chunk   (ops.py:17-45, 48-93; sample_clip.py:184-215)
 //   tok[b,n,c*l+j] = z[b,c,n*s+j]
 // =====================================================================================================
-template <int VEC>
-__global__ void chunk1d_kernel(const float* __restrict__ z, float* __restrict__ tok, int C, int L, int N, int length,
-                               int stride, int64_t n_vec) {
-  int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  if (v >= n_vec) return;
-  int64_t o = v * VEC;
-  int64_t r = o;
-  int j = r % length; r /= length;
-  int c = r % C; r /= C;
-  int n = r % N; r /= N;
-  int64_t b = r;
-  int64_t s = (b * C + c) * (int64_t)L + (int64_t)n * stride + j;
-  if (VEC == 2) {
-    *reinterpret_cast<float2*>(tok + o) = __ldg(reinterpret_cast<const float2*>(z + s));
-  } else {
-    tok[o] = __ldg(z + s);
+template <int VEC, typename I>
+__global__ void __launch_bounds__(256) chunk1d_kernel(const float* __restrict__ z, float* __restrict__ tok, int C, int L,
+                                                      int N, int length, int stride, int64_t n_vec) {
+  using V = typename VecOf<VEC>::type;
+  const int64_t v0 = (blockIdx.x * (int64_t)EW_UNROLL) * blockDim.x + threadIdx.x;
+  V val[EW_UNROLL];
+#pragma unroll
+  for (int u = 0; u < EW_UNROLL; ++u) {
+    const int64_t v = v0 + (int64_t)u * blockDim.x;
+    if (v < n_vec) {
+      I r = (I)(v * VEC);
+      int j = r % length; r /= length;
+      int c = r % C; r /= C;
+      int n = r % N; r /= N;
+      const I sidx = (r * C + c) * (I)L + (I)n * stride + j;
+      val[u] = __ldg(reinterpret_cast<const V*>(z + sidx));
+    }
+  }
+#pragma unroll
+  for (int u = 0; u < EW_UNROLL; ++u) {
+    const int64_t v = v0 + (int64_t)u * blockDim.x;
+    if (v < n_vec) *reinterpret_cast<V*>(tok + v * VEC) = val[u];
   }
 }
 
@@ -134,9 +160,13 @@ int launch_chunk1d(const float* z, float* tok, int B, int C, int L, int length, 
   bool al8 = ((reinterpret_cast<uintptr_t>(z) | reinterpret_cast<uintptr_t>(tok)) & 7) == 0;
   int vec = (length % 2 == 0 && stride % 2 == 0 && L % 2 == 0 && al8) ? 2 : 1;
   int64_t n_vec = total / vec;
+  const bool small = (int64_t)B * C * L < (int64_t(1) << 31) && total < (int64_t(1) << 31);
+  const int blocks = cdiv(n_vec, 256 * EW_UNROLL);
   LaunchScope ls(KIND_TOKENIZE, s);
-  if (vec == 2) chunk1d_kernel<2><<<cdiv(n_vec, 256), 256, 0, s>>>(z, tok, C, L, N, length, stride, n_vec);
-  else chunk1d_kernel<1><<<cdiv(n_vec, 256), 256, 0, s>>>(z, tok, C, L, N, length, stride, n_vec);
+  if (vec == 2 && small) chunk1d_kernel<2, uint32_t><<<blocks, 256, 0, s>>>(z, tok, C, L, N, length, stride, n_vec);
+  else if (vec == 2) chunk1d_kernel<2, int64_t><<<blocks, 256, 0, s>>>(z, tok, C, L, N, length, stride, n_vec);
+  else if (small) chunk1d_kernel<1, uint32_t><<<blocks, 256, 0, s>>>(z, tok, C, L, N, length, stride, n_vec);
+  else chunk1d_kernel<1, int64_t><<<blocks, 256, 0, s>>>(z, tok, C, L, N, length, stride, n_vec);
   AVD_CUDA(cudaGetLastError());
   return 0;
 }
@@ -148,6 +178,10 @@ __device__ __forceinline__ float overlap_add_gather(const float* __restrict__ to
                                                     int length, int stride) {
   int L_ola = (N - 1) * stride + length;
   if (p >= L_ola) return 0.0f;
+  if (stride == length) {     // disjoint windows: exactly one term, 0.0f + v then / 1.0f as the reference computes it
+    const int i = p / length;
+    return __fdiv_rn(__fadd_rn(0.0f, __ldg(tok_b + ((int64_t)i * C + c) * length + (p - i * length))), 1.0f);
+  }
   int i_hi = p / stride;
   if (i_hi > N - 1) i_hi = N - 1;
   int i_lo = (p - length + stride) / stride;  // ceil((p-length+1)/stride)
@@ -167,11 +201,44 @@ __global__ void unchunk1d_kernel(const float* __restrict__ tok, float* __restric
                                  int stride, int L_out, int64_t total) {
   int64_t o = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (o >= total) return;
-  int p = o % L_out;
-  int64_t r = o / L_out;
-  int c = r % C;
-  int64_t b = r / C;
+  int p, c;
+  int64_t b;
+  if (total < (int64_t(1) << 31)) {
+    const uint32_t o32 = (uint32_t)o, r = o32 / (uint32_t)L_out;
+    p = (int)(o32 - r * (uint32_t)L_out);
+    b = r / (uint32_t)C;
+    c = (int)(r - (uint32_t)b * (uint32_t)C);
+  } else {
+    p = o % L_out;
+    int64_t r = o / L_out;
+    c = r % C;
+    b = r / C;
+  }
   z[o] = overlap_add_gather(tok + b * (int64_t)N * C * length, c, p, N, C, length, stride);
+}
+
+// Disjoint windows of 4 (the shipped audio tokeniser: chunk 4 / stride 4): one thread moves one window = one 16-byte
+// token read and two 8-byte latent stores (rows of L_out floats are only 8-byte aligned); window index N is the zero
+// padding past the last window.  Same arithmetic as the gather (0.0f + v, / 1.0f), so it stays bit-exact.
+__global__ void __launch_bounds__(256) unchunk1d_w4_kernel(const float* __restrict__ tok, float* __restrict__ z, int C,
+                                                           int N, int L_out, uint32_t total_w) {
+  const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
+  if (w >= total_w) return;
+  const int wpr = (L_out + 3) >> 2;                 // windows per (b, c) row, including the padding ones
+  const uint32_t row = w / wpr;                     // b * C + c
+  const int n = (int)(w - row * wpr);
+  const uint32_t b = row / C;
+  const int c = (int)(row - b * C);
+  float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (n < N) {
+    v = __ldg(reinterpret_cast<const float4*>(tok + (((int64_t)b * N + n) * C + c) * 4));
+    v.x = __fdiv_rn(__fadd_rn(0.0f, v.x), 1.0f); v.y = __fdiv_rn(__fadd_rn(0.0f, v.y), 1.0f);
+    v.z = __fdiv_rn(__fadd_rn(0.0f, v.z), 1.0f); v.w = __fdiv_rn(__fadd_rn(0.0f, v.w), 1.0f);
+  }
+  float* zr = z + (int64_t)row * L_out + 4 * n;
+  const int left = L_out - 4 * n;                   // elements of this window inside the row (L_out is even)
+  *reinterpret_cast<float2*>(zr) = make_float2(v.x, v.y);
+  if (left >= 4) *reinterpret_cast<float2*>(zr + 2) = make_float2(v.z, v.w);
 }
 
 int launch_unchunk1d(const float* tok, float* z, int B, int C, int N, int length, int stride, int L_out,
@@ -179,7 +246,11 @@ int launch_unchunk1d(const float* tok, float* z, int B, int C, int N, int length
   int64_t total = (int64_t)B * C * L_out;
   if (total <= 0) return 0;
   LaunchScope ls(KIND_TOKENIZE, s);
-  unchunk1d_kernel<<<cdiv(total, 256), 256, 0, s>>>(tok, z, C, N, length, stride, L_out, total);
+  const int64_t total_w = (int64_t)B * C * ((L_out + 3) / 4);
+  const bool w4 = length == 4 && stride == 4 && L_out % 2 == 0 && total_w < (int64_t(1) << 31) &&
+                  (reinterpret_cast<uintptr_t>(tok) & 15) == 0 && (reinterpret_cast<uintptr_t>(z) & 7) == 0;
+  if (w4) unchunk1d_w4_kernel<<<cdiv(total_w, 256), 256, 0, s>>>(tok, z, C, N, L_out, (uint32_t)total_w);
+  else unchunk1d_kernel<<<cdiv(total, 256), 256, 0, s>>>(tok, z, C, N, length, stride, L_out, total);
   AVD_CUDA(cudaGetLastError());
   return 0;
 }
@@ -240,16 +311,43 @@ __device__ __forceinline__ float ddim_update(const DdimCoef& c, float x, float e
   return __fadd_rn(r, __fmul_rn(c.sigma, zn));
 }
 
-__global__ void ddim_step_kernel(const float* __restrict__ x_t, const float* __restrict__ eps,
-                                 const float* __restrict__ noise, float* __restrict__ x_prev,
-                                 const int64_t* __restrict__ t_now, const int64_t* __restrict__ t_prev,
-                                 const float* __restrict__ alpha_bar, int64_t per_batch, float eta) {
-  int b = blockIdx.y;
-  DdimCoef c = ddim_coef(alpha_bar, t_now[b], t_prev[b], eta);
-  int64_t base = (int64_t)b * per_batch;
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < per_batch; i += (int64_t)gridDim.x * blockDim.x) {
-    float zn = (noise != nullptr) ? noise[base + i] : 0.0f;
-    x_prev[base + i] = ddim_update(c, x_t[base + i], eps[base + i], zn);
+template <int VEC>
+__global__ void __launch_bounds__(256) ddim_step_kernel(const float* __restrict__ x_t, const float* __restrict__ eps,
+                                                        const float* __restrict__ noise, float* __restrict__ x_prev,
+                                                        const int64_t* __restrict__ t_now, const int64_t* __restrict__ t_prev,
+                                                        const float* __restrict__ alpha_bar, int64_t per_batch, float eta) {
+  const int b = blockIdx.y;
+  const DdimCoef c = ddim_coef(alpha_bar, t_now[b], t_prev[b], eta);
+  const int64_t base = (int64_t)b * per_batch;
+  const int64_t step = (int64_t)gridDim.x * blockDim.x;
+  if (VEC == 4) {
+    const int64_t n4 = per_batch / 4;
+    const float4* x4 = reinterpret_cast<const float4*>(x_t + base);
+    const float4* e4 = reinterpret_cast<const float4*>(eps + base);
+    const float4* z4 = noise != nullptr ? reinterpret_cast<const float4*>(noise + base) : nullptr;
+    float4* o4 = reinterpret_cast<float4*>(x_prev + base);
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n4; i += 2 * step) {
+      const int64_t i1 = i + step;
+      const bool two = i1 < n4;
+      const float4 xa = x4[i], ea = e4[i];
+      const float4 za = z4 != nullptr ? z4[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+      float4 xb = xa, eb = ea, zb = za;
+      if (two) { xb = x4[i1]; eb = e4[i1]; if (z4 != nullptr) zb = z4[i1]; }
+      float4 r;
+      r.x = ddim_update(c, xa.x, ea.x, za.x); r.y = ddim_update(c, xa.y, ea.y, za.y);
+      r.z = ddim_update(c, xa.z, ea.z, za.z); r.w = ddim_update(c, xa.w, ea.w, za.w);
+      o4[i] = r;
+      if (two) {
+        r.x = ddim_update(c, xb.x, eb.x, zb.x); r.y = ddim_update(c, xb.y, eb.y, zb.y);
+        r.z = ddim_update(c, xb.z, eb.z, zb.z); r.w = ddim_update(c, xb.w, eb.w, zb.w);
+        o4[i1] = r;
+      }
+    }
+  } else {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < per_batch; i += step) {
+      float zn = (noise != nullptr) ? noise[base + i] : 0.0f;
+      x_prev[base + i] = ddim_update(c, x_t[base + i], eps[base + i], zn);
+    }
   }
 }
 
@@ -258,9 +356,17 @@ int launch_ddim_step(const float* x_t, const float* eps, const float* noise, flo
                      cudaStream_t s) {
   (void)T_train;
   if (B <= 0 || per_batch <= 0) return 0;
-  dim3 grid(std::min<int64_t>(cdiv(per_batch, 256), 1024), B);
+  const uintptr_t al = reinterpret_cast<uintptr_t>(x_t) | reinterpret_cast<uintptr_t>(eps) |
+                       reinterpret_cast<uintptr_t>(noise) | reinterpret_cast<uintptr_t>(x_prev);
+  const bool v4 = per_batch % 4 == 0 && (al & 15) == 0;
   LaunchScope ls(KIND_CFG_DDIM, s);
-  ddim_step_kernel<<<grid, 256, 0, s>>>(x_t, eps, noise, x_prev, t_now, t_prev, alpha_bar, per_batch, eta);
+  if (v4) {
+    dim3 grid(std::min<int64_t>(cdiv(per_batch / 4, 512), 1024), B);
+    ddim_step_kernel<4><<<grid, 256, 0, s>>>(x_t, eps, noise, x_prev, t_now, t_prev, alpha_bar, per_batch, eta);
+  } else {
+    dim3 grid(std::min<int64_t>(cdiv(per_batch, 256), 1024), B);
+    ddim_step_kernel<1><<<grid, 256, 0, s>>>(x_t, eps, noise, x_prev, t_now, t_prev, alpha_bar, per_batch, eta);
+  }
   AVD_CUDA(cudaGetLastError());
   return 0;
 }
@@ -273,31 +379,54 @@ __device__ __forceinline__ float cfg_mix(float ec, float en, float g) {
   return __fadd_rn(en, __fmul_rn(g, __fsub_rn(ec, en)));
 }
 
-template <int VEC>
-__global__ void cfg_ddim_video_kernel(const float* __restrict__ eps_c, const float* __restrict__ eps_n,
-                                      const float* __restrict__ z_t, float* __restrict__ z_prev, TubeDims d, float g,
-                                      int t_now, int t_prev, const float* __restrict__ alpha_bar, int64_t n_vec,
-                                      int64_t clip_elems, int64_t clip_stride) {
+template <int VEC, typename I>
+__global__ void __launch_bounds__(256) cfg_ddim_video_kernel(const float* __restrict__ eps_c, const float* __restrict__ eps_n,
+                                                             const float* __restrict__ z_t, float* __restrict__ z_prev,
+                                                             TubeDims d, float g, int t_now, int t_prev,
+                                                             const float* __restrict__ alpha_bar, int64_t n_vec,
+                                                             int64_t clip_elems, int64_t clip_stride) {
+  constexpr int U = 2;                              // vectors per thread: 6 independent 16-byte loads in flight
   pdl_wait();
   pdl_launch_dependents();
-  int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  if (v >= n_vec) return;
-  DdimCoef c = ddim_coef(alpha_bar, t_now, t_prev, 0.0f);
-  int64_t i = v * VEC;                              // latent index
-  int64_t o = tube_token_index_from_latent(d, i);   // token index of the same element
-  o += (i / clip_elems) * (clip_stride - clip_elems);   // eps rows of one clip may sit clip_stride elements apart
+  const int64_t v0 = (blockIdx.x * (int64_t)U) * blockDim.x + threadIdx.x;
+  const DdimCoef c = ddim_coef(alpha_bar, t_now, t_prev, 0.0f);
   if (VEC == 4) {
-    float4 ec = __ldg(reinterpret_cast<const float4*>(eps_c + o));
-    float4 en = __ldg(reinterpret_cast<const float4*>(eps_n + o));
-    float4 x = *reinterpret_cast<const float4*>(z_t + i);
-    float4 r;
-    r.x = ddim_update(c, x.x, cfg_mix(ec.x, en.x, g), 0.0f);
-    r.y = ddim_update(c, x.y, cfg_mix(ec.y, en.y, g), 0.0f);
-    r.z = ddim_update(c, x.z, cfg_mix(ec.z, en.z, g), 0.0f);
-    r.w = ddim_update(c, x.w, cfg_mix(ec.w, en.w, g), 0.0f);
-    *reinterpret_cast<float4*>(z_prev + i) = r;
+    float4 ec[U], en[U], x[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t v = v0 + (int64_t)u * blockDim.x;
+      if (v < n_vec) {
+        const I i = (I)(v * 4);                                       // latent index
+        I o = tube_token_index_from_latent<I>(d, i);                  // token index of the same element
+        o += (I)((i / (I)clip_elems) * (I)(clip_stride - clip_elems));  // eps rows of a clip may sit clip_stride apart
+        ec[u] = __ldg(reinterpret_cast<const float4*>(eps_c + o));
+        en[u] = __ldg(reinterpret_cast<const float4*>(eps_n + o));
+        x[u] = *reinterpret_cast<const float4*>(z_t + i);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t v = v0 + (int64_t)u * blockDim.x;
+      if (v < n_vec) {
+        float4 r;
+        r.x = ddim_update(c, x[u].x, cfg_mix(ec[u].x, en[u].x, g), 0.0f);
+        r.y = ddim_update(c, x[u].y, cfg_mix(ec[u].y, en[u].y, g), 0.0f);
+        r.z = ddim_update(c, x[u].z, cfg_mix(ec[u].z, en[u].z, g), 0.0f);
+        r.w = ddim_update(c, x[u].w, cfg_mix(ec[u].w, en[u].w, g), 0.0f);
+        *reinterpret_cast<float4*>(z_prev + v * 4) = r;
+      }
+    }
   } else {
-    z_prev[i] = ddim_update(c, z_t[i], cfg_mix(__ldg(eps_c + o), __ldg(eps_n + o), g), 0.0f);
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t v = v0 + (int64_t)u * blockDim.x;
+      if (v < n_vec) {
+        const I i = (I)v;
+        I o = tube_token_index_from_latent<I>(d, i);
+        o += (I)((i / (I)clip_elems) * (I)(clip_stride - clip_elems));
+        z_prev[i] = ddim_update(c, z_t[i], cfg_mix(__ldg(eps_c + o), __ldg(eps_n + o), g), 0.0f);
+      }
+    }
   }
 }
 
@@ -311,15 +440,28 @@ __global__ void cfg_ddim_audio_kernel(const float* __restrict__ eps_c, const flo
   int64_t o = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (o >= total) return;
   DdimCoef cf = ddim_coef(alpha_bar, t_now, t_prev, 0.0f);
-  int p = o % L;
-  int64_t r = o / L;
-  int c = r % C;
-  int64_t b = r / C;
+  int p, c;
+  int64_t b;
+  if (total < (int64_t(1) << 31)) {
+    const uint32_t o32 = (uint32_t)o, r = o32 / (uint32_t)L;
+    p = (int)(o32 - r * (uint32_t)L);
+    b = r / (uint32_t)C;
+    c = (int)(r - (uint32_t)b * (uint32_t)C);
+  } else {
+    p = o % L;
+    int64_t r = o / L;
+    c = r % C;
+    b = r / C;
+  }
   const float* ec_b = eps_c + b * clip_stride;
   const float* en_b = eps_n + b * clip_stride;
   float e = 0.0f;
   int L_ola = (N - 1) * stride + length;
-  if (p < L_ola) {
+  if (p < L_ola && stride == length) {   // disjoint windows: one term (0.0f + mix, / 1.0f as the reference computes it)
+    const int i = p / length;
+    const int64_t k = ((int64_t)i * C + c) * length + (p - i * length);
+    e = __fdiv_rn(__fadd_rn(0.0f, cfg_mix(__ldg(ec_b + k), __ldg(en_b + k), g)), 1.0f);
+  } else if (p < L_ola) {
     int i_hi = min(p / stride, N - 1);
     int i_lo = (p - length + 1 <= 0) ? 0 : (p - length + stride) / stride;
     float acc = 0.0f, cnt = 0.0f;
@@ -336,6 +478,42 @@ __global__ void cfg_ddim_audio_kernel(const float* __restrict__ eps_c, const flo
   z_prev[o] = ddim_update(cf, z_t[o], e, 0.0f);
 }
 
+// Same for disjoint windows of 4 (see unchunk1d_w4_kernel): per thread two 16-byte eps reads, z_t / z_prev as 8-byte pairs.
+__global__ void __launch_bounds__(256) cfg_ddim_audio_w4_kernel(const float* __restrict__ eps_c, const float* __restrict__ eps_n,
+                                                                const float* __restrict__ z_t, float* __restrict__ z_prev,
+                                                                int C, int L, int N, float g, int t_now, int t_prev,
+                                                                const float* __restrict__ alpha_bar, uint32_t total_w,
+                                                                int64_t clip_stride) {
+  pdl_wait();
+  pdl_launch_dependents();
+  const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
+  if (w >= total_w) return;
+  const DdimCoef cf = ddim_coef(alpha_bar, t_now, t_prev, 0.0f);
+  const int wpr = (L + 3) >> 2;
+  const uint32_t row = w / wpr;
+  const int n = (int)(w - row * wpr);
+  const uint32_t b = row / C;
+  const int c = (int)(row - b * C);
+  float4 e = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (n < N) {
+    const int64_t k = (int64_t)b * clip_stride + ((int64_t)n * C + c) * 4;
+    const float4 ec = __ldg(reinterpret_cast<const float4*>(eps_c + k));
+    const float4 en = __ldg(reinterpret_cast<const float4*>(eps_n + k));
+    e.x = __fdiv_rn(__fadd_rn(0.0f, cfg_mix(ec.x, en.x, g)), 1.0f);
+    e.y = __fdiv_rn(__fadd_rn(0.0f, cfg_mix(ec.y, en.y, g)), 1.0f);
+    e.z = __fdiv_rn(__fadd_rn(0.0f, cfg_mix(ec.z, en.z, g)), 1.0f);
+    e.w = __fdiv_rn(__fadd_rn(0.0f, cfg_mix(ec.w, en.w, g)), 1.0f);
+  }
+  const int64_t o = (int64_t)row * L + 4 * n;
+  const int left = L - 4 * n;
+  const float2 x0 = *reinterpret_cast<const float2*>(z_t + o);
+  *reinterpret_cast<float2*>(z_prev + o) = make_float2(ddim_update(cf, x0.x, e.x, 0.0f), ddim_update(cf, x0.y, e.y, 0.0f));
+  if (left >= 4) {
+    const float2 x1 = *reinterpret_cast<const float2*>(z_t + o + 2);
+    *reinterpret_cast<float2*>(z_prev + o + 2) = make_float2(ddim_update(cf, x1.x, e.z, 0.0f), ddim_update(cf, x1.y, e.w, 0.0f));
+  }
+}
+
 int launch_cfg_untok_ddim(const avd_cfg_ddim_args& a, const float* eps_c, const float* eps_n, const float* z_t,
                           float* z_prev, const float* alpha_bar, int64_t eps_clip_stride, cudaStream_t s) {
   if (a.target == AVD_TARGET_VIDEO) {
@@ -349,13 +527,19 @@ int launch_cfg_untok_ddim(const avd_cfg_ddim_args& a, const float* eps_c, const 
     bool v4 = (a.tw % 4 == 0) && ((al & 15) == 0);
     if (kind_skipped(KIND_CFG_DDIM)) return 0;
     LaunchScope ls(KIND_CFG_DDIM, s);
+    // 32-bit index math when every eps / latent index fits (the index map is a chain of divisions)
+    const bool small = (int64_t)a.B * clip_stride < (int64_t(1) << 31) && total < (int64_t(1) << 31);
     if (v4) {
       int64_t n_vec = total / 4;
-      AVD_CUDA(launch_pdl(cfg_ddim_video_kernel<4>, dim3(cdiv(n_vec, 256)), dim3(256), 0, s, eps_c, eps_n, z_t, z_prev, d,
-                          a.guidance, a.t_now, a.t_prev, alpha_bar, n_vec, clip_elems, clip_stride));
+      if (small)
+        AVD_CUDA(launch_pdl(cfg_ddim_video_kernel<4, uint32_t>, dim3(cdiv(n_vec, 512)), dim3(256), 0, s, eps_c, eps_n, z_t,
+                            z_prev, d, a.guidance, a.t_now, a.t_prev, alpha_bar, n_vec, clip_elems, clip_stride));
+      else
+        AVD_CUDA(launch_pdl(cfg_ddim_video_kernel<4, int64_t>, dim3(cdiv(n_vec, 512)), dim3(256), 0, s, eps_c, eps_n, z_t,
+                            z_prev, d, a.guidance, a.t_now, a.t_prev, alpha_bar, n_vec, clip_elems, clip_stride));
     } else {
-      AVD_CUDA(launch_pdl(cfg_ddim_video_kernel<1>, dim3(cdiv(total, 256)), dim3(256), 0, s, eps_c, eps_n, z_t, z_prev, d,
-                          a.guidance, a.t_now, a.t_prev, alpha_bar, total, clip_elems, clip_stride));
+      AVD_CUDA(launch_pdl(cfg_ddim_video_kernel<1, int64_t>, dim3(cdiv(total, 512)), dim3(256), 0, s, eps_c, eps_n, z_t,
+                          z_prev, d, a.guidance, a.t_now, a.t_prev, alpha_bar, total, clip_elems, clip_stride));
     }
     AVD_CUDA(cudaGetLastError());
   } else {
@@ -364,8 +548,17 @@ int launch_cfg_untok_ddim(const avd_cfg_ddim_args& a, const float* eps_c, const 
     if (kind_skipped(KIND_CFG_DDIM)) return 0;
     LaunchScope ls(KIND_CFG_DDIM, s);
     const int64_t clip_stride = eps_clip_stride > 0 ? eps_clip_stride : (int64_t)a.Nt * a.C * a.length;
-    AVD_CUDA(launch_pdl(cfg_ddim_audio_kernel, dim3(cdiv(total, 256)), dim3(256), 0, s, eps_c, eps_n, z_t, z_prev, a.C, a.L,
-                        a.Nt, a.length, a.stride, a.guidance, a.t_now, a.t_prev, alpha_bar, total, clip_stride));
+    const int64_t total_w = (int64_t)a.B * a.C * ((a.L + 3) / 4);
+    const uintptr_t al16 = reinterpret_cast<uintptr_t>(eps_c) | reinterpret_cast<uintptr_t>(eps_n);
+    const uintptr_t al8 = reinterpret_cast<uintptr_t>(z_t) | reinterpret_cast<uintptr_t>(z_prev);
+    const bool w4 = a.length == 4 && a.stride == 4 && a.L % 2 == 0 && clip_stride % 4 == 0 && (al16 & 15) == 0 &&
+                    (al8 & 7) == 0 && total_w < (int64_t(1) << 31);
+    if (w4)
+      AVD_CUDA(launch_pdl(cfg_ddim_audio_w4_kernel, dim3(cdiv(total_w, 256)), dim3(256), 0, s, eps_c, eps_n, z_t, z_prev, a.C,
+                          a.L, a.Nt, a.guidance, a.t_now, a.t_prev, alpha_bar, (uint32_t)total_w, clip_stride));
+    else
+      AVD_CUDA(launch_pdl(cfg_ddim_audio_kernel, dim3(cdiv(total, 256)), dim3(256), 0, s, eps_c, eps_n, z_t, z_prev, a.C, a.L,
+                          a.Nt, a.length, a.stride, a.guidance, a.t_now, a.t_prev, alpha_bar, total, clip_stride));
     AVD_CUDA(cudaGetLastError());
   }
   return 0;
