@@ -19,6 +19,8 @@
  *
  * Precision modes for the tensor-core GEMMs (bf16 operands, fp32 accumulation in TMEM):
  *   AVD_PREC_BF16   (1)  plain bf16 operands;
+ *   AVD_PREC_F16    (2)  plain fp16 operands (3 more mantissa bits than bf16 at the same tcgen05 kind::f16 rate;
+ *                        operands that may exceed the fp16 range are pre-scaled, see AVD_F16_XSCALE);
  *   AVD_PREC_BF16X3 (3)  operands split hi+lo, 3 partial products  (~16 mantissa bits);
  *   AVD_PREC_FP32   (6)  operands split hi+mid+lo, 6 partial products (~fp32 products).
  * An activation or weight matrix for mode p is stored as avd_nseg(p) bf16 matrices back to back
@@ -34,6 +36,10 @@ extern "C" {
 #endif
 
 #define AVD_PREC_BF16 1
+#define AVD_PREC_F16 2
+/* AVD_PREC_F16 operands that hold the residual stream x (the A operand of the QKV and fc1 GEMMs) carry this fixed
+ * power-of-two scale so that |x| up to 1.6e7 stays finite in fp16; the consuming GEMM undoes it through a_scale. */
+#define AVD_F16_XSCALE 0.00390625f
 #define AVD_PREC_BF16X3 3
 #define AVD_PREC_FP32 6
 
@@ -150,6 +156,9 @@ typedef struct {
   void* out_bf16;           /* bf16 [out_nseg][M][N] or NULL */
   int out_precision;        /* precision of the consumer of out_bf16 (selects the segment count) */
   float* ssq_out;           /* [M][N/64] partial sums of squares of v, or NULL */
+  float a_scale;            /* the accumulator is multiplied by this before everything else (0 means 1): undoes the
+                             * scale carried by a pre-scaled fp16 A operand */
+  float out_scale;          /* the 16-bit output (only it) is multiplied by this before rounding (0 means 1) */
 } avd_gemm_args;
 int avd_gemm(const avd_gemm_args* g, void* stream);
 

@@ -16,6 +16,8 @@ PKG = Path(__file__).resolve().parent
 LIB_PATH = PKG / "libavdiff_b200.so"
 
 AVD_PREC_BF16 = 1
+AVD_PREC_F16 = 2
+AVD_F16_XSCALE = 1.0 / 256.0
 AVD_PREC_BF16X3 = 3
 AVD_PREC_FP32 = 6
 AVD_TARGET_VIDEO = 0
@@ -23,7 +25,7 @@ AVD_TARGET_AUDIO = 1
 AVD_MAX_LAYERS = 64
 AVD_MAX_SHARED = 8
 
-PRECISIONS = {"bf16": AVD_PREC_BF16, "bf16x3": AVD_PREC_BF16X3, "fp32": AVD_PREC_FP32}
+PRECISIONS = {"bf16": AVD_PREC_BF16, "f16": AVD_PREC_F16, "bf16x3": AVD_PREC_BF16X3, "fp32": AVD_PREC_FP32}
 
 
 class AvdLibraryError(RuntimeError):
@@ -51,7 +53,8 @@ class GemmArgs(C.Structure):
     _fields_ = [("M", C.c_int), ("N", C.c_int), ("K", C.c_int), ("precision", C.c_int),
                 ("A", vp), ("W", vp), ("bias", fp), ("ssq_in", fp), ("ssq_parts", C.c_int),
                 ("rms_dim", C.c_int), ("rms_eps", C.c_float), ("resid", fp), ("act", C.c_int),
-                ("out_f32", fp), ("out_bf16", vp), ("out_precision", C.c_int), ("ssq_out", fp)]
+                ("out_f32", fp), ("out_bf16", vp), ("out_precision", C.c_int), ("ssq_out", fp),
+                ("a_scale", C.c_float), ("out_scale", C.c_float)]
 
 
 class BlockWeights(C.Structure):
@@ -191,10 +194,10 @@ def precision_code(p) -> int:
         if p not in PRECISIONS:
             raise ValueError(f"precision must be one of {sorted(PRECISIONS)}, got {p!r}")
         return PRECISIONS[p]
-    if p in (AVD_PREC_BF16, AVD_PREC_BF16X3, AVD_PREC_FP32):
+    if p in (AVD_PREC_BF16, AVD_PREC_F16, AVD_PREC_BF16X3, AVD_PREC_FP32):
         return int(p)
     raise ValueError(f"bad precision {p!r}")
 
 
 def nseg(p) -> int:
-    return {1: 1, 3: 2, 6: 3}[precision_code(p)]
+    return {1: 1, 2: 1, 3: 2, 6: 3}[precision_code(p)]

@@ -8,7 +8,8 @@ through the C ABI (avd_mmdt_blocks: tcgen05 GEMMs with fused RMSNorm-prologue / 
 epilogues + the joint-attention kernel).  Eval / no_grad only: this is the sampling path.
 
 ``precision``: "fp32" (6-pass split-bf16 tensor-core GEMMs + fp32 attention; rel-L2 ~1e-6 vs the reference),
-"bf16x3", or "bf16" (the timed mode).  Default comes from $AVDIFF_B200_PRECISION, else "fp32".
+"bf16x3", "bf16" (the timed mode), or "f16" (fp16 operands at the same tensor-core rate: 3 more mantissa bits; the
+residual-stream operand carries a fixed 2^-8 scale so that it cannot overflow).  Default comes from $AVDIFF_B200_PRECISION, else "fp32".
 """
 from __future__ import annotations
 
@@ -82,10 +83,13 @@ class MHA(nn.Module):
         wo = packing.pack_linear_weight(self.mha.out_proj.weight.detach(), prec)
         xa, _ = packing.rows_prepare(xc.view(M, d), prec)
         S = _lib.nseg(prec)
-        tc = prec == _lib.AVD_PREC_BF16
+        f16 = prec == _lib.AVD_PREC_F16
+        tc = prec == _lib.AVD_PREC_BF16 or f16
         qkv = torch.empty(M, 3 * d, device=xc.device, dtype=torch.bfloat16 if tc else torch.float32)
         packing.gemm(xa, wq, M, 3 * d, d, prec, bias=self.mha.in_proj_bias.detach(),
-                     out_bf16=qkv if tc else None, out_f32=None if tc else qkv, out_precision=_lib.AVD_PREC_BF16)
+                     out_bf16=qkv if tc else None, out_f32=None if tc else qkv,
+                     out_precision=prec if f16 else _lib.AVD_PREC_BF16,
+                     a_scale=1.0 / _lib.AVD_F16_XSCALE if f16 else 0.0)   # rows_prepare pre-scales fp16 operands
         att = torch.empty(S, M, d, device=xc.device, dtype=torch.bfloat16)
         _lib.check(_lib.load().avd_attention(qkv.data_ptr(), 0 if tc else 1, att.data_ptr(), prec, B, N, H, d // H,
                                              _lib.stream_ptr()))
@@ -119,7 +123,8 @@ class MLP(nn.Module):
         xa, _ = packing.rows_prepare(xc.view(M, d), prec)
         S = _lib.nseg(prec)
         u = torch.empty(S, M, hid, device=xc.device, dtype=torch.bfloat16)
-        packing.gemm(xa, w1, M, hid, d, prec, bias=self.fc1.bias.detach(), act=1, out_bf16=u, out_precision=prec)
+        packing.gemm(xa, w1, M, hid, d, prec, bias=self.fc1.bias.detach(), act=1, out_bf16=u, out_precision=prec,
+                     a_scale=1.0 / _lib.AVD_F16_XSCALE if prec == _lib.AVD_PREC_F16 else 0.0)
         y = torch.empty(M, d, device=xc.device, dtype=torch.float32)
         packing.gemm(u, w2, M, d, hid, prec, bias=self.fc2.bias.detach(), out_f32=y)
         return y.view(xc.shape)
@@ -219,7 +224,7 @@ class MMDiT(nn.Module):
         if self.cfg.norm.lower() != "rmsnorm":
             raise NotImplementedError('only norm="rmsnorm" is implemented (SURVEY.md §8 N4)')
         if self.cfg.d_model % self.cfg.n_heads or (self.cfg.d_model // self.cfg.n_heads) != 64 and \
-                _lib.precision_code(self.precision) == _lib.AVD_PREC_BF16:
+                _lib.precision_code(self.precision) in (_lib.AVD_PREC_BF16, _lib.AVD_PREC_F16):
             raise NotImplementedError("the tcgen05 attention kernel is built for head_dim 64")
         return self._runner.run(self, self.state_dict(), self.cfg.n_layers, self.cfg.n_heads, self.precision, x,
                                 apply_final_norm=True)

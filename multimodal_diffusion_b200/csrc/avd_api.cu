@@ -188,6 +188,7 @@ static int sampler_layout(const avd_sampler* s, SamplerLayout* L) {
   L->S_core = nseg_of(s->core.precision);
   L->S_head = nseg_of(s->head.precision);
   AVD_REQUIRE(L->S_core > 0 && L->S_head > 0, "bad precision");
+  AVD_REQUIRE(!is_f16(s->head.precision), "the noise head has no fp16 mode (use bf16, bf16x3 or fp32)");
   L->Nv = (s->T / s->tt) * (s->H / s->th) * (s->W / s->tw);
   L->Na = (s->Fa - s->chunk_len) / s->chunk_stride + 1;
   L->N = L->Nv + L->Na;
@@ -216,7 +217,7 @@ static int sampler_layout(const avd_sampler* s, SamplerLayout* L) {
   L->x = take(M * d * 4);
   L->xa = take((int64_t)L->S_core * M * d * 2);
   L->ssq = take(M * L->parts * 4);
-  L->qkv = take(M * 3 * d * (s->core.precision == AVD_PREC_BF16 ? 2 : 4));
+  L->qkv = take(M * 3 * d * ((s->core.precision == AVD_PREC_BF16 || is_f16(s->core.precision)) ? 2 : 4));
   L->att = take((int64_t)L->S_core * M * d * 2);
   L->hmid = take((int64_t)L->S_core * M * dm * 2);
   // the head runs over ALL rows of the joint sequences (the target rows are picked by the CFG/DDIM kernel): with one
@@ -241,7 +242,10 @@ static int core_blocks(const avd_core_weights* w, const float* x_in, const void*
   AVD_REQUIRE(d % 64 == 0 && w->n_heads > 0 && d % w->n_heads == 0, "bad d_model / n_heads");
   AVD_REQUIRE(w->n_layers > 0 && w->n_layers <= AVD_MAX_LAYERS, "bad layer count");
   const int M = n_seq * N, parts = d / 64, hd = d / w->n_heads;
-  const bool tc_attn = (w->precision == AVD_PREC_BF16);
+  const bool f16 = is_f16(w->precision);
+  const bool tc_attn = (w->precision == AVD_PREC_BF16) || f16;
+  // fp16 mode: the residual-stream operand xa holds x * AVD_F16_XSCALE; its consumers (QKV, fc1) undo the scale
+  const float x_unscale = f16 ? 1.0f / AVD_F16_XSCALE : 0.0f, x_scale = f16 ? AVD_F16_XSCALE : 0.0f;
   for (int l = 0; l < w->n_layers; ++l) {
     const avd_block_weights& b = w->blocks[l];
     const void* a_in = (l == 0) ? xa_in : ws->xa;
@@ -252,23 +256,26 @@ static int core_blocks(const avd_core_weights* w, const float* x_in, const void*
     g.M = M; g.N = 3 * d; g.K = d; g.precision = w->precision;
     g.A = a_in; g.W = b.w_qkv; g.bias = b.b_qkv;
     g.ssq_in = s_in; g.ssq_parts = parts; g.rms_dim = d; g.rms_eps = w->rms_eps;
-    if (tc_attn) { g.out_bf16 = ws->qkv; g.out_precision = AVD_PREC_BF16; }
+    g.a_scale = x_unscale;
+    if (tc_attn) { g.out_bf16 = ws->qkv; g.out_precision = f16 ? AVD_PREC_F16 : AVD_PREC_BF16; }
     else g.out_f32 = static_cast<float*>(ws->qkv);
     AVD_TRY(launch_gemm(g, st));
     // a = softmax(q k^T / sqrt(hd)) v
-    if (tc_attn) AVD_TRY(launch_attention_tc(ws->qkv, ws->att, S, n_seq, N, w->n_heads, hd, st));
+    if (tc_attn) AVD_TRY(launch_attention_tc(ws->qkv, ws->att, S, n_seq, N, w->n_heads, hd, st, f16));
     else AVD_TRY(launch_attention_f32(static_cast<const float*>(ws->qkv), ws->att, S, n_seq, N, w->n_heads, hd, st));
     // x = x + a W_o^T + b_o               (mmdt.py:97)
     g = avd_gemm_args{};
     g.M = M; g.N = d; g.K = d; g.precision = w->precision;
     g.A = ws->att; g.W = b.w_o; g.bias = b.b_o; g.resid = r_in;
     g.out_f32 = ws->x; g.out_bf16 = ws->xa; g.out_precision = w->precision; g.ssq_out = ws->ssq;
+    g.out_scale = x_scale;
     AVD_TRY(launch_gemm(g, st));
     // u = gelu(RMS2(x) W_1^T + b_1)       (mmdt.py:98 -> :78-79)
     g = avd_gemm_args{};
     g.M = M; g.N = w->d_mlp; g.K = d; g.precision = w->precision;
     g.A = ws->xa; g.W = b.w_fc1; g.bias = b.b_fc1;
     g.ssq_in = ws->ssq; g.ssq_parts = parts; g.rms_dim = d; g.rms_eps = w->rms_eps;
+    g.a_scale = x_unscale;
     g.act = tc_attn ? 2 : 1;   // bf16 mode: fast erf (|err| < 2e-7, far below the bf16 rounding of the result)
     g.out_bf16 = ws->hmid; g.out_precision = w->precision;
     AVD_TRY(launch_gemm(g, st));
@@ -277,7 +284,8 @@ static int core_blocks(const avd_core_weights* w, const float* x_in, const void*
     g.M = M; g.N = d; g.K = w->d_mlp; g.precision = w->precision;
     g.A = ws->hmid; g.W = b.w_fc2; g.bias = b.b_fc2; g.resid = ws->x;
     g.out_f32 = ws->x; g.out_bf16 = ws->xa; g.out_precision = w->precision; g.ssq_out = ws->ssq;
-    if (l == w->n_layers - 1 && last_out != nullptr) { g.out_bf16 = last_out; g.out_precision = last_prec; }
+    g.out_scale = x_scale;
+    if (l == w->n_layers - 1 && last_out != nullptr) { g.out_bf16 = last_out; g.out_precision = last_prec; g.out_scale = 0.0f; }
     AVD_TRY(launch_gemm(g, st));
   }
   return 0;
@@ -330,7 +338,7 @@ static BuildXArgs make_build_args(const avd_sampler* s, const SamplerLayout& L, 
   a.row_off = modality == 0 ? L.row_off_v : L.row_off_a;
   a.n_seq_total = L.n_seq;
   a.write_cond = cond; a.write_null = null;
-  a.nseg = L.S_core;
+  a.nseg = nseg_arg(s->core.precision, true);
   a.ssq_parts = L.parts;
   a.M = L.M;
   return a;
@@ -465,7 +473,7 @@ int avd_cfg_untok_ddim(const avd_cfg_ddim_args* a, const float* eps_cond, const 
 // ---- operand preparation
 int avd_pack_weight(const float* W, const float* col_scale, void* out_bf16, int N, int K, int precision, void* stream) {
   AVD_REQUIRE(nseg_of(precision) > 0, "bad precision");
-  return launch_pack_weight(W, col_scale, out_bf16, N, K, nseg_of(precision), AVD_STREAM(stream));
+  return launch_pack_weight(W, col_scale, out_bf16, N, K, nseg_arg(precision, false), AVD_STREAM(stream));
 }
 int avd_transpose_f32(const float* W, float* Wt, int N, int K, void* stream) {
   return launch_transpose(W, Wt, N, K, AVD_STREAM(stream));
@@ -473,7 +481,7 @@ int avd_transpose_f32(const float* W, float* Wt, int N, int K, void* stream) {
 int avd_rows_prepare(const float* x, void* xa_bf16, float* ssq, int M, int d, int precision, void* stream) {
   AVD_REQUIRE(nseg_of(precision) > 0, "bad precision");
   AVD_REQUIRE(d % 64 == 0, "d must be a multiple of 64");
-  return launch_rows_prepare(x, xa_bf16, ssq, M, d, nseg_of(precision), AVD_STREAM(stream));
+  return launch_rows_prepare(x, xa_bf16, ssq, M, d, nseg_arg(precision, true), AVD_STREAM(stream));
 }
 int avd_rmsnorm_rows(const float* x, const float* scale, int n_seq, int N, int row_off, int n_rows, int d, float eps,
                      float* out_f32, void* out_bf16, int precision, void* stream) {
@@ -481,12 +489,13 @@ int avd_rmsnorm_rows(const float* x, const float* scale, int n_seq, int N, int r
   AVD_REQUIRE(row_off >= 0 && n_rows >= 0 && row_off + n_rows <= N, "row window outside the sequence");
   AVD_REQUIRE(out_bf16 == nullptr || nseg_of(precision) > 0, "bad precision");
   return launch_rmsnorm_rows(x, scale, n_seq, N, row_off, n_rows, d, eps, out_f32, out_bf16,
-                             out_bf16 ? nseg_of(precision) : 0, AVD_STREAM(stream));
+                             out_bf16 ? nseg_arg(precision, false) : 0, AVD_STREAM(stream));
 }
 int avd_layernorm_act(const float* y, const float* w, const float* b, int M, int d, float eps, int apply_gelu,
                       float* out_f32, void* out_bf16, int precision, void* stream) {
   AVD_REQUIRE(d % 4 == 0, "d must be a multiple of 4");
   AVD_REQUIRE(out_bf16 == nullptr || nseg_of(precision) > 0, "bad precision");
+  AVD_REQUIRE(out_bf16 == nullptr || !is_f16(precision), "the noise head has no fp16 mode (use bf16, bf16x3 or fp32)");
   return launch_layernorm_act(y, w, b, M, d, eps, apply_gelu, out_f32, out_bf16, out_bf16 ? nseg_of(precision) : 0,
                               AVD_STREAM(stream));
 }
@@ -502,7 +511,8 @@ int avd_attention(const void* qkv, int qkv_is_f32, void* out_bf16, int out_preci
   if (qkv_is_f32)
     return launch_attention_f32(static_cast<const float*>(qkv), out_bf16, nseg_of(out_precision), n_seq, N, n_heads,
                                 head_dim, AVD_STREAM(stream));
-  return launch_attention_tc(qkv, out_bf16, nseg_of(out_precision), n_seq, N, n_heads, head_dim, AVD_STREAM(stream));
+  return launch_attention_tc(qkv, out_bf16, nseg_of(out_precision), n_seq, N, n_heads, head_dim, AVD_STREAM(stream),
+                             is_f16(out_precision));
 }
 
 // ---- core / head

@@ -69,7 +69,7 @@ __device__ __forceinline__ void att_mark(unsigned long long* trace, int slot) {
 // barrier slots
 enum { AB_Q = 0, AB_K = 1, AB_V = 2, AB_S = 3 /*+t*/, AB_P = 5 /*+t*/, AB_O = 7 /*+t*/, AB_R = 9 /*+t*/, AB_COUNT = 11 };
 
-template <bool ONE_BLOCK>   // ONE_BLOCK: N <= 192 keys, the whole score row stays in registers (single softmax pass)
+template <bool ONE_BLOCK, bool F16>   // F16: q/k/v, P and the output are fp16 (AVD_PREC_F16) instead of bf16.  ONE_BLOCK: N <= 192 keys, the whole score row stays in registers (single softmax pass)
 __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ,
                                                                  const __grid_constant__ CUtensorMap tmKV,
                                                                  const AttnParams p) {
@@ -166,7 +166,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
         mbar_wait(&bars[AB_K], ph);
         tc_fence_after();
         if (mark && j == 0) att_mark(trace, 2);
-        const uint32_t idesc_s = make_idesc_bf16(ATT_BQ, kv_n, 0, 0);
+        const uint32_t idesc_s = make_idesc_bf16(ATT_BQ, kv_n, 0, 0, F16);
 #pragma unroll
         for (int k = 0; k < ATT_HD / 16; ++k)
           umma_bf16_lh(tmem_base + t * 256, q_lo + 2 * k, k_lo + 2 * k, hi, idesc_s, k > 0 ? 1u : 0u);
@@ -222,7 +222,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
               p1 = c + 1 < lim ? p1 : 0.0f;
               l0 += p0;
               l1 += p1;
-              w[c >> 1] = pack_bf16x2(p0, p1);
+              w[c >> 1] = F16 ? pack_f16x2(p0, p1) : pack_bf16x2(p0, p1);
             }
             l_blk += l0 + l1;
             uint8_t* atom = sPt + (ch >> 1) * ATT_Q_BYTES + r * 128;
@@ -267,7 +267,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
             p1 = c + 1 < lim ? p1 : 0.0f;
             l0 += p0;
             l1 += p1;
-            w[c >> 1] = pack_bf16x2(p0, p1);
+            w[c >> 1] = F16 ? pack_f16x2(p0, p1) : pack_bf16x2(p0, p1);
           }
           l_blk += l0 + l1;
           uint8_t* atom = sPt + (ch >> 1) * ATT_Q_BYTES + r * 128;
@@ -288,7 +288,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
         mbar_wait(&bars[AB_V], ph);
         if (j > 0) mbar_wait(&bars[AB_R + t], ph ^ 1);     // O_t,j-1 has been read out of TMEM
         tc_fence_after();
-        const uint32_t idesc_o = make_idesc_bf16(ATT_BQ, ATT_HD, 0, 1);   // B = V is MN-major
+        const uint32_t idesc_o = make_idesc_bf16(ATT_BQ, ATT_HD, 0, 1, F16);   // B = V is MN-major
         const int ksteps = kv_n >> 4;
         for (int ks = 0; ks < ksteps; ++ks) {
           const uint32_t pa = p_lo + (((ks >> 2) * ATT_Q_BYTES + (ks & 3) * 32) >> 4);
@@ -342,7 +342,8 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
         uint32_t w[4];
         if (p.out_nseg == 1) {
 #pragma unroll
-          for (int k = 0; k < 4; ++k) w[k] = pack_bf16x2(rem[v4 * 8 + k * 2], rem[v4 * 8 + k * 2 + 1]);
+          for (int k = 0; k < 4; ++k)
+            w[k] = F16 ? pack_f16x2(rem[v4 * 8 + k * 2], rem[v4 * 8 + k * 2 + 1]) : pack_bf16x2(rem[v4 * 8 + k * 2], rem[v4 * 8 + k * 2 + 1]);
         } else {
 #pragma unroll
           for (int k = 0; k < 4; ++k) {
@@ -381,7 +382,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
 }
 
 int launch_attention_tc(const void* qkv_bf16, void* out, int out_nseg, int n_seq, int N, int n_heads, int hd,
-                        cudaStream_t s) {
+                        cudaStream_t s, bool f16) {
   AVD_REQUIRE(hd == ATT_HD, "tcgen05 attention kernel is built for head_dim 64");
   AVD_REQUIRE(n_seq > 0 && N > 0 && n_heads > 0, "empty attention");
   AVD_REQUIRE(out_nseg >= 1 && out_nseg <= 3, "bad output precision");
@@ -394,8 +395,10 @@ int launch_attention_tc(const void* qkv_bf16, void* out, int out_nseg, int n_seq
                             ATT_HD, ATT_BKV, &tmKV));
   static bool attr_set = false;
   if (!attr_set) {
-    AVD_CUDA(cudaFuncSetAttribute(attn_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM));
-    AVD_CUDA(cudaFuncSetAttribute(attn_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM));
+    AVD_CUDA(cudaFuncSetAttribute(attn_tc_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM));
+    AVD_CUDA(cudaFuncSetAttribute(attn_tc_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM));
+    AVD_CUDA(cudaFuncSetAttribute(attn_tc_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM));
+    AVD_CUDA(cudaFuncSetAttribute(attn_tc_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM));
     attr_set = true;
   }
   AttnParams p{};
@@ -423,8 +426,14 @@ int launch_attention_tc(const void* qkv_bf16, void* out, int out_nseg, int n_seq
   cfg.numAttrs = na;
   if (kind_skipped(KIND_ATTN_TC)) return 0;
   LaunchScope ls(KIND_ATTN_TC, s);
-  if (N <= ATT_BKV) AVD_CUDA(cudaLaunchKernelEx(&cfg, attn_tc_kernel<true>, tmQ, tmKV, p));
-  else AVD_CUDA(cudaLaunchKernelEx(&cfg, attn_tc_kernel<false>, tmQ, tmKV, p));
+  AVD_REQUIRE(!f16 || out_nseg == 1, "the fp16 attention output has one segment");
+  if (N <= ATT_BKV) {
+    if (f16) AVD_CUDA(cudaLaunchKernelEx(&cfg, attn_tc_kernel<true, true>, tmQ, tmKV, p));
+    else AVD_CUDA(cudaLaunchKernelEx(&cfg, attn_tc_kernel<true, false>, tmQ, tmKV, p));
+  } else {
+    if (f16) AVD_CUDA(cudaLaunchKernelEx(&cfg, attn_tc_kernel<false, true>, tmQ, tmKV, p));
+    else AVD_CUDA(cudaLaunchKernelEx(&cfg, attn_tc_kernel<false, false>, tmQ, tmKV, p));
+  }
   return 0;
 }
 

@@ -8,6 +8,7 @@
 // FMAs: those kernels are bit-exact against the CPU reference (see tests/test_gpu_elementwise.py).
 #include "avd_internal.h"
 #include "avd_ptx.cuh"
+#include <cuda_fp16.h>
 
 namespace avd {
 
@@ -567,7 +568,14 @@ int launch_cfg_untok_ddim(const avd_cfg_ddim_args& a, const float* eps_c, const 
 // =====================================================================================================
 // operand preparation
 // =====================================================================================================
+// nseg > 0: bf16 segments.  nseg < 0: ONE fp16 value (AVD_PREC_F16), saturated to the finite fp16 range;
+// NSEG_F16_X carries the residual-stream scale AVD_F16_XSCALE, NSEG_F16 is unscaled (weights, normalised values).
 __device__ __forceinline__ void store_split(__nv_bfloat16* base, int64_t seg_stride, int64_t idx, int nseg, float v) {
+  if (nseg < 0) {
+    const float sv = fminf(fmaxf(nseg == NSEG_F16_X ? v * AVD_F16_XSCALE : v, -65504.0f), 65504.0f);
+    reinterpret_cast<__half*>(base)[idx] = __float2half_rn(sv);
+    return;
+  }
   __nv_bfloat16 hi, mid, lo;
   split_bf16(v, hi, mid, lo);
   base[idx] = hi;

@@ -147,7 +147,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
       const int count = (iters - h + 1) >> 1;
       uint64_t* full = bars + h * STAGES;
       uint64_t* empty = bars + (2 + h) * STAGES;
-      const uint32_t idesc = make_idesc_bf16(GEMM_BM, BN, 0, 0);
+      const uint32_t idesc = make_idesc_bf16(GEMM_BM, BN, 0, 0, p.f16_in);
       const uint32_t desc_hi = smem_desc_hi_sw128(1024);
       const uint32_t a_lo0 = smem_desc_lo_sw128(smem_u32(smem + h * STAGES * S::STAGE_BYTES), 16);
       const uint32_t acc = tmem_acc + h * BN;
@@ -182,6 +182,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
     const bool live = row < p.M;
     const bool two_acc = iters > 1;
     const int act = p.act, out_nseg = p.out_nseg;
+    const bool f16_out = p.f16_out != 0;
+    const float out_scale = p.out_scale;
     const bool has_resid = p.has_resid != 0, has_f32 = p.out_f32 != nullptr;
     float* const ssq_out = p.ssq_out;
     float* ssq_x = bias_s + BN;                // [2][128] partial row sums handed from warp w+4 to warp w
@@ -194,6 +196,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
         for (int q = 0; q < p.ssq_parts; ++q) ss += p.ssq_in[(int64_t)row * p.ssq_parts + q];
         rinv = 1.0f / (sqrtf(ss) * p.inv_sqrt_rms_dim + p.rms_eps);
       }
+      rinv *= p.a_scale;
       rinv_s[quad * 32 + lane] = rinv;
       asm volatile("bar.arrive 1, 256;" ::: "memory");
     } else {
@@ -268,17 +271,32 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
       const int c0 = (ch & 1) * 4;
       if (packed_gelu) {
         uint8_t* bbox = bf_stage + ((ch >> 1) * 4 + quad) * GEMM_BOX + lane * 128;
+if (f16_out) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+          sts128u(bbox + (((c0 + c) ^ sw) << 4), gelu_pair_f16x2(v[8 * c], v[8 * c + 1]),
+                  gelu_pair_f16x2(v[8 * c + 2], v[8 * c + 3]), gelu_pair_f16x2(v[8 * c + 4], v[8 * c + 5]),
+                  gelu_pair_f16x2(v[8 * c + 6], v[8 * c + 7]));
+          } else {
 #pragma unroll
         for (int c = 0; c < 4; ++c)
           sts128u(bbox + (((c0 + c) ^ sw) << 4), gelu_pair_bf16x2(v[8 * c], v[8 * c + 1]),
                   gelu_pair_bf16x2(v[8 * c + 2], v[8 * c + 3]), gelu_pair_bf16x2(v[8 * c + 4], v[8 * c + 5]),
                   gelu_pair_bf16x2(v[8 * c + 6], v[8 * c + 7]));
+          }
       } else if (out_nseg == 1) {
         uint8_t* bbox = bf_stage + ((ch >> 1) * 4 + quad) * GEMM_BOX + lane * 128;
+if (f16_out) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+          sts128u(bbox + (((c0 + c) ^ sw) << 4), pack16(true, out_scale, v[8 * c], v[8 * c + 1]), pack16(true, out_scale, v[8 * c + 2], v[8 * c + 3]),
+                  pack16(true, out_scale, v[8 * c + 4], v[8 * c + 5]), pack16(true, out_scale, v[8 * c + 6], v[8 * c + 7]));
+          } else {
 #pragma unroll
         for (int c = 0; c < 4; ++c)
           sts128u(bbox + (((c0 + c) ^ sw) << 4), pack_bf16x2(v[8 * c], v[8 * c + 1]), pack_bf16x2(v[8 * c + 2], v[8 * c + 3]),
                   pack_bf16x2(v[8 * c + 4], v[8 * c + 5]), pack_bf16x2(v[8 * c + 6], v[8 * c + 7]));
+          }
       } else if (out_nseg > 1) {
         for (int sg = 0; sg < out_nseg; ++sg) {
           uint32_t w[16];
@@ -390,7 +408,7 @@ static int pipe_bytes_of(int bn) {
 
 int launch_gemm(const avd_gemm_args& g, cudaStream_t s) {
   const int nseg = nseg_of(g.precision);
-  AVD_REQUIRE(nseg > 0, "precision must be 1, 3 or 6");
+  AVD_REQUIRE(nseg > 0, "precision must be 1 (bf16), 2 (f16), 3 or 6");
   AVD_REQUIRE(g.M > 0 && g.N > 0 && g.K > 0, "empty GEMM");
   AVD_REQUIRE(g.K % GEMM_BK == 0, "K must be a multiple of 64");
   AVD_REQUIRE(g.N % 32 == 0, "N must be a multiple of 32");
@@ -401,12 +419,12 @@ int launch_gemm(const avd_gemm_args& g, cudaStream_t s) {
   AVD_REQUIRE(g.resid == nullptr || g.out_f32 != nullptr, "a residual needs the fp32 output");
   AVD_REQUIRE(g.act >= 0 && g.act <= 2, "act must be 0 (none), 1 (GELU erf) or 2 (GELU fast erf)");
   const int out_nseg = g.out_bf16 != nullptr ? nseg_of(g.out_precision) : 0;
-  AVD_REQUIRE(g.out_bf16 == nullptr || out_nseg > 0, "out_precision must be 1, 3 or 6");
+  AVD_REQUIRE(g.out_bf16 == nullptr || out_nseg > 0, "out_precision must be 1, 2, 3 or 6");
 
   GemmParams p{};
   p.M = g.M; p.N = g.N; p.K = g.K;
   // smallest partial products first so they are not absorbed by the large ones
-  if (g.precision == 1) { p.n_pairs = 1; p.pairs = 0x0; }
+  if (g.precision == 1 || g.precision == 2) { p.n_pairs = 1; p.pairs = 0x0; }
   else if (g.precision == 3) { p.n_pairs = 3; p.pairs = (0x4u) | (0x1u << 4) | (0x0u << 8); }  // (lo,hi) (hi,lo) (hi,hi)
   else {
     // segments 0=hi 1=mid 2=lo: (1,1) (2,0) (0,2) (1,0) (0,1) (0,0)
@@ -424,6 +442,10 @@ int launch_gemm(const avd_gemm_args& g, cudaStream_t s) {
   p.out_bf16 = static_cast<__nv_bfloat16*>(g.out_bf16);
   p.out_nseg = out_nseg;
   p.ssq_out = g.ssq_out;
+  p.f16_in = is_f16(g.precision) ? 1 : 0;
+  p.f16_out = (g.out_bf16 != nullptr && is_f16(g.out_precision)) ? 1 : 0;
+  p.a_scale = g.a_scale != 0.0f ? g.a_scale : 1.0f;
+  p.out_scale = g.out_scale != 0.0f ? g.out_scale : 1.0f;
   // Tile width: the widest BN that divides N, still gives >= ~0.8 waves of CTAs on 148 SMs, and whose epilogue staging
   // (fp32 tile unless it overwrites the residual tile, plus out_nseg bf16 tiles) fits the reused pipeline smem.
   // A residual tile needs dedicated smem, which only the narrow tiles can spare.

@@ -28,6 +28,10 @@ struct GemmParams {
   __nv_bfloat16* out_bf16;   // bf16 result segments [out_nseg][M][N] or nullptr
   int out_nseg;
   float* ssq_out;
+  int f16_in;                // operands are fp16 (AVD_PREC_F16) instead of bf16
+  int f16_out;               // out_bf16 holds fp16 (one segment)
+  float a_scale;             // multiplies the accumulator (folded into the row scale)
+  float out_scale;           // multiplies the 16-bit output only
   unsigned long long* trace; // debug: per-CTA phase timestamps (avd_debug_trace), nullptr in production
 };
 
@@ -76,6 +80,20 @@ __device__ __forceinline__ float gelu_fast(float x) {
 // where the result is stored as ONE bf16 segment (fc1 of the bf16 mode): |tanh form - erf form| <= 4.8e-4 and the
 // f16 arithmetic (2^-11) are both below the bf16 quantum (2^-9) of the stored value; rms over N(0,1) inputs 3e-4 vs
 // 1.1e-3 for the bf16 rounding itself.  ~10 instructions + 1 MUFU per PAIR instead of ~16 + 2 MUFU per element.
+// the same arithmetic, result kept as fp16x2 (fp16 mode; `scale` is the 16-bit output scale, 1 for the MLP hidden)
+__device__ __forceinline__ uint32_t gelu_pair_f16x2(float a, float b) {
+  const __half2 x = __floats2half2_rn(a, b);
+  const __half2 u = __hmul2(x, x);
+  const __half2 inner = __hfma2(__float2half2_rn(0.0356774081f), u, __float2half2_rn(0.7978845608f));
+  const __half2 w = __hmul2(x, inner);
+  uint32_t wi = *reinterpret_cast<const uint32_t*>(&w), ti;
+  asm("tanh.approx.f16x2 %0, %1;" : "=r"(ti) : "r"(wi));
+  const __half2 t = *reinterpret_cast<const __half2*>(&ti);
+  const __half2 h = __hmul2(x, __float2half2_rn(0.5f));
+  const __half2 o = __hfma2(h, t, h);
+  return *reinterpret_cast<const uint32_t*>(&o);
+}
+
 __device__ __forceinline__ uint32_t gelu_pair_bf16x2(float a, float b) {
   const __half2 x = __floats2half2_rn(a, b);
   const __half2 u = __hmul2(x, x);
@@ -89,6 +107,14 @@ __device__ __forceinline__ uint32_t gelu_pair_bf16x2(float a, float b) {
   return pack_bf16x2(o.x, o.y);
 }
 
+
+// 16-bit output conversion of the single-segment modes: bf16, or fp16 with the output scale and saturation
+__device__ __forceinline__ uint32_t pack16(bool f16, float scale, float a, float b) {
+  return f16 ? pack_f16x2(a * scale, b * scale) : pack_bf16x2(a, b);
+}
+__device__ __forceinline__ uint32_t gelu_pair16(bool f16, float a, float b) {
+  return f16 ? gelu_pair_f16x2(a, b) : gelu_pair_bf16x2(a, b);
+}
 
 // persistent kernel (avd_gemm_ps.cu); bn = 0 lets it choose the tile width
 int launch_gemm_ps(const avd_gemm_args& g, GemmParams p, int nseg, int force_bn, cudaStream_t s);

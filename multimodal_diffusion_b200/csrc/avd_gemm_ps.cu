@@ -174,7 +174,7 @@ __global__ void __launch_bounds__(PS_THREADS, 1) gemm_ps_kernel(const __grid_con
     // ------------------------------------------------------------------ MMA issuer h: iterations j = h (mod 2) of each tile
     if (lane == 0) {
       const int h = warp - 2;
-      const uint32_t idesc = make_idesc_bf16(GEMM_BM, BN, 0, 0);
+      const uint32_t idesc = make_idesc_bf16(GEMM_BM, BN, 0, 0, p.f16_in);
       const uint32_t desc_hi = smem_desc_hi_sw128(1024);
       const uint32_t a_lo0 = smem_desc_lo_sw128(smem_u32(smem), 16);
       for (int i = 0; i < my_tiles; ++i) {
@@ -211,6 +211,8 @@ __global__ void __launch_bounds__(PS_THREADS, 1) gemm_ps_kernel(const __grid_con
     const int quad = warp & 3;                 // TMEM lane quadrant this warp may access
     const int hf = e >> 2;                     // even / odd 32-column chunks
     const int act = p.act, out_nseg = p.out_nseg;
+    const bool f16_out = p.f16_out != 0;
+    const float out_scale = p.out_scale;
     const bool has_resid = p.has_resid != 0, has_f32 = p.out_f32 != nullptr;
     float* const ssq_out = p.ssq_out;
     const bool paired = (out_nseg > 0 || ssq_out != nullptr);   // the two warps of a quadrant share 64-column units
@@ -263,6 +265,7 @@ __global__ void __launch_bounds__(PS_THREADS, 1) gemm_ps_kernel(const __grid_con
         for (int q = 0; q < p.ssq_parts; ++q) ss += p.ssq_in[(int64_t)row * p.ssq_parts + q];
         rinv = 1.0f / (sqrtf(ss) * p.inv_sqrt_rms_dim + p.rms_eps);
       }
+      rinv *= p.a_scale;
       if (warp == 4 && lane == 0 && i == 0) trace_mark(trace, 4);
       if (lane == 0) {                           // one polling lane per warp, backing off: the issuing threads on the
         uint32_t spins = 0;                      // same SM sub-partition need the issue slots during the mainloop
@@ -340,17 +343,32 @@ __global__ void __launch_bounds__(PS_THREADS, 1) gemm_ps_kernel(const __grid_con
         const int c0 = (ch & 1) * 4;
         if (packed_gelu) {
           uint8_t* brow = bf_quad + lane * 128;
+if (f16_out) {
+#pragma unroll
+          for (int c = 0; c < 4; ++c)
+            sts128u(brow + (((c0 + c) ^ sw) << 4), gelu_pair_f16x2(v[8 * c], v[8 * c + 1]),
+                    gelu_pair_f16x2(v[8 * c + 2], v[8 * c + 3]), gelu_pair_f16x2(v[8 * c + 4], v[8 * c + 5]),
+                    gelu_pair_f16x2(v[8 * c + 6], v[8 * c + 7]));
+          } else {
 #pragma unroll
           for (int c = 0; c < 4; ++c)
             sts128u(brow + (((c0 + c) ^ sw) << 4), gelu_pair_bf16x2(v[8 * c], v[8 * c + 1]),
                     gelu_pair_bf16x2(v[8 * c + 2], v[8 * c + 3]), gelu_pair_bf16x2(v[8 * c + 4], v[8 * c + 5]),
                     gelu_pair_bf16x2(v[8 * c + 6], v[8 * c + 7]));
+          }
         } else if (out_nseg == 1) {
           uint8_t* brow = bf_quad + lane * 128;
+if (f16_out) {
+#pragma unroll
+          for (int c = 0; c < 4; ++c)
+            sts128u(brow + (((c0 + c) ^ sw) << 4), pack16(true, out_scale, v[8 * c], v[8 * c + 1]), pack16(true, out_scale, v[8 * c + 2], v[8 * c + 3]),
+                    pack16(true, out_scale, v[8 * c + 4], v[8 * c + 5]), pack16(true, out_scale, v[8 * c + 6], v[8 * c + 7]));
+          } else {
 #pragma unroll
           for (int c = 0; c < 4; ++c)
             sts128u(brow + (((c0 + c) ^ sw) << 4), pack_bf16x2(v[8 * c], v[8 * c + 1]), pack_bf16x2(v[8 * c + 2], v[8 * c + 3]),
                     pack_bf16x2(v[8 * c + 4], v[8 * c + 5]), pack_bf16x2(v[8 * c + 6], v[8 * c + 7]));
+          }
         } else if (out_nseg > 1) {
           for (int sg = 0; sg < out_nseg; ++sg) {
             uint32_t w[16];

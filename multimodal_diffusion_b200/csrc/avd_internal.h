@@ -52,7 +52,17 @@ struct LaunchScope {  // brackets one kernel launch; counts it and (optionally) 
   int slot;
 };
 
-inline int nseg_of(int precision) { return precision == 1 ? 1 : precision == 3 ? 2 : precision == 6 ? 3 : -1; }
+inline int nseg_of(int precision) {
+  return (precision == 1 || precision == 2) ? 1 : precision == 3 ? 2 : precision == 6 ? 3 : -1;
+}
+inline bool is_f16(int precision) { return precision == AVD_PREC_F16; }
+// `nseg` argument of the operand-writing kernels (avd_elementwise.cu store_split): > 0 bf16 segments; < 0 ONE fp16
+// value: NSEG_F16_X carries the residual-stream scale AVD_F16_XSCALE, NSEG_F16 is unscaled (weights, normalised values)
+constexpr int NSEG_F16_X = -1;
+constexpr int NSEG_F16 = -2;
+inline int nseg_arg(int precision, bool residual_stream) {
+  return is_f16(precision) ? (residual_stream ? NSEG_F16_X : NSEG_F16) : nseg_of(precision);
+}
 
 // ---- kernels (launchers) ------------------------------------------------------------------------
 // elementwise / data movement (avd_elementwise.cu)
@@ -110,7 +120,7 @@ extern int64_t g_dbg_trace_slots;
 
 // attention (avd_attn.cu)
 int launch_attention_tc(const void* qkv_bf16, void* out, int out_nseg, int n_seq, int N, int n_heads, int hd,
-                        cudaStream_t s);
+                        cudaStream_t s, bool f16 = false);
 int launch_attention_f32(const float* qkv, void* out, int out_nseg, int n_seq, int N, int n_heads, int hd,
                          cudaStream_t s);
 

@@ -162,12 +162,15 @@ __device__ __forceinline__ uint64_t make_smem_desc_sw128(uint32_t smem_addr, uin
 // Instruction descriptor for kind::f16 (bf16 x bf16 -> fp32), dense.
 //   [4,6) D fmt (1=f32)  [7,10) A fmt (1=bf16)  [10,13) B fmt  [15] A major  [16] B major (0=K, 1=MN)
 //   [17,23) N>>3  [24,29) M>>4
+// f16_operands != 0 selects fp16 x fp16 -> fp32 (A/B format 0) instead of bf16 (format 1): same pipe, same rate.
 __host__ __device__ __forceinline__ uint32_t make_idesc_bf16(uint32_t M, uint32_t N, uint32_t a_mn_major,
-                                                             uint32_t b_mn_major) {
+                                                             uint32_t b_mn_major, uint32_t f16_operands = 0) {
   uint32_t d = 0;
   d |= 1u << 4;
-  d |= 1u << 7;
-  d |= 1u << 10;
+  if (!f16_operands) {
+    d |= 1u << 7;
+    d |= 1u << 10;
+  }
   d |= (a_mn_major & 1u) << 15;
   d |= (b_mn_major & 1u) << 16;
   d |= ((N >> 3) & 0x3Fu) << 17;
@@ -243,6 +246,13 @@ __device__ __forceinline__ void split_bf16(float v, __nv_bfloat16& hi, __nv_bflo
   mid = __float2bfloat16_rn(r1);
   float r2 = r1 - __bfloat162float(mid);
   lo = __float2bfloat16_rn(r2);
+}
+
+// two floats -> fp16x2 with saturation to the largest finite fp16 (one F2FP.SATFINITE.F16.F32.PACK_AB)
+__device__ __forceinline__ uint32_t pack_f16x2(float a, float b) {
+  uint32_t r;
+  asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
+  return r;
 }
 
 __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {

@@ -155,7 +155,7 @@ def rows_prepare(x2d: torch.Tensor, precision: int):
 
 def gemm(A: torch.Tensor, W: torch.Tensor, M: int, N: int, K: int, precision: int, *, bias=None, ssq_in=None,
          rms_dim: int = 0, rms_eps: float = 0.0, resid=None, act: int = 0, out_f32=None, out_bf16=None,
-         out_precision: int = 0, ssq_out=None) -> None:
+         out_precision: int = 0, ssq_out=None, a_scale: float = 0.0, out_scale: float = 0.0) -> None:
     g = _lib.GemmArgs()
     g.M, g.N, g.K, g.precision = M, N, K, precision
     g.A, g.W, g.bias = A.data_ptr(), W.data_ptr(), _lib.ptr(bias)
@@ -165,6 +165,7 @@ def gemm(A: torch.Tensor, W: torch.Tensor, M: int, N: int, K: int, precision: in
     g.resid, g.act = _lib.ptr(resid), act
     g.out_f32, g.out_bf16, g.out_precision = _lib.ptr(out_f32), _lib.ptr(out_bf16), out_precision
     g.ssq_out = _lib.ptr(ssq_out)
+    g.a_scale, g.out_scale = a_scale, out_scale
     _lib.check(_lib.load().avd_gemm(C.byref(g), _lib.stream_ptr()))
 
 
@@ -176,7 +177,8 @@ def core_workspace(M: int, d: int, d_mlp: int, precision: int, device):
         "xa": torch.empty(S, M, d, device=device, dtype=torch.bfloat16),
         "ssq": torch.empty(M, d // 64, device=device, dtype=torch.float32),
         "qkv": torch.empty(M, 3 * d, device=device,
-                           dtype=torch.bfloat16 if precision == _lib.AVD_PREC_BF16 else torch.float32),
+                           dtype=torch.bfloat16 if precision in (_lib.AVD_PREC_BF16, _lib.AVD_PREC_F16)
+                           else torch.float32),   # 16-bit storage (bf16 or fp16 bits, per the precision mode)
         "att": torch.empty(S, M, d, device=device, dtype=torch.bfloat16),
         "hmid": torch.empty(S, M, d_mlp, device=device, dtype=torch.bfloat16),
     }

@@ -36,7 +36,7 @@ def T(a):
     return torch.from_numpy(np.asarray(a))
 
 
-@pytest.mark.parametrize("precision,tol", [("fp32", TOL_EPS_FP32), ("bf16x3", 2e-4), ("bf16", 8e-3)])
+@pytest.mark.parametrize("precision,tol", [("fp32", TOL_EPS_FP32), ("bf16x3", 2e-4), ("bf16", 8e-3), ("f16", 1.5e-3)])
 def test_mmdit_forward_vs_reference(dev, mods, precision, tol):
     g = golden("mvp_forward")
     core = mods[2]
@@ -119,7 +119,8 @@ def _sampler(mods, target, B, core_precision, head_precision, steps=50):
 
 
 @pytest.mark.parametrize("target", ["audio", "video"])
-@pytest.mark.parametrize("core_p,head_p,tol", [("fp32", "fp32", TOL_EPS_FP32), ("bf16", "bf16x3", TOL_EPS_BF16)])
+@pytest.mark.parametrize("core_p,head_p,tol", [("fp32", "fp32", TOL_EPS_FP32), ("bf16", "bf16x3", TOL_EPS_BF16),
+                                               ("f16", "bf16x3", TOL_EPS_BF16)])
 def test_sampler_first_steps_vs_oracle(dev, mods, w_cpu, target, core_p, head_p, tol):
     """Per-step eps of both CFG branches, the CFG-combined latent-layout eps and z_prev, B = 2, steps 0 and 1."""
     B = 2
@@ -154,10 +155,14 @@ def test_sampler_first_steps_vs_oracle(dev, mods, w_cpu, target, core_p, head_p,
             rec.append((err_hat, err_z))
     if core_p == "fp32":
         assert max(r[0] for r in rec) < 5 * tol
+    if core_p == "f16":
+        # the half-precision tolerance (1e-2) also holds for the CFG-COMBINED eps, which guidance 3.5 amplifies
+        assert max(r[0] for r in rec) < tol
 
 
 @pytest.mark.parametrize("name,target", [("v2a", "audio"), ("a2v", "video")])
-@pytest.mark.parametrize("core_p,head_p,tol", [("fp32", "fp32", 2e-3), ("bf16", "bf16x3", TOL_FINAL)])
+@pytest.mark.parametrize("core_p,head_p,tol", [("fp32", "fp32", 2e-3), ("bf16", "bf16x3", TOL_FINAL),
+                                               ("f16", "bf16x3", TOL_FINAL)])
 def test_sampler_50_steps_vs_reference(dev, mods, name, target, core_p, head_p, tol):
     """Final latent of the reference's own sample_one_direction run (B = 1, 50 steps, injected latents)."""
     g = golden(f"sample_{name}")
