@@ -196,6 +196,22 @@ def attn_flops_per_call(cfg, batch: int) -> float:
     return cfg.sampler_steps * cfg.n_layers * 2 * batch * 4.0 * N * N * cfg.d_model
 
 
+def ncu_traffic_bytes():
+    """dram read + write bytes per GEMM launch from the committed `ncu --set full` capture of one block's four GEMM
+    launches at the bench shapes (profiles/r1d_gemm_mvp_ncu_full_summary.csv: cold-cache, serialised replays), or None."""
+    import csv
+    f = ROOT / "profiles" / "r1d_gemm_mvp_ncu_full_summary.csv"
+    try:
+        rows = list(csv.reader(f.open()))
+        hdr, units = rows[0], rows[1]
+        ir, iw = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
+        scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+        tot = [float(r[ir]) * scale[units[ir]] + float(r[iw]) * scale[units[iw]] for r in rows[2:] if len(r) > max(ir, iw)]
+        return sum(tot) / len(tot) if tot else None
+    except Exception:
+        return None
+
+
 def run_ours(args) -> None:
     import torch
     import torch.distributed as dist
@@ -327,7 +343,7 @@ def run_ours(args) -> None:
                 "achieved": gemm_tflops, "peak": pk["bf16_tflops_sustained"], "unit": "TFLOP/s",
                 "frac": gemm_tflops / pk["bf16_tflops_sustained"],
                 "peak_source": f"{pk['source']} sustained bf16 (kernel timed inside a long step)",
-                "traffic": None, "launches": g["launches"], "us_per_launch": g.get("us_per_launch"),
+                "traffic": ncu_traffic_bytes(), "launches": g["launches"], "us_per_launch": g.get("us_per_launch"),
                 "share_of_step": g["ms"] / total_prof_ms,
                 "timing": "CUDA events around replays of a graph holding only this family's launches of one call"}
     kernels = {k: {"launches": v["launches"], "us_per_launch": round(v["us_per_launch"], 3),
