@@ -48,7 +48,10 @@ struct GemmSmem {
 // After the last MMA has retired the pipeline region is reused as epilogue staging: fp32 result boxes first (when
 // there is no residual tile to overwrite), then out_nseg bf16 tiles.  Every staging box is 32 rows x 128 B with the
 // 128-byte swizzle the TMA store expects, written by the warp that owns those 32 TMEM lanes.
-template <int BN, int STAGES>
+// MODE specialises the epilogue at compile time (the runtime-flag version executes ~1.5x the instructions per chunk, and
+// the epilogue is instruction-issue bound): 0 generic; 1 one 16-bit output segment only (QKV); 2 the same with the
+// packed GELU (fc1); 3 residual + fp32 + one 16-bit segment + row sums of squares (out-proj, fc2).
+template <int BN, int STAGES, int MODE>
 __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA,
                                                                   const __grid_constant__ CUtensorMap tmB,
                                                                   const __grid_constant__ CUtensorMap tmR,
@@ -59,7 +62,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
   uint8_t* smem = gemm_smem;
   if ((smem_u32(smem) & 1023u) != 0) __trap();   // 128B-swizzle tiles need 1024-B aligned bases
   uint8_t* res_tile = smem + S::PIPE_BYTES;
-  uint8_t* tail = res_tile + (p.has_resid ? S::F32_TILE : 0);
+  const bool k_resid = MODE == 0 ? (p.has_resid != 0) : (MODE == 3);
+  uint8_t* tail = res_tile + (k_resid ? S::F32_TILE : 0);
   uint64_t* bars = reinterpret_cast<uint64_t*>(tail);
   // per pipeline h: full[h*STAGES + s], empty[(2 + h)*STAGES + s]; then acc[2], res
   uint64_t* acc_bar = bars + 4 * STAGES;
@@ -79,7 +83,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
-    if (p.has_resid) tma_prefetch_desc(&tmR);
+    if (k_resid) tma_prefetch_desc(&tmR);
     for (int i = 0; i < 4 * STAGES + 3; ++i) mbar_init(&bars[i], 1);
     fence_barrier_init();
   }
@@ -120,7 +124,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
         kb += 2;
         while (kb >= kblocks) { kb -= kblocks; ++pi; }
       }
-      if (h == 0 && p.has_resid) {
+      if (h == 0 && k_resid) {
         mbar_expect_tx(res_bar, S::F32_TILE);
         for (int ch = 0; ch < BN / 32; ++ch)
           for (int q = 0; q < 4; ++q)
@@ -181,10 +185,12 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
     const int row = m0 + quad * 32 + lane;
     const bool live = row < p.M;
     const bool two_acc = iters > 1;
-    const int act = p.act, out_nseg = p.out_nseg;
+    const int act = MODE == 0 ? p.act : (MODE == 2 ? 2 : 0);
+    const int out_nseg = MODE == 0 ? p.out_nseg : 1;
     const bool f16_out = p.f16_out != 0;
     const float out_scale = p.out_scale;
-    const bool has_resid = p.has_resid != 0, has_f32 = p.out_f32 != nullptr;
+    const bool has_resid = k_resid, has_f32 = MODE == 0 ? (p.out_f32 != nullptr) : (MODE == 3);
+    const bool has_ssq = MODE == 0 ? (p.ssq_out != nullptr) : (MODE == 3);
     float* const ssq_out = p.ssq_out;
     float* ssq_x = bias_s + BN;                // [2][128] partial row sums handed from warp w+4 to warp w
     float* rinv_s = ssq_x + 256;               // [128] RMSNorm row scales, computed by warps 4..7 during the mainloop
@@ -234,7 +240,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
         tmem_ld_32x32(t_row + (ch + 2) * 32, r);
         if (two_acc) tmem_ld_32x32(t_row + BN + (ch + 2) * 32, r1);
       }
-      if (threadIdx.x == 128 && ch == hf) trace_mark(trace, 8);
+      if (MODE == 0 && threadIdx.x == 128 && ch == hf) trace_mark(trace, 8);
 #pragma unroll
       for (int j = 0; j < 32; j += 4) {
         const float4 b4 = *reinterpret_cast<const float4*>(bias_s + ch * 32 + j);
@@ -249,7 +255,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
           v[4 * c] += x4.x; v[4 * c + 1] += x4.y; v[4 * c + 2] += x4.z; v[4 * c + 3] += x4.w;
         }
       }
-      const bool packed_gelu = (act == 2 && out_nseg == 1 && !has_f32 && ssq_out == nullptr);
+      const bool packed_gelu = (act == 2 && out_nseg == 1 && !has_f32 && !has_ssq);
       if (act == 1) {
 #pragma unroll
         for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
@@ -257,13 +263,13 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
 #pragma unroll
         for (int j = 0; j < 32; ++j) v[j] = gelu_fast(v[j]);
       }
-      if (threadIdx.x == 128 && ch == hf) trace_mark(trace, 9);
+      if (MODE == 0 && threadIdx.x == 128 && ch == hf) trace_mark(trace, 9);
       if (has_f32) {
 #pragma unroll
         for (int c = 0; c < 8; ++c) sts128(fbox + ((c ^ sw) << 4), v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
       }
       float ssq_acc = 0.0f;
-      if (ssq_out != nullptr) {
+      if (has_ssq) {
 #pragma unroll
         for (int j = 0; j < 32; ++j) ssq_acc = fmaf(v[j], v[j], ssq_acc);
         if (hf == 1) ssq_x[((ch >> 1) & 1) * 128 + quad * 32 + lane] = ssq_acc;
@@ -314,11 +320,11 @@ if (f16_out) {
             sts128u(bbox + (((c0 + c) ^ sw) << 4), w[4 * c], w[4 * c + 1], w[4 * c + 2], w[4 * c + 3]);
         }
       }
-      if (threadIdx.x == 128 && ch == hf) trace_mark(trace, 10);
-      const bool paired = (out_nseg > 0 || ssq_out != nullptr);   // the two warps of a quadrant share 64-column units
+      if (MODE == 0 && threadIdx.x == 128 && ch == hf) trace_mark(trace, 10);
+      const bool paired = (out_nseg > 0 || has_ssq);   // the two warps of a quadrant share 64-column units
       if (paired) named_bar_sync(2 + quad, 64); else __syncwarp();
-      if (threadIdx.x == 128 && ch == hf) trace_mark(trace, 11);
-      if (hf == 0 && ssq_out != nullptr && live)
+      if (MODE == 0 && threadIdx.x == 128 && ch == hf) trace_mark(trace, 11);
+      if (hf == 0 && has_ssq && live)
         ssq_out[(int64_t)row * (p.N / 64) + ((n0 + ch * 32) >> 6)] = ssq_acc + ssq_x[((ch >> 1) & 1) * 128 + quad * 32 + lane];
       // staged boxes -> global, coalesced: 8 lanes cover one 128-byte row, one warp instruction covers 4 rows
       const int rr = lane >> 3, cc = lane & 7;
@@ -344,7 +350,7 @@ if (f16_out) {
           }
         }
       }
-      if (threadIdx.x == 128 && ch == hf) trace_mark(trace, 12);
+      if (MODE == 0 && threadIdx.x == 128 && ch == hf) trace_mark(trace, 12);
     }
     if (threadIdx.x == 128) trace_mark(trace, 6);
   }
@@ -368,12 +374,15 @@ static int env_int(const char* name, int dflt) {
 
 template <int BN, int STAGES>
 static int launch_gemm_bn(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmR, const GemmParams& p,
-                          cudaStream_t s) {
+                          int mode, cudaStream_t s) {
   using S = GemmSmem<BN, STAGES>;
+  using KernelFn = void (*)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const GemmParams);
+  static const KernelFn kernels[4] = {gemm_tc_kernel<BN, STAGES, 0>, gemm_tc_kernel<BN, STAGES, 1>,
+                                      gemm_tc_kernel<BN, STAGES, 2>, gemm_tc_kernel<BN, STAGES, 3>};
   static bool attr_set = false;
   if (!attr_set) {
-    AVD_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  S::total(BN <= 64)));
+    for (int m = 0; m < 4; ++m)
+      AVD_CUDA(cudaFuncSetAttribute(kernels[m], cudaFuncAttributeMaxDynamicSharedMemorySize, S::total(BN <= 64)));
     attr_set = true;
   }
   cudaLaunchConfig_t cfg{};
@@ -392,7 +401,7 @@ static int launch_gemm_bn(const CUtensorMap& tmA, const CUtensorMap& tmB, const 
   cfg.numAttrs = na;
   if (kind_skipped(KIND_GEMM)) return 0;
   LaunchScope ls(KIND_GEMM, s);
-  AVD_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<BN, STAGES>, tmA, tmB, tmR, p));
+  AVD_CUDA(cudaLaunchKernelEx(&cfg, kernels[mode], tmA, tmB, tmR, p));
   return 0;
 }
 
@@ -490,12 +499,19 @@ int launch_gemm(const avd_gemm_args& g, cudaStream_t s) {
   tmR = tmA;   // placeholder when unused (never dereferenced)
   if (g.resid != nullptr)
     AVD_TRY(get_tensor_map_3d(g.resid, 4, g.N, g.M, 1, (uint64_t)g.N * 4, (uint64_t)g.M * g.N * 4, 32, 32, &tmR));
+  // epilogue specialisation (see the kernel's MODE); the phase trace and every other combination use the generic one
+  int mode = 0;
+  const bool one16 = g.out_bf16 != nullptr && out_nseg == 1;
+  if (one16 && g.out_f32 == nullptr && g.resid == nullptr && g.ssq_out == nullptr && g.act == 0) mode = 1;
+  else if (one16 && g.out_f32 == nullptr && g.resid == nullptr && g.ssq_out == nullptr && g.act == 2) mode = 2;
+  else if (one16 && g.out_f32 != nullptr && g.resid != nullptr && g.ssq_out != nullptr && g.act == 0) mode = 3;
+  if (p.trace != nullptr || bn < 64 || env_int("AVD_GEMM_GENERIC", 0)) mode = 0;
   switch (bn) {
-    case 256: return launch_gemm_bn<256, 2>(tmA, tmB, tmR, p, s);
-    case 192: return launch_gemm_bn<192, 2>(tmA, tmB, tmR, p, s);
-    case 128: return launch_gemm_bn<128, 3>(tmA, tmB, tmR, p, s);
-    case 64: return launch_gemm_bn<64, 3>(tmA, tmB, tmR, p, s);
-    default: return launch_gemm_bn<32, 3>(tmA, tmB, tmR, p, s);
+    case 256: return launch_gemm_bn<256, 2>(tmA, tmB, tmR, p, mode, s);
+    case 192: return launch_gemm_bn<192, 2>(tmA, tmB, tmR, p, mode, s);
+    case 128: return launch_gemm_bn<128, 3>(tmA, tmB, tmR, p, mode, s);
+    case 64: return launch_gemm_bn<64, 3>(tmA, tmB, tmR, p, mode, s);
+    default: return launch_gemm_bn<32, 3>(tmA, tmB, tmR, p, mode, s);
   }
 }
 
