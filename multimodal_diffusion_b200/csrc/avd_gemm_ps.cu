@@ -47,7 +47,9 @@ struct PsPlan {
   int f32_off, bf_off, tail_off;   // byte offsets of the staging regions and the barrier block
 };
 
-template <int BN>
+// MODE: compile-time epilogue specialisation, as in gemm_tc_kernel (0 generic, 1 one 16-bit segment, 2 + packed GELU,
+// 3 residual + fp32 + one 16-bit segment + row sums of squares).
+template <int BN, int MODE>
 __global__ void __launch_bounds__(PS_THREADS, 1) gemm_ps_kernel(const __grid_constant__ CUtensorMap tmA,
                                                                 const __grid_constant__ CUtensorMap tmB,
                                                                 const __grid_constant__ CUtensorMap tmR,
@@ -102,7 +104,7 @@ __global__ void __launch_bounds__(PS_THREADS, 1) gemm_ps_kernel(const __grid_con
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
-    if (p.has_resid) tma_prefetch_desc(&tmR);
+    if (MODE == 0 ? (p.has_resid != 0) : (MODE == 3)) tma_prefetch_desc(&tmR);
     for (int i = 0; i < 2 * PS_MAX_STAGES; ++i) mbar_init(&full[i], 1);       // full, empty
     for (int i = 0; i < 2; ++i) mbar_init(&acc_full[i], 2);                   // one arrival per issuer
     for (int i = 0; i < 2; ++i) mbar_init(&acc_empty[i], 8);                  // one arrival per epilogue warp
@@ -210,13 +212,16 @@ __global__ void __launch_bounds__(PS_THREADS, 1) gemm_ps_kernel(const __grid_con
     const int e = warp - 4;
     const int quad = warp & 3;                 // TMEM lane quadrant this warp may access
     const int hf = e >> 2;                     // even / odd 32-column chunks
-    const int act = p.act, out_nseg = p.out_nseg;
+    const int act = MODE == 0 ? p.act : (MODE == 2 ? 2 : 0);
+    const int out_nseg = MODE == 0 ? p.out_nseg : 1;
     const bool f16_out = p.f16_out != 0;
     const float out_scale = p.out_scale;
-    const bool has_resid = p.has_resid != 0, has_f32 = p.out_f32 != nullptr;
+    const bool has_resid = MODE == 0 ? (p.has_resid != 0) : (MODE == 3);
+    const bool has_f32 = MODE == 0 ? (p.out_f32 != nullptr) : (MODE == 3);
+    const bool has_ssq = MODE == 0 ? (p.ssq_out != nullptr) : (MODE == 3);
     float* const ssq_out = p.ssq_out;
-    const bool paired = (out_nseg > 0 || ssq_out != nullptr);   // the two warps of a quadrant share 64-column units
-    const bool packed_gelu = (act == 2 && out_nseg == 1 && !has_f32 && ssq_out == nullptr);
+    const bool paired = (out_nseg > 0 || has_ssq);   // the two warps of a quadrant share 64-column units
+    const bool packed_gelu = (act == 2 && out_nseg == 1 && !has_f32 && !has_ssq);
     uint8_t* const fbox0 = smem + plan.f32_off + e * 2 * GEMM_BOX;              // this warp's fp32 staging boxes: the
     // residual chunk q of the warp's chunk sequence lands in box q & 1 (prefetched while chunk q - 1 is processed)
     // and the fp32 result overwrites it in place; without a residual only box 0 is used
@@ -335,7 +340,7 @@ __global__ void __launch_bounds__(PS_THREADS, 1) gemm_ps_kernel(const __grid_con
           for (int c = 0; c < 8; ++c) sts128(frow + ((c ^ sw) << 4), v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
         }
         float ssq_acc = 0.0f;
-        if (ssq_out != nullptr) {
+        if (has_ssq) {
 #pragma unroll
           for (int j = 0; j < 32; ++j) ssq_acc = fmaf(v[j], v[j], ssq_acc);
           if (hf == 1) ssq_x[quad * 32 + lane] = ssq_acc;
@@ -387,7 +392,7 @@ if (f16_out) {
           }
         }
         if (paired) named_bar_sync(2 + quad, 64); else __syncwarp();
-        if (hf == 0 && ssq_out != nullptr && live)
+        if (hf == 0 && has_ssq && live)
           ssq_out[(int64_t)row * (p.N / 64) + ((n0 + ch * 32) >> 6)] = ssq_acc + ssq_x[quad * 32 + lane];
         // staged boxes -> global, coalesced: 8 lanes cover one 128-byte row, one warp instruction covers 4 rows
         if (has_f32) {
@@ -454,10 +459,14 @@ static int ps_num_sms() {
 
 template <int BN>
 static int launch_ps_bn(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmR, const GemmParams& p,
-                        const PsPlan& plan, int smem_bytes, int grid, cudaStream_t s) {
+                        const PsPlan& plan, int smem_bytes, int grid, int mode, cudaStream_t s) {
+  using KernelFn = void (*)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const GemmParams, const PsPlan);
+  static const KernelFn kernels[4] = {gemm_ps_kernel<BN, 0>, gemm_ps_kernel<BN, 1>, gemm_ps_kernel<BN, 2>,
+                                      gemm_ps_kernel<BN, 3>};
   static bool attr_set = false;
   if (!attr_set) {
-    AVD_CUDA(cudaFuncSetAttribute(gemm_ps_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, PS_SMEM_MAX + 1024));
+    for (int m = 0; m < 4; ++m)
+      AVD_CUDA(cudaFuncSetAttribute(kernels[m], cudaFuncAttributeMaxDynamicSharedMemorySize, PS_SMEM_MAX + 1024));
     attr_set = true;
   }
   cudaLaunchConfig_t cfg{};
@@ -476,7 +485,7 @@ static int launch_ps_bn(const CUtensorMap& tmA, const CUtensorMap& tmB, const CU
   cfg.numAttrs = na;
   if (kind_skipped(KIND_GEMM)) return 0;
   LaunchScope ls(KIND_GEMM, s);
-  AVD_CUDA(cudaLaunchKernelEx(&cfg, gemm_ps_kernel<BN>, tmA, tmB, tmR, p, plan));
+  AVD_CUDA(cudaLaunchKernelEx(&cfg, kernels[mode], tmA, tmB, tmR, p, plan));
   return 0;
 }
 
@@ -565,10 +574,16 @@ int launch_gemm_ps(const avd_gemm_args& g, GemmParams p, int nseg, int force_bn,
   tmR = tmA;   // placeholder when unused (never dereferenced)
   if (g.resid != nullptr)
     AVD_TRY(get_tensor_map_3d(g.resid, 4, g.N, g.M, 1, (uint64_t)g.N * 4, (uint64_t)g.M * g.N * 4, 32, 32, &tmR));
+  int mode = 0;
+  const bool one16 = g.out_bf16 != nullptr && out_nseg == 1;
+  if (one16 && g.out_f32 == nullptr && g.resid == nullptr && g.ssq_out == nullptr && g.act == 0) mode = 1;
+  else if (one16 && g.out_f32 == nullptr && g.resid == nullptr && g.ssq_out == nullptr && g.act == 2) mode = 2;
+  else if (one16 && g.out_f32 != nullptr && g.resid != nullptr && g.ssq_out != nullptr && g.act == 0) mode = 3;
+  if (p.trace != nullptr || bn < 64 || ps_env_int("AVD_GEMM_GENERIC", 0)) mode = 0;
   switch (bn) {
-    case 128: return launch_ps_bn<128>(tmA, tmB, tmR, p, plan, smem_bytes, grid, s);
-    case 64: return launch_ps_bn<64>(tmA, tmB, tmR, p, plan, smem_bytes, grid, s);
-    default: return launch_ps_bn<32>(tmA, tmB, tmR, p, plan, smem_bytes, grid, s);
+    case 128: return launch_ps_bn<128>(tmA, tmB, tmR, p, plan, smem_bytes, grid, mode, s);
+    case 64: return launch_ps_bn<64>(tmA, tmB, tmR, p, plan, smem_bytes, grid, mode, s);
+    default: return launch_ps_bn<32>(tmA, tmB, tmR, p, plan, smem_bytes, grid, mode, s);
   }
 }
 
