@@ -793,8 +793,11 @@ int launch_layernorm_act(const float* y, const float* w, const float* b, int M, 
 constexpr int BX_R = 4;      // tokens per CTA
 constexpr int BX_J = 4;      // adapter columns per thread (d_adapt <= 256 * BX_J)
 constexpr int BX_THREADS = 256;
-constexpr int BX_KU = 8;     // weight rows fetched per batch (independent loads in flight)
 
+// KU = weight rows fetched per batch (KU x BX_J independent loads in flight per thread).  The first batch is issued
+// BEFORE griddepcontrol.wait (weights do not depend on the previous kernel): with KU = 32 the whole audio adapter
+// (d_tok = 32) is in registers when the latent arrives; later batches are double-buffered.
+template <int KU>
 __global__ void __launch_bounds__(BX_THREADS) build_x_kernel(BuildXArgs a, const float* __restrict__ z,
                                                             const float* __restrict__ wt,
                                                             const float* __restrict__ bias,
@@ -818,6 +821,17 @@ __global__ void __launch_bounds__(BX_THREADS) build_x_kernel(BuildXArgs a, const
     const int c = tid + j * BX_THREADS;
     bv[j] = (c < a.d_adapt) ? __ldg(bias + c) : 0.0f;
   }
+  float wv[KU][BX_J];
+  auto load_batch = [&](int k0) {
+#pragma unroll
+    for (int u = 0; u < KU; ++u)
+#pragma unroll
+      for (int j = 0; j < BX_J; ++j) {
+        const int c = tid + j * BX_THREADS;
+        wv[u][j] = (j < ncol && c < a.d_adapt && k0 + u < a.d_tok) ? __ldg(wt + (int64_t)(k0 + u) * a.d_adapt + c) : 0.0f;
+      }
+  };
+  load_batch(0);
   pdl_wait();
   pdl_launch_dependents();
 
@@ -849,23 +863,35 @@ __global__ void __launch_bounds__(BX_THREADS) build_x_kernel(BuildXArgs a, const
   for (int r = 0; r < BX_R; ++r)
 #pragma unroll
     for (int j = 0; j < BX_J; ++j) acc[r][j] = 0.0f;
-  for (int k0 = 0; k0 < a.d_tok; k0 += BX_KU) {
-    float wv[BX_KU][BX_J];
+  if constexpr (KU >= 32) {          // single batch (the launcher guarantees d_tok <= KU): consume wv in place
 #pragma unroll
-    for (int u = 0; u < BX_KU; ++u)
-#pragma unroll
-      for (int j = 0; j < BX_J; ++j) {
-        const int c = tid + j * BX_THREADS;
-        wv[u][j] = (j < ncol && c < a.d_adapt && k0 + u < a.d_tok) ? __ldg(wt + (int64_t)(k0 + u) * a.d_adapt + c) : 0.0f;
-      }
-#pragma unroll
-    for (int u = 0; u < BX_KU; ++u) {
-      if (k0 + u < a.d_tok) {
+    for (int u = 0; u < KU; ++u) {
+      if (u < a.d_tok) {
 #pragma unroll
         for (int r = 0; r < BX_R; ++r) {
-          const float t = tok[r * a.d_tok + k0 + u];
+          const float t = tok[r * a.d_tok + u];
 #pragma unroll
           for (int j = 0; j < BX_J; ++j) acc[r][j] = fmaf(t, wv[u][j], acc[r][j]);
+        }
+      }
+    }
+  } else {
+    for (int k0 = 0; k0 < a.d_tok; k0 += KU) {
+      float wc[KU][BX_J];
+#pragma unroll
+      for (int u = 0; u < KU; ++u)
+#pragma unroll
+        for (int j = 0; j < BX_J; ++j) wc[u][j] = wv[u][j];
+      if (k0 + KU < a.d_tok) load_batch(k0 + KU);        // next batch flies while this one is consumed
+#pragma unroll
+      for (int u = 0; u < KU; ++u) {
+        if (k0 + u < a.d_tok) {
+#pragma unroll
+          for (int r = 0; r < BX_R; ++r) {
+            const float t = tok[r * a.d_tok + k0 + u];
+#pragma unroll
+            for (int j = 0; j < BX_J; ++j) acc[r][j] = fmaf(t, wc[u][j], acc[r][j]);
+          }
         }
       }
     }
@@ -929,12 +955,16 @@ int launch_build_x(const BuildXArgs& a, const float* z, const float* wt, const f
   int groups = (a.n_tok + BX_R - 1) / BX_R;
   size_t smem = (size_t)BX_R * a.d_tok * sizeof(float);
   if (smem > 48 * 1024) {
-    AVD_CUDA(cudaFuncSetAttribute(build_x_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    AVD_CUDA(cudaFuncSetAttribute(build_x_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   }
   if (kind_skipped(KIND_BUILD_X)) return 0;
   LaunchScope ls(KIND_BUILD_X, s);
-  AVD_CUDA(launch_pdl(build_x_kernel, dim3(a.B * groups), dim3(BX_THREADS), smem, s, a, z, wt, bias, temb, x,
-                      static_cast<__nv_bfloat16*>(xa), ssq));
+  if (a.d_tok <= 32)
+    AVD_CUDA(launch_pdl(build_x_kernel<32>, dim3(a.B * groups), dim3(BX_THREADS), smem, s, a, z, wt, bias, temb, x,
+                        static_cast<__nv_bfloat16*>(xa), ssq));
+  else
+    AVD_CUDA(launch_pdl(build_x_kernel<8>, dim3(a.B * groups), dim3(BX_THREADS), smem, s, a, z, wt, bias, temb, x,
+                        static_cast<__nv_bfloat16*>(xa), ssq));
   return 0;
 }
 
