@@ -194,7 +194,10 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
 #pragma unroll
         for (int i = 0; i < 3; ++i) {
           const int lim = kv_valid - (ch0 + i) * 32;
-          if (lim > 0) {
+          if (lim >= 32) {                           // whole chunk of valid keys: no masking
+#pragma unroll
+            for (int c = 0; c < 32; ++c) mx[c & 3] = fmaxf(mx[c & 3], __uint_as_float(x[i][c]));
+          } else if (lim > 0) {
 #pragma unroll
             for (int c = 0; c < 32; ++c) mx[c & 3] = fmaxf(mx[c & 3], c < lim ? __uint_as_float(x[i][c]) : -INFINITY);
           }
@@ -214,15 +217,26 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
           if (lim > -16) {                           // chunks wholly past round16(keys) are never read by the PV MMA
             float l0 = 0.0f, l1 = 0.0f;
             uint32_t w[16];
+            if (lim >= 32) {                         // whole chunk of valid keys: no masking
 #pragma unroll
-            for (int c = 0; c < 32; c += 2) {
-              float p0 = ex2_approx(fmaf(__uint_as_float(x[i][c]), sc, -m_sc));
-              float p1 = ex2_approx(fmaf(__uint_as_float(x[i][c + 1]), sc, -m_sc));
-              p0 = c < lim ? p0 : 0.0f;
-              p1 = c + 1 < lim ? p1 : 0.0f;
-              l0 += p0;
-              l1 += p1;
-              w[c >> 1] = F16 ? pack_f16x2(p0, p1) : pack_bf16x2(p0, p1);
+              for (int c = 0; c < 32; c += 2) {
+                const float p0 = ex2_approx(fmaf(__uint_as_float(x[i][c]), sc, -m_sc));
+                const float p1 = ex2_approx(fmaf(__uint_as_float(x[i][c + 1]), sc, -m_sc));
+                l0 += p0;
+                l1 += p1;
+                w[c >> 1] = F16 ? pack_f16x2(p0, p1) : pack_bf16x2(p0, p1);
+              }
+            } else {
+#pragma unroll
+              for (int c = 0; c < 32; c += 2) {
+                float p0 = ex2_approx(fmaf(__uint_as_float(x[i][c]), sc, -m_sc));
+                float p1 = ex2_approx(fmaf(__uint_as_float(x[i][c + 1]), sc, -m_sc));
+                p0 = c < lim ? p0 : 0.0f;
+                p1 = c + 1 < lim ? p1 : 0.0f;
+                l0 += p0;
+                l1 += p1;
+                w[c >> 1] = F16 ? pack_f16x2(p0, p1) : pack_bf16x2(p0, p1);
+              }
             }
             l_blk += l0 + l1;
             uint8_t* atom = sPt + (ch >> 1) * ATT_Q_BYTES + r * 128;
