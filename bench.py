@@ -44,7 +44,7 @@ def parse_args():
     ap.add_argument("--batch", type=int, default=8, help="clips per GPU per sampling call")
     ap.add_argument("--core-precision", default="f16",
                     help="f16 (default: fp16 operands, fp32 accumulation; meets every tolerance of the hot-path spec), bf16, bf16x3, fp32")
-    ap.add_argument("--head-precision", default="bf16x3")
+    ap.add_argument("--head-precision", default="f16")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-sample-steps", type=int, default=4, help="DDIM steps of the CPU-baseline sample")
     return ap.parse_args()

@@ -209,7 +209,8 @@ typedef struct {
 } avd_head_weights;
 
 /* MultiModalNoiseHead.forward for one modality (noise_heads.py:201-220).  h: bf16 segments [S][M][d_in];
- * act_a/act_b: bf16 [S][M][hidden] scratch; y: fp32 [M][hidden] scratch; eps: fp32 [M][d_out]. */
+ * act_a/act_b: bf16 [S][M][hidden] scratch; y: fp32 [M][hidden] scratch; eps: fp32 [M][d_out].
+ * AVD_PREC_F16: h is fp16 pre-scaled by AVD_F16_XSCALE (what avd_rows_prepare writes); scratch holds fp16. */
 int avd_head_forward(const avd_head_weights* w, const void* h, int M, void* act_a, void* act_b, float* y, float* eps,
                      void* stream);
 

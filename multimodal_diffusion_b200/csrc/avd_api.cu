@@ -188,7 +188,6 @@ static int sampler_layout(const avd_sampler* s, SamplerLayout* L) {
   L->S_core = nseg_of(s->core.precision);
   L->S_head = nseg_of(s->head.precision);
   AVD_REQUIRE(L->S_core > 0 && L->S_head > 0, "bad precision");
-  AVD_REQUIRE(!is_f16(s->head.precision), "the noise head has no fp16 mode (use bf16, bf16x3 or fp32)");
   L->Nv = (s->T / s->tt) * (s->H / s->th) * (s->W / s->tw);
   L->Na = (s->Fa - s->chunk_len) / s->chunk_stride + 1;
   L->N = L->Nv + L->Na;
@@ -285,7 +284,9 @@ static int core_blocks(const avd_core_weights* w, const float* x_in, const void*
     g.A = ws->hmid; g.W = b.w_fc2; g.bias = b.b_fc2; g.resid = ws->x;
     g.out_f32 = ws->x; g.out_bf16 = ws->xa; g.out_precision = w->precision; g.ssq_out = ws->ssq;
     g.out_scale = x_scale;
-    if (l == w->n_layers - 1 && last_out != nullptr) { g.out_bf16 = last_out; g.out_precision = last_prec; g.out_scale = 0.0f; }
+    if (l == w->n_layers - 1 && last_out != nullptr) {   // the head's operand: pre-scaled too when the head runs in fp16
+      g.out_bf16 = last_out; g.out_precision = last_prec; g.out_scale = is_f16(last_prec) ? AVD_F16_XSCALE : 0.0f;
+    }
     AVD_TRY(launch_gemm(g, st));
   }
   return 0;
@@ -293,8 +294,10 @@ static int core_blocks(const avd_core_weights* w, const float* x_in, const void*
 
 // ssq_in (optional): row sums of squares of h; then the input projection applies the RMSNorm row scale
 // 1/(sqrt(ssq/rms_dim) + rms_eps) in its epilogue (the norm's `scale` vector is folded into w_in by the packer).
+// h_a_scale: undoes the scale carried by h (1/AVD_F16_XSCALE when h is the pre-scaled fp16 residual stream; 0 = none).
 static int head_forward(const avd_head_weights* w, const void* h, int M, void* act_a, void* act_b, float* y,
-                        float* eps, const float* ssq_in, int ssq_parts, int rms_dim, float rms_eps, cudaStream_t st) {
+                        float* eps, const float* ssq_in, int ssq_parts, int rms_dim, float rms_eps, float h_a_scale,
+                        cudaStream_t st) {
   AVD_REQUIRE(w != nullptr, "null head");
   AVD_REQUIRE(w->n_shared >= 0 && w->n_shared <= AVD_MAX_SHARED, "bad shared-layer count");
   const int S = nseg_of(w->precision);
@@ -304,6 +307,7 @@ static int head_forward(const avd_head_weights* w, const void* h, int M, void* a
   g.M = M; g.N = w->hidden; g.K = w->d_in; g.precision = w->precision;
   g.A = h; g.W = w->w_in; g.bias = w->b_in; g.out_bf16 = act_a; g.out_precision = w->precision;
   g.ssq_in = ssq_in; g.ssq_parts = ssq_parts; g.rms_dim = rms_dim; g.rms_eps = rms_eps;
+  g.a_scale = h_a_scale;
   AVD_TRY(launch_gemm(g, st));
   void* cur = act_a;
   void* nxt = act_b;
@@ -312,7 +316,8 @@ static int head_forward(const avd_head_weights* w, const void* h, int M, void* a
     g.M = M; g.N = w->hidden; g.K = w->hidden; g.precision = w->precision;
     g.A = cur; g.W = w->w_s[i]; g.bias = w->b_s[i]; g.out_f32 = y;
     AVD_TRY(launch_gemm(g, st));
-    AVD_TRY(launch_layernorm_act(y, w->ln_w[i], w->ln_b[i], M, w->hidden, w->ln_eps, 1, nullptr, nxt, S, st));
+    AVD_TRY(launch_layernorm_act(y, w->ln_w[i], w->ln_b[i], M, w->hidden, w->ln_eps, 1, nullptr, nxt,
+                                 nseg_arg(w->precision, false), st));
     void* t = cur; cur = nxt; nxt = t;
   }
   g = avd_gemm_args{};                       // eps = out_proj[m](x)   (noise_heads.py:219)
@@ -495,8 +500,7 @@ int avd_layernorm_act(const float* y, const float* w, const float* b, int M, int
                       float* out_f32, void* out_bf16, int precision, void* stream) {
   AVD_REQUIRE(d % 4 == 0, "d must be a multiple of 4");
   AVD_REQUIRE(out_bf16 == nullptr || nseg_of(precision) > 0, "bad precision");
-  AVD_REQUIRE(out_bf16 == nullptr || !is_f16(precision), "the noise head has no fp16 mode (use bf16, bf16x3 or fp32)");
-  return launch_layernorm_act(y, w, b, M, d, eps, apply_gelu, out_f32, out_bf16, out_bf16 ? nseg_of(precision) : 0,
+  return launch_layernorm_act(y, w, b, M, d, eps, apply_gelu, out_f32, out_bf16, out_bf16 ? nseg_arg(precision, false) : 0,
                               AVD_STREAM(stream));
 }
 
@@ -522,7 +526,9 @@ int avd_mmdt_blocks(const avd_core_weights* w, const float* x_in, const void* xa
 }
 int avd_head_forward(const avd_head_weights* w, const void* h, int M, void* act_a, void* act_b, float* y, float* eps,
                      void* stream) {
-  return head_forward(w, h, M, act_a, act_b, y, eps, nullptr, 0, 0, 0.0f, AVD_STREAM(stream));
+  // fp16 mode: h is a residual-stream operand as avd_rows_prepare writes it (pre-scaled by AVD_F16_XSCALE)
+  return head_forward(w, h, M, act_a, act_b, y, eps, nullptr, 0, 0, 0.0f,
+                      (w != nullptr && is_f16(w->precision)) ? 1.0f / AVD_F16_XSCALE : 0.0f, AVD_STREAM(stream));
 }
 
 // ---- sampler
@@ -581,7 +587,8 @@ int avd_sample_step(const avd_sampler* s, int step, float* z, float* eps_tap, vo
   float* eps = reinterpret_cast<float*>(ws + L.eps);
   if (!(dbg_skip & 8))
   AVD_TRY(head_forward(&s->head, ws + L.h, (int)L.M, ws + L.act_a, ws + L.act_b, reinterpret_cast<float*>(ws + L.y), eps,
-                       cw.ssq, L.parts, L.d, s->core.rms_eps, st));
+                       cw.ssq, L.parts, L.d, s->core.rms_eps,
+                       is_f16(s->head.precision) ? 1.0f / AVD_F16_XSCALE : 0.0f, st));
   const int row_off = s->target == AVD_TARGET_VIDEO ? L.row_off_v : L.row_off_a;
   const float* eps_c = eps + (int64_t)row_off * L.Dt;                          // rows of clip b: sequence b
   const float* eps_n = eps + ((int64_t)s->B * L.N + row_off) * L.Dt;           //                 sequence B + b

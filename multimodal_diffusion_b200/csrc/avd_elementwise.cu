@@ -754,7 +754,9 @@ __global__ void __launch_bounds__(256) layernorm_act_kernel(const float* __restr
       }
       int64_t idx = (int64_t)row * d + c;
       if (out_f32 != nullptr) *reinterpret_cast<float4*>(out_f32 + idx) = make_float4(o[0], o[1], o[2], o[3]);
-      if (out_bf16 != nullptr) {
+      if (out_bf16 != nullptr && nseg < 0) {       // one fp16 value (AVD_PREC_F16; normalised values: unscaled)
+        *reinterpret_cast<uint2*>(out_bf16 + idx) = make_uint2(pack_f16x2(o[0], o[1]), pack_f16x2(o[2], o[3]));
+      } else if (out_bf16 != nullptr) {
         for (int sg = 0; sg < nseg; ++sg) {        // hi / mid / lo bf16 terms, 4 columns = one 8-byte store
           uint32_t pk[2];
 #pragma unroll

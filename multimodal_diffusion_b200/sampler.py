@@ -116,7 +116,7 @@ class FusedSampler:
     """
 
     def __init__(self, cfg: HotPathConfig, adapt_v, adapt_a, core, head, target: str, batch: int,
-                 device="cuda", core_precision="f16", head_precision="bf16x3"):
+                 device="cuda", core_precision="f16", head_precision="f16"):
         if target not in ("audio", "video"):
             raise ValueError("target must be 'audio' or 'video'")
         if cfg.eta != 0.0:

@@ -71,7 +71,8 @@ def test_block_and_submodules_vs_reference(dev, mods, w_cpu):
         assert rel_l2(blk.mlp(blk.norm1(X)), want_mlp) < TOL_EPS_FP32
 
 
-@pytest.mark.parametrize("precision,tol", [("fp32", TOL_EPS_FP32), ("bf16x3", 1e-4), ("bf16", TOL_EPS_BF16)])
+@pytest.mark.parametrize("precision,tol", [("fp32", TOL_EPS_FP32), ("bf16x3", 1e-4), ("f16", 2e-3),
+                                           ("bf16", TOL_EPS_BF16)])
 def test_head_vs_reference(dev, mods, precision, tol):
     g = golden("mvp_forward")
     head = mods[3]
@@ -120,7 +121,7 @@ def _sampler(mods, target, B, core_precision, head_precision, steps=50):
 
 @pytest.mark.parametrize("target", ["audio", "video"])
 @pytest.mark.parametrize("core_p,head_p,tol", [("fp32", "fp32", TOL_EPS_FP32), ("bf16", "bf16x3", TOL_EPS_BF16),
-                                               ("f16", "bf16x3", TOL_EPS_BF16)])
+                                               ("f16", "bf16x3", TOL_EPS_BF16), ("f16", "f16", TOL_EPS_BF16)])
 def test_sampler_first_steps_vs_oracle(dev, mods, w_cpu, target, core_p, head_p, tol):
     """Per-step eps of both CFG branches, the CFG-combined latent-layout eps and z_prev, B = 2, steps 0 and 1."""
     B = 2
@@ -162,7 +163,7 @@ def test_sampler_first_steps_vs_oracle(dev, mods, w_cpu, target, core_p, head_p,
 
 @pytest.mark.parametrize("name,target", [("v2a", "audio"), ("a2v", "video")])
 @pytest.mark.parametrize("core_p,head_p,tol", [("fp32", "fp32", 2e-3), ("bf16", "bf16x3", TOL_FINAL),
-                                               ("f16", "bf16x3", TOL_FINAL)])
+                                               ("f16", "bf16x3", TOL_FINAL), ("f16", "f16", TOL_FINAL)])
 def test_sampler_50_steps_vs_reference(dev, mods, name, target, core_p, head_p, tol):
     """Final latent of the reference's own sample_one_direction run (B = 1, 50 steps, injected latents)."""
     g = golden(f"sample_{name}")
