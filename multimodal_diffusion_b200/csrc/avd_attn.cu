@@ -97,8 +97,9 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
   const int colQ = head * ATT_HD, colK = p.d + head * ATT_HD, colV = 2 * p.d + head * ATT_HD;
   const int nkv = (p.N + ATT_BKV - 1) / ATT_BKV;
 
-  if (tid == 0) {
-    for (int i = 0; i < AB_COUNT; ++i) {
+  if (warp == 1) {                       // one barrier per lane
+    if (lane < AB_COUNT) {
+      const int i = lane;
       uint32_t count = 1;
       if ((i >= AB_P && i < AB_O) || i >= AB_R) {       // arrivals: the warp pairs of the tile that own valid query rows
         const int rows = min(ATT_BQ, p.N - q_first - ((i - AB_P) & 1) * ATT_BQ);
@@ -107,12 +108,11 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
       mbar_init(&bars[i], count);
     }
     fence_barrier_init();
+  } else if (warp == 2 && lane == 0) {
+    tma_prefetch_desc(&tmQ);
+    tma_prefetch_desc(&tmKV);
   }
-  if (warp == 0) {
-    if (lane == 0) { tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmKV); }
-    __syncwarp();
-    tmem_alloc<ATT_TMEM_COLS>(tmem_slot);
-  }
+  if (warp == 0) tmem_alloc<ATT_TMEM_COLS>(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();

@@ -80,12 +80,13 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
   unsigned long long* const trace = p.trace;
 
   if (threadIdx.x == 0) trace_mark(trace, 0);
-  if (warp == 0 && lane == 0) {
+  if (warp == 0) {                       // one barrier per lane instead of a serial loop on the critical setup path
+    if (lane < 4 * STAGES + 3) mbar_init(&bars[lane], 1);
+    fence_barrier_init();
+  } else if (warp == 1 && lane == 0) {   // descriptor prefetches off the initialising warp
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
     if (k_resid) tma_prefetch_desc(&tmR);
-    for (int i = 0; i < 4 * STAGES + 3; ++i) mbar_init(&bars[i], 1);
-    fence_barrier_init();
   }
   if (warp == 2) tmem_alloc<TMEM_COLS>(tmem_slot);
   if (warp >= 4) {

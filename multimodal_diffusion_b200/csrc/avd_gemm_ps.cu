@@ -101,15 +101,16 @@ __global__ void __launch_bounds__(PS_THREADS, 1) gemm_ps_kernel(const __grid_con
 
   unsigned long long* const trace = p.trace;
   if (threadIdx.x == 0) trace_mark(trace, 0);
-  if (warp == 0 && lane == 0) {
+  if (warp == 0) {                       // one barrier (or two) per lane instead of a serial loop
+    if (lane < 2 * PS_MAX_STAGES) mbar_init(&full[lane], 1);                  // full, empty
+    if (lane < 2) mbar_init(&acc_full[lane], 2);                              // one arrival per issuer
+    if (lane < 2) mbar_init(&acc_empty[lane], 8);                             // one arrival per epilogue warp
+    if (lane < 16) mbar_init(&res_bar[lane], 1);
+    fence_barrier_init();
+  } else if (warp == 1 && lane == 0) {   // descriptor prefetches off the initialising warp
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
     if (MODE == 0 ? (p.has_resid != 0) : (MODE == 3)) tma_prefetch_desc(&tmR);
-    for (int i = 0; i < 2 * PS_MAX_STAGES; ++i) mbar_init(&full[i], 1);       // full, empty
-    for (int i = 0; i < 2; ++i) mbar_init(&acc_full[i], 2);                   // one arrival per issuer
-    for (int i = 0; i < 2; ++i) mbar_init(&acc_empty[i], 8);                  // one arrival per epilogue warp
-    for (int i = 0; i < 16; ++i) mbar_init(&res_bar[i], 1);
-    fence_barrier_init();
   }
   if (warp == 2) tmem_alloc<TMEM_COLS>(tmem_slot);
   tc_fence_before();
