@@ -35,7 +35,9 @@ constexpr int ATT_Q_BYTES = ATT_BQ * ATT_HD * 2;     // 16 KB: [128 rows][64 bf1
 constexpr int ATT_KV_BYTES = ATT_BKV * ATT_HD * 2;   // 24 KB
 constexpr int ATT_P_BYTES = 3 * ATT_Q_BYTES;         // three 64-key swizzle atoms of [128 rows][128 B]
 constexpr int ATT_XCHG_BYTES = (8 + 4) * 128 * 4;    // row-max exchange [2 bufs][2 tiles][2 halves][128], row-sum [2][2][128]
-constexpr int ATT_SMEM = 2 * ATT_Q_BYTES + 2 * ATT_KV_BYTES + 2 * ATT_P_BYTES + ATT_XCHG_BYTES + 256;
+constexpr int ATT_THIN_ROWS = 8;                     // a second query tile with at most this many rows is "thin"
+constexpr int ATT_THIN_BYTES = ATT_THIN_ROWS * ATT_BKV * 4 + 64;   // its raw scores [8][192] fp32 + row sums
+constexpr int ATT_SMEM = 2 * ATT_Q_BYTES + 2 * ATT_KV_BYTES + 2 * ATT_P_BYTES + ATT_XCHG_BYTES + 256 + ATT_THIN_BYTES;
 constexpr uint32_t ATT_TMEM_COLS = 512;
 
 struct AttnParams {
@@ -64,6 +66,32 @@ __device__ __forceinline__ void att_mark(unsigned long long* trace, int slot) {
     trace[(cta * 16 + slot) * 2] = g;
     trace[(cta * 16 + slot) * 2 + 1] = c;
   }
+}
+
+// Softmax of ONE row of a thin query tile by one whole warp (lane = key column mod 32), from the raw scores the tile's
+// TMEM-reading warps dumped to smem.  A thin tile (the 5 rows 128..132 of the 133-token joint sequence) would otherwise
+// cost its two TMEM-lane-bound warps a full 160 MUFU instructions for 5 live lanes, all on scheduler 0: the longest
+// chain in the kernel.  Writes P (16-bit, K-major 128B-swizzled 64-key atoms, zero past the valid keys) and the row sum.
+template <bool F16>
+__device__ __forceinline__ void thin_row_softmax(const float* srow, uint8_t* sPt, float* l_out, int i, int lane,
+                                                 int kv_valid, int kv_n, float sc) {
+  float mx = -INFINITY;
+  for (int c = lane; c < kv_valid; c += 32) mx = fmaxf(mx, srow[c]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  const float m_sc = mx * sc;
+  float l = 0.0f;
+  for (int c = lane; c < kv_n; c += 32) {
+    const float pv = c < kv_valid ? ex2_approx(fmaf(srow[c], sc, -m_sc)) : 0.0f;
+    l += pv;
+    uint8_t* dst = sPt + (c >> 6) * ATT_Q_BYTES + i * 128 + ((((c & 63) >> 3) ^ (i & 7)) << 4) + (c & 7) * 2;
+    if (F16) *reinterpret_cast<__half*>(dst) = __float2half_rn(pv);
+    else *reinterpret_cast<__nv_bfloat16*>(dst) = __float2bfloat16_rn(pv);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) l += __shfl_xor_sync(0xffffffffu, l, o);
+  if (lane == 0) l_out[i] = l;
+  fence_async_smem();   // P (generic-proxy stores) -> visible to the tensor core's async-proxy reads
 }
 
 // barrier slots
@@ -96,6 +124,12 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
   const int n_tiles = (p.N - q_first > ATT_BQ) ? 2 : 1;          // active query tiles of this CTA
   const int colQ = head * ATT_HD, colK = p.d + head * ATT_HD, colV = 2 * p.d + head * ATT_HD;
   const int nkv = (p.N + ATT_BKV - 1) / ATT_BKV;
+  // thin second tile: its softmax is spread over the tile's 8 warps (one row each) through smem instead of running
+  // thread-per-row on the two warps that may touch its TMEM lanes
+  const int rows1 = p.N - q_first - ATT_BQ;
+  const bool thin = ONE_BLOCK && n_tiles == 2 && rows1 <= ATT_THIN_ROWS;
+  float* thin_sc = reinterpret_cast<float*>(sP + 2 * ATT_P_BYTES + ATT_XCHG_BYTES + 256);   // [8][ATT_BKV]
+  float* thin_l = thin_sc + ATT_THIN_ROWS * ATT_BKV;                                        // [8]
 
   if (warp == 1) {                       // one barrier per lane
     if (lane < AB_COUNT) {
@@ -190,6 +224,25 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
         for (int i = 0; i < 3; ++i)
           if (i == 0 || ch0 + i < nch) tmem_ld_32x32(tmem_S + (ch0 + i) * 32, x[i]);   // columns past the keys are masked
         tmem_ld_wait();
+        if (thin && t == 1) {
+          if (r < rows1) {                           // raw scores of the live rows -> smem
+#pragma unroll
+            for (int i = 0; i < 3; ++i)
+              if (ch0 + i < nch) {
+                float4* dst = reinterpret_cast<float4*>(thin_sc + r * ATT_BKV + (ch0 + i) * 32);
+#pragma unroll
+                for (int c = 0; c < 8; ++c)
+                  dst[c] = make_float4(__uint_as_float(x[i][4 * c]), __uint_as_float(x[i][4 * c + 1]),
+                                       __uint_as_float(x[i][4 * c + 2]), __uint_as_float(x[i][4 * c + 3]));
+              }
+          }
+          named_bar_sync(9, 256);                    // all 8 warps of the tile: scores are in smem
+          if ((warp & 7) < rows1)
+            thin_row_softmax<F16>(thin_sc + (warp & 7) * ATT_BKV, sPt, thin_l, warp & 7, lane, kv_valid, kv_n, sc);
+          named_bar_sync(10, 256);                   // P rows and row sums written
+          alpha = 0.0f;
+          l_blk = (sp == 0 && r < rows1) ? thin_l[r] : 0.0f;
+        } else {
         float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
         for (int i = 0; i < 3; ++i) {
@@ -247,6 +300,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
                   make_uint4(w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
           }
         }
+        }   // !thin
       } else {
         // ---- pass 1: row max over this thread's valid keys
         float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
@@ -384,6 +438,13 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
       if (sg + 1 < p.out_nseg) named_bar_sync(pair_bar, 64);
     }
     if (mark) att_mark(trace, 10);
+  } else if (thin && (warp >> 3) == 1) {
+    // ------------------------------------------------------------------ the other six warps of a thin tile: one row each
+    named_bar_sync(9, 256);
+    if ((warp & 7) < rows1)
+      thin_row_softmax<F16>(thin_sc + (warp & 7) * ATT_BKV, sP + ATT_P_BYTES, thin_l, warp & 7, lane, p.N,
+                            (p.N + 15) & ~15, p.scale_log2e);
+    named_bar_sync(10, 256);
   }
 
   tc_fence_before();

@@ -31,10 +31,12 @@
 
 namespace avd {
 
-template <int BN, int STAGES>   // STAGES = ring depth of EACH of the two pipelines
+// STAGES = ring depth of EACH of the two pipelines.  PAIR: the CTA is one half of a cta_group::2 pair and stages only
+// half of the weight tile's rows (the other half lives in the peer's shared memory).
+template <int BN, int STAGES, bool PAIR = false>
 struct GemmSmem {
   static constexpr int A_BYTES = GEMM_BM * GEMM_BK * 2;
-  static constexpr int B_BYTES = BN * GEMM_BK * 2;
+  static constexpr int B_BYTES = (PAIR ? BN / 2 : BN) * GEMM_BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int PIPE_BYTES = 2 * STAGES * STAGE_BYTES;
   static constexpr int F32_TILE = GEMM_BM * BN * 4;
@@ -51,12 +53,18 @@ struct GemmSmem {
 // MODE specialises the epilogue at compile time (the runtime-flag version executes ~1.5x the instructions per chunk, and
 // the epilogue is instruction-issue bound): 0 generic; 1 one 16-bit output segment only (QKV); 2 the same with the
 // packed GELU (fc1); 3 residual + fp32 + one 16-bit segment + row sums of squares (out-proj, fc2).
-template <int BN, int STAGES, int MODE>
+//
+// PAIR: two CTAs with consecutive blockIdx.x (cluster 2x1x1, the two SMs of a TPC) compute a 256 x BN tile with
+// tcgen05.mma.cta_group::2.  Each CTA loads its own 128 rows of A and BN/2 of the W rows, every TMA completes on the
+// LEADER's full barrier, the leader's two issuer threads run the M=256 MMAs and their commits arrive on both CTAs'
+// barriers; each CTA then drains its own 128 accumulator rows exactly as in the single-CTA kernel.  Per SM the smem port
+// moves (16 KB + BN/2 x 128 B) x 2 per k-block instead of (16 KB + BN x 128 B) x 2.
+template <int BN, int STAGES, int MODE, bool PAIR>
 __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA,
                                                                   const __grid_constant__ CUtensorMap tmB,
                                                                   const __grid_constant__ CUtensorMap tmR,
                                                                   const GemmParams p) {
-  using S = GemmSmem<BN, STAGES>;
+  using S = GemmSmem<BN, STAGES, PAIR>;
   constexpr uint32_t TMEM_COLS = BN <= 32 ? 64 : BN <= 64 ? 128 : BN <= 128 ? 256 : 512;   // two accumulators
   extern __shared__ __align__(1024) uint8_t gemm_smem[];
   uint8_t* smem = gemm_smem;
@@ -73,8 +81,12 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int m0 = blockIdx.y * GEMM_BM;
-  const int n0 = blockIdx.x * BN;
+  // PAIR grids put the row tiles on x: a CTA pair is two CTAs whose cluster rank differs in the last bit, and the
+  // launch is rejected ("cluster misconfiguration") unless the cluster's x extent is even
+  const int m0 = (PAIR ? blockIdx.x : blockIdx.y) * GEMM_BM;
+  const int n0 = (PAIR ? blockIdx.y : blockIdx.x) * BN;
+  const uint32_t rank = PAIR ? cluster_ctarank() : 0u;   // 0 = the pair's leader (issues the MMAs, owns the full barriers)
+  const int n0b = n0 + (PAIR ? (int)rank * (BN / 2) : 0);   // first W row this CTA stages
   const int kblocks = p.K / GEMM_BK;
   const int iters = kblocks * p.n_pairs;
   unsigned long long* const trace = p.trace;
@@ -83,18 +95,28 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
   if (warp == 0) {                       // one barrier per lane instead of a serial loop on the critical setup path
     if (lane < 4 * STAGES + 3) mbar_init(&bars[lane], 1);
     fence_barrier_init();
+    if (MODE == 0 && lane == 0) trace_mark(trace, 14);
   } else if (warp == 1 && lane == 0) {   // descriptor prefetches off the initialising warp
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
     if (k_resid) tma_prefetch_desc(&tmR);
   }
-  if (warp == 2) tmem_alloc<TMEM_COLS>(tmem_slot);
-  if (warp >= 4) {
-    for (int t = threadIdx.x - 128; t < BN; t += 128)
-      bias_s[t] = p.bias != nullptr ? p.bias[n0 + t] : 0.0f;   // weights: not produced by the previous kernel
+  if (warp == 2) {
+    if (PAIR) tmem_alloc_2cta<TMEM_COLS>(tmem_slot); else tmem_alloc<TMEM_COLS>(tmem_slot);
+    if (MODE == 0 && lane == 0) trace_mark(trace, 15);
+  }
+  // bias (weights: not produced by the previous kernel): the global loads are issued here but only land in smem after
+  // the setup barrier, so their latency is off the path to the first TMA / MMA
+  float bias_r[2] = {0.0f, 0.0f};
+  if (warp >= 4 && p.bias != nullptr) {
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const int t = threadIdx.x - 128 + u * 128;
+      if (t < BN) bias_r[u] = __ldg(p.bias + n0 + t);
+    }
   }
   tc_fence_before();
-  __syncthreads();
+  if (PAIR) cluster_sync_all(); else __syncthreads();   // the peer must see initialised barriers before it signals them
   tc_fence_after();
   const uint32_t tmem_acc = *tmem_slot;
   pdl_launch_dependents();
@@ -113,15 +135,25 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
       while (kb >= kblocks) { kb -= kblocks; ++pi; }
       int kb_w = kb, pi_w = pi;                          // the weight loads of the first ring pass run ahead
       const int pre = count < STAGES ? count : STAGES;
+      // PAIR: both CTAs' boxes complete on the leader's barrier, which expects the bytes of both
+      const uint32_t full0 = PAIR ? mapa_u32(smem_u32(full), 0) : 0u;
+      auto expect = [&](int j) {
+        if (!PAIR) mbar_expect_tx(&full[j], S::STAGE_BYTES);
+        else if (rank == 0) mbar_expect_tx(&full[j], 2 * S::STAGE_BYTES);
+      };
+      auto load = [&](void* dst, const CUtensorMap* tm, int j, int c0, int c1, int c2) {
+        if (PAIR) tma_load_3d_2sm(dst, tm, full0 + 8u * j, c0, c1, c2);
+        else tma_load_3d(dst, tm, &full[j], c0, c1, c2);
+      };
       for (int j = 0; j < pre; ++j) {
-        mbar_expect_tx(&full[j], S::STAGE_BYTES);
-        tma_load_3d(ring + j * S::STAGE_BYTES + S::A_BYTES, &tmB, &full[j], kb_w * GEMM_BK, n0, (pairs >> (4 * pi_w)) & 3);
+        expect(j);
+        load(ring + j * S::STAGE_BYTES + S::A_BYTES, &tmB, j, kb_w * GEMM_BK, n0b, (pairs >> (4 * pi_w)) & 3);
         kb_w += 2;
         while (kb_w >= kblocks) { kb_w -= kblocks; ++pi_w; }
       }
       pdl_wait();
       for (int j = 0; j < pre; ++j) {
-        tma_load_3d(ring + j * S::STAGE_BYTES, &tmA, &full[j], kb * GEMM_BK, m0, (pairs >> (4 * pi + 2)) & 3);
+        load(ring + j * S::STAGE_BYTES, &tmA, j, kb * GEMM_BK, m0, (pairs >> (4 * pi + 2)) & 3);
         kb += 2;
         while (kb >= kblocks) { kb -= kblocks; ++pi; }
       }
@@ -137,9 +169,9 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
         mbar_wait(&empty[st], ph);
         uint8_t* dst = ring + st * S::STAGE_BYTES;
         const uint32_t pr = pairs >> (4 * pi);
-        mbar_expect_tx(&full[st], S::STAGE_BYTES);
-        tma_load_3d(dst, &tmA, &full[st], kb * GEMM_BK, m0, (pr >> 2) & 3);
-        tma_load_3d(dst + S::A_BYTES, &tmB, &full[st], kb * GEMM_BK, n0, pr & 3);
+        expect(st);
+        load(dst, &tmA, st, kb * GEMM_BK, m0, (pr >> 2) & 3);
+        load(dst + S::A_BYTES, &tmB, st, kb * GEMM_BK, n0b, pr & 3);
         kb += 2;
         while (kb >= kblocks) { kb -= kblocks; ++pi; }
         if (++st == STAGES) { st = 0; ph ^= 1; }
@@ -147,12 +179,12 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
     }
   } else if (warp < 4) {
     // ------------------------------------------------------------------ MMA issuer of pipeline h
-    if (lane == 0) {
+    if (lane == 0 && rank == 0) {
       const int h = warp - 2;
       const int count = (iters - h + 1) >> 1;
       uint64_t* full = bars + h * STAGES;
       uint64_t* empty = bars + (2 + h) * STAGES;
-      const uint32_t idesc = make_idesc_bf16(GEMM_BM, BN, 0, 0, p.f16_in);
+      const uint32_t idesc = make_idesc_bf16(PAIR ? 2 * GEMM_BM : GEMM_BM, BN, 0, 0, p.f16_in);
       const uint32_t desc_hi = smem_desc_hi_sw128(1024);
       const uint32_t a_lo0 = smem_desc_lo_sw128(smem_u32(smem + h * STAGES * S::STAGE_BYTES), 16);
       const uint32_t acc = tmem_acc + h * BN;
@@ -164,13 +196,18 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
         tc_fence_after();
         const uint32_t b_lo = a_lo + (S::A_BYTES >> 4);
 #pragma unroll
-        for (int k = 0; k < GEMM_BK / 16; ++k)     // +32 bytes (2 x 16-byte units) per 16-wide k step
-          umma_bf16_lh(acc, a_lo + 2 * k, b_lo + 2 * k, desc_hi, idesc, (j > 0 || k > 0) ? 1u : 0u);
-        if (j + STAGES < count) umma_commit(&empty[st]);   // stage reusable once these MMAs have read it
+        for (int k = 0; k < GEMM_BK / 16; ++k) {   // +32 bytes (2 x 16-byte units) per 16-wide k step
+          if (PAIR) umma_2cta_lh(acc, a_lo + 2 * k, b_lo + 2 * k, desc_hi, idesc, (j > 0 || k > 0) ? 1u : 0u);
+          else umma_bf16_lh(acc, a_lo + 2 * k, b_lo + 2 * k, desc_hi, idesc, (j > 0 || k > 0) ? 1u : 0u);
+        }
+        if (j + STAGES < count) {                  // stage reusable (in both CTAs) once these MMAs have read it
+          if (PAIR) umma_commit_2cta(&empty[st]); else umma_commit(&empty[st]);
+        }
         a_lo += S::STAGE_BYTES >> 4;
         if (++st == STAGES) { st = 0; ph ^= 1; a_lo = a_lo0; }
       }
-      if (count > 0) umma_commit(&acc_bar[h]);     // accumulator h complete
+      if (PAIR) umma_commit_2cta(&acc_bar[h]);     // (the host only pairs CTAs when both pipelines have work)
+      else if (count > 0) umma_commit(&acc_bar[h]);   // accumulator h complete
       else mbar_arrive(&acc_bar[h]);               // nothing to do for this pipeline (a single k-block)
       if (h == 0) trace_mark(trace, 3);
     }
@@ -198,6 +235,11 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
     pdl_wait();
     float rinv = 1.0f;
     if (hf == 1) {
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const int t = threadIdx.x - 128 + u * 128;
+        if (t < BN) bias_s[t] = bias_r[u];
+      }
       if (p.ssq_in != nullptr && live) {
         float ss = 0.0f;
         for (int q = 0; q < p.ssq_parts; ++q) ss += p.ssq_in[(int64_t)row * p.ssq_parts + q];
@@ -205,7 +247,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
       }
       rinv *= p.a_scale;
       rinv_s[quad * 32 + lane] = rinv;
-      asm volatile("bar.arrive 1, 256;" ::: "memory");
+      named_bar_sync(1, 256);                  // (not arrive: these warps read the bias tile the others wrote)
     } else {
       named_bar_sync(1, 256);
       rinv = rinv_s[quad * 32 + lane];
@@ -357,10 +399,10 @@ if (f16_out) {
   }
 
   tc_fence_before();
-  __syncthreads();
+  if (PAIR) cluster_sync_all(); else __syncthreads();   // neither CTA of a pair may retire while the other still drains
   if (warp == 2) {
     tc_fence_after();
-    tmem_dealloc<TMEM_COLS>(tmem_acc);
+    if (PAIR) tmem_dealloc_2cta<TMEM_COLS>(tmem_acc); else tmem_dealloc<TMEM_COLS>(tmem_acc);
   }
   if (threadIdx.x == 0) trace_mark(trace, 7);
 }
@@ -373,13 +415,13 @@ static int env_int(const char* name, int dflt) {
   return v ? std::atoi(v) : dflt;
 }
 
-template <int BN, int STAGES>
+template <int BN, int STAGES, bool PAIR = false>
 static int launch_gemm_bn(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmR, const GemmParams& p,
                           int mode, cudaStream_t s) {
-  using S = GemmSmem<BN, STAGES>;
+  using S = GemmSmem<BN, STAGES, PAIR>;
   using KernelFn = void (*)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const GemmParams);
-  static const KernelFn kernels[4] = {gemm_tc_kernel<BN, STAGES, 0>, gemm_tc_kernel<BN, STAGES, 1>,
-                                      gemm_tc_kernel<BN, STAGES, 2>, gemm_tc_kernel<BN, STAGES, 3>};
+  static const KernelFn kernels[4] = {gemm_tc_kernel<BN, STAGES, 0, PAIR>, gemm_tc_kernel<BN, STAGES, 1, PAIR>,
+                                      gemm_tc_kernel<BN, STAGES, 2, PAIR>, gemm_tc_kernel<BN, STAGES, 3, PAIR>};
   static bool attr_set = false;
   if (!attr_set) {
     for (int m = 0; m < 4; ++m)
@@ -387,15 +429,24 @@ static int launch_gemm_bn(const CUtensorMap& tmA, const CUtensorMap& tmB, const 
     attr_set = true;
   }
   cudaLaunchConfig_t cfg{};
-  cfg.gridDim = dim3(p.N / BN, (p.M + GEMM_BM - 1) / GEMM_BM);
+  const int mt = (p.M + GEMM_BM - 1) / GEMM_BM;
+  // a pair = two consecutive row tiles (the last may be empty)
+  cfg.gridDim = PAIR ? dim3((mt + 1) & ~1, p.N / BN) : dim3(p.N / BN, mt);
   cfg.blockDim = dim3(GEMM_THREADS);
   cfg.dynamicSmemBytes = S::total(p.has_resid != 0);
   cfg.stream = s;
-  cudaLaunchAttribute attrs[1];
+  cudaLaunchAttribute attrs[2];
   int na = 0;
   if (pdl_enabled()) {
     attrs[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attrs[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  if (PAIR) {
+    attrs[na].id = cudaLaunchAttributeClusterDimension;
+    attrs[na].val.clusterDim.x = 2;
+    attrs[na].val.clusterDim.y = 1;
+    attrs[na].val.clusterDim.z = 1;
     ++na;
   }
   cfg.attrs = attrs;
@@ -497,6 +548,9 @@ int launch_gemm(const avd_gemm_args& g, cudaStream_t s) {
   CUtensorMap tmA, tmB, tmR;
   AVD_TRY(get_tensor_map_3d(g.A, 2, g.K, g.M, nseg, (uint64_t)g.K * 2, (uint64_t)g.M * g.K * 2, GEMM_BK, GEMM_BM, &tmA));
   AVD_TRY(get_tensor_map_3d(g.W, 2, g.K, g.N, nseg, (uint64_t)g.K * 2, (uint64_t)g.N * g.K * 2, GEMM_BK, bn, &tmB));
+  CUtensorMap tmBh = tmB;   // box of bn/2 weight rows: what one CTA of a pair stages
+  if (bn >= 64)
+    AVD_TRY(get_tensor_map_3d(g.W, 2, g.K, g.N, nseg, (uint64_t)g.K * 2, (uint64_t)g.N * g.K * 2, GEMM_BK, bn / 2, &tmBh));
   tmR = tmA;   // placeholder when unused (never dereferenced)
   if (g.resid != nullptr)
     AVD_TRY(get_tensor_map_3d(g.resid, 4, g.N, g.M, 1, (uint64_t)g.N * 4, (uint64_t)g.M * g.N * 4, 32, 32, &tmR));
@@ -507,6 +561,25 @@ int launch_gemm(const avd_gemm_args& g, cudaStream_t s) {
   else if (one16 && g.out_f32 == nullptr && g.resid == nullptr && g.ssq_out == nullptr && g.act == 2) mode = 2;
   else if (one16 && g.out_f32 != nullptr && g.resid != nullptr && g.ssq_out != nullptr && g.act == 0) mode = 3;
   if (p.trace != nullptr || bn < 64 || env_int("AVD_GEMM_GENERIC", 0)) mode = 0;
+  // CTA pairs (cta_group::2): each SM stages half of the weight tile.  Needs both pipelines busy in the leader, a
+  // specialised epilogue, and the padded grid (an even number of row tiles) still within one wave.
+  const int pair_on = env_int("AVD_GEMM_PAIR", 0);
+  int sms_now = 148;
+  {
+    int dev = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms_now, cudaDevAttrMultiProcessorCount, dev);
+  }
+  const bool pair = pair_on != 0 && (mode != 0 || pair_on == 2) && mt >= 2 && (g.K / GEMM_BK) * p.n_pairs >= 2 &&
+                    (int64_t)((mt + 1) & ~1) * (g.N / bn) <= sms_now;
+  if (pair) {
+    switch (bn) {
+      case 256: return launch_gemm_bn<256, 3, true>(tmA, tmBh, tmR, p, mode, s);
+      case 192: return launch_gemm_bn<192, 3, true>(tmA, tmBh, tmR, p, mode, s);
+      case 128: return launch_gemm_bn<128, 4, true>(tmA, tmBh, tmR, p, mode, s);
+      case 64: return launch_gemm_bn<64, 4, true>(tmA, tmBh, tmR, p, mode, s);
+      default: break;
+    }
+  }
   switch (bn) {
     case 256: return launch_gemm_bn<256, 2>(tmA, tmB, tmR, p, mode, s);
     case 192: return launch_gemm_bn<192, 2>(tmA, tmB, tmR, p, mode, s);

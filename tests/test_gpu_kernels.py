@@ -211,6 +211,18 @@ def test_gemm_split_precision(dev, M, N, K, precision, tol):
     assert rel_l2(got, want) < tol
 
 
+@pytest.mark.parametrize("M,N,K", [(2128, 1536, 512), (300, 512, 512), (266, 512, 2048), (2128, 2048, 512)])
+def test_gemm_cta_pair(dev, monkeypatch, M, N, K):
+    """The cta_group::2 variant (two SMs on one 256-row tile, opt-in through AVD_GEMM_PAIR) against the same exact
+    bf16 products, and bit-identical to the single-CTA kernel (same k order per accumulator)."""
+    monkeypatch.setenv("AVD_GEMM_PAIR", "2")
+    got, want, _, _ = _gemm_case(dev, M, N, K, "bf16")
+    monkeypatch.setenv("AVD_GEMM_PAIR", "0")
+    base, _, _, _ = _gemm_case(dev, M, N, K, "bf16")
+    assert rel_l2(got, want) < 2e-6
+    assert torch.equal(got, base)
+
+
 def test_gemm_fused_epilogue(dev):
     """RMSNorm-as-row-scale prologue, bias, residual, GELU(erf), bf16-segment output and row ssq of the result."""
     from multimodal_diffusion_b200 import _lib, packing
@@ -241,7 +253,8 @@ def _attn_ref(qkv, n_seq, N, H, hd):
     return (p @ v).permute(0, 2, 1, 3).reshape(n_seq * N, d)
 
 
-@pytest.mark.parametrize("n_seq,N", [(2, 133), (1, 128), (3, 445), (2, 16), (1, 300)])
+@pytest.mark.parametrize("n_seq,N", [(2, 133), (1, 128), (3, 445), (2, 16), (1, 300), (2, 129), (2, 136), (1, 137),
+                                      (1, 192)])
 def test_attention_tcgen05(dev, lib, n_seq, N):
     from multimodal_diffusion_b200 import _lib
     H, hd = 8, 64

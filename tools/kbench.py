@@ -176,7 +176,8 @@ def main() -> None:
             ck = (t[:, :, 1] - t[:, 0:1, 1]).float()   # cycles since CTA start
             names = ["start", "setup done", "-", "pipe0: last mma issued", "epi: rinv+resid ready",
                      "epi: acc ready", "epi: stores read", "exit", "ch0: tmem ld done", "ch0: math done",
-                     "ch0: sts done", "ch0: fence+syncwarp", "ch0: tma store issued", "last chunk issued"]
+                     "ch0: sts done", "ch0: fence+syncwarp", "ch0: tma store issued", "-",
+                     "setup: barriers initialised", "setup: tmem allocated"]
             if v4:
                 names = ["start", "setup done", "iss0: first stage landed", "iss0: last mma issued",
                          "epi: tile0 rinv/resid issued", "epi: tile0 acc ready", "epi: tile0 done", "exit",
