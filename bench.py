@@ -198,9 +198,13 @@ def attn_flops_per_call(cfg, batch: int) -> float:
 
 def ncu_traffic_bytes():
     """dram read + write bytes per GEMM launch from the committed `ncu --set full` capture of one block's four GEMM
-    launches at the bench shapes (profiles/r1d_gemm_mvp_ncu_full_summary.csv: cold-cache, serialised replays), or None."""
+    launches at the bench shapes (the newest profiles/r*_gemm_mvp_ncu_full_summary.csv, written by
+    tools/round_artifacts.sh: cold-cache, serialised replays), or None."""
     import csv
-    f = ROOT / "profiles" / "r1d_gemm_mvp_ncu_full_summary.csv"
+    found = sorted((ROOT / "profiles").glob("r*_gemm_mvp_ncu_full_summary.csv"))
+    if not found:
+        return None
+    f = found[-1]
     try:
         rows = list(csv.reader(f.open()))
         hdr, units = rows[0], rows[1]

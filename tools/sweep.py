@@ -3,7 +3,7 @@
     python tools/sweep.py [--out gpurun_out/sweep.json] [--max-tokens 131072] [--check]
 
 For joint sequence length N in {512 .. 16384} x batch B in {1 .. 64} (cells above --max-tokens rows are skipped) it
-runs the mvp.yaml MMDiT (d = 512, L = 8, H = 8, MLP 2048, random init) forward in bf16 mode through
+runs the mvp.yaml MMDiT (d = 512, L = 8, H = 8, MLP 2048, random init) forward in --precision mode (bf16 / f16) through
 avd_mmdt_blocks on unit-rms activations, times it with CUDA events (warm-up, then the median of `iters` runs), and
 times the GEMM family and the attention family separately by replaying the same call with the other kernels
 dropped (avd_debug_skip_kinds).  FLOPs are SURVEY.md §8(d)'s algorithmic figures: GEMM 24 d^2 per token-layer,
@@ -113,8 +113,8 @@ def main() -> None:
             rows.append(row)
             print(json.dumps(row), flush=True)
             del x, xa, ssq, ws, bufs
-    out = {"what": "MMDT forward (mvp.yaml core, bf16 mode) on 1 x B200: CUDA-event medians; gemm/attn = same call with "
-                   "the other kernel families dropped", "peak_tflops": peak,
+    out = {"what": f"MMDT forward (mvp.yaml core, {args.precision} mode) on 1 x B200: CUDA-event medians; gemm/attn = same "
+                   "call with the other kernel families dropped", "peak_tflops": peak,
            "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained", "precision": args.precision, "rows": rows}
     Path(args.out).parent.mkdir(parents=True, exist_ok=True)
     Path(args.out).write_text(json.dumps(out, indent=1))
