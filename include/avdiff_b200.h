@@ -91,6 +91,17 @@ int avd_chunk1d(const float* z, float* tok, int B, int C, int L, int length, int
  * tok[B,N,C*length] -> z[B,C,L_out]; windows summed in order i=0..N-1, divided by max(count,1e-8) */
 int avd_unchunk1d(const float* tok, float* z, int B, int C, int N, int length, int stride, int L_out, void* stream);
 
+/* ---------------------------------------------------------------- streaming driver: stitching
+ * stream_infer.crossfade_audio (avdiff/models/infer/stream_infer.py:82-113): chunks[N,L] fp32, one fade window w[L]
+ * (all ones for fade_s <= 0; the cosine fade otherwise, computed by the caller with the reference's numpy formula) ->
+ * out[(N-1)*hop + L] = sum_i chunk_i*w / max(sum_i w, 1e-6), windows added in order i = 0..N-1.  Bit-exact. */
+int avd_crossfade_audio(const float* chunks, const float* w, float* out, int N, int L, int hop, void* stream);
+/* stream_infer.crossfade_video (stream_infer.py:116-143): chunks[N,T,frame_bytes] uint8 (frame_bytes = H*W*3), one
+ * weight per frame w[T] -> out[(N-1)*hop + T, frame_bytes] uint8 = trunc(clip(sum_i (u8/255)*w / max(sum w,1e-6),0,1)*255).
+ * Bit-exact. */
+int avd_crossfade_video(const uint8_t* chunks, const float* w, uint8_t* out, int N, int T, int64_t frame_bytes, int hop,
+                        void* stream);
+
 /* ---------------------------------------------------------------- schedules */
 /* su.timestep_embedding (avdiff/utils/schedule_utils.py:64-86): t[B] (float) -> emb[B,dim] = [cos | sin] (+0 pad if odd) */
 int avd_timestep_embedding(const float* t, float* emb, int B, int dim, float max_period, void* stream);

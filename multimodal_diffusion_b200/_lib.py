@@ -114,6 +114,8 @@ _SIGNATURES = {
     "avd_tube_unpatch": (_I, [fp, fp, _I, _I, _I, _I, _I, _I, _I, _I, vp]),
     "avd_chunk1d": (_I, [fp, fp, _I, _I, _I, _I, _I, vp]),
     "avd_unchunk1d": (_I, [fp, fp, _I, _I, _I, _I, _I, _I, vp]),
+    "avd_crossfade_audio": (_I, [fp, fp, fp, _I, _I, _I, vp]),
+    "avd_crossfade_video": (_I, [vp, fp, vp, _I, _I, C.c_int64, _I, vp]),
     "avd_timestep_embedding": (_I, [fp, fp, _I, _I, C.c_float, vp]),
     "avd_ddim_step": (_I, [fp, fp, fp, fp, i64p, i64p, fp, _I, _I, C.c_int64, C.c_float, vp]),
     "avd_cfg_untok_ddim": (_I, [C.POINTER(CfgDdimArgs), fp, fp, fp, fp, fp, vp]),

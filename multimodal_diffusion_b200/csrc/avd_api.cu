@@ -449,6 +449,15 @@ int avd_unchunk1d(const float* tok, float* z, int B, int C, int N, int length, i
   return launch_unchunk1d(tok, z, B, C, N, length, stride, L_out, AVD_STREAM(stream));
 }
 
+// ---- streaming driver stitching
+int avd_crossfade_audio(const float* chunks, const float* w, float* out, int N, int L, int hop, void* stream) {
+  return launch_crossfade_audio(chunks, w, out, N, L, hop, AVD_STREAM(stream));
+}
+int avd_crossfade_video(const uint8_t* chunks, const float* w, uint8_t* out, int N, int T, int64_t frame_bytes, int hop,
+                        void* stream) {
+  return launch_crossfade_video(chunks, w, out, N, T, frame_bytes, hop, AVD_STREAM(stream));
+}
+
 // ---- schedules
 int avd_timestep_embedding(const float* t, float* emb, int B, int dim, float max_period, void* stream) {
   AVD_REQUIRE(dim > 0 && max_period > 0, "bad embedding shape");

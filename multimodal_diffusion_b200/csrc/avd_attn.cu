@@ -49,12 +49,31 @@ struct AttnParams {
   int out_nseg;
   float scale_log2e;  // (1/sqrt(hd)) * log2(e)
   unsigned long long* trace;   // debug phase stamps (avd_debug_trace)
+  int poly_exp;     // multi-block path: every second exponential on the FMA pipe (ex2_poly)
 };
 
 __device__ __forceinline__ float ex2_approx(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
+}
+
+// 2^x for x <= 0 on the FMA / ALU pipes: round-to-integer through the 1.5 * 2^23 constant, a degree-4 near-minimax
+// polynomial for 2^f on [-0.5, 0.5] (max relative error 2.9e-6 in fp32, below the 16-bit rounding P gets), and the integer
+// part added into the exponent field.  Used for every second exponential of the MULTI-BLOCK path only: with 16 softmax
+// warps per SM and 49 152 exponentials per 192-key block that path is bound by the 16-lane MUFU pipe (the split
+// FlashAttention-4 describes); in the single-block kernel (8 warps, latency bound) the same change cost 24 %.
+__device__ __forceinline__ float ex2_poly(float x) {
+  x = fmaxf(x, -125.0f);                       // keeps the result a normal number (scores this far down round to 0 in P)
+  const float xf = x + 12582912.0f;
+  const float n = xf - 12582912.0f;
+  const float f = x - n;
+  float q = 0.009582850150763988f;
+  q = fmaf(q, f, 0.055906426161527634f);
+  q = fmaf(q, f, 0.24024099111557007f);
+  q = fmaf(q, f, 0.6931241750717163f);
+  q = fmaf(q, f, 1.0f);
+  return __int_as_float(__float_as_int(q) + (__float_as_int(xf) << 23));
 }
 
 __device__ __forceinline__ void att_mark(unsigned long long* trace, int slot) {
@@ -124,6 +143,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
   const int n_tiles = (p.N - q_first > ATT_BQ) ? 2 : 1;          // active query tiles of this CTA
   const int colQ = head * ATT_HD, colK = p.d + head * ATT_HD, colV = 2 * p.d + head * ATT_HD;
   const int nkv = (p.N + ATT_BKV - 1) / ATT_BKV;
+  const bool POLY_EXP = p.poly_exp != 0;
   // thin second tile: its softmax is spread over the tile's 8 warps (one row each) through smem instead of running
   // thread-per-row on the two warps that may touch its TMEM lanes
   const int rows1 = p.N - q_first - ATT_BQ;
@@ -327,15 +347,35 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
           const int lim = kv_valid - ch * 32;
           float l0 = 0.0f, l1 = 0.0f;
           uint32_t w[16];
+          if (lim >= 32 && POLY_EXP) {               // whole chunk of valid keys, MUFU and FMA pipes share the exponentials
 #pragma unroll
-          for (int c = 0; c < 32; c += 2) {
-            float p0 = ex2_approx(fmaf(__uint_as_float(x[c]), sc, -m_sc));
-            float p1 = ex2_approx(fmaf(__uint_as_float(x[c + 1]), sc, -m_sc));
-            p0 = c < lim ? p0 : 0.0f;
-            p1 = c + 1 < lim ? p1 : 0.0f;
-            l0 += p0;
-            l1 += p1;
-            w[c >> 1] = F16 ? pack_f16x2(p0, p1) : pack_bf16x2(p0, p1);
+            for (int c = 0; c < 32; c += 2) {
+              const float p0 = ex2_approx(fmaf(__uint_as_float(x[c]), sc, -m_sc));
+              const float p1 = ex2_poly(fmaf(__uint_as_float(x[c + 1]), sc, -m_sc));
+              l0 += p0;
+              l1 += p1;
+              w[c >> 1] = F16 ? pack_f16x2(p0, p1) : pack_bf16x2(p0, p1);
+            }
+          } else if (lim >= 32) {
+#pragma unroll
+            for (int c = 0; c < 32; c += 2) {
+              const float p0 = ex2_approx(fmaf(__uint_as_float(x[c]), sc, -m_sc));
+              const float p1 = ex2_approx(fmaf(__uint_as_float(x[c + 1]), sc, -m_sc));
+              l0 += p0;
+              l1 += p1;
+              w[c >> 1] = F16 ? pack_f16x2(p0, p1) : pack_bf16x2(p0, p1);
+            }
+          } else {
+#pragma unroll
+            for (int c = 0; c < 32; c += 2) {
+              float p0 = ex2_approx(fmaf(__uint_as_float(x[c]), sc, -m_sc));
+              float p1 = ex2_approx(fmaf(__uint_as_float(x[c + 1]), sc, -m_sc));
+              p0 = c < lim ? p0 : 0.0f;
+              p1 = c + 1 < lim ? p1 : 0.0f;
+              l0 += p0;
+              l1 += p1;
+              w[c >> 1] = F16 ? pack_f16x2(p0, p1) : pack_bf16x2(p0, p1);
+            }
           }
           l_blk += l0 + l1;
           uint8_t* atom = sPt + (ch >> 1) * ATT_Q_BYTES + r * 128;
@@ -482,6 +522,10 @@ int launch_attention_tc(const void* qkv_bf16, void* out, int out_nseg, int n_seq
   p.out_nseg = out_nseg;
   p.scale_log2e = (1.0f / sqrtf((float)hd)) * 1.4426950408889634f;
   {
+    const char* e = std::getenv("AVD_ATTN_POLY");
+    p.poly_exp = e ? std::atoi(e) : 1;
+  }
+  {
     const int64_t n_ctas = (int64_t)((N + 2 * ATT_BQ - 1) / (2 * ATT_BQ)) * n_heads * n_seq;
     p.trace = (g_dbg_trace != nullptr && n_ctas * 32 <= g_dbg_trace_slots) ? g_dbg_trace : nullptr;
   }
@@ -502,7 +546,8 @@ int launch_attention_tc(const void* qkv_bf16, void* out, int out_nseg, int n_seq
   if (kind_skipped(KIND_ATTN_TC)) return 0;
   LaunchScope ls(KIND_ATTN_TC, s);
   AVD_REQUIRE(!f16 || out_nseg == 1, "the fp16 attention output has one segment");
-  if (N <= ATT_BKV) {
+  static const int one_block_on = std::getenv("AVD_ATTN_ONE") ? std::atoi(std::getenv("AVD_ATTN_ONE")) : 1;   // A/B switch
+  if (N <= ATT_BKV && one_block_on) {
     if (f16) AVD_CUDA(cudaLaunchKernelEx(&cfg, attn_tc_kernel<true, true>, tmQ, tmKV, p));
     else AVD_CUDA(cudaLaunchKernelEx(&cfg, attn_tc_kernel<true, false>, tmQ, tmKV, p));
   } else {

@@ -71,6 +71,9 @@ int launch_tube_patch(const float* src, float* dst, int B, int C, int T, int H, 
 int launch_chunk1d(const float* z, float* tok, int B, int C, int L, int length, int stride, cudaStream_t s);
 int launch_unchunk1d(const float* tok, float* z, int B, int C, int N, int length, int stride, int L_out,
                      cudaStream_t s);
+int launch_crossfade_audio(const float* chunks, const float* w, float* out, int N, int L, int hop, cudaStream_t s);
+int launch_crossfade_video(const uint8_t* chunks, const float* w, uint8_t* out, int N, int T, int64_t F, int hop,
+                           cudaStream_t s);
 int launch_timestep_embedding(const float* t, float* emb, int B, int dim, float max_period, cudaStream_t s);
 int launch_ddim_step(const float* x_t, const float* eps, const float* noise, float* x_prev, const int64_t* t_now,
                      const int64_t* t_prev, const float* alpha_bar, int T_train, int B, int64_t per_batch, float eta,

@@ -277,3 +277,45 @@ def test_attention_fp32(dev, lib, n_seq, N):
     _lib.check(lib.avd_attention(qd.data_ptr(), 1, out.data_ptr(), _lib.AVD_PREC_FP32, n_seq, N, H, hd,
                                  _lib.stream_ptr()))
     assert rel_l2(out.float().sum(0).cpu(), _attn_ref(qkv, n_seq, N, H, hd)) < 2e-6
+
+
+# ------------------------------------------------------------------------------------------ streaming stitchers (§8f N2)
+def test_crossfade_audio_bit_exact(dev):
+    """avd_crossfade_audio through the stream_infer mirror: reference fixtures, then seeded sizes against the oracle
+    (vector path hop % 4 == 0, scalar path, gaps, one window, resident CUDA tensors)."""
+    from oracle import stream_oracle as so
+    from multimodal_diffusion_b200.avdiff.models.infer import stream_infer as si
+    g = golden("stream")
+    win, hop = (int(v) for v in g["a_win_hop"])
+    assert np.array_equal(si.crossfade_audio(g["a_gen"], 1000, hop, win, 0.25), g["a_fade"])
+    assert np.array_equal(si.crossfade_audio(g["a_gen"], 1000, hop, win, 0.0), g["a_rect"])
+    assert np.array_equal(si.crossfade_audio(g["a_gen2"], 1000, 333, 1001, 0.1), g["a_odd"])
+    assert np.array_equal(si.crossfade_audio(g["a_gen2"], 1000, 1200, 1001, 0.05), g["a_gap"])
+    assert np.array_equal(si.crossfade_audio(g["a_gen2"], 1000, 500, 1001, 0.7), g["a_overlapfade"])
+    rng = np.random.default_rng(5)
+    for n, L, h, fade_s in ((1, 4096, 1024, 0.01), (9, 48000, 16000, 0.25), (17, 4000, 500, 0.02), (4, 999, 7, 0.0),
+                            (3, 64, 64, 0.0), (6, 2048, 4096, 0.03)):
+        ch = (rng.standard_normal((n, L)) * 3).astype(np.float32)
+        want = so.crossfade_audio(ch, 16000, h, L, fade_s)
+        assert np.array_equal(si.crossfade_audio(ch, 16000, h, L, fade_s), want), (n, L, h)
+        got = si.crossfade_audio(torch.from_numpy(ch).to(dev), 16000, h, L, fade_s)
+        assert got.is_cuda and np.array_equal(got.cpu().numpy(), want)
+    with pytest.raises(ValueError):
+        si.crossfade_audio(np.zeros((2, 100), np.float32), 16000, 50, 100, 1.0)      # fade longer than the window
+
+
+def test_crossfade_video_bit_exact(dev):
+    from oracle import stream_oracle as so
+    from multimodal_diffusion_b200.avdiff.models.infer import stream_infer as si
+    g = golden("stream")
+    vwin, vhop = (int(v) for v in g["v_win_hop"])
+    assert np.array_equal(si.crossfade_video(g["v_gen"], vhop, vwin, 4), g["v_fade"])
+    assert np.array_equal(si.crossfade_video(g["v_gen"], vhop, vwin, 0), g["v_nofade"])
+    assert np.array_equal(si.crossfade_video(g["v_gen2"], 5, 7, 3), g["v_odd"])
+    rng = np.random.default_rng(6)
+    for n, T, H, W, h, fade in ((1, 48, 16, 16, 16, 4), (7, 48, 128, 128, 16, 4), (5, 12, 9, 7, 5, 0), (3, 8, 4, 4, 20, 2)):
+        ch = rng.integers(0, 256, size=(n, T, H, W, 3), dtype=np.uint8)
+        want = so.crossfade_video(ch, h, T, fade)
+        assert np.array_equal(si.crossfade_video(ch, h, T, fade), want), (n, T, H, W, h)
+        got = si.crossfade_video(torch.from_numpy(ch).to(dev), h, T, fade)
+        assert got.is_cuda and np.array_equal(got.cpu().numpy(), want)

@@ -252,3 +252,17 @@ def test_long_context_a2v_10s(dev, mods, w_cpu):
     fs.step(0, z, tap)
     assert rel_l2(tap[:1], e_c) < TOL_EPS_FP32 and rel_l2(tap[1:], e_n) < TOL_EPS_FP32
     assert rel_l2(z, z_or) < 1e-4
+
+
+def test_stream_sample_windows_as_batch(dev, mods):
+    """§8f N2: the windows of a long prompt run as the batch dimension of the fused sampler; the result must not depend
+    on the batch size (5 windows through a batch-2 sampler, last call padded, against a batch-1 sampler)."""
+    from multimodal_diffusion_b200.avdiff.models.infer.stream_infer import stream_sample
+    zp = randn(71, 5, 8, 12, 16, 16).to(dev)
+    zi = randn(72, 5, 8, 150).to(dev)
+    a = stream_sample(_sampler(mods, "audio", 2, "f16", "f16", steps=4), zp, z_init_windows=zi)
+    b = stream_sample(_sampler(mods, "audio", 1, "f16", "f16", steps=4), zp, z_init_windows=zi)
+    assert a.shape == (5, 8, 150) and torch.equal(a, b)
+    c = stream_sample(_sampler(mods, "audio", 2, "f16", "f16", steps=4), zp, base_seed=9)
+    d = stream_sample(_sampler(mods, "audio", 1, "f16", "f16", steps=4), zp, base_seed=9)
+    assert torch.equal(c, d) and not torch.equal(a, c)

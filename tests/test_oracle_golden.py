@@ -145,3 +145,34 @@ def test_batched_oracle_equals_per_clip_runs():
     for b in range(2):
         z1 = orc.sample_loop(cfg, w, "audio", zp[b:b + 1], zi[b:b + 1])
         assert rel_l2(zb[b:b + 1], z1) < 1e-5
+
+
+# ------------------------------------------------------------------------------------------ streaming driver (§8f N2)
+def test_stream_oracle_and_host_split_match_reference():
+    """oracle/stream_oracle.py and the product's host-side window splitting against outputs of the reference's own
+    stream_infer functions (tests/golden/stream.npz, generated by make_golden_stream.py): bit-exact."""
+    from oracle import stream_oracle as so
+    from multimodal_diffusion_b200.avdiff.models.infer import stream_infer as si
+    g = golden("stream")
+    win, hop = (int(v) for v in g["a_win_hop"])
+    for split_a, split_v in ((so.split_audio, so.split_frames), (si.split_audio_into_windows, si.split_frames_into_windows)):
+        ch, w_, h_ = split_a(g["a_y"], 1000, 3.0, 1.0)
+        assert (w_, h_) == (win, hop) and np.array_equal(ch, g["a_chunks"])
+        assert np.array_equal(split_a(g["a_y"][:2500], 1000, 3.0, 1.0)[0], g["a_short"])
+        vch, vw, vh = split_v(g["v_frames"], 16, 3.0, 1.0)
+        assert (vw, vh) == tuple(int(v) for v in g["v_win_hop"]) and np.array_equal(vch, g["v_chunks"])
+        assert np.array_equal(split_v(g["v_frames"][:30], 16, 3.0, 1.0)[0], g["v_short"])
+    assert np.array_equal(so.crossfade_audio(g["a_gen"], 1000, hop, win, 0.25), g["a_fade"])
+    assert np.array_equal(so.crossfade_audio(g["a_gen"], 1000, hop, win, 0.0), g["a_rect"])
+    assert np.array_equal(so.crossfade_audio(g["a_gen2"], 1000, 333, 1001, 0.1), g["a_odd"])
+    assert np.array_equal(so.crossfade_audio(g["a_gen2"], 1000, 1200, 1001, 0.05), g["a_gap"])
+    assert np.array_equal(so.crossfade_audio(g["a_gen2"], 1000, 500, 1001, 0.7), g["a_overlapfade"])
+    vwin, vhop = (int(v) for v in g["v_win_hop"])
+    assert np.array_equal(so.crossfade_video(g["v_gen"], vhop, vwin, 4), g["v_fade"])
+    assert np.array_equal(so.crossfade_video(g["v_gen"], vhop, vwin, 0), g["v_nofade"])
+    assert np.array_equal(so.crossfade_video(g["v_gen2"], 5, 7, 3), g["v_odd"])
+    assert np.array_equal(si.audio_fade_window(3000, 250), so.audio_window(3000, 250))
+    assert np.array_equal(si.video_fade_window(48, 4), so.video_window(48, 4))
+    # hop larger than the window and a hop that overshoots the end (the while-loop's exit conditions)
+    for total, w_, h_ in ((10, 3, 8), (10, 3, 20), (9, 3, 3), (10, 3, 3)):
+        assert si._window_starts(total, w_, h_) == so.window_starts(total, w_, h_)

@@ -11,6 +11,7 @@ algorithmic bytes / time against MEASURED_PEAKS.json `hbm_gbs`:
   fused CFG + un-tokenise + DDIM (video, audio)   16 B per target-latent element (eps_c, eps_n, z_t read; z_prev written)
   ddim_step (standalone)    12 B per element
   rows_prepare (fp32 rows -> bf16 operand + row sums of squares)   6 B per element
+  crossfade_audio / crossfade_video (stream stitching)   4 + 4 B per window / output sample; 1 + 1 B per pixel byte
 """
 from __future__ import annotations
 
@@ -96,6 +97,20 @@ def main() -> None:
     xa = torch.empty(1, M, 512, device=dev, dtype=torch.bfloat16)
     ssq = torch.empty(M, 8, device=dev)
     report("rows_prepare (fp32 -> bf16 operand + ssq)", timed(lambda: _lib.check(lib.avd_rows_prepare(x.data_ptr(), xa.data_ptr(), ssq.data_ptr(), M, 512, _lib.AVD_PREC_BF16, st()))), x.numel() * 6)
+
+    # streaming stitchers: every window sample read once, every output sample written once
+    nw, Lw, hopw = 1024, 48000, 16000                       # 1024 windows of 3 s at 16 kHz, 1 s hop
+    chunks = torch.randn(nw, Lw, device=dev)
+    wnd = torch.ones(Lw, device=dev)
+    outa = torch.empty((nw - 1) * hopw + Lw, device=dev)
+    report("crossfade_audio (3 s windows, 1 s hop)", timed(lambda: _lib.check(lib.avd_crossfade_audio(chunks.data_ptr(), wnd.data_ptr(), outa.data_ptr(), nw, Lw, hopw, st()))), chunks.numel() * 4 + outa.numel() * 4)
+    del chunks, outa
+    nv, Tv, Fv, hopv = 192, 48, 128 * 128 * 3, 16           # 192 windows of 48 frames 128x128x3, 16-frame hop
+    vch = torch.randint(0, 256, (nv, Tv, Fv), device=dev, dtype=torch.uint8)
+    wv = torch.ones(Tv, device=dev)
+    outv = torch.empty(((nv - 1) * hopv + Tv, Fv), device=dev, dtype=torch.uint8)
+    report("crossfade_video (48-frame windows, 16-frame hop)", timed(lambda: _lib.check(lib.avd_crossfade_video(vch.data_ptr(), wv.data_ptr(), outv.data_ptr(), nv, Tv, Fv, hopv, st()))), vch.numel() + outv.numel())
+    del vch, outv
 
     out = {"what": "byte-moving kernels at HBM-streaming sizes on 1 x B200; algorithmic bytes / CUDA-event time",
            "hbm_peak_gbs": peak, "peak_source": "MEASURED_PEAKS.json hbm_gbs (torch copy, read+write bytes)", "rows": rows}

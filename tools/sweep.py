@@ -53,6 +53,7 @@ def main() -> None:
     ap.add_argument("--iters", type=int, default=5)
     ap.add_argument("--check", action="store_true")
     ap.add_argument("--precision", default="bf16")
+    ap.add_argument("--cells", default="", help="comma-separated NxB cells to run instead of the whole grid")
     args = ap.parse_args()
 
     dev = torch.device("cuda:0")
@@ -78,8 +79,11 @@ def main() -> None:
         print(f"check N=512 B=2 {args.precision}: rel-L2 vs fp32 oracle = {rel_l2(got, want):.3e}", flush=True)
 
     rows = []
-    for N in (512, 1024, 2048, 4096, 8192, 16384):
-        for B in (1, 2, 4, 8, 16, 32, 64):
+    grid = [(N, B) for N in (512, 1024, 2048, 4096, 8192, 16384) for B in (1, 2, 4, 8, 16, 32, 64)]
+    if args.cells:
+        grid = [tuple(int(v) for v in c.split("x")) for c in args.cells.split(",")]
+    for N, B in grid:
+        if True:
             M = B * N
             if M > args.max_tokens:
                 continue
