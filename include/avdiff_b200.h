@@ -96,6 +96,11 @@ int avd_unchunk1d(const float* tok, float* z, int B, int C, int N, int length, i
  * (all ones for fade_s <= 0; the cosine fade otherwise, computed by the caller with the reference's numpy formula) ->
  * out[(N-1)*hop + L] = sum_i chunk_i*w / max(sum_i w, 1e-6), windows added in order i = 0..N-1.  Bit-exact. */
 int avd_crossfade_audio(const float* chunks, const float* w, float* out, int N, int L, int hop, void* stream);
+/* ops.overlap_add_1d with a window (avdiff/utils/ops.py:82-92, apply_hann=True): windows[rows,N,W] * win[W] summed in
+ * order i = 0..N-1 into y[rows,(N-1)*stride+W], divided by max(sum of win, norm_floor) (1e-8 in ops.py).  Bit-exact;
+ * win is computed by the caller (torch.hann_window).  rows <= 65535. */
+int avd_overlap_add_win(const float* windows, const float* win, float* y, int rows, int N, int W, int stride,
+                        float norm_floor, void* stream);
 /* stream_infer.crossfade_video (stream_infer.py:116-143): chunks[N,T,frame_bytes] uint8 (frame_bytes = H*W*3), one
  * weight per frame w[T] -> out[(N-1)*hop + T, frame_bytes] uint8 = trunc(clip(sum_i (u8/255)*w / max(sum w,1e-6),0,1)*255).
  * Bit-exact. */

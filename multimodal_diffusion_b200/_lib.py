@@ -115,6 +115,7 @@ _SIGNATURES = {
     "avd_chunk1d": (_I, [fp, fp, _I, _I, _I, _I, _I, vp]),
     "avd_unchunk1d": (_I, [fp, fp, _I, _I, _I, _I, _I, _I, vp]),
     "avd_crossfade_audio": (_I, [fp, fp, fp, _I, _I, _I, vp]),
+    "avd_overlap_add_win": (_I, [fp, fp, fp, _I, _I, _I, _I, C.c_float, vp]),
     "avd_crossfade_video": (_I, [vp, fp, vp, _I, _I, C.c_int64, _I, vp]),
     "avd_timestep_embedding": (_I, [fp, fp, _I, _I, C.c_float, vp]),
     "avd_ddim_step": (_I, [fp, fp, fp, fp, i64p, i64p, fp, _I, _I, C.c_int64, C.c_float, vp]),

@@ -41,9 +41,8 @@ def chunk_1d(x: torch.Tensor, length: int, stride: int, dim: int = -1) -> torch.
 def overlap_add_1d(windows: torch.Tensor, stride: int, length: Optional[int] = None, dim_windows: int = -2,
                    apply_hann: bool = False) -> torch.Tensor:
     """Reference: avdiff/utils/ops.py:48-93.  Windows are summed in order i = 0..N-1 (the reference's
-    sequential ``+=``) and divided by max(overlap count, 1e-8).  C ABI: avd_unchunk1d."""
-    if apply_hann:
-        raise NotImplementedError("apply_hann=True is not on the sampling hot path (SURVEY.md §8 N4)")
+    sequential ``+=``) and divided by max(overlap count, 1e-8).  C ABI: avd_unchunk1d; with apply_hann=True the
+    windows are weighted by torch.hann_window(W) and divided by the summed weights (avd_overlap_add_win)."""
     if length is None:
         length = windows.size(-1)
     nd = windows.dim()
@@ -59,7 +58,14 @@ def overlap_add_1d(windows: torch.Tensor, stride: int, length: Optional[int] = N
     rows = 1
     for s in prefix:
         rows *= int(s)
-    if rows > 0 and L_out > 0:
+    if rows > 0 and L_out > 0 and apply_hann:
+        win = torch.hann_window(W, dtype=torch.float32).to(w.device)     # the reference's window, computed by torch
+        for r0 in range(0, rows, 65535):                                  # grid.y limit of the kernel
+            r1 = min(rows, r0 + 65535)
+            _lib.check(_lib.load().avd_overlap_add_win(w.reshape(rows, N, W)[r0:r1].data_ptr(), win.data_ptr(),
+                                                       y.reshape(rows, L_out)[r0:r1].data_ptr(), r1 - r0, N, W,
+                                                       stride, 1e-8, _lib.stream_ptr()))
+    elif rows > 0 and L_out > 0:
         _lib.check(_lib.load().avd_unchunk1d(w.data_ptr(), y.data_ptr(), rows, 1, N, W, stride, L_out,
                                              _lib.stream_ptr()))
     return y

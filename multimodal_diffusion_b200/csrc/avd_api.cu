@@ -453,6 +453,10 @@ int avd_unchunk1d(const float* tok, float* z, int B, int C, int N, int length, i
 int avd_crossfade_audio(const float* chunks, const float* w, float* out, int N, int L, int hop, void* stream) {
   return launch_crossfade_audio(chunks, w, out, N, L, hop, AVD_STREAM(stream));
 }
+int avd_overlap_add_win(const float* windows, const float* win, float* y, int rows, int N, int W, int stride,
+                        float norm_floor, void* stream) {
+  return launch_overlap_add_win(windows, win, y, rows, N, W, stride, norm_floor, AVD_STREAM(stream));
+}
 int avd_crossfade_video(const uint8_t* chunks, const float* w, uint8_t* out, int N, int T, int64_t frame_bytes, int hop,
                         void* stream) {
   return launch_crossfade_video(chunks, w, out, N, T, frame_bytes, hop, AVD_STREAM(stream));

@@ -72,6 +72,8 @@ int launch_chunk1d(const float* z, float* tok, int B, int C, int L, int length, 
 int launch_unchunk1d(const float* tok, float* z, int B, int C, int N, int length, int stride, int L_out,
                      cudaStream_t s);
 int launch_crossfade_audio(const float* chunks, const float* w, float* out, int N, int L, int hop, cudaStream_t s);
+int launch_overlap_add_win(const float* chunks, const float* w, float* out, int rows, int N, int L, int hop,
+                           float norm_floor, cudaStream_t s);
 int launch_crossfade_video(const uint8_t* chunks, const float* w, uint8_t* out, int N, int T, int64_t F, int hop,
                            cudaStream_t s);
 int launch_timestep_embedding(const float* t, float* emb, int B, int dim, float max_period, cudaStream_t s);

@@ -13,11 +13,15 @@
 namespace avd {
 
 // ---------------------------------------------------------------------------------------------------- audio
-// chunks [N, L] fp32, w [L] fp32, out [(N-1)*hop + L] fp32
+// chunks [rows, N, L] fp32, w [L] fp32, out [rows, (N-1)*hop + L] fp32; blockIdx.y = row.  rows = 1 and floor = 1e-6 is
+// stream_infer.crossfade_audio; rows = B*C, w = hann and floor = 1e-8 is ops.overlap_add_1d(apply_hann=True)
+// (avdiff/utils/ops.py:82-92), the same arithmetic in torch.
 template <int VEC>
 __global__ void __launch_bounds__(256) crossfade_audio_kernel(const float* __restrict__ chunks,
                                                               const float* __restrict__ w, float* __restrict__ out,
-                                                              int N, int L, int hop, int64_t T_out) {
+                                                              int N, int L, int hop, int64_t T_out, float floor_) {
+  chunks += (int64_t)blockIdx.y * N * L;
+  out += (int64_t)blockIdx.y * T_out;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x * VEC;
   for (int64_t t0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * VEC; t0 < T_out; t0 += stride) {
     // windows covering t0 .. t0+VEC-1 (VEC > 1 only when hop % VEC == 0 and L % VEC == 0: the VEC samples then share
@@ -48,30 +52,36 @@ __global__ void __launch_bounds__(256) crossfade_audio_kernel(const float* __res
     }
     float r[VEC];
 #pragma unroll
-    for (int v = 0; v < VEC; ++v) r[v] = __fdiv_rn(acc[v], fmaxf(nrm[v], 1e-6f));   // (:111-112)
+    for (int v = 0; v < VEC; ++v) r[v] = __fdiv_rn(acc[v], fmaxf(nrm[v], floor_));   // (:111-112)
     if (VEC == 4) *reinterpret_cast<float4*>(out + t0) = make_float4(r[0], r[1 % VEC], r[2 % VEC], r[3 % VEC]);
     else out[t0] = r[0];
   }
 }
 
-int launch_crossfade_audio(const float* chunks, const float* w, float* out, int N, int L, int hop, cudaStream_t s) {
+int launch_overlap_add_win(const float* chunks, const float* w, float* out, int rows, int N, int L, int hop,
+                           float norm_floor, cudaStream_t s) {
   AVD_REQUIRE(chunks != nullptr && w != nullptr && out != nullptr, "null pointer");
-  AVD_REQUIRE(N > 0 && L > 0 && hop > 0, "crossfade_audio needs N, L, hop > 0");
+  AVD_REQUIRE(rows > 0 && rows <= 65535 && N > 0 && L > 0 && hop > 0, "windowed overlap-add needs 0 < rows <= 65535 and N, L, hop > 0");
   const int64_t T_out = (int64_t)(N - 1) * hop + L;
   int dev = 0, sms = 148;
   if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  const bool vec4 = (hop % 4 == 0) && (L % 4 == 0) && ((reinterpret_cast<uintptr_t>(chunks) | reinterpret_cast<uintptr_t>(w) |
+  const bool vec4 = (hop % 4 == 0) && (L % 4 == 0) && (T_out % 4 == 0) && ((reinterpret_cast<uintptr_t>(chunks) | reinterpret_cast<uintptr_t>(w) |
                                                         reinterpret_cast<uintptr_t>(out)) % 16 == 0);
   const int64_t items = vec4 ? T_out / 4 : T_out;
   int64_t blocks = (items + 255) / 256;
-  const int64_t cap = (int64_t)sms * 16;               // grid-stride beyond 16 resident blocks per SM
+  const int64_t cap = ((int64_t)sms * 16 + rows - 1) / rows;   // grid-stride beyond 16 resident blocks per SM
   if (blocks > cap) blocks = cap;
   if (kind_skipped(KIND_TOKENIZE)) return 0;
   LaunchScope ls(KIND_TOKENIZE, s);
-  if (vec4) crossfade_audio_kernel<4><<<(unsigned)blocks, 256, 0, s>>>(chunks, w, out, N, L, hop, T_out);
-  else crossfade_audio_kernel<1><<<(unsigned)blocks, 256, 0, s>>>(chunks, w, out, N, L, hop, T_out);
+  const dim3 grid((unsigned)blocks, (unsigned)rows);
+  if (vec4) crossfade_audio_kernel<4><<<grid, 256, 0, s>>>(chunks, w, out, N, L, hop, T_out, norm_floor);
+  else crossfade_audio_kernel<1><<<grid, 256, 0, s>>>(chunks, w, out, N, L, hop, T_out, norm_floor);
   AVD_CUDA(cudaGetLastError());
   return 0;
+}
+
+int launch_crossfade_audio(const float* chunks, const float* w, float* out, int N, int L, int hop, cudaStream_t s) {
+  return launch_overlap_add_win(chunks, w, out, 1, N, L, hop, 1e-6f, s);
 }
 
 // ---------------------------------------------------------------------------------------------------- video

@@ -55,6 +55,16 @@ def main() -> None:
     d["v_gen2"] = vgen2
     d["v_odd"] = ref.crossfade_video(vgen2, hop=5, win=7, fade_f=3)
     d["v_short"] = ref.split_frames_into_windows(fr[:30], fps=16, win_s=3.0, hop_s=1.0)[0]
+    # ops.overlap_add_1d(apply_hann=True) (avdiff/utils/ops.py:82-92): same arithmetic with a Hann window, clamp 1e-8
+    import torch
+    from avdiff.utils import ops
+    hw = rng.standard_normal((5, 3, 9, 5)).astype(np.float32)
+    d["hann_in"] = hw
+    for s in (3, 5, 7):
+        d[f"hann_s{s}"] = ops.overlap_add_1d(torch.from_numpy(hw), stride=s, apply_hann=True).numpy()
+    hw2 = rng.standard_normal((2, 8, 37, 16)).astype(np.float32)
+    d["hann_in2"] = hw2
+    d["hann2_s4"] = ops.overlap_add_1d(torch.from_numpy(hw2), stride=4, apply_hann=True).numpy()
     np.savez_compressed(OUT / "stream.npz", **d)
     print({k: v.shape for k, v in d.items()})
 

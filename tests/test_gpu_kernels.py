@@ -304,6 +304,20 @@ def test_crossfade_audio_bit_exact(dev):
         si.crossfade_audio(np.zeros((2, 100), np.float32), 16000, 50, 100, 1.0)      # fade longer than the window
 
 
+def test_overlap_add_hann_bit_exact(dev):
+    """ops.overlap_add_1d(apply_hann=True) (§8f N4) through avd_overlap_add_win against the reference's outputs."""
+    from multimodal_diffusion_b200.avdiff.utils import ops
+    g = golden("stream")
+    w = torch.from_numpy(g["hann_in"]).to(dev)
+    for s in (3, 5, 7):
+        assert np.array_equal(ops.overlap_add_1d(w, stride=s, apply_hann=True).cpu().numpy(), g[f"hann_s{s}"])
+    w2 = torch.from_numpy(g["hann_in2"]).to(dev)
+    assert np.array_equal(ops.overlap_add_1d(w2, stride=4, apply_hann=True).cpu().numpy(), g["hann2_s4"])
+    x = randn(31, 3, 20, 12, 8)                                   # windows on dim 2 (not the default -2)
+    want = orc.overlap_add_1d(x, stride=5, dim_windows=2, apply_hann=True)
+    assert torch.equal(ops.overlap_add_1d(x.to(dev), stride=5, dim_windows=2, apply_hann=True).cpu(), want)
+
+
 def test_crossfade_video_bit_exact(dev):
     from oracle import stream_oracle as so
     from multimodal_diffusion_b200.avdiff.models.infer import stream_infer as si

@@ -173,6 +173,11 @@ def test_stream_oracle_and_host_split_match_reference():
     assert np.array_equal(so.crossfade_video(g["v_gen2"], 5, 7, 3), g["v_odd"])
     assert np.array_equal(si.audio_fade_window(3000, 250), so.audio_window(3000, 250))
     assert np.array_equal(si.video_fade_window(48, 4), so.video_window(48, 4))
+    for s in (3, 5, 7):
+        assert np.array_equal(orc.overlap_add_1d(torch.from_numpy(g["hann_in"]), stride=s, apply_hann=True).numpy(),
+                              g[f"hann_s{s}"])
+    assert np.array_equal(orc.overlap_add_1d(torch.from_numpy(g["hann_in2"]), stride=4, apply_hann=True).numpy(),
+                          g["hann2_s4"])
     # hop larger than the window and a hop that overshoots the end (the while-loop's exit conditions)
     for total, w_, h_ in ((10, 3, 8), (10, 3, 20), (9, 3, 3), (10, 3, 3)):
         assert si._window_starts(total, w_, h_) == so.window_starts(total, w_, h_)
