@@ -185,6 +185,10 @@ int avd_gemm(const avd_gemm_args* g, void* stream);
  * out: bf16 segments [nseg(out_precision)][n_seq*N][d]. */
 int avd_attention(const void* qkv, int qkv_is_f32, void* out_bf16, int out_precision, int n_seq, int N, int n_heads,
                   int head_dim, void* stream);
+/* the same with nn.MultiheadAttention's key_padding_mask (mmdt.py:58-60) as bit words [n_seq][ceil(N/32)] (bit set =
+ * key ignored; layout of avd_core_workspace.key_mask); key_mask == NULL is avd_attention */
+int avd_attention_masked(const void* qkv, int qkv_is_f32, void* out_bf16, int out_precision, int n_seq, int N,
+                         int n_heads, int head_dim, const unsigned int* key_mask, void* stream);
 
 /* ---------------------------------------------------------------- K6: MMDT core + noise head */
 typedef struct {
@@ -207,6 +211,9 @@ typedef struct {
  *   att bf16 [S][M,d]; hmid bf16 [S][M,d_mlp]. */
 typedef struct {
   float* x; void* xa; float* ssq; void* qkv; void* att; void* hmid;
+  /* MMDiT.forward's key_padding_mask (mmdt.py:58-60, 134-147) packed as bits: word [seq * ceil(N/32) + k/32], bit k%32
+   * set = key k of sequence seq is padding and takes no part in any softmax.  NULL = no mask (what the sampler uses). */
+  const unsigned int* key_mask;
 } avd_core_workspace;
 
 /* MMDiT.forward minus the final norm (mmdt.py:146-147): runs n_layers blocks.  Reads the input residual

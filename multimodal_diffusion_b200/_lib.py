@@ -69,7 +69,7 @@ class CoreWeights(C.Structure):
 
 
 class CoreWorkspace(C.Structure):
-    _fields_ = [("x", fp), ("xa", vp), ("ssq", fp), ("qkv", vp), ("att", vp), ("hmid", vp)]
+    _fields_ = [("x", fp), ("xa", vp), ("ssq", fp), ("qkv", vp), ("att", vp), ("hmid", vp), ("key_mask", vp)]
 
 
 class HeadWeights(C.Structure):
@@ -127,6 +127,7 @@ _SIGNATURES = {
     "avd_layernorm_act": (_I, [fp, fp, fp, _I, _I, C.c_float, _I, fp, vp, _I, vp]),
     "avd_gemm": (_I, [C.POINTER(GemmArgs), vp]),
     "avd_attention": (_I, [vp, _I, vp, _I, _I, _I, _I, _I, vp]),
+    "avd_attention_masked": (_I, [vp, _I, vp, _I, _I, _I, _I, _I, vp, vp]),
     "avd_mmdt_blocks": (_I, [C.POINTER(CoreWeights), fp, vp, fp, C.POINTER(CoreWorkspace), _I, _I, vp]),
     "avd_head_forward": (_I, [C.POINTER(HeadWeights), vp, _I, vp, vp, fp, fp, vp]),
     "avd_sampler_workspace_bytes": (C.c_int64, [C.POINTER(SamplerArgs)]),

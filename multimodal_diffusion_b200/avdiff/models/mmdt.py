@@ -73,11 +73,16 @@ class MHA(nn.Module):
     def forward(self, x: torch.Tensor, attn_mask: Optional[torch.Tensor] = None,
                 key_padding_mask: Optional[torch.Tensor] = None):
         _no_grad_only(self)
-        if attn_mask is not None or key_padding_mask is not None:
-            raise NotImplementedError("attention masks are not used by the sampler (SURVEY.md §8 N4)")
+        if attn_mask is not None:
+            raise NotImplementedError("attn_mask is not used by MMDiT or the sampler (SURVEY.md §8 N4)")
         xc = _lib.require_cuda_f32(x, "x")
         B, N, d = xc.shape
         M, H = B * N, self.mha.num_heads
+        bits = None
+        if key_padding_mask is not None:
+            if key_padding_mask.shape != (B, N) or key_padding_mask.dtype != torch.bool:
+                raise ValueError("key_padding_mask must be a bool tensor of shape [B, N]")
+            bits = packing.pack_key_padding_mask(key_padding_mask.to(xc.device))
         prec = _lib.precision_code(self.precision)
         wq = packing.pack_linear_weight(self.mha.in_proj_weight.detach(), prec)
         wo = packing.pack_linear_weight(self.mha.out_proj.weight.detach(), prec)
@@ -91,8 +96,9 @@ class MHA(nn.Module):
                      out_precision=prec if f16 else _lib.AVD_PREC_BF16,
                      a_scale=1.0 / _lib.AVD_F16_XSCALE if f16 else 0.0)   # rows_prepare pre-scales fp16 operands
         att = torch.empty(S, M, d, device=xc.device, dtype=torch.bfloat16)
-        _lib.check(_lib.load().avd_attention(qkv.data_ptr(), 0 if tc else 1, att.data_ptr(), prec, B, N, H, d // H,
-                                             _lib.stream_ptr()))
+        _lib.check(_lib.load().avd_attention_masked(qkv.data_ptr(), 0 if tc else 1, att.data_ptr(), prec, B, N, H,
+                                                    d // H, None if bits is None else bits.data_ptr(),
+                                                    _lib.stream_ptr()))
         y = torch.empty(M, d, device=xc.device, dtype=torch.float32)
         packing.gemm(att, wo, M, d, d, prec, bias=self.mha.out_proj.bias.detach(), out_f32=y)
         return y.view(B, N, d)
@@ -138,7 +144,7 @@ class _CoreRunner:
         self._key = None
 
     def run(self, owner: nn.Module, sd, n_layers: int, n_heads: int, precision, x: torch.Tensor,
-            apply_final_norm: bool) -> torch.Tensor:
+            apply_final_norm: bool, key_padding_mask: Optional[torch.Tensor] = None) -> torch.Tensor:
         xc = _lib.require_cuda_f32(x, "x")
         B, N, d = xc.shape
         prec = _lib.precision_code(precision)
@@ -153,6 +159,11 @@ class _CoreRunner:
             return out
         xa, ssq = packing.rows_prepare(xc.view(M, d), prec)
         ws, bufs = packing.core_workspace(M, d, pc.d_mlp, prec, xc.device)
+        if key_padding_mask is not None:
+            if key_padding_mask.shape != (B, N) or key_padding_mask.dtype != torch.bool:
+                raise ValueError("key_padding_mask must be a bool tensor of shape [B, N]")
+            bits = packing.pack_key_padding_mask(key_padding_mask.to(xc.device))
+            ws.key_mask = bits.data_ptr()
         _lib.check(_lib.load().avd_mmdt_blocks(C.byref(pc.struct), xc.data_ptr(), xa.data_ptr(), ssq.data_ptr(),
                                                C.byref(ws), B, N, _lib.stream_ptr()))
         if not apply_final_norm:
@@ -178,13 +189,14 @@ class Block(nn.Module):
     def forward(self, x: torch.Tensor, attn_mask: Optional[torch.Tensor] = None,
                 key_padding_mask: Optional[torch.Tensor] = None):
         _no_grad_only(self)
-        if attn_mask is not None or key_padding_mask is not None:
-            raise NotImplementedError("attention masks are not used by the sampler (SURVEY.md §8 N4)")
+        if attn_mask is not None:
+            raise NotImplementedError("attn_mask is not used by MMDiT or the sampler (SURVEY.md §8 N4)")
         if not isinstance(self.norm1, RMSNorm):
             raise NotImplementedError('only norm="rmsnorm" is implemented (SURVEY.md §8 N4)')
         sd = {"blocks.0." + k: v for k, v in self.state_dict().items()}
         sd["final_norm.scale"] = torch.ones_like(self.norm1.scale)
-        return self._runner.run(self, sd, 1, self.n_heads, self.precision, x, apply_final_norm=False)
+        return self._runner.run(self, sd, 1, self.n_heads, self.precision, x, apply_final_norm=False,
+                                key_padding_mask=key_padding_mask)
 
 
 @dataclass
@@ -219,12 +231,10 @@ class MMDiT(nn.Module):
         _no_grad_only(self)
         if self.training and self.cfg.token_dropout > 0.0:
             raise NotImplementedError("token_dropout is a training-time feature; the sampler runs in eval mode")
-        if key_padding_mask is not None:
-            raise NotImplementedError("key_padding_mask is never passed by the sampler (SURVEY.md §8 N4)")
         if self.cfg.norm.lower() != "rmsnorm":
             raise NotImplementedError('only norm="rmsnorm" is implemented (SURVEY.md §8 N4)')
         if self.cfg.d_model % self.cfg.n_heads or (self.cfg.d_model // self.cfg.n_heads) != 64 and \
                 _lib.precision_code(self.precision) in (_lib.AVD_PREC_BF16, _lib.AVD_PREC_F16):
             raise NotImplementedError("the tcgen05 attention kernel is built for head_dim 64")
         return self._runner.run(self, self.state_dict(), self.cfg.n_layers, self.cfg.n_heads, self.precision, x,
-                                apply_final_norm=True)
+                                apply_final_norm=True, key_padding_mask=key_padding_mask)

@@ -260,8 +260,9 @@ static int core_blocks(const avd_core_weights* w, const float* x_in, const void*
     else g.out_f32 = static_cast<float*>(ws->qkv);
     AVD_TRY(launch_gemm(g, st));
     // a = softmax(q k^T / sqrt(hd)) v
-    if (tc_attn) AVD_TRY(launch_attention_tc(ws->qkv, ws->att, S, n_seq, N, w->n_heads, hd, st, f16));
-    else AVD_TRY(launch_attention_f32(static_cast<const float*>(ws->qkv), ws->att, S, n_seq, N, w->n_heads, hd, st));
+    if (tc_attn) AVD_TRY(launch_attention_tc(ws->qkv, ws->att, S, n_seq, N, w->n_heads, hd, st, f16, ws->key_mask));
+    else AVD_TRY(launch_attention_f32(static_cast<const float*>(ws->qkv), ws->att, S, n_seq, N, w->n_heads, hd, st,
+                                      ws->key_mask));
     // x = x + a W_o^T + b_o               (mmdt.py:97)
     g = avd_gemm_args{};
     g.M = M; g.N = d; g.K = d; g.precision = w->precision;
@@ -522,14 +523,18 @@ int avd_gemm(const avd_gemm_args* g, void* stream) {
   AVD_REQUIRE(g != nullptr, "null args");
   return launch_gemm(*g, AVD_STREAM(stream));
 }
-int avd_attention(const void* qkv, int qkv_is_f32, void* out_bf16, int out_precision, int n_seq, int N, int n_heads,
-                  int head_dim, void* stream) {
+int avd_attention_masked(const void* qkv, int qkv_is_f32, void* out_bf16, int out_precision, int n_seq, int N,
+                         int n_heads, int head_dim, const unsigned int* key_mask, void* stream) {
   AVD_REQUIRE(nseg_of(out_precision) > 0, "bad precision");
   if (qkv_is_f32)
     return launch_attention_f32(static_cast<const float*>(qkv), out_bf16, nseg_of(out_precision), n_seq, N, n_heads,
-                                head_dim, AVD_STREAM(stream));
+                                head_dim, AVD_STREAM(stream), key_mask);
   return launch_attention_tc(qkv, out_bf16, nseg_of(out_precision), n_seq, N, n_heads, head_dim, AVD_STREAM(stream),
-                             is_f16(out_precision));
+                             is_f16(out_precision), key_mask);
+}
+int avd_attention(const void* qkv, int qkv_is_f32, void* out_bf16, int out_precision, int n_seq, int N, int n_heads,
+                  int head_dim, void* stream) {
+  return avd_attention_masked(qkv, qkv_is_f32, out_bf16, out_precision, n_seq, N, n_heads, head_dim, nullptr, stream);
 }
 
 // ---- core / head
@@ -586,7 +591,7 @@ int avd_sample_step(const avd_sampler* s, int step, float* z, float* eps_tap, vo
   AVD_TRY(launch_build_x(a, z, tgt_mod == 0 ? s->wv_t : s->wa_t, tgt_mod == 0 ? s->bv : s->ba,
                          s->temb_steps + (int64_t)step * s->tstep_dim, x_init, ws + L.xa_init, ssq_init, st));
   // (2) 2B co-batched sequences through the blocks
-  avd_core_workspace cw;
+  avd_core_workspace cw{};                       // key_mask = NULL: the sampler never pads (sample_clip.py:341)
   cw.x = reinterpret_cast<float*>(ws + L.x);
   cw.xa = ws + L.xa;
   cw.ssq = reinterpret_cast<float*>(ws + L.ssq);

@@ -50,6 +50,8 @@ struct AttnParams {
   float scale_log2e;  // (1/sqrt(hd)) * log2(e)
   unsigned long long* trace;   // debug phase stamps (avd_debug_trace)
   int poly_exp;     // multi-block path: every second exponential on the FMA pipe (ex2_poly)
+  const uint32_t* kmask;   // key_padding_mask as bits [n_seq][kmask_words] (bit = 1: key ignored) or NULL
+  int kmask_words;         // ceil(N / 32)
 };
 
 __device__ __forceinline__ float ex2_approx(float x) {
@@ -93,15 +95,19 @@ __device__ __forceinline__ void att_mark(unsigned long long* trace, int slot) {
 // chain in the kernel.  Writes P (16-bit, K-major 128B-swizzled 64-key atoms, zero past the valid keys) and the row sum.
 template <bool F16>
 __device__ __forceinline__ void thin_row_softmax(const float* srow, uint8_t* sPt, float* l_out, int i, int lane,
-                                                 int kv_valid, int kv_n, float sc) {
+                                                 int kv_valid, int kv_n, float sc, const uint32_t* kmask) {
   float mx = -INFINITY;
-  for (int c = lane; c < kv_valid; c += 32) mx = fmaxf(mx, srow[c]);
+  uint32_t dead = 0;                                  // bit k: this lane's k-th column (lane + 32 k) is a padded key
+  if (kmask != nullptr)
+    for (int c = lane, k = 0; c < kv_valid; c += 32, ++k) dead |= ((kmask[c >> 5] >> lane) & 1u) << k;
+  for (int c = lane, k = 0; c < kv_valid; c += 32, ++k)
+    if (!((dead >> k) & 1u)) mx = fmaxf(mx, srow[c]);
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
   const float m_sc = mx * sc;
   float l = 0.0f;
-  for (int c = lane; c < kv_n; c += 32) {
-    const float pv = c < kv_valid ? ex2_approx(fmaf(srow[c], sc, -m_sc)) : 0.0f;
+  for (int c = lane, k = 0; c < kv_n; c += 32, ++k) {
+    const float pv = (c < kv_valid && !((dead >> k) & 1u)) ? ex2_approx(fmaf(srow[c], sc, -m_sc)) : 0.0f;
     l += pv;
     uint8_t* dst = sPt + (c >> 6) * ATT_Q_BYTES + i * 128 + ((((c & 63) >> 3) ^ (i & 7)) << 4) + (c & 7) * 2;
     if (F16) *reinterpret_cast<__half*>(dst) = __float2half_rn(pv);
@@ -116,7 +122,7 @@ __device__ __forceinline__ void thin_row_softmax(const float* srow, uint8_t* sPt
 // barrier slots
 enum { AB_Q = 0, AB_K = 1, AB_V = 2, AB_S = 3 /*+t*/, AB_P = 5 /*+t*/, AB_O = 7 /*+t*/, AB_R = 9 /*+t*/, AB_COUNT = 11 };
 
-template <bool ONE_BLOCK, bool F16>   // F16: q/k/v, P and the output are fp16 (AVD_PREC_F16) instead of bf16.  ONE_BLOCK: N <= 192 keys, the whole score row stays in registers (single softmax pass)
+template <bool ONE_BLOCK, bool F16, bool MASKED>   // MASKED: key_padding_mask bits present (its own instantiation: the single-block kernel sits at its 128-register limit). F16: q/k/v, P and the output are fp16 (AVD_PREC_F16) instead of bf16.  ONE_BLOCK: N <= 192 keys, the whole score row stays in registers (single softmax pass)
 __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ,
                                                                  const __grid_constant__ CUtensorMap tmKV,
                                                                  const AttnParams p) {
@@ -144,6 +150,14 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
   const int colQ = head * ATT_HD, colK = p.d + head * ATT_HD, colV = 2 * p.d + head * ATT_HD;
   const int nkv = (p.N + ATT_BKV - 1) / ATT_BKV;
   const bool POLY_EXP = p.poly_exp != 0;
+  // (the mask pointer is read from the kernel parameters where it is used: keeping it live costs the single-block
+  // kernel, which sits at its 128-register limit, a spill)
+  // bit c set = column c of 32-key chunk `ch` of key block `j` takes part in the softmax (inside the sequence, not padded)
+  auto valid_bits = [&](int j, int ch, int lim) -> uint32_t {
+    uint32_t v = lim >= 32 ? 0xffffffffu : (lim > 0 ? ((1u << lim) - 1u) : 0u);
+    if (MASKED && lim > 0) v &= ~p.kmask[(size_t)blockIdx.z * p.kmask_words + j * (ATT_BKV / 32) + ch];
+    return v;
+  };
   // thin second tile: its softmax is spread over the tile's 8 warps (one row each) through smem instead of running
   // thread-per-row on the two warps that may touch its TMEM lanes
   const int rows1 = p.N - q_first - ATT_BQ;
@@ -258,21 +272,24 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
           }
           named_bar_sync(9, 256);                    // all 8 warps of the tile: scores are in smem
           if ((warp & 7) < rows1)
-            thin_row_softmax<F16>(thin_sc + (warp & 7) * ATT_BKV, sPt, thin_l, warp & 7, lane, kv_valid, kv_n, sc);
+            thin_row_softmax<F16>(thin_sc + (warp & 7) * ATT_BKV, sPt, thin_l, warp & 7, lane, kv_valid, kv_n, sc,
+                                  MASKED ? p.kmask + (size_t)blockIdx.z * p.kmask_words : nullptr);
           named_bar_sync(10, 256);                   // P rows and row sums written
           alpha = 0.0f;
           l_blk = (sp == 0 && r < rows1) ? thin_l[r] : 0.0f;
         } else {
         float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
+#pragma unroll
         for (int i = 0; i < 3; ++i) {
-          const int lim = kv_valid - (ch0 + i) * 32;
-          if (lim >= 32) {                           // whole chunk of valid keys: no masking
+          const uint32_t vb = valid_bits(j, ch0 + i, kv_valid - (ch0 + i) * 32);
+          if (vb == 0xffffffffu) {                   // whole chunk of valid keys: no masking
 #pragma unroll
             for (int c = 0; c < 32; ++c) mx[c & 3] = fmaxf(mx[c & 3], __uint_as_float(x[i][c]));
-          } else if (lim > 0) {
+          } else if (vb != 0u) {
 #pragma unroll
-            for (int c = 0; c < 32; ++c) mx[c & 3] = fmaxf(mx[c & 3], c < lim ? __uint_as_float(x[i][c]) : -INFINITY);
+            for (int c = 0; c < 32; ++c)
+              mx[c & 3] = fmaxf(mx[c & 3], ((vb >> c) & 1u) ? __uint_as_float(x[i][c]) : -INFINITY);
           }
         }
         const float m_part = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
@@ -290,7 +307,8 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
           if (lim > -16) {                           // chunks wholly past round16(keys) are never read by the PV MMA
             float l0 = 0.0f, l1 = 0.0f;
             uint32_t w[16];
-            if (lim >= 32) {                         // whole chunk of valid keys: no masking
+            const uint32_t vb = valid_bits(j, ch, lim);
+            if (vb == 0xffffffffu) {                 // whole chunk of valid keys: no masking
 #pragma unroll
               for (int c = 0; c < 32; c += 2) {
                 const float p0 = ex2_approx(fmaf(__uint_as_float(x[i][c]), sc, -m_sc));
@@ -304,8 +322,8 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
               for (int c = 0; c < 32; c += 2) {
                 float p0 = ex2_approx(fmaf(__uint_as_float(x[i][c]), sc, -m_sc));
                 float p1 = ex2_approx(fmaf(__uint_as_float(x[i][c + 1]), sc, -m_sc));
-                p0 = c < lim ? p0 : 0.0f;
-                p1 = c + 1 < lim ? p1 : 0.0f;
+                p0 = ((vb >> c) & 1u) ? p0 : 0.0f;
+                p1 = ((vb >> (c + 1)) & 1u) ? p1 : 0.0f;
                 l0 += p0;
                 l1 += p1;
                 w[c >> 1] = F16 ? pack_f16x2(p0, p1) : pack_bf16x2(p0, p1);
@@ -328,26 +346,27 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
           uint32_t x[32];
           tmem_ld_32x32(tmem_S + ch * 32, x);
           tmem_ld_wait();
-          const int lim = kv_valid - ch * 32;
+          const uint32_t vm = valid_bits(j, ch, kv_valid - ch * 32);
 #pragma unroll
-          for (int c = 0; c < 32; ++c) mx[c & 3] = fmaxf(mx[c & 3], c < lim ? __uint_as_float(x[c]) : -INFINITY);
+          for (int c = 0; c < 32; ++c) mx[c & 3] = fmaxf(mx[c & 3], ((vm >> c) & 1u) ? __uint_as_float(x[c]) : -INFINITY);
         }
         const float m_part = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
         xm[sp * 128 + r] = m_part;
         named_bar_sync(pair_bar, 64);
         const float m_new = fmaxf(m_run, fmaxf(m_part, xm[(sp ^ 1) * 128 + r]));
-        alpha = ex2_approx((m_run - m_new) * sc);   // m_run = -inf on the first block -> 0
-        const float m_sc = m_new * sc;
+        const float m_use = m_new == -INFINITY ? 0.0f : m_new;   // every key so far padded: keep the exponents finite
+        alpha = ex2_approx((m_run - m_use) * sc);   // m_run = -inf on the first block -> 0
+        const float m_sc = m_use * sc;
         m_run = m_new;
         // ---- pass 2: p = exp2(s*c - m*c), row sum, P -> smem (K-major, 128B swizzle, 64-key atoms)
         for (int ch = ch0; ch < ch1; ++ch) {
           uint32_t x[32];
           tmem_ld_32x32(tmem_S + ch * 32, x);
           tmem_ld_wait();
-          const int lim = kv_valid - ch * 32;
+          const uint32_t vm = valid_bits(j, ch, kv_valid - ch * 32);
           float l0 = 0.0f, l1 = 0.0f;
           uint32_t w[16];
-          if (lim >= 32 && POLY_EXP) {               // whole chunk of valid keys, MUFU and FMA pipes share the exponentials
+          if (vm == 0xffffffffu && POLY_EXP) {               // whole chunk of valid keys, MUFU and FMA pipes share the exponentials
 #pragma unroll
             for (int c = 0; c < 32; c += 2) {
               const float p0 = ex2_approx(fmaf(__uint_as_float(x[c]), sc, -m_sc));
@@ -356,7 +375,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
               l1 += p1;
               w[c >> 1] = F16 ? pack_f16x2(p0, p1) : pack_bf16x2(p0, p1);
             }
-          } else if (lim >= 32) {
+          } else if (vm == 0xffffffffu) {
 #pragma unroll
             for (int c = 0; c < 32; c += 2) {
               const float p0 = ex2_approx(fmaf(__uint_as_float(x[c]), sc, -m_sc));
@@ -370,8 +389,8 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
             for (int c = 0; c < 32; c += 2) {
               float p0 = ex2_approx(fmaf(__uint_as_float(x[c]), sc, -m_sc));
               float p1 = ex2_approx(fmaf(__uint_as_float(x[c + 1]), sc, -m_sc));
-              p0 = c < lim ? p0 : 0.0f;
-              p1 = c + 1 < lim ? p1 : 0.0f;
+              p0 = ((vm >> c) & 1u) ? p0 : 0.0f;
+              p1 = ((vm >> (c + 1)) & 1u) ? p1 : 0.0f;
               l0 += p0;
               l1 += p1;
               w[c >> 1] = F16 ? pack_f16x2(p0, p1) : pack_bf16x2(p0, p1);
@@ -483,7 +502,8 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
     named_bar_sync(9, 256);
     if ((warp & 7) < rows1)
       thin_row_softmax<F16>(thin_sc + (warp & 7) * ATT_BKV, sP + ATT_P_BYTES, thin_l, warp & 7, lane, p.N,
-                            (p.N + 15) & ~15, p.scale_log2e);
+                            (p.N + 15) & ~15, p.scale_log2e,
+                            MASKED ? p.kmask + (size_t)blockIdx.z * p.kmask_words : nullptr);
     named_bar_sync(10, 256);
   }
 
@@ -497,7 +517,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
 }
 
 int launch_attention_tc(const void* qkv_bf16, void* out, int out_nseg, int n_seq, int N, int n_heads, int hd,
-                        cudaStream_t s, bool f16) {
+                        cudaStream_t s, bool f16, const uint32_t* kmask) {
   AVD_REQUIRE(hd == ATT_HD, "tcgen05 attention kernel is built for head_dim 64");
   AVD_REQUIRE(n_seq > 0 && N > 0 && n_heads > 0, "empty attention");
   AVD_REQUIRE(out_nseg >= 1 && out_nseg <= 3, "bad output precision");
@@ -508,12 +528,18 @@ int launch_attention_tc(const void* qkv_bf16, void* out, int out_nseg, int n_seq
                             ATT_HD, ATT_BQ, &tmQ));
   AVD_TRY(get_tensor_map_3d(qkv_bf16, 2, (uint64_t)3 * d, (uint64_t)M, 1, (uint64_t)3 * d * 2, (uint64_t)M * 3 * d * 2,
                             ATT_HD, ATT_BKV, &tmKV));
+  using AttnFn = void (*)(const CUtensorMap, const CUtensorMap, const AttnParams);
+  // [one_block][f16][masked]
+  static const AttnFn kernels[2][2][2] = {
+      {{attn_tc_kernel<false, false, false>, attn_tc_kernel<false, false, true>},
+       {attn_tc_kernel<false, true, false>, attn_tc_kernel<false, true, true>}},
+      {{attn_tc_kernel<true, false, false>, attn_tc_kernel<true, false, true>},
+       {attn_tc_kernel<true, true, false>, attn_tc_kernel<true, true, true>}}};
   static bool attr_set = false;
   if (!attr_set) {
-    AVD_CUDA(cudaFuncSetAttribute(attn_tc_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM));
-    AVD_CUDA(cudaFuncSetAttribute(attn_tc_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM));
-    AVD_CUDA(cudaFuncSetAttribute(attn_tc_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM));
-    AVD_CUDA(cudaFuncSetAttribute(attn_tc_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM));
+    for (int a = 0; a < 8; ++a)
+      AVD_CUDA(cudaFuncSetAttribute(kernels[a >> 2][(a >> 1) & 1][a & 1], cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    ATT_SMEM));
     attr_set = true;
   }
   AttnParams p{};
@@ -521,9 +547,11 @@ int launch_attention_tc(const void* qkv_bf16, void* out, int out_nseg, int n_seq
   p.out = static_cast<__nv_bfloat16*>(out);
   p.out_nseg = out_nseg;
   p.scale_log2e = (1.0f / sqrtf((float)hd)) * 1.4426950408889634f;
+  p.kmask = kmask;
+  p.kmask_words = (N + 31) / 32;
   {
     const char* e = std::getenv("AVD_ATTN_POLY");
-    p.poly_exp = e ? std::atoi(e) : 1;
+    p.poly_exp = e ? std::atoi(e) : 0;   // measured 12 % slower on B200: off unless asked for
   }
   {
     const int64_t n_ctas = (int64_t)((N + 2 * ATT_BQ - 1) / (2 * ATT_BQ)) * n_heads * n_seq;
@@ -547,13 +575,8 @@ int launch_attention_tc(const void* qkv_bf16, void* out, int out_nseg, int n_seq
   LaunchScope ls(KIND_ATTN_TC, s);
   AVD_REQUIRE(!f16 || out_nseg == 1, "the fp16 attention output has one segment");
   static const int one_block_on = std::getenv("AVD_ATTN_ONE") ? std::atoi(std::getenv("AVD_ATTN_ONE")) : 1;   // A/B switch
-  if (N <= ATT_BKV && one_block_on) {
-    if (f16) AVD_CUDA(cudaLaunchKernelEx(&cfg, attn_tc_kernel<true, true>, tmQ, tmKV, p));
-    else AVD_CUDA(cudaLaunchKernelEx(&cfg, attn_tc_kernel<true, false>, tmQ, tmKV, p));
-  } else {
-    if (f16) AVD_CUDA(cudaLaunchKernelEx(&cfg, attn_tc_kernel<false, true>, tmQ, tmKV, p));
-    else AVD_CUDA(cudaLaunchKernelEx(&cfg, attn_tc_kernel<false, false>, tmQ, tmKV, p));
-  }
+  AVD_CUDA(cudaLaunchKernelEx(&cfg, kernels[(N <= ATT_BKV && one_block_on) ? 1 : 0][f16 ? 1 : 0][kmask != nullptr ? 1 : 0],
+                              tmQ, tmKV, p));
   return 0;
 }
 
@@ -566,7 +589,8 @@ constexpr int AF_ROWS = 16;   // query rows per CTA
 
 __global__ void __launch_bounds__(AF_WARPS * 32) attn_f32_kernel(const float* __restrict__ qkv,
                                                                  __nv_bfloat16* __restrict__ out, int out_nseg, int N,
-                                                                 int d, int hd, int64_t M, float scale) {
+                                                                 int d, int hd, int64_t M, float scale,
+                                                                 const uint32_t* __restrict__ kmask, int kmask_words) {
   extern __shared__ float af_smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   float* sc = af_smem + (size_t)warp * N;                 // scores of this warp's current row
@@ -594,7 +618,8 @@ __global__ void __launch_bounds__(AF_WARPS * 32) attn_f32_kernel(const float* __
         acc = fmaf(qs[c + 2], k4.z, acc); acc = fmaf(qs[c + 3], k4.w, acc);
       }
       acc *= scale;
-      sc[j] = acc;
+      if (kmask != nullptr && ((kmask[(size_t)seq * kmask_words + (j >> 5)] >> (j & 31)) & 1u)) acc = -INFINITY;
+      sc[j] = acc;                               // padded key: exp(-inf - mx) = 0 below
       mx = fmaxf(mx, acc);
     }
 #pragma unroll
@@ -628,7 +653,7 @@ __global__ void __launch_bounds__(AF_WARPS * 32) attn_f32_kernel(const float* __
 }
 
 int launch_attention_f32(const float* qkv, void* out, int out_nseg, int n_seq, int N, int n_heads, int hd,
-                         cudaStream_t s) {
+                         cudaStream_t s, const uint32_t* kmask) {
   AVD_REQUIRE(hd % 4 == 0 && hd <= 256, "head_dim must be a multiple of 4, <= 256");
   AVD_REQUIRE(n_seq > 0 && N > 0 && n_heads > 0, "empty attention");
   const int d = n_heads * hd;
@@ -641,7 +666,7 @@ int launch_attention_f32(const float* qkv, void* out, int out_nseg, int n_seq, i
   if (kind_skipped(KIND_ATTN_F32)) return 0;
   LaunchScope ls(KIND_ATTN_F32, s);
   attn_f32_kernel<<<grid, AF_WARPS * 32, smem, s>>>(qkv, static_cast<__nv_bfloat16*>(out), out_nseg, N, d, hd,
-                                                    (int64_t)n_seq * N, 1.0f / sqrtf((float)hd));
+                                                    (int64_t)n_seq * N, 1.0f / sqrtf((float)hd), kmask, (N + 31) / 32);
   AVD_CUDA(cudaGetLastError());
   return 0;
 }

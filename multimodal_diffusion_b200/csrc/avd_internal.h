@@ -125,9 +125,9 @@ extern int64_t g_dbg_trace_slots;
 
 // attention (avd_attn.cu)
 int launch_attention_tc(const void* qkv_bf16, void* out, int out_nseg, int n_seq, int N, int n_heads, int hd,
-                        cudaStream_t s, bool f16 = false);
+                        cudaStream_t s, bool f16 = false, const uint32_t* kmask = nullptr);
 int launch_attention_f32(const float* qkv, void* out, int out_nseg, int n_seq, int N, int n_heads, int hd,
-                         cudaStream_t s);
+                         cudaStream_t s, const uint32_t* kmask = nullptr);
 
 // ---- TMA descriptor cache (avd_api.cu) ----------------------------------------------------------
 // bf16 tensor [d2][d1][d0] (d0 contiguous), box [1][box1][box0], SWIZZLE_128B (box0 * 2 bytes must be 128).

@@ -185,4 +185,17 @@ def core_workspace(M: int, d: int, d_mlp: int, precision: int, device):
     ws = _lib.CoreWorkspace()
     for k, t in bufs.items():
         setattr(ws, k, t.data_ptr())
+    ws.key_mask = None
     return ws, bufs
+
+
+def pack_key_padding_mask(mask: torch.Tensor) -> torch.Tensor:
+    """[B, N] bool (True = padding key, nn.MultiheadAttention's convention) -> int32 [B, ceil(N/32)] bit words, the
+    layout avd_core_workspace.key_mask documents."""
+    B, N = mask.shape
+    words = (N + 31) // 32
+    m = torch.zeros(B, words * 32, device=mask.device, dtype=torch.int64)
+    m[:, :N] = mask.to(torch.int64)
+    weights = torch.ones(32, device=mask.device, dtype=torch.int64) << torch.arange(32, device=mask.device)
+    packed = (m.view(B, words, 32) * weights).sum(-1)                  # 0 .. 2^32-1
+    return torch.where(packed >= 2 ** 31, packed - 2 ** 32, packed).to(torch.int32).contiguous()

@@ -279,6 +279,41 @@ def test_attention_fp32(dev, lib, n_seq, N):
     assert rel_l2(out.float().sum(0).cpu(), _attn_ref(qkv, n_seq, N, H, hd)) < 2e-6
 
 
+def _attn_ref_masked(qkv, n_seq, N, H, hd, mask):
+    d = H * hd
+    q, k, v = qkv.double().view(n_seq, N, 3, H, hd).permute(2, 0, 3, 1, 4)
+    s = (q @ k.transpose(-1, -2) / math.sqrt(hd)).masked_fill(mask[:, None, None, :], float("-inf"))
+    return (torch.softmax(s, dim=-1) @ v).permute(0, 2, 1, 3).reshape(n_seq * N, d)
+
+
+@pytest.mark.parametrize("n_seq,N", [(3, 133), (2, 128), (2, 445), (2, 40)])
+def test_attention_key_padding_mask(dev, lib, n_seq, N):
+    """nn.MultiheadAttention's key_padding_mask (mmdt.py:58-60; §8f N4) on both attention kernels: trailing padding of
+    different lengths per sequence plus scattered padded keys (a whole 32-key chunk among them)."""
+    from multimodal_diffusion_b200 import _lib, packing
+    H, hd = 8, 64
+    gen = torch.Generator().manual_seed(11)
+    mask = torch.rand(n_seq, N, generator=gen) < 0.15
+    for b in range(n_seq):
+        mask[b, N - 1 - 7 * b:] = True                  # ragged tails
+    if N > 100:
+        mask[0, 32:64] = True                           # one chunk fully padded
+    mask[:, 0] = False                                  # every row keeps at least one key
+    bits = packing.pack_key_padding_mask(mask.to(dev))
+    qkv = (randn(2, n_seq * N, 3 * H * hd) * 1.5)
+    want = _attn_ref_masked(qkv.bfloat16().float(), n_seq, N, H, hd, mask)
+    out = torch.zeros(1, n_seq * N, H * hd, device=dev, dtype=torch.bfloat16)
+    qd = qkv.bfloat16().to(dev)
+    _lib.check(lib.avd_attention_masked(qd.data_ptr(), 0, out.data_ptr(), _lib.AVD_PREC_BF16, n_seq, N, H, hd,
+                                        bits.data_ptr(), _lib.stream_ptr()))
+    assert rel_l2(out[0].float().cpu(), want) < 8e-3
+    out32 = torch.zeros(3, n_seq * N, H * hd, device=dev, dtype=torch.bfloat16)
+    q32 = qkv.to(dev)
+    _lib.check(lib.avd_attention_masked(q32.data_ptr(), 1, out32.data_ptr(), _lib.AVD_PREC_FP32, n_seq, N, H, hd,
+                                        bits.data_ptr(), _lib.stream_ptr()))
+    assert rel_l2(out32.float().sum(0).cpu(), _attn_ref_masked(qkv, n_seq, N, H, hd, mask)) < 3e-6
+
+
 # ------------------------------------------------------------------------------------------ streaming stitchers (§8f N2)
 def test_crossfade_audio_bit_exact(dev):
     """avd_crossfade_audio through the stream_infer mirror: reference fixtures, then seeded sizes against the oracle

@@ -254,6 +254,25 @@ def test_long_context_a2v_10s(dev, mods, w_cpu):
     assert rel_l2(z, z_or) < 1e-4
 
 
+@pytest.mark.parametrize("precision,tol", [("fp32", TOL_EPS_FP32), ("f16", 2e-3)])
+def test_mmdit_key_padding_mask(dev, mods, w_cpu, precision, tol):
+    """MMDiT.forward(x, key_padding_mask) (mmdt.py:134-147; §8f N4) against the oracle; outputs at padded positions are
+    defined too (padded QUERIES still attend to the valid keys), so the whole tensor is compared."""
+    core = mods[2]
+    core.precision = precision
+    x = randn(81, 3, 133, 512)
+    mask = torch.zeros(3, 133, dtype=torch.bool)
+    mask[0, 120:] = True
+    mask[1, 96:] = True                                  # e.g. a clip without audio tokens
+    mask[2, 5:9] = True
+    with torch.no_grad():
+        got = core(x.to(dev), key_padding_mask=mask.to(dev)).cpu()
+        want = orc.mmdit_forward(w_cpu["core"], x, 8, 8, key_padding_mask=mask)
+        plain = core(x.to(dev)).cpu()
+    assert rel_l2(got, want) < tol
+    assert rel_l2(plain[1], want[1]) > 5 * tol           # the mask matters (37 of 133 keys padded)
+
+
 def test_stream_sample_windows_as_batch(dev, mods):
     """§8f N2: the windows of a long prompt run as the batch dimension of the fused sampler; the result must not depend
     on the batch size (5 windows through a batch-2 sampler, last call padded, against a batch-1 sampler)."""
