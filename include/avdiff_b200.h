@@ -196,6 +196,9 @@ typedef struct {
   const void* w_o;    const float* b_o;     /* [d,d] */
   const void* w_fc1;  const float* b_fc1;   /* [d_mlp,d] with norm2.scale folded */
   const void* w_fc2;  const float* b_fc2;   /* [d,d_mlp] */
+  /* norm="layernorm" (mmdt.py:45-46, nn.LayerNorm): blocks.i.norm{1,2}.{weight,bias} [d]; w_qkv / w_fc1 are then packed
+   * WITHOUT a folded scale.  NULL for rmsnorm. */
+  const float* ln1_w; const float* ln1_b; const float* ln2_w; const float* ln2_b;
 } avd_block_weights;
 
 typedef struct {
@@ -204,6 +207,8 @@ typedef struct {
   float rms_eps;
   avd_block_weights blocks[AVD_MAX_LAYERS];
   const float* final_scale;                 /* final_norm.scale [d] */
+  int norm_kind;                            /* 0 = rmsnorm (folded into the following GEMM), 1 = layernorm (own pass) */
+  float ln_eps;                             /* nn.LayerNorm eps (1e-5) */
 } avd_core_weights;
 
 /* Caller-allocated work buffers for M = n_seq*N rows (S = avd_nseg(precision)):

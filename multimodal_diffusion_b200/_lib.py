@@ -59,13 +59,15 @@ class GemmArgs(C.Structure):
 
 class BlockWeights(C.Structure):
     _fields_ = [("w_qkv", vp), ("b_qkv", fp), ("w_o", vp), ("b_o", fp),
-                ("w_fc1", vp), ("b_fc1", fp), ("w_fc2", vp), ("b_fc2", fp)]
+                ("w_fc1", vp), ("b_fc1", fp), ("w_fc2", vp), ("b_fc2", fp),
+                ("ln1_w", fp), ("ln1_b", fp), ("ln2_w", fp), ("ln2_b", fp)]
 
 
 class CoreWeights(C.Structure):
     _fields_ = [("d_model", C.c_int), ("n_heads", C.c_int), ("n_layers", C.c_int), ("d_mlp", C.c_int),
                 ("precision", C.c_int), ("rms_eps", C.c_float),
-                ("blocks", BlockWeights * AVD_MAX_LAYERS), ("final_scale", fp)]
+                ("blocks", BlockWeights * AVD_MAX_LAYERS), ("final_scale", fp),
+                ("norm_kind", C.c_int), ("ln_eps", C.c_float)]
 
 
 class CoreWorkspace(C.Structure):

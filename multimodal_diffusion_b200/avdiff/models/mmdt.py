@@ -168,6 +168,11 @@ class _CoreRunner:
                                                C.byref(ws), B, N, _lib.stream_ptr()))
         if not apply_final_norm:
             return bufs["x"].view(B, N, d)
+        if pc.layernorm:
+            _lib.check(_lib.load().avd_layernorm_act(bufs["x"].data_ptr(), pc.final_ln_w.data_ptr(),
+                                                     pc.final_ln_b.data_ptr(), M, d, 1e-5, 0, out.data_ptr(), None, 0,
+                                                     _lib.stream_ptr()))
+            return out
         _lib.check(_lib.load().avd_rmsnorm_rows(bufs["x"].data_ptr(), pc.final_scale.data_ptr(), 1, M, 0, M, d,
                                                 1e-6, out.data_ptr(), None, 0, _lib.stream_ptr()))
         return out
@@ -191,10 +196,12 @@ class Block(nn.Module):
         _no_grad_only(self)
         if attn_mask is not None:
             raise NotImplementedError("attn_mask is not used by MMDiT or the sampler (SURVEY.md §8 N4)")
-        if not isinstance(self.norm1, RMSNorm):
-            raise NotImplementedError('only norm="rmsnorm" is implemented (SURVEY.md §8 N4)')
         sd = {"blocks.0." + k: v for k, v in self.state_dict().items()}
-        sd["final_norm.scale"] = torch.ones_like(self.norm1.scale)
+        if isinstance(self.norm1, RMSNorm):
+            sd["final_norm.scale"] = torch.ones_like(self.norm1.scale)
+        else:                                                   # the runner only uses it to pick the norm kind / width
+            sd["final_norm.weight"] = torch.ones_like(self.norm1.weight)
+            sd["final_norm.bias"] = torch.zeros_like(self.norm1.bias)
         return self._runner.run(self, sd, 1, self.n_heads, self.precision, x, apply_final_norm=False,
                                 key_padding_mask=key_padding_mask)
 
@@ -231,8 +238,6 @@ class MMDiT(nn.Module):
         _no_grad_only(self)
         if self.training and self.cfg.token_dropout > 0.0:
             raise NotImplementedError("token_dropout is a training-time feature; the sampler runs in eval mode")
-        if self.cfg.norm.lower() != "rmsnorm":
-            raise NotImplementedError('only norm="rmsnorm" is implemented (SURVEY.md §8 N4)')
         if self.cfg.d_model % self.cfg.n_heads or (self.cfg.d_model // self.cfg.n_heads) != 64 and \
                 _lib.precision_code(self.precision) in (_lib.AVD_PREC_BF16, _lib.AVD_PREC_F16):
             raise NotImplementedError("the tcgen05 attention kernel is built for head_dim 64")

@@ -244,12 +244,23 @@ static int core_blocks(const avd_core_weights* w, const float* x_in, const void*
   const bool f16 = is_f16(w->precision);
   const bool tc_attn = (w->precision == AVD_PREC_BF16) || f16;
   // fp16 mode: the residual-stream operand xa holds x * AVD_F16_XSCALE; its consumers (QKV, fc1) undo the scale
-  const float x_unscale = f16 ? 1.0f / AVD_F16_XSCALE : 0.0f, x_scale = f16 ? AVD_F16_XSCALE : 0.0f;
+  // norm="layernorm": LayerNorm subtracts the row mean, so it cannot ride the GEMM as a row scale like RMSNorm does; it
+  // is its own pass over the fp32 residual stream (layernorm_act_kernel) writing the operand of the QKV / fc1 GEMM
+  const bool ln = w->norm_kind == 1;
+  AVD_REQUIRE(!ln || last_out == nullptr, "the fused sampler supports norm=\"rmsnorm\" cores only");
+  const float x_unscale = (f16 && !ln) ? 1.0f / AVD_F16_XSCALE : 0.0f, x_scale = f16 ? AVD_F16_XSCALE : 0.0f;
   for (int l = 0; l < w->n_layers; ++l) {
     const avd_block_weights& b = w->blocks[l];
     const void* a_in = (l == 0) ? xa_in : ws->xa;
     const float* s_in = (l == 0) ? ssq_in : ws->ssq;
     const float* r_in = (l == 0) ? x_in : ws->x;
+    if (ln) {
+      AVD_REQUIRE(b.ln1_w != nullptr && b.ln1_b != nullptr && b.ln2_w != nullptr && b.ln2_b != nullptr, "missing LayerNorm weights");
+      AVD_TRY(launch_layernorm_act(r_in, b.ln1_w, b.ln1_b, M, d, w->ln_eps, 0, nullptr, ws->xa,
+                                   nseg_arg(w->precision, false), st));
+      a_in = ws->xa;
+      s_in = nullptr;
+    }
     // qkv = RMS1(x) W_in^T + b_in        (mmdt.py:97 -> :60)
     avd_gemm_args g{};
     g.M = M; g.N = 3 * d; g.K = d; g.precision = w->precision;
@@ -273,8 +284,10 @@ static int core_blocks(const avd_core_weights* w, const float* x_in, const void*
     // u = gelu(RMS2(x) W_1^T + b_1)       (mmdt.py:98 -> :78-79)
     g = avd_gemm_args{};
     g.M = M; g.N = w->d_mlp; g.K = d; g.precision = w->precision;
+    if (ln) AVD_TRY(launch_layernorm_act(ws->x, b.ln2_w, b.ln2_b, M, d, w->ln_eps, 0, nullptr, ws->xa,
+                                         nseg_arg(w->precision, false), st));
     g.A = ws->xa; g.W = b.w_fc1; g.bias = b.b_fc1;
-    g.ssq_in = ws->ssq; g.ssq_parts = parts; g.rms_dim = d; g.rms_eps = w->rms_eps;
+    g.ssq_in = ln ? nullptr : ws->ssq; g.ssq_parts = parts; g.rms_dim = d; g.rms_eps = w->rms_eps;
     g.a_scale = x_unscale;
     g.act = tc_attn ? 2 : 1;   // bf16 mode: fast erf (|err| < 2e-7, far below the bf16 rounding of the result)
     g.out_bf16 = ws->hmid; g.out_precision = w->precision;

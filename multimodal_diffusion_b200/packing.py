@@ -46,21 +46,22 @@ class PackedCore:
                  rms_eps: float = 1e-6):
         self.precision = _lib.precision_code(precision)
         self.n_layers, self.n_heads = int(n_layers), int(n_heads)
-        if "final_norm.scale" not in sd:
-            raise NotImplementedError('only norm="rmsnorm" cores are supported (SURVEY.md §8 N4)')
+        self.layernorm = "final_norm.scale" not in sd          # build_norm (mmdt.py:45-46): nn.LayerNorm has weight/bias
+        if self.layernorm and "final_norm.weight" not in sd:
+            raise ValueError("state_dict has neither final_norm.scale (rmsnorm) nor final_norm.weight (layernorm)")
         if self.n_layers > _lib.AVD_MAX_LAYERS:
             raise ValueError(f"at most {_lib.AVD_MAX_LAYERS} layers")
         self.keep: List[torch.Tensor] = []
         w = _lib.CoreWeights()
-        d = int(sd["final_norm.scale"].numel())
+        d = int(sd["final_norm.weight" if self.layernorm else "final_norm.scale"].numel())
         self.d_model = d
         self.d_mlp = int(sd["blocks.0.mlp.fc1.weight"].shape[0])
         w.d_model, w.n_heads, w.n_layers, w.d_mlp = d, self.n_heads, self.n_layers, self.d_mlp
         w.precision, w.rms_eps = self.precision, float(rms_eps)
         for i in range(self.n_layers):
             p = f"blocks.{i}."
-            s1 = _dev_f32(sd[p + "norm1.scale"], device)
-            s2 = _dev_f32(sd[p + "norm2.scale"], device)
+            s1 = None if self.layernorm else _dev_f32(sd[p + "norm1.scale"], device)
+            s2 = None if self.layernorm else _dev_f32(sd[p + "norm2.scale"], device)
             wq = pack_linear_weight(_dev_f32(sd[p + "attn.mha.in_proj_weight"], device), self.precision, s1)
             wo = pack_linear_weight(_dev_f32(sd[p + "attn.mha.out_proj.weight"], device), self.precision)
             w1 = pack_linear_weight(_dev_f32(sd[p + "mlp.fc1.weight"], device), self.precision, s2)
@@ -75,7 +76,17 @@ class PackedCore:
             bw.w_o, bw.b_o = wo.data_ptr(), bo.data_ptr()
             bw.w_fc1, bw.b_fc1 = w1.data_ptr(), b1.data_ptr()
             bw.w_fc2, bw.b_fc2 = w2.data_ptr(), b2.data_ptr()
-        self.final_scale = _dev_f32(sd["final_norm.scale"], device)
+            if self.layernorm:
+                lnp = [_dev_f32(sd[p + k], device) for k in ("norm1.weight", "norm1.bias", "norm2.weight", "norm2.bias")]
+                self.keep += lnp
+                bw.ln1_w, bw.ln1_b, bw.ln2_w, bw.ln2_b = (t.data_ptr() for t in lnp)
+        w.norm_kind, w.ln_eps = (1 if self.layernorm else 0), 1e-5
+        if self.layernorm:
+            self.final_ln_w = _dev_f32(sd["final_norm.weight"], device)
+            self.final_ln_b = _dev_f32(sd["final_norm.bias"], device)
+            self.final_scale = torch.ones(d, device=device, dtype=torch.float32)
+        else:
+            self.final_scale = _dev_f32(sd["final_norm.scale"], device)
         w.final_scale = self.final_scale.data_ptr()
         self.struct = w
         self.device = device

@@ -129,6 +129,9 @@ class FusedSampler:
             raise _lib.AvdError("FusedSampler needs a CUDA device (no CPU path)")
         with torch.cuda.device(self.device):
             _lib.check(lib.avd_device_check())
+        if "final_norm.scale" not in _state_dict_of(core):
+            raise NotImplementedError('the fused sampler supports norm="rmsnorm" cores (every shipped config); a '
+                                      'norm="layernorm" MMDiT runs through MMDiT.forward')
         self.core = packing.PackedCore(_state_dict_of(core), cfg.n_layers, cfg.n_heads, core_precision, self.device)
         # final_norm.scale is folded into the head's input projection (the norm itself runs in that GEMM's epilogue)
         self.head = packing.PackedHead(_state_dict_of(head), target, head_precision, self.device,

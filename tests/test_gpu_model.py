@@ -273,6 +273,29 @@ def test_mmdit_key_padding_mask(dev, mods, w_cpu, precision, tol):
     assert rel_l2(plain[1], want[1]) > 5 * tol           # the mask matters (37 of 133 keys padded)
 
 
+@pytest.mark.parametrize("precision,tol", [("fp32", TOL_EPS_FP32), ("f16", 2e-3), ("bf16", 1e-2)])
+def test_mmdit_layernorm_variant(dev, precision, tol):
+    """MMDiT(norm="layernorm") (mmdt.py:45-46; §8f N4): LayerNorm runs as its own pass in front of the QKV / fc1 GEMMs."""
+    from multimodal_diffusion_b200.avdiff.models.mmdt import MMDiT
+    torch.manual_seed(5)
+    core = MMDiT(d_model=512, n_layers=3, n_heads=8, mlp_ratio=4.0, dropout=0.0, norm="layernorm").eval()
+    with torch.no_grad():                       # non-trivial affine parameters
+        for k, v in core.state_dict().items():
+            if "norm" in k:
+                v.copy_(1.0 + 0.2 * randn(hash(k) % 1000, *v.shape) if k.endswith("weight") else 0.1 * randn(hash(k) % 999, *v.shape))
+    sd = {k: v.clone() for k, v in core.state_dict().items()}
+    x = randn(91, 2, 133, 512) * 2 + 0.7        # a row mean the norm has to remove
+    core = core.to(dev)
+    core.precision = precision
+    with torch.no_grad():
+        got = core(x.to(dev)).cpu()
+        blk = core.blocks[1]
+        blk.precision = precision
+        got_blk = blk(x.to(dev)).cpu()
+    assert rel_l2(got, orc.mmdit_forward(sd, x, 3, 8)) < tol
+    assert rel_l2(got_blk, orc.block_forward(sd, 1, x, 8)) < tol
+
+
 def test_stream_sample_windows_as_batch(dev, mods):
     """§8f N2: the windows of a long prompt run as the batch dimension of the fused sampler; the result must not depend
     on the batch size (5 windows through a batch-2 sampler, last call padded, against a batch-1 sampler)."""
