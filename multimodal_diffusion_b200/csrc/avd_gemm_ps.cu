@@ -57,8 +57,13 @@ __global__ void __launch_bounds__(PS_THREADS, 1) gemm_ps_kernel(const __grid_con
   constexpr int A_BYTES = GEMM_BM * GEMM_BK * 2;
   constexpr int B_BYTES = BN * GEMM_BK * 2;
   constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  constexpr uint32_t TMEM_COLS = BN <= 32 ? 128 : BN <= 64 ? 256 : 512;   // 2 buffers x 2 issuers x BN columns
-  static_assert(BN <= 128, "four accumulators of BN columns must fit the 512 TMEM columns");
+  // BN = 256 ("column split", CS): the two issuers share every k-block and each owns 128 of the tile's 256 columns
+  // (two M128 N128 MMAs per k-step instead of one per issuer on alternating k-blocks), so a tile needs ONE 256-column
+  // accumulator and two tiles fit the 512 TMEM columns.  Why: the smem port carries 2 x (16 KB A + BN x 128 B W) per
+  // k-block; at BN = 128 that is 512 cycles for 256 cycles of MMA, at BN = 256 it is 768 for 512.
+  constexpr bool CS = BN == 256;
+  constexpr uint32_t TMEM_COLS = BN <= 32 ? 128 : BN <= 64 ? 256 : 512;   // 2 buffers x 2 issuers x BN columns (CS: 2 x 256)
+  static_assert(BN <= 128 || CS, "four accumulators of BN columns must fit the 512 TMEM columns");
   constexpr int NCH = BN / 32;
   extern __shared__ __align__(1024) uint8_t ps_smem[];
   uint8_t* smem = ps_smem;
@@ -102,7 +107,7 @@ __global__ void __launch_bounds__(PS_THREADS, 1) gemm_ps_kernel(const __grid_con
   unsigned long long* const trace = p.trace;
   if (threadIdx.x == 0) trace_mark(trace, 0);
   if (warp == 0) {                       // one barrier (or two) per lane instead of a serial loop
-    if (lane < 2 * PS_MAX_STAGES) mbar_init(&full[lane], 1);                  // full, empty
+    if (lane < 2 * PS_MAX_STAGES) mbar_init(&full[lane], (CS && lane >= PS_MAX_STAGES) ? 2 : 1);   // full, empty (CS: both issuers release a slot)
     if (lane < 2) mbar_init(&acc_full[lane], 2);                              // one arrival per issuer
     if (lane < 2) mbar_init(&acc_empty[lane], 8);                             // one arrival per epilogue warp
     if (lane < 16) mbar_init(&res_bar[lane], 1);
@@ -177,9 +182,34 @@ __global__ void __launch_bounds__(PS_THREADS, 1) gemm_ps_kernel(const __grid_con
     // ------------------------------------------------------------------ MMA issuer h: iterations j = h (mod 2) of each tile
     if (lane == 0) {
       const int h = warp - 2;
-      const uint32_t idesc = make_idesc_bf16(GEMM_BM, BN, 0, 0, p.f16_in);
+      const uint32_t idesc = make_idesc_bf16(GEMM_BM, CS ? 128 : BN, 0, 0, p.f16_in);
       const uint32_t desc_hi = smem_desc_hi_sw128(1024);
       const uint32_t a_lo0 = smem_desc_lo_sw128(smem_u32(smem), 16);
+      if (CS) {
+        // column split: every k-block of every tile, this issuer's 128 columns (W rows 128 h .. 128 h + 127 of the stage)
+        int slot = 0;
+        uint32_t ph = 0;
+        for (int i = 0; i < my_tiles; ++i) {
+          const int b = i & 1;
+          wait(&acc_empty[b], ((i >> 1) & 1) ^ 1, 2, i);
+          tc_fence_after();
+          const uint32_t acc = tmem_base + b * BN + h * 128;
+          for (int j = 0; j < ipt; ++j) {
+            wait(&full[slot], ph, 3, i * ipt + j);
+            tc_fence_after();
+            if (h == 0 && i == 0 && j == 0) trace_mark(trace, 2);
+            const uint32_t a_lo = a_lo0 + slot * (STAGE_BYTES >> 4);
+            const uint32_t b_lo = a_lo + (A_BYTES >> 4) + h * ((128 * GEMM_BK * 2) >> 4);
+#pragma unroll
+            for (int k = 0; k < GEMM_BK / 16; ++k)
+              umma_bf16_lh(acc, a_lo + 2 * k, b_lo + 2 * k, desc_hi, idesc, (j > 0 || k > 0) ? 1u : 0u);
+            umma_commit(&empty[slot]);                     // second of the two arrivals frees the slot
+            if (++slot == stages) { slot = 0; ph ^= 1; }
+          }
+          umma_commit(&acc_full[b]);
+          if (h == 0 && i == my_tiles - 1) trace_mark(trace, 3);
+        }
+      } else
       for (int i = 0; i < my_tiles; ++i) {
         const int b = i & 1;
         const int base = i * ipt;                          // global iteration of this tile's first k-block
@@ -260,10 +290,12 @@ __global__ void __launch_bounds__(PS_THREADS, 1) gemm_ps_kernel(const __grid_con
       const int row = m0 + quad * 32 + lane;
       const bool live = row < p.M;
       // lane l keeps bias[n0 + 32 ch + l] of this warp's (at most two) chunks; broadcast by shuffle in the chunk loop
-      float bias_a = 0.0f, bias_b = 0.0f;
+      float bias_a = 0.0f, bias_b = 0.0f, bias_c = 0.0f, bias_d = 0.0f;
       if (p.bias != nullptr) {
         if (hf < NCH) bias_a = __ldg(p.bias + n0 + hf * 32 + lane);
         if (hf + 2 < NCH) bias_b = __ldg(p.bias + n0 + (hf + 2) * 32 + lane);
+        if (hf + 4 < NCH) bias_c = __ldg(p.bias + n0 + (hf + 4) * 32 + lane);
+        if (hf + 6 < NCH) bias_d = __ldg(p.bias + n0 + (hf + 6) * 32 + lane);
       }
       float rinv = 1.0f;
       if (p.ssq_in != nullptr && live) {
@@ -283,8 +315,9 @@ __global__ void __launch_bounds__(PS_THREADS, 1) gemm_ps_kernel(const __grid_con
       __syncwarp();
       tc_fence_after();
       if (warp == 4 && lane == 0) trace_mark(trace, i == 0 ? 5 : 8);
-      const bool two_acc = ipt > 1;          // with a single k-block the tile sits in issuer ((i * ipt) & 1)'s accumulator
-      const uint32_t t_row = tmem_base + (b * 2 + (two_acc ? 0 : ((i * ipt) & 1))) * BN + ((uint32_t)(quad * 32) << 16);
+      const bool two_acc = !CS && ipt > 1;   // with a single k-block the tile sits in issuer ((i * ipt) & 1)'s accumulator
+      const uint32_t t_row = tmem_base + (CS ? b * BN : (b * 2 + (two_acc ? 0 : ((i * ipt) & 1))) * BN) +
+                             ((uint32_t)(quad * 32) << 16);
       uint32_t r[32], r1[32];
       if (hf < NCH) {
         tmem_ld_32x32(t_row + hf * 32, r);
@@ -314,7 +347,8 @@ __global__ void __launch_bounds__(PS_THREADS, 1) gemm_ps_kernel(const __grid_con
           if (lane == 0) mbar_arrive(&acc_empty[b]);
         }
         {
-          const float bl = (ch == hf) ? bias_a : bias_b;
+          const int ci = (ch - hf) >> 1;
+          const float bl = ci == 0 ? bias_a : ci == 1 ? bias_b : ci == 2 ? bias_c : bias_d;
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] = fmaf(v[j], rinv, __shfl_sync(0xffffffffu, bl, j));
         }
@@ -539,12 +573,12 @@ int launch_gemm_ps(const avd_gemm_args& g, GemmParams p, int nseg, int force_bn,
     if (out_nseg > 1) epi *= 1.0 + 0.3 * (out_nseg - 1);
     return ml + (waves - 1) * (ml > epi ? ml : epi) + epi;
   };
-  const int cands[3] = {128, 64, 32};
+  const int cands[4] = {256, 128, 64, 32};
   int bn = 0;
   if (force_bn > 0 && usable(force_bn)) bn = force_bn;
   if (bn == 0) {
     double best = 0.0;
-    for (int i = 0; i < 3; ++i)
+    for (int i = ps_env_int("AVD_PS_NO256", 0) ? 1 : 0; i < 4; ++i)
       if (usable(cands[i])) {
         const double c = cost(cands[i]);
         if (bn == 0 || c < best) { bn = cands[i]; best = c; }
@@ -582,6 +616,7 @@ int launch_gemm_ps(const avd_gemm_args& g, GemmParams p, int nseg, int force_bn,
   else if (one16 && g.out_f32 != nullptr && g.resid != nullptr && g.ssq_out != nullptr && g.act == 0) mode = 3;
   if (p.trace != nullptr || bn < 64 || ps_env_int("AVD_GEMM_GENERIC", 0)) mode = 0;
   switch (bn) {
+    case 256: return launch_ps_bn<256>(tmA, tmB, tmR, p, plan, smem_bytes, grid, mode, s);
     case 128: return launch_ps_bn<128>(tmA, tmB, tmR, p, plan, smem_bytes, grid, mode, s);
     case 64: return launch_ps_bn<64>(tmA, tmB, tmR, p, plan, smem_bytes, grid, mode, s);
     default: return launch_ps_bn<32>(tmA, tmB, tmR, p, plan, smem_bytes, grid, mode, s);

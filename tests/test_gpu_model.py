@@ -219,19 +219,26 @@ def test_full_size_v2a_batch8_properties(dev, mods):
     assert torch.equal(fs.sample(zp.to(dev), zi.to(dev)), z)
 
 
-def test_full_size_a2v_batch64_sharding_invariance(dev, mods):
+@pytest.mark.parametrize("core_p,head_p,tol", [("fp32", "fp32", 1e-5), ("f16", "f16", 5e-3)])
+def test_full_size_a2v_batch64_sharding_invariance(dev, mods, core_p, head_p, tol):
     """BASELINE.json configs[2] (A2V, B = 64): the clip-sharded result (8 shards of 8, as 8 GPUs would compute it)
-    equals the single-batch result clip by clip.  5 steps keep the test short; the property is step-independent."""
+    equals the single-batch result clip by clip.  5 steps keep the test short; the property is step-independent.
+    Batch 64 runs the persistent GEMMs (256-wide column-split tiles for QKV / fc1), batch 8 the one-tile kernels: the two
+    accumulate the k-blocks in a different order, so outside fp32 mode the results agree to the rounding noise of the
+    16-bit activations (amplified by guidance 3.5), not bit for bit."""
     from multimodal_diffusion_b200.sampler import clip_noise, shard_range
     n = 64
     zp = torch.stack([clip_noise((8, 150), i, 1000) for i in range(n)])
     zi = torch.stack([clip_noise((8, 12, 16, 16), i, 2000) for i in range(n)])
-    full = _sampler(mods, "video", n, "bf16", "bf16x3", steps=5).sample(zp.to(dev), zi.to(dev))
-    fs8 = _sampler(mods, "video", 8, "bf16", "bf16x3", steps=5)
+    full = _sampler(mods, "video", n, core_p, head_p, steps=5).sample(zp.to(dev), zi.to(dev))
+    fs8 = _sampler(mods, "video", 8, core_p, head_p, steps=5)
+    worst = 0.0
     for r in range(8):
         lo, hi = shard_range(n, r, 8)
         part = fs8.sample(zp[lo:hi].to(dev), zi[lo:hi].to(dev))
-        assert rel_l2(part, full[lo:hi]) < 1e-5
+        worst = max(worst, rel_l2(part, full[lo:hi]))
+    print(f"[sharding {core_p}] worst shard rel-L2 {worst:.3e}")
+    assert worst < tol
 
 
 def test_long_context_a2v_10s(dev, mods, w_cpu):
