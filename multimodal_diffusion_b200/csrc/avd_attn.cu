@@ -59,6 +59,18 @@ __device__ __forceinline__ float ex2_approx(float x) {
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
+// The exponentials of a 32-score chunk, issued back to back.  Left to itself the compiler interleaves each MUFU.EX2 with
+// the FADD / F2FP that consumes the previous one, and with two softmax warps per scheduler every such pair then waits out
+// the MUFU latency (the SASS showed MUFU, FADD, MUFU, FADD ...).  The volatile asm keeps the 32 independent MUFUs together;
+// sums and packs follow.  What remains is the pipe itself: 16 exponentials per cycle per SM, i.e. 8 cycles per warp
+// instruction on each scheduler -- 128 rows x 160 key columns = 1280 cycles per CTA, which is what the phase trace shows.
+__device__ __forceinline__ void ex2_chunk(const uint32_t (&x)[32], float sc, float neg_m_sc, float (&e)[32]) {
+#pragma unroll
+  for (int c = 0; c < 32; ++c) {
+    const float a = fmaf(__uint_as_float(x[c]), sc, neg_m_sc);
+    asm volatile("ex2.approx.ftz.f32 %0, %1;" : "=f"(e[c]) : "f"(a));
+  }
+}
 
 // 2^x for x <= 0 on the FMA / ALU pipes: round-to-integer through the 1.5 * 2^23 constant, a degree-4 near-minimax
 // polynomial for 2^f on [-0.5, 0.5] (max relative error 2.9e-6 in fp32, below the 16-bit rounding P gets), and the integer
@@ -308,11 +320,13 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
             float l0 = 0.0f, l1 = 0.0f;
             uint32_t w[16];
             const uint32_t vb = valid_bits(j, ch, lim);
+            float e[32];
+            ex2_chunk(x[i], sc, -m_sc, e);
             if (vb == 0xffffffffu) {                 // whole chunk of valid keys: no masking
 #pragma unroll
               for (int c = 0; c < 32; c += 2) {
-                const float p0 = ex2_approx(fmaf(__uint_as_float(x[i][c]), sc, -m_sc));
-                const float p1 = ex2_approx(fmaf(__uint_as_float(x[i][c + 1]), sc, -m_sc));
+                const float p0 = e[c];
+                const float p1 = e[c + 1];
                 l0 += p0;
                 l1 += p1;
                 w[c >> 1] = F16 ? pack_f16x2(p0, p1) : pack_bf16x2(p0, p1);
@@ -320,8 +334,8 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
             } else {
 #pragma unroll
               for (int c = 0; c < 32; c += 2) {
-                float p0 = ex2_approx(fmaf(__uint_as_float(x[i][c]), sc, -m_sc));
-                float p1 = ex2_approx(fmaf(__uint_as_float(x[i][c + 1]), sc, -m_sc));
+                float p0 = e[c];
+                float p1 = e[c + 1];
                 p0 = ((vb >> c) & 1u) ? p0 : 0.0f;
                 p1 = ((vb >> (c + 1)) & 1u) ? p1 : 0.0f;
                 l0 += p0;
