@@ -390,10 +390,12 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
               w[c >> 1] = F16 ? pack_f16x2(p0, p1) : pack_bf16x2(p0, p1);
             }
           } else if (vm == 0xffffffffu) {
+            float e[32];
+            ex2_chunk(x, sc, -m_sc, e);
 #pragma unroll
             for (int c = 0; c < 32; c += 2) {
-              const float p0 = ex2_approx(fmaf(__uint_as_float(x[c]), sc, -m_sc));
-              const float p1 = ex2_approx(fmaf(__uint_as_float(x[c + 1]), sc, -m_sc));
+              const float p0 = e[c];
+              const float p1 = e[c + 1];
               l0 += p0;
               l1 += p1;
               w[c >> 1] = F16 ? pack_f16x2(p0, p1) : pack_bf16x2(p0, p1);
