@@ -555,7 +555,13 @@ int launch_gemm_ps(const avd_gemm_args& g, GemmParams p, int nseg, int force_bn,
   //   mainloop of a tile  = k-block iterations x max(TMA ingest at ~110 B/cycle/SM, 4 MMAs of max(BN/2, 48) cycles)
   //   epilogue of a tile  = (BN / 64) chunk rounds of the 8 epilogue warps
   //   time = first mainloop + (waves - 1) x max(mainloop, epilogue) + last epilogue
-  static const int c_epi = ps_env_int("AVD_PS_EPI_CYCLES", 1500);
+  //   (epilogue constants: 1500 cycles per 64-column round for the generic / residual epilogues, 1100 for the specialised
+  //   16-bit-only ones, GELU +10 %: with the old 1500 / +30 % the model kept fc1 on 128-wide tiles, 12 % slower than
+  //   256-wide at M = 4256 .. 17024, tools/kbench.py --M with AVD_GEMM_BN=256)
+  static const int c_epi_env = ps_env_int("AVD_PS_EPI_CYCLES", 0);
+  const bool fast16 = g.out_bf16 != nullptr && out_nseg == 1 && g.out_f32 == nullptr && g.resid == nullptr &&
+                      g.ssq_out == nullptr;
+  const int c_epi = c_epi_env > 0 ? c_epi_env : (fast16 ? 1100 : 1500);
   auto usable = [&](int bn) {
     if (g.N % bn != 0) return false;
     if ((g.ssq_out != nullptr || g.out_bf16 != nullptr) && bn < 64) return false;
@@ -569,7 +575,7 @@ int launch_gemm_ps(const avd_gemm_args& g, GemmParams p, int nseg, int force_bn,
     const double mma = 4.0 * (bn / 2 > 52 ? bn / 2 : 52);
     const double ml = ipt * (ingest > mma ? ingest : mma);
     double epi = (bn >= 64 ? bn / 64 : 1) * (double)c_epi;
-    if (g.act != 0) epi *= 1.3;
+    if (g.act != 0) epi *= fast16 ? 1.1 : 1.3;
     if (out_nseg > 1) epi *= 1.0 + 0.3 * (out_nseg - 1);
     return ml + (waves - 1) * (ml > epi ? ml : epi) + epi;
   };
