@@ -368,3 +368,31 @@ def test_crossfade_video_bit_exact(dev):
         assert np.array_equal(si.crossfade_video(ch, h, T, fade), want), (n, T, H, W, h)
         got = si.crossfade_video(torch.from_numpy(ch).to(dev), h, T, fade)
         assert got.is_cuda and np.array_equal(got.cpu().numpy(), want)
+
+
+def test_stream_kernels_stay_in_bounds(dev, lib):
+    """Guard bands around the outputs of the stitching kernels (odd sizes: scalar and vector paths, grid tails): no
+    byte outside [(N-1)*hop + L] may change.  (compute-sanitizer is not available on the pool.)"""
+    from multimodal_diffusion_b200 import _lib
+    G = 1024
+    for n, L, hop in ((3, 1001, 333), (5, 4096, 1024), (2, 64, 200), (7, 48000, 16000)):
+        T_out = (n - 1) * hop + L
+        ch = torch.randn(n, L, device=dev)
+        w = torch.rand(L, device=dev)
+        buf = torch.full((T_out + 2 * G,), 7.0, device=dev)
+        _lib.check(lib.avd_crossfade_audio(ch.data_ptr(), w.data_ptr(), buf[G:].data_ptr(), n, L, hop, _lib.stream_ptr()))
+        assert bool((buf[:G] == 7.0).all()) and bool((buf[G + T_out:] == 7.0).all())
+        rows = 3
+        chr_ = torch.randn(rows, n, L, device=dev)
+        buf = torch.full((rows * T_out + 2 * G,), 7.0, device=dev)
+        _lib.check(lib.avd_overlap_add_win(chr_.data_ptr(), w.data_ptr(), buf[G:].data_ptr(), rows, n, L, hop, 1e-8,
+                                           _lib.stream_ptr()))
+        assert bool((buf[:G] == 7.0).all()) and bool((buf[G + rows * T_out:] == 7.0).all())
+        assert not bool((buf[G:G + rows * T_out] == 7.0).all())
+    for n, T, F, hop in ((3, 7, 45, 5), (4, 12, 48 * 3, 4), (2, 5, 16 * 16 * 3, 9)):
+        T_out = (n - 1) * hop + T
+        ch = torch.randint(0, 256, (n, T, F), device=dev, dtype=torch.uint8)
+        w = torch.rand(T, device=dev)
+        buf = torch.full((T_out * F + 2 * G,), 9, device=dev, dtype=torch.uint8)
+        _lib.check(lib.avd_crossfade_video(ch.data_ptr(), w.data_ptr(), buf[G:].data_ptr(), n, T, F, hop, _lib.stream_ptr()))
+        assert bool((buf[:G] == 9).all()) and bool((buf[G + T_out * F:] == 9).all())
