@@ -12,7 +12,19 @@ GOLDEN = ROOT / "tests" / "golden"
 if str(ROOT) not in sys.path:
     sys.path.insert(0, str(ROOT))
 
-from oracle import avdiff_oracle as orc  # noqa: E402  (tests are allowed to import the oracle)
+
+
+class _LazyOracle:
+    """`orc.<name>` resolves into oracle/avdiff_oracle.py on first use.  The oracle is imported lazily so that callers
+    which only need `randn` / `seeded_modules` (bench.py's own arm, tools/) never load anything under oracle/: only the
+    tests, `__graft_entry__.smoke()` and bench.py's CPU legs touch `orc`."""
+
+    def __getattr__(self, name):
+        from oracle import avdiff_oracle
+        return getattr(avdiff_oracle, name)
+
+
+orc = _LazyOracle()
 
 SEEDS = {"adapt_v": 100, "adapt_a": 101, "core": 102, "head": 103}   # same as tests/golden/make_golden.py
 
