@@ -69,15 +69,23 @@ const char* avd_prof_kind_name(int kind);
 /* synchronises the recorded events; returns total ms and launch count of `kind` */
 int avd_prof_collect(int kind, double* total_ms, int64_t* launches);
 int64_t avd_launch_count(void);              /* kernels launched by this library so far */
-/* Debug only: GEMM CTAs write 8 x (globaltimer ns, clock64) phase stamps into dev_u64[cta*16 ..] when the
- * grid fits n_u64; NULL switches it off (the default). */
+/* Debug only, compiled in with -DAVD_DEBUG_HOOKS (`python -m multimodal_diffusion_b200.build --debug-hooks`); the default
+ * build returns -1.  GEMM CTAs write 8 x (globaltimer ns, clock64) phase stamps into dev_u64[cta*16 ..] when the grid
+ * fits n_u64; NULL switches it off. */
 int avd_debug_trace(void* dev_u64, int64_t n_u64);
-/* Measurement aid: bit k of mask set -> kernels of profiler kind k are not launched (results are then meaningless).
- * bench.py uses it to time, with CUDA events, a graph that holds only the GEMM launches of a sampling call. */
-int avd_debug_skip_kinds(int mask);
-/* Debug only: out256[0] = number of barrier waits of the persistent GEMM that timed out since the last call, then
- * from out256[8] up to 30 records {tag, cta, thread, counter, parity, N, K, grid*1000+BN}; the call clears them. */
+/* out256[0] = number of barrier waits of the persistent GEMM that timed out since the last call (each of them also
+ * traps, so the launch fails), then from out256[8] up to 30 records {tag, cta, thread, counter, parity, N, K,
+ * grid*1000+BN}; the call clears them. */
 int avd_debug_gemm_timeout(unsigned int* out256);
+/* Asynchronous failures.  A device-side protocol timeout (bounded mbarrier / flag waits) traps, which fails the launch;
+ * it also leaves a record in host-mapped memory.  avd_check_errors() is the host's hard-error check: it returns 0 when
+ * no record exists and the device has no sticky error, else -1 with the details in avd_last_error().  It does not
+ * synchronise: call it after the caller's own stream/device synchronise (FusedSampler does). */
+int avd_check_errors(void);
+/* Tuning switches (tile width, kernel variant, PDL ...).  Each has an AVD_<NAME> environment variable that is read ONCE
+ * when the library is first used; afterwards only these calls change them.  Unknown name: -1. */
+int avd_set_option(const char* name, int value);
+int avd_get_option(const char* name, int* value);
 
 /* ---------------------------------------------------------------- K1: tokenisers (bit-exact fp32 moves) */
 /* ops.tube_patch_video (avdiff/utils/ops.py:100-119): z[B,C,T,H,W] -> tok[B,(T/t)(H/h)(W/w),C*t*h*w] */
@@ -116,6 +124,11 @@ int avd_timestep_embedding(const float* t, float* emb, int B, int dim, float max
 int avd_ddim_step(const float* x_t, const float* eps_hat, const float* noise, float* x_prev, const int64_t* t_now,
                   const int64_t* t_prev, const float* alpha_bar, int T_train, int B, int64_t per_batch, float eta,
                   void* stream);
+/* The z ~ N(0,1) of ddim_step's eta > 0 branch (schedule_utils.py:197, torch.randn_like) as a counter-based generator:
+ * out[b][e] = normal(Philox4x32-10(key = seed, counter = (e / 4, clip0 + b, step, 0)))[e % 4], Box-Muller on pairs.
+ * A clip's noise depends only on (seed, its GLOBAL index, step, element): results do not depend on how clips are
+ * batched or sharded over GPUs.  The fused loop (avd_sampler.eta > 0) draws exactly these values. */
+int avd_philox_normal(float* out, uint64_t seed, int64_t clip0, int step, int B, int64_t per_clip, void* stream);
 
 /* ---------------------------------------------------------------- K7: fused CFG + un-tokenise + DDIM */
 /* sample_clip.py:342-348 (audio) / 381-389 (video): eps = eps_n + g (eps_c - eps_n) -> latent layout -> ddim_step(eta=0).
@@ -129,6 +142,10 @@ typedef struct {
   float guidance;
   int t_now, t_prev;          /* integer timesteps (t_prev may be -1) */
   int T_train;
+  float eta;                  /* > 0: adds sigma * z (schedule_utils.py:185-197), z as avd_philox_normal draws it */
+  int step;                   /* Philox counter word (the sampler's step index) */
+  uint64_t seed;
+  int64_t clip0;              /* global index of clip 0 of this batch */
 } avd_cfg_ddim_args;
 int avd_cfg_untok_ddim(const avd_cfg_ddim_args* a, const float* eps_cond, const float* eps_null, const float* z_t,
                        float* z_prev, const float* alpha_bar, void* stream);
@@ -145,8 +162,11 @@ int avd_rows_prepare(const float* x, void* xa_bf16, float* ssq, int M, int d, in
  * y = scale * x / (||x||/sqrt(d) + eps).  Output compact [n_seq*n_rows, d] as fp32 and/or bf16 segments. */
 int avd_rmsnorm_rows(const float* x, const float* scale, int n_seq, int N, int row_off, int n_rows, int d, float eps,
                      float* out_f32, void* out_bf16, int precision, void* stream);
-/* nn.LayerNorm(d, eps) + GELU(erf) (noise_heads.py:139-146): y[M,d] fp32 -> bf16 segments and/or fp32.
- * apply_gelu = 0 gives a plain LayerNorm. */
+/* 16-bit operand range check (fp16 mode): counts the elements of buf[n] (fp16 bit patterns) that are +-65504 (what the
+ * saturating packs produce on overflow), inf or NaN into *counter (atomicAdd).  Zero cost unless called. */
+int avd_f16_range_scan(const void* buf, int64_t n, unsigned int* counter, void* stream);
+/* nn.LayerNorm(d, eps) + activation (noise_heads.py:139-146): y[M,d] fp32 -> bf16 segments and/or fp32.
+ * apply_gelu: 0 plain LayerNorm, 1 GELU(erf), 2 LeakyReLU(0.1), 3 ReLU (noise_heads._make_activation, :22-31). */
 int avd_layernorm_act(const float* y, const float* w, const float* b, int M, int d, float eps, int apply_gelu,
                       float* out_f32, void* out_bf16, int precision, void* stream);
 
@@ -209,6 +229,8 @@ typedef struct {
   const float* final_scale;                 /* final_norm.scale [d] */
   int norm_kind;                            /* 0 = rmsnorm (folded into the following GEMM), 1 = layernorm (own pass) */
   float ln_eps;                             /* nn.LayerNorm eps (1e-5) */
+  const float* final_ln_w;                  /* norm="layernorm": final_norm.weight / .bias [d] (used by the fused sampler) */
+  const float* final_ln_b;
 } avd_core_weights;
 
 /* Caller-allocated work buffers for M = n_seq*N rows (S = avd_nseg(precision)):
@@ -219,6 +241,11 @@ typedef struct {
   /* MMDiT.forward's key_padding_mask (mmdt.py:58-60, 134-147) packed as bits: word [seq * ceil(N/32) + k/32], bit k%32
    * set = key k of sequence seq is padding and takes no part in any softmax.  NULL = no mask (what the sampler uses). */
   const unsigned int* key_mask;
+  /* fp16 mode range check: when not NULL, every 16-bit operand buffer is scanned after each block (avd_f16_range_scan)
+   * and saturated / non-finite values are counted here.  NULL (the timed configuration) = no scan kernels. */
+  unsigned int* f16_sat_count;
+  /* measurement aid for THIS call only: bit k set = kernels of profiler kind k are not launched (results meaningless) */
+  int profile_skip_kinds;
 } avd_core_workspace;
 
 /* MMDiT.forward minus the final norm (mmdt.py:146-147): runs n_layers blocks.  Reads the input residual
@@ -231,9 +258,12 @@ typedef struct {
   int precision;
   float ln_eps;
   const void* w_in;  const float* b_in;                      /* input_proj[m]  */
-  const void* w_s[AVD_MAX_SHARED]; const float* b_s[AVD_MAX_SHARED];    /* shared[i][0]   */
-  const float* ln_w[AVD_MAX_SHARED]; const float* ln_b[AVD_MAX_SHARED]; /* shared[i][1]   */
+  /* the trunk: shared[i] followed by the modality-specific blocks spec[m][j] (or shared_specific_trunk[j]); all are
+   * Linear -> LayerNorm -> activation (noise_heads.py:139-172), n_shared counts both kinds */
+  const void* w_s[AVD_MAX_SHARED]; const float* b_s[AVD_MAX_SHARED];    /* block[i][0]   */
+  const float* ln_w[AVD_MAX_SHARED]; const float* ln_b[AVD_MAX_SHARED]; /* block[i][1]   */
   const void* w_out; const float* b_out;                     /* out_proj[m]    */
+  int activation;                                            /* 0 / 1 GELU(erf), 2 LeakyReLU(0.1), 3 ReLU (noise_heads.py:22-31) */
 } avd_head_weights;
 
 /* MultiModalNoiseHead.forward for one modality (noise_heads.py:201-220).  h: bf16 segments [S][M][d_in];
@@ -262,6 +292,18 @@ typedef struct {
   avd_head_weights head;            /* the TARGET modality's head */
   void* workspace;                  /* >= avd_sampler_workspace_bytes() */
   int64_t workspace_bytes;
+  /* ---- generality; all zero / NULL = the shipped sampler ---- */
+  float eta;                        /* ddim_eta > 0: stochastic DDIM, z from Philox (avd_philox_normal) */
+  uint64_t seed;
+  int64_t clip_index0;              /* global index of clip 0 (shard offset): keeps eta > 0 results shard-invariant */
+  /* per-token additive rows applied after the adapter: [Nv][d - tstep_dim] / [Na][d - tstep_dim], e.g. positional +
+   * modality embeddings (adapters.py:41-127) summed by the caller; NULL = none */
+  const float* add_v; const float* add_a;
+  /* ADDITIVE time embedding (the trainer's variant, trainer.py:45-49: tokens + emb): [S][d - tstep_dim] per step for
+   * the target rows and [d - tstep_dim] for t = 0 (prompt rows); NULL = none.  tstep_dim may then be 0. */
+  const float* tadd_steps; const float* tadd_zero;
+  int profile_skip_kinds;           /* measurement aid, see avd_core_workspace.profile_skip_kinds */
+  unsigned int* f16_sat_count;      /* fp16 range check of every operand buffer after each block / the head; NULL = off */
 } avd_sampler;
 
 int64_t avd_sampler_workspace_bytes(const avd_sampler* s);

@@ -46,7 +46,8 @@ class CfgDdimArgs(C.Structure):
                 ("C", C.c_int), ("T", C.c_int), ("H", C.c_int), ("W", C.c_int),
                 ("tt", C.c_int), ("th", C.c_int), ("tw", C.c_int),
                 ("L", C.c_int), ("length", C.c_int), ("stride", C.c_int), ("Nt", C.c_int),
-                ("guidance", C.c_float), ("t_now", C.c_int), ("t_prev", C.c_int), ("T_train", C.c_int)]
+                ("guidance", C.c_float), ("t_now", C.c_int), ("t_prev", C.c_int), ("T_train", C.c_int),
+                ("eta", C.c_float), ("step", C.c_int), ("seed", C.c_uint64), ("clip0", C.c_int64)]
 
 
 class GemmArgs(C.Structure):
@@ -67,11 +68,12 @@ class CoreWeights(C.Structure):
     _fields_ = [("d_model", C.c_int), ("n_heads", C.c_int), ("n_layers", C.c_int), ("d_mlp", C.c_int),
                 ("precision", C.c_int), ("rms_eps", C.c_float),
                 ("blocks", BlockWeights * AVD_MAX_LAYERS), ("final_scale", fp),
-                ("norm_kind", C.c_int), ("ln_eps", C.c_float)]
+                ("norm_kind", C.c_int), ("ln_eps", C.c_float), ("final_ln_w", fp), ("final_ln_b", fp)]
 
 
 class CoreWorkspace(C.Structure):
-    _fields_ = [("x", fp), ("xa", vp), ("ssq", fp), ("qkv", vp), ("att", vp), ("hmid", vp), ("key_mask", vp)]
+    _fields_ = [("x", fp), ("xa", vp), ("ssq", fp), ("qkv", vp), ("att", vp), ("hmid", vp), ("key_mask", vp),
+                ("f16_sat_count", vp), ("profile_skip_kinds", C.c_int)]
 
 
 class HeadWeights(C.Structure):
@@ -80,7 +82,7 @@ class HeadWeights(C.Structure):
                 ("w_in", vp), ("b_in", fp),
                 ("w_s", vp * AVD_MAX_SHARED), ("b_s", fp * AVD_MAX_SHARED),
                 ("ln_w", fp * AVD_MAX_SHARED), ("ln_b", fp * AVD_MAX_SHARED),
-                ("w_out", vp), ("b_out", fp)]
+                ("w_out", vp), ("b_out", fp), ("activation", C.c_int)]
 
 
 class SamplerArgs(C.Structure):
@@ -92,7 +94,10 @@ class SamplerArgs(C.Structure):
                 ("timesteps_host", i64p), ("temb_steps", fp), ("temb_zero", fp), ("alpha_bar", fp),
                 ("wv_t", fp), ("bv", fp), ("wa_t", fp), ("ba", fp),
                 ("core", CoreWeights), ("head", HeadWeights),
-                ("workspace", vp), ("workspace_bytes", C.c_int64)]
+                ("workspace", vp), ("workspace_bytes", C.c_int64),
+                ("eta", C.c_float), ("seed", C.c_uint64), ("clip_index0", C.c_int64),
+                ("add_v", fp), ("add_a", fp), ("tadd_steps", fp), ("tadd_zero", fp),
+                ("profile_skip_kinds", C.c_int), ("f16_sat_count", vp)]
 
 
 # name -> (restype, argtypes); every symbol include/avdiff_b200.h declares
@@ -110,8 +115,12 @@ _SIGNATURES = {
     "avd_prof_collect": (_I, [_I, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     "avd_launch_count": (C.c_int64, []),
     "avd_debug_trace": (_I, [vp, C.c_int64]),
-    "avd_debug_skip_kinds": (_I, [_I]),
     "avd_debug_gemm_timeout": (_I, [C.POINTER(C.c_uint)]),
+    "avd_check_errors": (_I, []),
+    "avd_set_option": (_I, [C.c_char_p, _I]),
+    "avd_get_option": (_I, [C.c_char_p, C.POINTER(_I)]),
+    "avd_philox_normal": (_I, [fp, C.c_uint64, C.c_int64, _I, _I, C.c_int64, vp]),
+    "avd_f16_range_scan": (_I, [vp, C.c_int64, vp, vp]),
     "avd_tube_patch": (_I, [fp, fp, _I, _I, _I, _I, _I, _I, _I, _I, vp]),
     "avd_tube_unpatch": (_I, [fp, fp, _I, _I, _I, _I, _I, _I, _I, _I, vp]),
     "avd_chunk1d": (_I, [fp, fp, _I, _I, _I, _I, _I, vp]),
@@ -176,8 +185,36 @@ def check(rc: int) -> None:
         raise AvdError(load().avd_last_error().decode("utf-8", "replace"))
 
 
-def stream_ptr() -> int:
-    return torch.cuda.current_stream().cuda_stream
+def stream_ptr(device=None) -> int:
+    """The raw cudaStream_t of torch's current stream on `device` (default: the current device)."""
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+def set_option(name: str, value: int) -> None:
+    """Tuning switch of the library (include/avdiff_b200.h: avd_set_option); the AVD_* environment variables are read
+    once at load, later changes go through here."""
+    check(load().avd_set_option(name.encode(), int(value)))
+
+
+def get_option(name: str) -> int:
+    v = C.c_int(0)
+    check(load().avd_get_option(name.encode(), C.byref(v)))
+    return int(v.value)
+
+
+class option:
+    """Context manager: `with _lib.option("gemm_pair", 2): ...` sets a tuning switch and restores it."""
+
+    def __init__(self, name: str, value: int):
+        self.name, self.value = name, value
+
+    def __enter__(self):
+        self.prev = get_option(self.name)
+        set_option(self.name, self.value)
+        return self
+
+    def __exit__(self, *exc):
+        set_option(self.name, self.prev)
 
 
 def ptr(t: Optional[torch.Tensor]) -> Optional[int]:

@@ -10,7 +10,9 @@ from __future__ import annotations
 
 import math
 from dataclasses import dataclass
-from typing import Literal
+from typing import Literal, Optional, Tuple
+
+import numpy as np
 
 import torch
 import torch.nn as nn
@@ -134,3 +136,26 @@ class TimestepEmbedder(nn.Module):
     def forward(self, t: torch.Tensor) -> torch.Tensor:
         base = su.timestep_embedding(t, dim=self.cfg.dim) if t.is_cuda else su.timestep_embedding_host(t, self.cfg.dim)
         return self.mlp(base) if self.mlp is not None else base
+
+
+@torch.no_grad()
+def token_additive_table(*, modality_embedding: Optional["ModalityEmbedding"] = None, modality: Optional[str] = None,
+                         positional=None, grid: Tuple[int, ...] = ()) -> torch.Tensor:
+    """The per-token rows [N, d] that `ModalityEmbedding` (adapters.py:41-52) and a positional embedding
+    (adapters.py:65-127) ADD to the adapted tokens of one modality, summed once on the host: the table
+    ``FusedSampler(add_v=..., add_a=...)`` hands to the fused input builder, which adds it in the adapter's epilogue
+     instead of running two more elementwise passes per step.
+    grid: (Tt, Hh, Ww) for PositionalEmbedding3D, (N,) for PositionalEmbedding1D."""
+    table = None
+    if positional is not None:
+        dev = next((p.device for p in positional.parameters()), torch.device("cpu"))
+        pe = positional(1, *grid, dev, torch.float32)[0]
+        table = pe.detach().clone().float()
+    if modality_embedding is not None:
+        vec = modality_embedding.lookup.weight[modality_embedding.index[modality]].detach().float()
+        n = int(table.shape[0]) if table is not None else int(np.prod(grid))
+        # same association as the modules applied in sequence: (x + modality) + positional
+        table = vec.view(1, -1).expand(n, -1).clone() if table is None else vec.view(1, -1).to(table.device) + table
+    if table is None:
+        raise ValueError("give a modality embedding and / or a positional embedding")
+    return table.contiguous()

@@ -95,8 +95,7 @@ class NoisePredictionHead(nn.Module):
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         _no_grad_only(self)
-        if self._activation != "gelu":
-            raise NotImplementedError("only GELU heads run on the GPU path")
+        act_code = packing.activation_code(self._activation)
         xc = _lib.require_cuda_f32(x, "x")
         in_shape = xc.shape
         cur = xc.reshape(-1, in_shape[-1])
@@ -117,7 +116,7 @@ class NoisePredictionHead(nn.Module):
                 ln = mods[i + 1]
                 a = torch.empty(S, M, N, device=xc.device, dtype=torch.bfloat16)
                 _lib.check(_lib.load().avd_layernorm_act(y.data_ptr(), ln.weight.data_ptr(), ln.bias.data_ptr(), M, N,
-                                                         float(ln.eps), 1, None, a.data_ptr(), prec,
+                                                         float(ln.eps), act_code, None, a.data_ptr(), prec,
                                                          _lib.stream_ptr()))
                 i += 4
             else:
@@ -172,12 +171,16 @@ class MultiModalNoiseHead(nn.Module):
     def get_output_dim(self, modality: str) -> int:
         return int(self.output_dims[modality])
 
+    def ln_eps(self) -> float:
+        """eps of the trunk's nn.LayerNorm modules (all built alike, noise_heads.py:139-146)."""
+        for mod in self.modules():
+            if isinstance(mod, nn.LayerNorm):
+                return float(mod.eps)
+        return 1e-5
+
     def forward(self, inputs: Dict[str, torch.Tensor], return_dict: bool = True) \
             -> Union[Dict[str, torch.Tensor], torch.Tensor]:
         _no_grad_only(self)
-        if self._activation != "gelu" or self._n_spec > 1:
-            raise NotImplementedError("the GPU head implements the sampler's configuration (GELU, identity "
-                                      "modality-specific trunk; sample_clip.py:99-107)")
         outputs: Dict[str, torch.Tensor] = {}
         for m in self.modalities:
             if m not in inputs or inputs[m] is None:
@@ -186,7 +189,8 @@ class MultiModalNoiseHead(nn.Module):
             in_shape = x.shape
             sd = self.state_dict()
             ph = self._cache.get(self, m, self.precision, x.device,
-                                 lambda: packing.PackedHead(sd, m, self.precision, x.device))
+                                 lambda: packing.PackedHead(sd, m, self.precision, x.device,
+                                                            ln_eps=self.ln_eps(), activation=self._activation))
             eps = _run_head(ph, x.reshape(-1, in_shape[-1]))
             outputs[m] = eps.view(*in_shape[:-1], self.output_dims[m])
         if return_dict:

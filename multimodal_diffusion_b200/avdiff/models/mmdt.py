@@ -32,6 +32,9 @@ def _no_grad_only(mod: nn.Module) -> None:
     if torch.is_grad_enabled() and any(p.requires_grad for p in mod.parameters()):
         raise RuntimeError("multimodal_diffusion_b200 implements the sampling (inference) path only: call under "
                            "torch.no_grad() (the reference's sampler is @torch.no_grad, sample_clip.py:220)")
+    if mod.training and any(isinstance(m, nn.Dropout) and m.p > 0.0 for m in mod.modules()):
+        raise RuntimeError("module is in training mode with dropout > 0, which the reference would apply; the kernels "
+                           "implement the eval-mode forward only: call .eval() first (sample_clip.py:98,108)")
 
 
 class RMSNorm(nn.Module):
@@ -129,7 +132,9 @@ class MLP(nn.Module):
         xa, _ = packing.rows_prepare(xc.view(M, d), prec)
         S = _lib.nseg(prec)
         u = torch.empty(S, M, hid, device=xc.device, dtype=torch.bfloat16)
-        packing.gemm(xa, w1, M, hid, d, prec, bias=self.fc1.bias.detach(), act=1, out_bf16=u, out_precision=prec,
+        # 16-bit modes take the epilogue's packed GELU exactly as the fused core does (avd_api.cu core_blocks: act = 2)
+        act = 2 if prec in (_lib.AVD_PREC_BF16, _lib.AVD_PREC_F16) else 1
+        packing.gemm(xa, w1, M, hid, d, prec, bias=self.fc1.bias.detach(), act=act, out_bf16=u, out_precision=prec,
                      a_scale=1.0 / _lib.AVD_F16_XSCALE if prec == _lib.AVD_PREC_F16 else 0.0)
         y = torch.empty(M, d, device=xc.device, dtype=torch.float32)
         packing.gemm(u, w2, M, d, hid, prec, bias=self.fc2.bias.detach(), out_f32=y)

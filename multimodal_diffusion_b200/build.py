@@ -1,6 +1,6 @@
 """In-tree build of libavdiff_b200.so (sm_100a only) with nvcc.
 
-    python -m multimodal_diffusion_b200.build [--force] [--verbose]
+    python -m multimodal_diffusion_b200.build [--force] [--verbose] [--debug-hooks]
 
 nvcc cross-compiles without a GPU, so this runs in the CPU-only build container; the resulting
 .so is git-ignored but travels with the working tree to the GPU box.
@@ -44,9 +44,10 @@ def _stamp() -> str:
     return h.hexdigest()
 
 
-def build(force: bool = False, verbose: bool = False) -> Path:
+def build(force: bool = False, verbose: bool = False, debug_hooks: bool = False) -> Path:
+    """debug_hooks: compile the in-kernel phase trace (avd_debug_trace) in; the default build has no debug hooks."""
     stamp_file = OBJ_DIR / "stamp.txt"
-    stamp = _stamp()
+    stamp = _stamp() + ("+debug-hooks" if debug_hooks else "")
     if not force and LIB.exists() and stamp_file.exists() and stamp_file.read_text() == stamp:
         return LIB
     OBJ_DIR.mkdir(parents=True, exist_ok=True)
@@ -54,7 +55,7 @@ def build(force: bool = False, verbose: bool = False) -> Path:
 
     def compile_one(src: str) -> Path:
         obj = OBJ_DIR / (Path(src).stem + ".o")
-        cmd = [nvcc, *NVCC_FLAGS, "-c", str(CSRC / src), "-o", str(obj)]
+        cmd = [nvcc, *NVCC_FLAGS, *(["-DAVD_DEBUG_HOOKS"] if debug_hooks else []), "-c", str(CSRC / src), "-o", str(obj)]
         res = subprocess.run(cmd, capture_output=True, text=True)
         (OBJ_DIR / (Path(src).stem + ".ptxas.log")).write_text(res.stderr)
         if res.returncode != 0:
@@ -74,5 +75,5 @@ def build(force: bool = False, verbose: bool = False) -> Path:
 
 
 if __name__ == "__main__":
-    out = build(force="--force" in sys.argv, verbose="--verbose" in sys.argv)
+    out = build(force="--force" in sys.argv, verbose="--verbose" in sys.argv, debug_hooks="--debug-hooks" in sys.argv)
     print(out)

@@ -7,8 +7,11 @@ namespace avd { int ps_debug_read(unsigned int* out8); }
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <deque>
 #include <mutex>
+#include <set>
 #include <unordered_map>
+#include <utility>
 #include <vector>
 
 namespace avd {
@@ -106,6 +109,8 @@ struct MapKeyHash {
 };
 static std::mutex g_map_mu;
 static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> g_maps;
+static std::deque<MapKey> g_map_order;          // insertion order: the oldest half is evicted when the cache is full
+constexpr size_t MAP_CACHE_MAX = 8192;
 
 // [d2][d1][d0] tensor (d0 contiguous) of bf16 (elem_bytes 2) or fp32 (4); box [1][box1][box0] with
 // box0 * elem_bytes == 128 (one 128-byte swizzle row).
@@ -141,8 +146,14 @@ int get_tensor_map_3d(const void* base, int elem_bytes, uint64_t d0, uint64_t d1
                         CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) AVD_FAIL("cuTensorMapEncodeTiled failed with CUresult " + std::to_string((int)r));
-  if (g_maps.size() > 8192) g_maps.clear();
+  if (g_maps.size() >= MAP_CACHE_MAX) {          // a sampler holds a few hundred maps; evict oldest-first, never wholesale
+    for (size_t i = 0; i < MAP_CACHE_MAX / 2 && !g_map_order.empty(); ++i) {
+      g_maps.erase(g_map_order.front());
+      g_map_order.pop_front();
+    }
+  }
   g_maps.emplace(key, m);
+  g_map_order.push_back(key);
   *out = m;
   return 0;
 }
@@ -152,15 +163,48 @@ int get_tensor_map_bf16_3d(const void* base, uint64_t d0, uint64_t d1, uint64_t 
   return get_tensor_map_3d(base, 2, d0, d1, d2, stride1_bytes, stride2_bytes, box0, box1, out);
 }
 
-int g_skip_kinds = 0;
+thread_local int t_skip_kinds = 0;
 
-bool pdl_enabled() {
-  static int v = -1;
-  if (v < 0) {
-    const char* e = std::getenv("AVD_PDL");
-    v = (e == nullptr || std::atoi(e) != 0) ? 1 : 0;
-  }
-  return v == 1;
+struct OptionDesc { const char* name; const char* env; int Options::*field; int dflt; };
+static const OptionDesc kOptions[] = {
+    {"pdl", "AVD_PDL", &Options::pdl, 1},
+    {"gemm_bn", "AVD_GEMM_BN", &Options::gemm_bn, 0},
+    {"gemm_v", "AVD_GEMM_V", &Options::gemm_v, 0},
+    {"gemm_generic", "AVD_GEMM_GENERIC", &Options::gemm_generic, 0},
+    {"gemm_pair", "AVD_GEMM_PAIR", &Options::gemm_pair, 0},
+    {"ps_max_stages", "AVD_PS_MAX_STAGES", &Options::ps_max_stages, 0},
+    {"ps_epi_cycles", "AVD_PS_EPI_CYCLES", &Options::ps_epi_cycles, 0},
+    {"ps_no256", "AVD_PS_NO256", &Options::ps_no256, 0},
+    {"attn_poly", "AVD_ATTN_POLY", &Options::attn_poly, 0},
+    {"attn_one", "AVD_ATTN_ONE", &Options::attn_one, 1},
+    {"chains", "AVD_CHAINS", &Options::chains, 1},
+    {"bx_wide", "AVD_BX_WIDE", &Options::bx_wide, -1},
+};
+
+Options& options() {
+  static Options o = [] {
+    Options v{};
+    for (const OptionDesc& d : kOptions) {
+      const char* e = std::getenv(d.env);
+      v.*(d.field) = (e != nullptr && *e != 0) ? std::atoi(e) : d.dflt;
+    }
+    return v;
+  }();
+  return o;
+}
+
+bool pdl_enabled() { return options().pdl != 0; }
+
+int ensure_dyn_smem(const void* fn, int bytes) {
+  static std::mutex mu;
+  static std::set<std::pair<int, const void*>> done;
+  int dev = 0;
+  AVD_CUDA(cudaGetDevice(&dev));
+  std::lock_guard<std::mutex> lk(mu);
+  if (done.count({dev, fn})) return 0;
+  AVD_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+  done.insert({dev, fn});
+  return 0;
 }
 
 static inline int64_t align_up(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
@@ -195,7 +239,8 @@ static int sampler_layout(const avd_sampler* s, SamplerLayout* L) {
   L->Da = s->Ca * s->chunk_len;
   L->d = s->core.d_model;
   L->d_adapt = L->d - s->tstep_dim;
-  AVD_REQUIRE(L->d_adapt > 0, "tstep_dim must be smaller than d_model");
+  AVD_REQUIRE(s->tstep_dim >= 0 && L->d_adapt > 0, "tstep_dim must be in [0, d_model)");
+  AVD_REQUIRE(s->tstep_dim == 0 || (s->temb_steps != nullptr && s->temb_zero != nullptr), "missing timestep-embedding tables");
   AVD_REQUIRE(L->d % 64 == 0, "d_model must be a multiple of 64");
   AVD_REQUIRE(s->head.d_in == L->d, "head input width must equal d_model");
   L->row_off_v = 0;
@@ -231,15 +276,37 @@ static int sampler_layout(const avd_sampler* s, SamplerLayout* L) {
   return 0;
 }
 
+// One fork/join stream set per device for the "chains" schedule (see core_blocks).  The library owns these few streams
+// and events; they carry no state between calls.
+struct ChainStreams {
+  cudaStream_t side[3] = {nullptr, nullptr, nullptr};
+  cudaEvent_t fork = nullptr;
+  cudaEvent_t join[3] = {nullptr, nullptr, nullptr};
+};
+static int chain_streams(ChainStreams** out) {
+  static std::mutex mu;
+  static std::unordered_map<int, ChainStreams> per_dev;
+  int dev = 0;
+  AVD_CUDA(cudaGetDevice(&dev));
+  std::lock_guard<std::mutex> lk(mu);
+  ChainStreams& c = per_dev[dev];
+  if (c.fork == nullptr) {
+    AVD_CUDA(cudaEventCreateWithFlags(&c.fork, cudaEventDisableTiming));
+    for (int i = 0; i < 3; ++i) {
+      AVD_CUDA(cudaStreamCreateWithFlags(&c.side[i], cudaStreamNonBlocking));
+      AVD_CUDA(cudaEventCreateWithFlags(&c.join[i], cudaEventDisableTiming));
+    }
+  }
+  *out = &c;
+  return 0;
+}
+
+// The blocks for rows [0, n_seq * N) of the given buffers on ONE stream.
 // last_out / last_prec: when given, the last block's residual stream leaves as bf16 segments of that precision in
 // last_out (the noise head's operand) instead of ws->xa.
-static int core_blocks(const avd_core_weights* w, const float* x_in, const void* xa_in, const float* ssq_in,
-                       const avd_core_workspace* ws, int n_seq, int N, void* last_out, int last_prec, cudaStream_t st) {
-  AVD_REQUIRE(w != nullptr && ws != nullptr, "null argument");
+static int core_blocks_rows(const avd_core_weights* w, const float* x_in, const void* xa_in, const float* ssq_in,
+                            const avd_core_workspace* ws, int n_seq, int N, void* last_out, int last_prec, cudaStream_t st) {
   const int d = w->d_model, S = nseg_of(w->precision);
-  AVD_REQUIRE(S > 0, "bad precision");
-  AVD_REQUIRE(d % 64 == 0 && w->n_heads > 0 && d % w->n_heads == 0, "bad d_model / n_heads");
-  AVD_REQUIRE(w->n_layers > 0 && w->n_layers <= AVD_MAX_LAYERS, "bad layer count");
   const int M = n_seq * N, parts = d / 64, hd = d / w->n_heads;
   const bool f16 = is_f16(w->precision);
   const bool tc_attn = (w->precision == AVD_PREC_BF16) || f16;
@@ -247,7 +314,6 @@ static int core_blocks(const avd_core_weights* w, const float* x_in, const void*
   // norm="layernorm": LayerNorm subtracts the row mean, so it cannot ride the GEMM as a row scale like RMSNorm does; it
   // is its own pass over the fp32 residual stream (layernorm_act_kernel) writing the operand of the QKV / fc1 GEMM
   const bool ln = w->norm_kind == 1;
-  AVD_REQUIRE(!ln || last_out == nullptr, "the fused sampler supports norm=\"rmsnorm\" cores only");
   const float x_unscale = (f16 && !ln) ? 1.0f / AVD_F16_XSCALE : 0.0f, x_scale = f16 ? AVD_F16_XSCALE : 0.0f;
   for (int l = 0; l < w->n_layers; ++l) {
     const avd_block_weights& b = w->blocks[l];
@@ -298,10 +364,63 @@ static int core_blocks(const avd_core_weights* w, const float* x_in, const void*
     g.A = ws->hmid; g.W = b.w_fc2; g.bias = b.b_fc2; g.resid = ws->x;
     g.out_f32 = ws->x; g.out_bf16 = ws->xa; g.out_precision = w->precision; g.ssq_out = ws->ssq;
     g.out_scale = x_scale;
+    void* xa_out = ws->xa;
     if (l == w->n_layers - 1 && last_out != nullptr) {   // the head's operand: pre-scaled too when the head runs in fp16
       g.out_bf16 = last_out; g.out_precision = last_prec; g.out_scale = is_f16(last_prec) ? AVD_F16_XSCALE : 0.0f;
+      xa_out = last_out;
     }
     AVD_TRY(launch_gemm(g, st));
+    if (f16 && ws->f16_sat_count != nullptr) {           // range check of this block's 16-bit operands (not in the timed path)
+      AVD_TRY(launch_f16_range_scan(ws->qkv, (int64_t)M * 3 * d, ws->f16_sat_count, st));
+      AVD_TRY(launch_f16_range_scan(ws->att, (int64_t)M * d, ws->f16_sat_count, st));
+      AVD_TRY(launch_f16_range_scan(ws->hmid, (int64_t)M * w->d_mlp, ws->f16_sat_count, st));
+      if (xa_out != last_out || is_f16(last_prec))
+        AVD_TRY(launch_f16_range_scan(xa_out, (int64_t)M * d, ws->f16_sat_count, st));
+    }
+  }
+  return 0;
+}
+
+// "chains" schedule (options().chains = C > 1, 16-bit single-segment modes): the n_seq sequences are independent, so they
+// are split into C groups whose block sequences run on forked streams and join before the head.  Kernels of different
+// groups then overlap on the device (one group's epilogue / launch latency under another group's mainloop) at the cost of
+// narrower grids per launch.  Off by default; bench.py --chains measures it.
+static int core_blocks(const avd_core_weights* w, const float* x_in, const void* xa_in, const float* ssq_in,
+                       const avd_core_workspace* ws, int n_seq, int N, void* last_out, int last_prec, cudaStream_t st) {
+  AVD_REQUIRE(w != nullptr && ws != nullptr, "null argument");
+  const int d = w->d_model, S = nseg_of(w->precision);
+  AVD_REQUIRE(S > 0, "bad precision");
+  AVD_REQUIRE(d % 64 == 0 && w->n_heads > 0 && d % w->n_heads == 0, "bad d_model / n_heads");
+  AVD_REQUIRE(w->n_layers > 0 && w->n_layers <= AVD_MAX_LAYERS, "bad layer count");
+  AVD_REQUIRE(w->norm_kind == 0 || last_out == nullptr, "a layernorm core hands the fp32 residual stream to its final norm");
+  int C = options().chains;
+  if (C > 4) C = 4;
+  const bool can_chain = C > 1 && S == 1 && n_seq % C == 0 && n_seq / C >= 2 && ws->key_mask == nullptr &&
+                         (last_out == nullptr || nseg_of(last_prec) == 1);
+  if (!can_chain) return core_blocks_rows(w, x_in, xa_in, ssq_in, ws, n_seq, N, last_out, last_prec, st);
+  ChainStreams* cs = nullptr;
+  AVD_TRY(chain_streams(&cs));
+  const int seq_c = n_seq / C;
+  const int64_t rows = (int64_t)seq_c * N, parts = d / 64;
+  AVD_CUDA(cudaEventRecord(cs->fork, st));
+  for (int c = 0; c < C; ++c) {
+    cudaStream_t sc = c == 0 ? st : cs->side[c - 1];
+    if (c > 0) AVD_CUDA(cudaStreamWaitEvent(sc, cs->fork, 0));
+    const int64_t r0 = c * rows;
+    avd_core_workspace wc = *ws;
+    wc.x = ws->x + r0 * d;
+    wc.xa = static_cast<uint8_t*>(ws->xa) + r0 * d * 2;
+    wc.ssq = ws->ssq + r0 * parts;
+    wc.qkv = static_cast<uint8_t*>(ws->qkv) + r0 * 3 * d * 2;
+    wc.att = static_cast<uint8_t*>(ws->att) + r0 * d * 2;
+    wc.hmid = static_cast<uint8_t*>(ws->hmid) + r0 * w->d_mlp * 2;
+    void* lo = last_out != nullptr ? static_cast<uint8_t*>(last_out) + r0 * d * 2 : nullptr;
+    AVD_TRY(core_blocks_rows(w, x_in + r0 * d, static_cast<const uint8_t*>(xa_in) + r0 * d * 2, ssq_in + r0 * parts, &wc,
+                             seq_c, N, lo, last_prec, sc));
+    if (c > 0) {
+      AVD_CUDA(cudaEventRecord(cs->join[c - 1], sc));
+      AVD_CUDA(cudaStreamWaitEvent(st, cs->join[c - 1], 0));
+    }
   }
   return 0;
 }
@@ -314,6 +433,7 @@ static int head_forward(const avd_head_weights* w, const void* h, int M, void* a
                         cudaStream_t st) {
   AVD_REQUIRE(w != nullptr, "null head");
   AVD_REQUIRE(w->n_shared >= 0 && w->n_shared <= AVD_MAX_SHARED, "bad shared-layer count");
+  AVD_REQUIRE(w->activation >= 0 && w->activation <= 3, "activation must be 0/1 (GELU), 2 (LeakyReLU 0.1) or 3 (ReLU)");
   const int S = nseg_of(w->precision);
   AVD_REQUIRE(S > 0, "bad precision");
   avd_gemm_args g{};
@@ -330,8 +450,8 @@ static int head_forward(const avd_head_weights* w, const void* h, int M, void* a
     g.M = M; g.N = w->hidden; g.K = w->hidden; g.precision = w->precision;
     g.A = cur; g.W = w->w_s[i]; g.bias = w->b_s[i]; g.out_f32 = y;
     AVD_TRY(launch_gemm(g, st));
-    AVD_TRY(launch_layernorm_act(y, w->ln_w[i], w->ln_b[i], M, w->hidden, w->ln_eps, 1, nullptr, nxt,
-                                 nseg_arg(w->precision, false), st));
+    AVD_TRY(launch_layernorm_act(y, w->ln_w[i], w->ln_b[i], M, w->hidden, w->ln_eps, w->activation <= 1 ? 1 : w->activation,
+                                 nullptr, nxt, nseg_arg(w->precision, false), st));
     void* t = cur; cur = nxt; nxt = t;
   }
   g = avd_gemm_args{};                       // eps = out_proj[m](x)   (noise_heads.py:219)
@@ -433,14 +553,50 @@ int avd_debug_gemm_timeout(unsigned int* out8) {
   return ps_debug_read(out8);
 }
 
-int avd_debug_skip_kinds(int mask) {
-  g_skip_kinds = mask;
-  return 0;
-}
 int avd_debug_trace(void* dev_u64, int64_t n_u64) {
+#ifdef AVD_DEBUG_HOOKS
   g_dbg_trace = static_cast<unsigned long long*>(dev_u64);
   g_dbg_trace_slots = dev_u64 ? n_u64 : 0;
   return 0;
+#else
+  (void)dev_u64; (void)n_u64;
+  AVD_FAIL("phase tracing is compiled out of this build (python -m multimodal_diffusion_b200.build --debug-hooks)");
+#endif
+}
+
+int avd_check_errors(void) {
+  unsigned int rec[256];
+  AVD_TRY(ps_debug_read(rec));
+  if (rec[0] != 0) {
+    std::string msg = "persistent GEMM: " + std::to_string(rec[0]) + " barrier wait(s) timed out; first record {tag " +
+                      std::to_string(rec[8]) + ", cta " + std::to_string(rec[9]) + ", thread " + std::to_string(rec[10]) +
+                      ", counter " + std::to_string(rec[11]) + ", parity " + std::to_string(rec[12]) + ", N " +
+                      std::to_string(rec[13]) + ", K " + std::to_string(rec[14]) + ", grid*1000+BN " +
+                      std::to_string(rec[15]) + "}";
+    AVD_FAIL(msg);
+  }
+  cudaError_t e = cudaPeekAtLastError();
+  if (e != cudaSuccess) AVD_FAIL(std::string("CUDA error pending on this device: ") + cudaGetErrorString(e));
+  return 0;
+}
+
+int avd_set_option(const char* name, int value) {
+  AVD_REQUIRE(name != nullptr, "null option name");
+  for (const OptionDesc& d : kOptions)
+    if (std::strcmp(d.name, name) == 0) {
+      options().*(d.field) = value;
+      return 0;
+    }
+  AVD_FAIL(std::string("unknown option '") + name + "'");
+}
+int avd_get_option(const char* name, int* value) {
+  AVD_REQUIRE(name != nullptr && value != nullptr, "null argument");
+  for (const OptionDesc& d : kOptions)
+    if (std::strcmp(d.name, name) == 0) {
+      *value = options().*(d.field);
+      return 0;
+    }
+  AVD_FAIL(std::string("unknown option '") + name + "'");
 }
 
 // ---- tokenisers
@@ -489,10 +645,18 @@ int avd_ddim_step(const float* x_t, const float* eps_hat, const float* noise, fl
   return launch_ddim_step(x_t, eps_hat, noise, x_prev, t_now, t_prev, alpha_bar, T_train, B, per_batch, eta,
                           AVD_STREAM(stream));
 }
+int avd_philox_normal(float* out, uint64_t seed, int64_t clip0, int step, int B, int64_t per_clip, void* stream) {
+  AVD_REQUIRE(out != nullptr || B * per_clip == 0, "null output");
+  return launch_philox_normal(out, seed, clip0, step, B, per_clip, AVD_STREAM(stream));
+}
+int avd_f16_range_scan(const void* buf, int64_t n, unsigned int* counter, void* stream) {
+  return launch_f16_range_scan(buf, n, counter, AVD_STREAM(stream));
+}
 int avd_cfg_untok_ddim(const avd_cfg_ddim_args* a, const float* eps_cond, const float* eps_null, const float* z_t,
                        float* z_prev, const float* alpha_bar, void* stream) {
   AVD_REQUIRE(a != nullptr, "null args");
   AVD_REQUIRE(a->t_now < a->T_train && a->t_prev < a->T_train, "timestep out of range");
+  AVD_REQUIRE(a->eta >= 0.0f, "eta must be >= 0");
   if (a->target == AVD_TARGET_VIDEO) {
     AVD_REQUIRE(a->tt > 0 && a->th > 0 && a->tw > 0 && a->T % a->tt == 0 && a->H % a->th == 0 && a->W % a->tw == 0,
                 "tube sizes must divide latent dims");
@@ -553,6 +717,8 @@ int avd_attention(const void* qkv, int qkv_is_f32, void* out_bf16, int out_preci
 // ---- core / head
 int avd_mmdt_blocks(const avd_core_weights* w, const float* x_in, const void* xa_in, const float* ssq_in,
                     const avd_core_workspace* ws, int n_seq, int N, void* stream) {
+  AVD_REQUIRE(ws != nullptr, "null workspace");
+  SkipKindsScope sk(ws->profile_skip_kinds);
   return core_blocks(w, x_in, xa_in, ssq_in, ws, n_seq, N, nullptr, 0, AVD_STREAM(stream));
 }
 int avd_head_forward(const avd_head_weights* w, const void* h, int M, void* act_a, void* act_b, float* y, float* eps,
@@ -573,6 +739,7 @@ int avd_sample_prepare(const avd_sampler* s, const float* z_prompt, void* stream
   SamplerLayout L;
   AVD_TRY(sampler_layout(s, &L));
   AVD_REQUIRE(s->workspace != nullptr && s->workspace_bytes >= L.total, "workspace too small");
+  SkipKindsScope sk(s->profile_skip_kinds);
   cudaStream_t st = AVD_STREAM(stream);
   uint8_t* ws = static_cast<uint8_t*>(s->workspace);
   // null-branch prompt rows are all-zero rows that stay in the sequence (sample_clip.py:338 / 377)
@@ -584,7 +751,8 @@ int avd_sample_prepare(const avd_sampler* s, const float* z_prompt, void* stream
   const float* wt = prompt_mod == 0 ? s->wv_t : s->wa_t;
   const float* bias = prompt_mod == 0 ? s->bv : s->ba;
   return launch_build_x(a, z_prompt, wt, bias, s->temb_zero, reinterpret_cast<float*>(ws + L.x_init),
-                        ws + L.xa_init, reinterpret_cast<float*>(ws + L.ssq_init), st);
+                        ws + L.xa_init, reinterpret_cast<float*>(ws + L.ssq_init), st,
+                        prompt_mod == 0 ? s->add_v : s->add_a, s->tadd_zero);
 }
 
 int avd_sample_step(const avd_sampler* s, int step, float* z, float* eps_tap, void* stream) {
@@ -592,17 +760,20 @@ int avd_sample_step(const avd_sampler* s, int step, float* z, float* eps_tap, vo
   AVD_TRY(sampler_layout(s, &L));
   AVD_REQUIRE(s->workspace != nullptr && s->workspace_bytes >= L.total, "workspace too small");
   AVD_REQUIRE(step >= 0 && step < s->steps, "step out of range");
+  AVD_REQUIRE(s->eta >= 0.0f, "eta must be >= 0");
+  SkipKindsScope sk(s->profile_skip_kinds);
   cudaStream_t st = AVD_STREAM(stream);
   uint8_t* ws = static_cast<uint8_t*>(s->workspace);
   float* x_init = reinterpret_cast<float*>(ws + L.x_init);
   float* ssq_init = reinterpret_cast<float*>(ws + L.ssq_init);
-  static const int dbg_skip = std::getenv("AVD_DBG_STEP_SKIP") ? std::atoi(std::getenv("AVD_DBG_STEP_SKIP")) : 0;  // timing aid
+  const bool ln = s->core.norm_kind == 1;
   // (1) target rows of the joint sequence, identical in the cond and null sequences
   const int tgt_mod = s->target == AVD_TARGET_VIDEO ? 0 : 1;
   BuildXArgs a = make_build_args(s, L, tgt_mod, true, true);
-  if (!(dbg_skip & 1))
   AVD_TRY(launch_build_x(a, z, tgt_mod == 0 ? s->wv_t : s->wa_t, tgt_mod == 0 ? s->bv : s->ba,
-                         s->temb_steps + (int64_t)step * s->tstep_dim, x_init, ws + L.xa_init, ssq_init, st));
+                         s->tstep_dim > 0 ? s->temb_steps + (int64_t)step * s->tstep_dim : nullptr, x_init,
+                         ws + L.xa_init, ssq_init, st, tgt_mod == 0 ? s->add_v : s->add_a,
+                         s->tadd_steps != nullptr ? s->tadd_steps + (int64_t)step * L.d_adapt : nullptr));
   // (2) 2B co-batched sequences through the blocks
   avd_core_workspace cw{};                       // key_mask = NULL: the sampler never pads (sample_clip.py:341)
   cw.x = reinterpret_cast<float*>(ws + L.x);
@@ -611,15 +782,29 @@ int avd_sample_step(const avd_sampler* s, int step, float* z, float* eps_tap, vo
   cw.qkv = ws + L.qkv;
   cw.att = ws + L.att;
   cw.hmid = ws + L.hmid;
-  if (!(dbg_skip & 2))
-  AVD_TRY(core_blocks(&s->core, x_init, ws + L.xa_init, ssq_init, &cw, L.n_seq, L.N, ws + L.h, s->head.precision, st));
-  // (3)+(4) final_norm folded into the input projection of the target modality's noise head, over all rows (F9: the
-  // non-target head is never evaluated; the target rows are selected by the CFG/DDIM kernel below)
+  cw.f16_sat_count = s->f16_sat_count;
   float* eps = reinterpret_cast<float*>(ws + L.eps);
-  if (!(dbg_skip & 8))
-  AVD_TRY(head_forward(&s->head, ws + L.h, (int)L.M, ws + L.act_a, ws + L.act_b, reinterpret_cast<float*>(ws + L.y), eps,
-                       cw.ssq, L.parts, L.d, s->core.rms_eps,
-                       is_f16(s->head.precision) ? 1.0f / AVD_F16_XSCALE : 0.0f, st));
+  if (!ln) {
+    AVD_TRY(core_blocks(&s->core, x_init, ws + L.xa_init, ssq_init, &cw, L.n_seq, L.N, ws + L.h, s->head.precision, st));
+    // (3)+(4) final RMSNorm folded into the input projection of the target modality's noise head, over all rows (F9:
+    // the non-target head is never evaluated; the target rows are selected by the CFG/DDIM kernel below)
+    AVD_TRY(head_forward(&s->head, ws + L.h, (int)L.M, ws + L.act_a, ws + L.act_b, reinterpret_cast<float*>(ws + L.y), eps,
+                         cw.ssq, L.parts, L.d, s->core.rms_eps,
+                         is_f16(s->head.precision) ? 1.0f / AVD_F16_XSCALE : 0.0f, st));
+  } else {
+    // norm="layernorm" (mmdt.py:45-46): the final nn.LayerNorm is its own pass over the fp32 residual stream and writes
+    // the head's (unscaled) operand; the head's input projection then needs no row scale
+    AVD_REQUIRE(s->core.final_ln_w != nullptr && s->core.final_ln_b != nullptr, "missing final_norm.weight / .bias");
+    AVD_TRY(core_blocks(&s->core, x_init, ws + L.xa_init, ssq_init, &cw, L.n_seq, L.N, nullptr, 0, st));
+    AVD_TRY(launch_layernorm_act(cw.x, s->core.final_ln_w, s->core.final_ln_b, (int)L.M, L.d, s->core.ln_eps, 0, nullptr,
+                                 ws + L.h, nseg_arg(s->head.precision, false), st));
+    AVD_TRY(head_forward(&s->head, ws + L.h, (int)L.M, ws + L.act_a, ws + L.act_b, reinterpret_cast<float*>(ws + L.y), eps,
+                         nullptr, 0, 0, 0.0f, 0.0f, st));
+  }
+  if (is_f16(s->head.precision) && s->f16_sat_count != nullptr) {
+    AVD_TRY(launch_f16_range_scan(ws + L.act_a, L.M * s->head.hidden, s->f16_sat_count, st));
+    if (s->head.n_shared > 0) AVD_TRY(launch_f16_range_scan(ws + L.act_b, L.M * s->head.hidden, s->f16_sat_count, st));
+  }
   const int row_off = s->target == AVD_TARGET_VIDEO ? L.row_off_v : L.row_off_a;
   const float* eps_c = eps + (int64_t)row_off * L.Dt;                          // rows of clip b: sequence b
   const float* eps_n = eps + ((int64_t)s->B * L.N + row_off) * L.Dt;           //                 sequence B + b
@@ -636,8 +821,8 @@ int avd_sample_step(const avd_sampler* s, int step, float* z, float* eps_tap, vo
   c.t_now = (int)s->timesteps_host[step];
   c.t_prev = (int)s->timesteps_host[step + 1];
   c.T_train = s->T_train;
+  c.eta = s->eta; c.step = step; c.seed = s->seed; c.clip0 = s->clip_index0;
   AVD_REQUIRE(c.t_now >= 0 && c.t_now < s->T_train && c.t_prev < s->T_train, "timestep out of range");
-  if (dbg_skip & 16) return 0;
   return launch_cfg_untok_ddim(c, eps_c, eps_n, z, z, s->alpha_bar, (int64_t)L.N * L.Dt, st);
 }
 

@@ -551,13 +551,6 @@ int launch_attention_tc(const void* qkv_bf16, void* out, int out_nseg, int n_seq
        {attn_tc_kernel<false, true, false>, attn_tc_kernel<false, true, true>}},
       {{attn_tc_kernel<true, false, false>, attn_tc_kernel<true, false, true>},
        {attn_tc_kernel<true, true, false>, attn_tc_kernel<true, true, true>}}};
-  static bool attr_set = false;
-  if (!attr_set) {
-    for (int a = 0; a < 8; ++a)
-      AVD_CUDA(cudaFuncSetAttribute(kernels[a >> 2][(a >> 1) & 1][a & 1], cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    ATT_SMEM));
-    attr_set = true;
-  }
   AttnParams p{};
   p.N = N; p.d = d; p.n_heads = n_heads; p.M = M;
   p.out = static_cast<__nv_bfloat16*>(out);
@@ -565,10 +558,7 @@ int launch_attention_tc(const void* qkv_bf16, void* out, int out_nseg, int n_seq
   p.scale_log2e = (1.0f / sqrtf((float)hd)) * 1.4426950408889634f;
   p.kmask = kmask;
   p.kmask_words = (N + 31) / 32;
-  {
-    const char* e = std::getenv("AVD_ATTN_POLY");
-    p.poly_exp = e ? std::atoi(e) : 0;   // measured 12 % slower on B200: off unless asked for
-  }
+  p.poly_exp = options().attn_poly;      // measured 12 % slower on B200: off unless asked for
   {
     const int64_t n_ctas = (int64_t)((N + 2 * ATT_BQ - 1) / (2 * ATT_BQ)) * n_heads * n_seq;
     p.trace = (g_dbg_trace != nullptr && n_ctas * 32 <= g_dbg_trace_slots) ? g_dbg_trace : nullptr;
@@ -590,9 +580,9 @@ int launch_attention_tc(const void* qkv_bf16, void* out, int out_nseg, int n_seq
   if (kind_skipped(KIND_ATTN_TC)) return 0;
   LaunchScope ls(KIND_ATTN_TC, s);
   AVD_REQUIRE(!f16 || out_nseg == 1, "the fp16 attention output has one segment");
-  static const int one_block_on = std::getenv("AVD_ATTN_ONE") ? std::atoi(std::getenv("AVD_ATTN_ONE")) : 1;   // A/B switch
-  AVD_CUDA(cudaLaunchKernelEx(&cfg, kernels[(N <= ATT_BKV && one_block_on) ? 1 : 0][f16 ? 1 : 0][kmask != nullptr ? 1 : 0],
-                              tmQ, tmKV, p));
+  const AttnFn fn = kernels[(N <= ATT_BKV && options().attn_one) ? 1 : 0][f16 ? 1 : 0][kmask != nullptr ? 1 : 0];
+  AVD_TRY(ensure_dyn_smem(reinterpret_cast<const void*>(fn), ATT_SMEM));   // once per device
+  AVD_CUDA(cudaLaunchKernelEx(&cfg, fn, tmQ, tmKV, p));
   return 0;
 }
 

@@ -281,6 +281,73 @@ int launch_timestep_embedding(const float* t, float* emb, int B, int dim, float 
 }
 
 // =====================================================================================================
+// Counter-based N(0,1) for ddim_step's eta > 0 branch (schedule_utils.py:185-197: sigma * randn_like(x_t)).
+// Philox4x32-10 (Salmon et al., SC'11; the generator behind curand / torch's CUDA randn) keyed by the sampler seed, with
+// the counter (element / 4, global clip index, step, 0): a clip's noise does not depend on its position in a batch or on
+// the GPU that samples it.  Box-Muller turns the four words into four normals ((u0,u1) -> n0,n1; (u2,u3) -> n2,n3).
+// =====================================================================================================
+__device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1,
+                                              uint32_t (&out)[4]) {
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+    const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+    const uint32_t n0 = hi1 ^ c1 ^ k0, n1 = lo1, n2 = hi0 ^ c3 ^ k1, n3 = lo0;
+    c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+    k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+  }
+  out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+
+__device__ __forceinline__ float philox_normal(uint64_t seed, int64_t clip, int step, int64_t elem) {
+  uint32_t w[4];
+  const uint64_t blk = (uint64_t)elem >> 2;
+  philox4x32_10((uint32_t)blk, (uint32_t)clip, (uint32_t)step, (uint32_t)(blk >> 32) ^ (uint32_t)((uint64_t)clip >> 32),
+                (uint32_t)seed, (uint32_t)(seed >> 32), w);
+  const int lane = (int)(elem & 3);
+  // u in (0, 1]: (w + 1) * 2^-32, so log(u) is finite
+  const float u_r = __fmul_rn(__fadd_rn((float)(w[lane & 2] >> 8), 1.0f), 5.9604644775390625e-8f);      // 24 bits
+  const float u_a = __fmul_rn((float)(w[(lane & 2) + 1] >> 8), 5.9604644775390625e-8f);
+  const float rad = sqrtf(-2.0f * logf(u_r));
+  float sn, cs;
+  sincospif(2.0f * u_a, &sn, &cs);
+  return (lane & 1) ? rad * sn : rad * cs;
+}
+
+__global__ void philox_normal_kernel(float* __restrict__ out, uint64_t seed, int64_t clip0, int step, int64_t per_clip) {
+  const int b = blockIdx.y;
+  for (int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; e < per_clip; e += (int64_t)gridDim.x * blockDim.x)
+    out[(int64_t)b * per_clip + e] = philox_normal(seed, clip0 + b, step, e);
+}
+
+int launch_philox_normal(float* out, uint64_t seed, int64_t clip0, int step, int B, int64_t per_clip, cudaStream_t s) {
+  if (B <= 0 || per_clip <= 0) return 0;
+  AVD_REQUIRE(B <= 65535, "batch too large for one launch");
+  LaunchScope ls(KIND_MISC, s);
+  philox_normal_kernel<<<dim3(std::min<int64_t>(cdiv(per_clip, 256), 1024), B), 256, 0, s>>>(out, seed, clip0, step, per_clip);
+  AVD_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// fp16 operand range check: counts +-65504 (the saturating packs' overflow value), inf and NaN bit patterns
+__global__ void f16_range_scan_kernel(const uint16_t* __restrict__ buf, int64_t n, unsigned int* __restrict__ counter) {
+  unsigned int bad = 0;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    bad += ((buf[i] & 0x7FFFu) >= 0x7BFFu) ? 1u : 0u;
+  bad = __reduce_add_sync(0xffffffffu, bad);
+  if ((threadIdx.x & 31) == 0 && bad != 0) atomicAdd(counter, bad);
+}
+
+int launch_f16_range_scan(const void* buf, int64_t n, unsigned int* counter, cudaStream_t s) {
+  if (n <= 0) return 0;
+  AVD_REQUIRE(buf != nullptr && counter != nullptr, "null argument");
+  LaunchScope ls(KIND_MISC, s);
+  f16_range_scan_kernel<<<std::min<int64_t>(cdiv(n, 256 * 8), 2048), 256, 0, s>>>(static_cast<const uint16_t*>(buf), n, counter);
+  AVD_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// =====================================================================================================
 // DDIM   (schedule_utils.py:146-200)
 // =====================================================================================================
 struct DdimCoef {
@@ -376,6 +443,13 @@ int launch_ddim_step(const float* x_t, const float* eps, const float* noise, flo
 // K7: fused CFG combine + un-tokenise + DDIM(eta=0)   (sample_clip.py:342-348 / 381-389)
 //   16 B per target-latent element: reads eps_cond, eps_null (token layout) and z_t, writes z_prev.
 // =====================================================================================================
+struct NoiseArgs {      // eta > 0 (schedule_utils.py:185-197): z of element e of clip b = philox_normal(seed, clip0 + b, step, e)
+  float eta;
+  int step;
+  uint64_t seed;
+  int64_t clip0;
+};
+
 __device__ __forceinline__ float cfg_mix(float ec, float en, float g) {
   return __fadd_rn(en, __fmul_rn(g, __fsub_rn(ec, en)));
 }
@@ -385,12 +459,12 @@ __global__ void __launch_bounds__(256) cfg_ddim_video_kernel(const float* __rest
                                                              const float* __restrict__ z_t, float* __restrict__ z_prev,
                                                              TubeDims d, float g, int t_now, int t_prev,
                                                              const float* __restrict__ alpha_bar, int64_t n_vec,
-                                                             int64_t clip_elems, int64_t clip_stride) {
+                                                             int64_t clip_elems, int64_t clip_stride, NoiseArgs nz) {
   constexpr int U = 2;                              // vectors per thread: 6 independent 16-byte loads in flight
   pdl_wait();
   pdl_launch_dependents();
   const int64_t v0 = (blockIdx.x * (int64_t)U) * blockDim.x + threadIdx.x;
-  const DdimCoef c = ddim_coef(alpha_bar, t_now, t_prev, 0.0f);
+  const DdimCoef c = ddim_coef(alpha_bar, t_now, t_prev, VEC == 1 ? nz.eta : 0.0f);   // eta > 0 takes the scalar path
   if (VEC == 4) {
     float4 ec[U], en[U], x[U];
 #pragma unroll
@@ -425,7 +499,9 @@ __global__ void __launch_bounds__(256) cfg_ddim_video_kernel(const float* __rest
         const I i = (I)v;
         I o = tube_token_index_from_latent<I>(d, i);
         o += (I)((i / (I)clip_elems) * (I)(clip_stride - clip_elems));
-        z_prev[i] = ddim_update(c, z_t[i], cfg_mix(__ldg(eps_c + o), __ldg(eps_n + o), g), 0.0f);
+        const float zn = nz.eta > 0.0f ? philox_normal(nz.seed, nz.clip0 + (int64_t)(i / (I)clip_elems), nz.step,
+                                                       (int64_t)(i % (I)clip_elems)) : 0.0f;
+        z_prev[i] = ddim_update(c, z_t[i], cfg_mix(__ldg(eps_c + o), __ldg(eps_n + o), g), zn);
       }
     }
   }
@@ -435,12 +511,13 @@ __global__ void __launch_bounds__(256) cfg_ddim_video_kernel(const float* __rest
 __global__ void cfg_ddim_audio_kernel(const float* __restrict__ eps_c, const float* __restrict__ eps_n,
                                       const float* __restrict__ z_t, float* __restrict__ z_prev, int C, int L, int N,
                                       int length, int stride, float g, int t_now, int t_prev,
-                                      const float* __restrict__ alpha_bar, int64_t total, int64_t clip_stride) {
+                                      const float* __restrict__ alpha_bar, int64_t total, int64_t clip_stride,
+                                      NoiseArgs nz) {
   pdl_wait();
   pdl_launch_dependents();
   int64_t o = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (o >= total) return;
-  DdimCoef cf = ddim_coef(alpha_bar, t_now, t_prev, 0.0f);
+  DdimCoef cf = ddim_coef(alpha_bar, t_now, t_prev, nz.eta);
   int p, c;
   int64_t b;
   if (total < (int64_t(1) << 31)) {
@@ -476,7 +553,8 @@ __global__ void cfg_ddim_audio_kernel(const float* __restrict__ eps_c, const flo
     }
     e = __fdiv_rn(acc, fmaxf(cnt, 1e-8f));
   }
-  z_prev[o] = ddim_update(cf, z_t[o], e, 0.0f);
+  const float zn = nz.eta > 0.0f ? philox_normal(nz.seed, nz.clip0 + b, nz.step, (int64_t)c * L + p) : 0.0f;
+  z_prev[o] = ddim_update(cf, z_t[o], e, zn);
 }
 
 // Same for disjoint windows of 4 (see unchunk1d_w4_kernel): per thread two 16-byte eps reads, z_t / z_prev as 8-byte pairs.
@@ -525,7 +603,8 @@ int launch_cfg_untok_ddim(const avd_cfg_ddim_args& a, const float* eps_c, const 
     if (total <= 0) return 0;
     uintptr_t al = reinterpret_cast<uintptr_t>(eps_c) | reinterpret_cast<uintptr_t>(eps_n) |
                    reinterpret_cast<uintptr_t>(z_t) | reinterpret_cast<uintptr_t>(z_prev);
-    bool v4 = (a.tw % 4 == 0) && ((al & 15) == 0);
+    const NoiseArgs nz{a.eta, a.step, a.seed, a.clip0};
+    bool v4 = (a.tw % 4 == 0) && ((al & 15) == 0) && !(a.eta > 0.0f);
     if (kind_skipped(KIND_CFG_DDIM)) return 0;
     LaunchScope ls(KIND_CFG_DDIM, s);
     // 32-bit index math when every eps / latent index fits (the index map is a chain of divisions)
@@ -534,13 +613,13 @@ int launch_cfg_untok_ddim(const avd_cfg_ddim_args& a, const float* eps_c, const 
       int64_t n_vec = total / 4;
       if (small)
         AVD_CUDA(launch_pdl(cfg_ddim_video_kernel<4, uint32_t>, dim3(cdiv(n_vec, 512)), dim3(256), 0, s, eps_c, eps_n, z_t,
-                            z_prev, d, a.guidance, a.t_now, a.t_prev, alpha_bar, n_vec, clip_elems, clip_stride));
+                            z_prev, d, a.guidance, a.t_now, a.t_prev, alpha_bar, n_vec, clip_elems, clip_stride, nz));
       else
         AVD_CUDA(launch_pdl(cfg_ddim_video_kernel<4, int64_t>, dim3(cdiv(n_vec, 512)), dim3(256), 0, s, eps_c, eps_n, z_t,
-                            z_prev, d, a.guidance, a.t_now, a.t_prev, alpha_bar, n_vec, clip_elems, clip_stride));
+                            z_prev, d, a.guidance, a.t_now, a.t_prev, alpha_bar, n_vec, clip_elems, clip_stride, nz));
     } else {
       AVD_CUDA(launch_pdl(cfg_ddim_video_kernel<1, int64_t>, dim3(cdiv(total, 512)), dim3(256), 0, s, eps_c, eps_n, z_t,
-                          z_prev, d, a.guidance, a.t_now, a.t_prev, alpha_bar, total, clip_elems, clip_stride));
+                          z_prev, d, a.guidance, a.t_now, a.t_prev, alpha_bar, total, clip_elems, clip_stride, nz));
     }
     AVD_CUDA(cudaGetLastError());
   } else {
@@ -552,14 +631,15 @@ int launch_cfg_untok_ddim(const avd_cfg_ddim_args& a, const float* eps_c, const 
     const int64_t total_w = (int64_t)a.B * a.C * ((a.L + 3) / 4);
     const uintptr_t al16 = reinterpret_cast<uintptr_t>(eps_c) | reinterpret_cast<uintptr_t>(eps_n);
     const uintptr_t al8 = reinterpret_cast<uintptr_t>(z_t) | reinterpret_cast<uintptr_t>(z_prev);
+    const NoiseArgs nz{a.eta, a.step, a.seed, a.clip0};
     const bool w4 = a.length == 4 && a.stride == 4 && a.L % 2 == 0 && clip_stride % 4 == 0 && (al16 & 15) == 0 &&
-                    (al8 & 7) == 0 && total_w < (int64_t(1) << 31);
+                    (al8 & 7) == 0 && total_w < (int64_t(1) << 31) && !(a.eta > 0.0f);
     if (w4)
       AVD_CUDA(launch_pdl(cfg_ddim_audio_w4_kernel, dim3(cdiv(total_w, 256)), dim3(256), 0, s, eps_c, eps_n, z_t, z_prev, a.C,
                           a.L, a.Nt, a.guidance, a.t_now, a.t_prev, alpha_bar, (uint32_t)total_w, clip_stride));
     else
       AVD_CUDA(launch_pdl(cfg_ddim_audio_kernel, dim3(cdiv(total, 256)), dim3(256), 0, s, eps_c, eps_n, z_t, z_prev, a.C, a.L,
-                          a.Nt, a.length, a.stride, a.guidance, a.t_now, a.t_prev, alpha_bar, total, clip_stride));
+                          a.Nt, a.length, a.stride, a.guidance, a.t_now, a.t_prev, alpha_bar, total, clip_stride, nz));
     AVD_CUDA(cudaGetLastError());
   }
   return 0;
@@ -706,7 +786,8 @@ int launch_rmsnorm_rows(const float* x, const float* scale, int n_seq, int N, in
   return 0;
 }
 
-// LayerNorm (+ GELU erf) rows; one warp per row held in registers (d <= 1024), two-pass statistics in fp32.
+// LayerNorm (+ activation: 1 GELU erf, 2 LeakyReLU(0.1), 3 ReLU) rows; one warp per row held in registers (d <= 1024), two-pass
+// statistics in fp32.
 constexpr int LN_MAX_V4 = 8;   // float4 per lane
 __global__ void __launch_bounds__(256) layernorm_act_kernel(const float* __restrict__ y, const float* __restrict__ w,
                                                             const float* __restrict__ b, int M, int d, float eps, int gelu,
@@ -748,9 +829,15 @@ __global__ void __launch_bounds__(256) layernorm_act_kernel(const float* __restr
       float4 bb = *reinterpret_cast<const float4*>(b + c);
       float o[4] = {(v[i].x - mu) * rstd * ww.x + bb.x, (v[i].y - mu) * rstd * ww.y + bb.y,
                     (v[i].z - mu) * rstd * ww.z + bb.z, (v[i].w - mu) * rstd * ww.w + bb.w};
-      if (gelu) {
+      if (gelu == 1) {
 #pragma unroll
         for (int k = 0; k < 4; ++k) o[k] = gelu_erf(o[k]);
+      } else if (gelu == 2) {                      // nn.LeakyReLU(0.1)
+#pragma unroll
+        for (int k = 0; k < 4; ++k) o[k] = o[k] >= 0.0f ? o[k] : __fmul_rn(o[k], 0.1f);
+      } else if (gelu == 3) {                      // nn.ReLU
+#pragma unroll
+        for (int k = 0; k < 4; ++k) o[k] = fmaxf(o[k], 0.0f);
       }
       int64_t idx = (int64_t)row * d + c;
       if (out_f32 != nullptr) *reinterpret_cast<float4*>(out_f32 + idx) = make_float4(o[0], o[1], o[2], o[3]);
@@ -777,6 +864,7 @@ int launch_layernorm_act(const float* y, const float* w, const float* b, int M, 
                          float* out_f32, void* out_bf16, int nseg, cudaStream_t s) {
   if (M <= 0) return 0;
   AVD_REQUIRE(d % 128 == 0 && d <= 128 * LN_MAX_V4, "LayerNorm rows must be a multiple of 128 wide, at most 1024");
+  AVD_REQUIRE(gelu >= 0 && gelu <= 3, "activation must be 0 (none), 1 (GELU), 2 (LeakyReLU 0.1) or 3 (ReLU)");
   if (kind_skipped(KIND_LN_ACT)) return 0;
   LaunchScope ls(KIND_LN_ACT, s);
   AVD_CUDA(launch_pdl(layernorm_act_kernel, dim3(cdiv(M, 8)), dim3(256), 0, s, y, w, b, M, d, eps, gelu, out_f32,
@@ -804,7 +892,9 @@ __global__ void __launch_bounds__(BX_THREADS) build_x_kernel(BuildXArgs a, const
                                                             const float* __restrict__ wt,
                                                             const float* __restrict__ bias,
                                                             const float* __restrict__ temb, float* __restrict__ x,
-                                                            __nv_bfloat16* __restrict__ xa, float* __restrict__ ssq) {
+                                                            __nv_bfloat16* __restrict__ xa, float* __restrict__ ssq,
+                                                            const float* __restrict__ add_rows,
+                                                            const float* __restrict__ tadd) {
   extern __shared__ float bx_smem[];
   float* tok = bx_smem;                       // [BX_R][d_tok]
   __shared__ float red[BX_R][BX_THREADS / 32];
@@ -913,6 +1003,8 @@ __global__ void __launch_bounds__(BX_THREADS) build_x_kernel(BuildXArgs a, const
       int c = tid + j * BX_THREADS;
       if (live && c < a.d_adapt) {
         float v = acc[r][j] + bv[j];
+        if (add_rows != nullptr) v += __ldg(add_rows + (int64_t)n * a.d_adapt + c);   // positional + modality embeddings
+        if (tadd != nullptr) v += __ldg(tadd + c);                                    // additive time embedding
         part += v * v;
         if (a.write_cond) { x[row_c + c] = v; store_split(xa, seg_stride, row_c + c, a.nseg, v); }
         if (a.write_null) { x[row_n + c] = v; store_split(xa, seg_stride, row_n + c, a.nseg, v); }
@@ -949,24 +1041,168 @@ __global__ void __launch_bounds__(BX_THREADS) build_x_kernel(BuildXArgs a, const
   }
 }
 
+// The same for many tokens (A2V: 96 video tokens x batch per step): 32 tokens per CTA so that each adapter weight, read
+// once per CTA from L2, feeds 32 rows (the 4-token kernel re-reads the 256 KB video adapter 1536 times at batch 64:
+// 393 MB of L2 traffic, 263 us).  Token values sit TRANSPOSED in smem ([k][32 rows]: one k = 8 broadcast 16-byte loads);
+// thread = adapter column(s), k ascending -> the same fp32 summation order as build_x_kernel.
+constexpr int BXW_R = 32;
+constexpr int BXW_J = 2;       // adapter columns per thread (d_adapt <= 512)
+__global__ void __launch_bounds__(BX_THREADS) build_x_wide_kernel(BuildXArgs a, const float* __restrict__ z,
+                                                                 const float* __restrict__ wt,
+                                                                 const float* __restrict__ bias,
+                                                                 const float* __restrict__ temb, float* __restrict__ x,
+                                                                 __nv_bfloat16* __restrict__ xa, float* __restrict__ ssq,
+                                                                 const float* __restrict__ add_rows,
+                                                                 const float* __restrict__ tadd) {
+  extern __shared__ float bx_smem[];
+  float* tok = bx_smem;                       // [d_tok][BXW_R]
+  __shared__ float red[BXW_R][BX_THREADS / 32];
+  const int groups = (a.n_tok + BXW_R - 1) / BXW_R;
+  const int b = blockIdx.x / groups;
+  const int n0 = (blockIdx.x % groups) * BXW_R;
+  const int tid = threadIdx.x;
+  const int ncol = (a.d_adapt + BX_THREADS - 1) / BX_THREADS;
+  float bv[BXW_J];
+#pragma unroll
+  for (int j = 0; j < BXW_J; ++j) {
+    const int c = tid + j * BX_THREADS;
+    bv[j] = (c < a.d_adapt) ? __ldg(bias + c) : 0.0f;
+  }
+  pdl_wait();
+  pdl_launch_dependents();
+  for (int idx = tid; idx < BXW_R * a.d_tok; idx += BX_THREADS) {
+    const int r = idx % BXW_R, k = idx / BXW_R;           // consecutive threads = consecutive tokens: conflict-free smem stores
+    const int n = n0 + r;
+    float v = 0.0f;
+    if (n < a.n_tok) {
+      int64_t src;
+      if (a.modality == 0) {
+        const int Hh = a.H / a.th, Ww = a.W / a.tw;
+        const int wk = n % Ww, hj = (n / Ww) % Hh, ti = n / (Ww * Hh);
+        const int dw = k % a.tw, dh = (k / a.tw) % a.th, dt = (k / (a.tw * a.th)) % a.tt, c = k / (a.tw * a.th * a.tt);
+        src = ((((int64_t)b * a.C + c) * a.T + (ti * a.tt + dt)) * a.H + (hj * a.th + dh)) * a.W + (wk * a.tw + dw);
+      } else {
+        const int j = k % a.length, c = k / a.length;
+        src = ((int64_t)b * a.C + c) * a.L + (int64_t)n * a.stride + j;
+      }
+      v = z[src];
+    }
+    tok[k * BXW_R + r] = v;
+  }
+  __syncthreads();
+  float acc[BXW_R][BXW_J];
+#pragma unroll
+  for (int r = 0; r < BXW_R; ++r)
+#pragma unroll
+    for (int j = 0; j < BXW_J; ++j) acc[r][j] = 0.0f;
+  constexpr int KU = 4;
+  for (int k0 = 0; k0 < a.d_tok; k0 += KU) {
+    float w[KU][BXW_J];
+#pragma unroll
+    for (int u = 0; u < KU; ++u)
+#pragma unroll
+      for (int j = 0; j < BXW_J; ++j) {
+        const int c = tid + j * BX_THREADS;
+        w[u][j] = (j < ncol && c < a.d_adapt && k0 + u < a.d_tok) ? __ldg(wt + (int64_t)(k0 + u) * a.d_adapt + c) : 0.0f;
+      }
+#pragma unroll
+    for (int u = 0; u < KU; ++u) {
+      if (k0 + u < a.d_tok) {
+        const float4* t4 = reinterpret_cast<const float4*>(tok + (k0 + u) * BXW_R);
+#pragma unroll
+        for (int q = 0; q < BXW_R / 4; ++q) {
+          const float4 t = t4[q];
+#pragma unroll
+          for (int j = 0; j < BXW_J; ++j) {
+            if (j < ncol) {
+              acc[4 * q][j] = fmaf(t.x, w[u][j], acc[4 * q][j]);
+              acc[4 * q + 1][j] = fmaf(t.y, w[u][j], acc[4 * q + 1][j]);
+              acc[4 * q + 2][j] = fmaf(t.z, w[u][j], acc[4 * q + 2][j]);
+              acc[4 * q + 3][j] = fmaf(t.w, w[u][j], acc[4 * q + 3][j]);
+            }
+          }
+        }
+      }
+    }
+  }
+  const int64_t seg_stride = a.M * (int64_t)a.d;
+#pragma unroll
+  for (int r = 0; r < BXW_R; ++r) {
+    const int n = n0 + r;
+    const bool live = n < a.n_tok;
+    float part = 0.0f;
+    const int64_t row_c = ((int64_t)b * a.N + a.row_off + n) * a.d;
+    const int64_t row_n = ((int64_t)(a.B + b) * a.N + a.row_off + n) * a.d;
+#pragma unroll
+    for (int j = 0; j < BXW_J; ++j) {
+      const int c = tid + j * BX_THREADS;
+      if (live && j < ncol && c < a.d_adapt) {
+        float v = acc[r][j] + bv[j];
+        if (add_rows != nullptr) v += __ldg(add_rows + (int64_t)n * a.d_adapt + c);
+        if (tadd != nullptr) v += __ldg(tadd + c);
+        part += v * v;
+        if (a.write_cond) { x[row_c + c] = v; store_split(xa, seg_stride, row_c + c, a.nseg, v); }
+        if (a.write_null) { x[row_n + c] = v; store_split(xa, seg_stride, row_n + c, a.nseg, v); }
+      }
+    }
+    for (int c2 = tid; c2 < a.tstep_dim; c2 += BX_THREADS) {
+      if (live) {
+        const float v = __ldg(temb + c2);
+        const int c = a.d_adapt + c2;
+        part += v * v;
+        if (a.write_cond) { x[row_c + c] = v; store_split(xa, seg_stride, row_c + c, a.nseg, v); }
+        if (a.write_null) { x[row_n + c] = v; store_split(xa, seg_stride, row_n + c, a.nseg, v); }
+      }
+    }
+    part = warp_sum(part);
+    if ((tid & 31) == 0) red[r][tid >> 5] = part;
+  }
+  __syncthreads();
+  for (int idx = tid; idx < BXW_R * a.ssq_parts; idx += BX_THREADS) {
+    const int r = idx / a.ssq_parts, p = idx % a.ssq_parts;
+    const int n = n0 + r;
+    if (n < a.n_tok) {
+      float v = 0.0f;
+      if (p == 0) {
+#pragma unroll
+        for (int wv = 0; wv < BX_THREADS / 32; ++wv) v += red[r][wv];
+      }
+      if (a.write_cond) ssq[((int64_t)b * a.N + a.row_off + n) * a.ssq_parts + p] = v;
+      if (a.write_null) ssq[((int64_t)(a.B + b) * a.N + a.row_off + n) * a.ssq_parts + p] = v;
+    }
+  }
+}
+
 int launch_build_x(const BuildXArgs& a, const float* z, const float* wt, const float* bias, const float* temb,
-                   float* x, void* xa, float* ssq, cudaStream_t s) {
+                   float* x, void* xa, float* ssq, cudaStream_t s, const float* add_rows, const float* tadd) {
   AVD_REQUIRE(a.d_adapt <= BX_THREADS * BX_J, "adapter width too large for build_x");
   AVD_REQUIRE(a.d_tok * BX_R * 4 <= 160 * 1024, "token width too large for build_x");
+  AVD_REQUIRE(a.tstep_dim == 0 || temb != nullptr, "missing timestep-embedding row");
   if (a.B <= 0 || a.n_tok <= 0) return 0;
+  if (kind_skipped(KIND_BUILD_X)) return 0;
+  // many wide tokens (A2V video rows at batch >= 4): 32 tokens per CTA
+  const int wide_opt = options().bx_wide;
+  const bool wide = a.d_adapt <= BX_THREADS * BXW_J && a.d_tok * BXW_R * 4 <= 96 * 1024 &&
+                    (wide_opt == 1 || (wide_opt != 0 && a.d_tok > 32 && (int64_t)a.B * a.n_tok >= 384));
+  if (wide) {
+    const int groups = (a.n_tok + BXW_R - 1) / BXW_R;
+    const size_t smem = (size_t)BXW_R * a.d_tok * sizeof(float);
+    if (smem > 32 * 1024) AVD_TRY(ensure_dyn_smem(reinterpret_cast<const void*>(build_x_wide_kernel), 96 * 1024));
+    LaunchScope ls(KIND_BUILD_X, s);
+    AVD_CUDA(launch_pdl(build_x_wide_kernel, dim3(a.B * groups), dim3(BX_THREADS), smem, s, a, z, wt, bias, temb, x,
+                        static_cast<__nv_bfloat16*>(xa), ssq, add_rows, tadd));
+    return 0;
+  }
   int groups = (a.n_tok + BX_R - 1) / BX_R;
   size_t smem = (size_t)BX_R * a.d_tok * sizeof(float);
-  if (smem > 48 * 1024) {
-    AVD_CUDA(cudaFuncSetAttribute(build_x_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  }
-  if (kind_skipped(KIND_BUILD_X)) return 0;
+  if (smem > 48 * 1024) AVD_TRY(ensure_dyn_smem(reinterpret_cast<const void*>(build_x_kernel<8>), 160 * 1024));
   LaunchScope ls(KIND_BUILD_X, s);
   if (a.d_tok <= 32)
     AVD_CUDA(launch_pdl(build_x_kernel<32>, dim3(a.B * groups), dim3(BX_THREADS), smem, s, a, z, wt, bias, temb, x,
-                        static_cast<__nv_bfloat16*>(xa), ssq));
+                        static_cast<__nv_bfloat16*>(xa), ssq, add_rows, tadd));
   else
     AVD_CUDA(launch_pdl(build_x_kernel<8>, dim3(a.B * groups), dim3(BX_THREADS), smem, s, a, z, wt, bias, temb, x,
-                        static_cast<__nv_bfloat16*>(xa), ssq));
+                        static_cast<__nv_bfloat16*>(xa), ssq, add_rows, tadd));
   return 0;
 }
 

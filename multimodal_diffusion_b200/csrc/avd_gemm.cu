@@ -410,11 +410,6 @@ if (f16_out) {
 unsigned long long* g_dbg_trace = nullptr;
 int64_t g_dbg_trace_slots = 0;
 
-static int env_int(const char* name, int dflt) {
-  const char* v = std::getenv(name);
-  return v ? std::atoi(v) : dflt;
-}
-
 template <int BN, int STAGES, bool PAIR = false>
 static int launch_gemm_bn(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmR, const GemmParams& p,
                           int mode, cudaStream_t s) {
@@ -422,12 +417,7 @@ static int launch_gemm_bn(const CUtensorMap& tmA, const CUtensorMap& tmB, const 
   using KernelFn = void (*)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const GemmParams);
   static const KernelFn kernels[4] = {gemm_tc_kernel<BN, STAGES, 0, PAIR>, gemm_tc_kernel<BN, STAGES, 1, PAIR>,
                                       gemm_tc_kernel<BN, STAGES, 2, PAIR>, gemm_tc_kernel<BN, STAGES, 3, PAIR>};
-  static bool attr_set = false;
-  if (!attr_set) {
-    for (int m = 0; m < 4; ++m)
-      AVD_CUDA(cudaFuncSetAttribute(kernels[m], cudaFuncAttributeMaxDynamicSharedMemorySize, S::total(BN <= 64)));
-    attr_set = true;
-  }
+  AVD_TRY(ensure_dyn_smem(reinterpret_cast<const void*>(kernels[mode]), S::total(BN <= 64)));   // once per device
   cudaLaunchConfig_t cfg{};
   const int mt = (p.M + GEMM_BM - 1) / GEMM_BM;
   // a pair = two consecutive row tiles (the last may be empty)
@@ -522,7 +512,7 @@ int launch_gemm(const avd_gemm_args& g, cudaStream_t s) {
   };
   const int cands[5] = {256, 192, 128, 64, 32};
   int bn = 0;
-  const int force_bn = env_int("AVD_GEMM_BN", 0);
+  const int force_bn = options().gemm_bn;
   if (force_bn > 0 && usable(force_bn)) bn = force_bn;
   for (int i = 0; i < 5 && bn == 0; ++i)
     if (usable(cands[i]) && (int64_t)mt * (g.N / cands[i]) >= 120) bn = cands[i];
@@ -533,7 +523,7 @@ int launch_gemm(const avd_gemm_args& g, cudaStream_t s) {
   // Two kernels.  While the tiles chosen above fit one wave of CTAs the one-tile-per-CTA kernel of this file wins (wide
   // tiles, every warp on the epilogue); beyond one wave the persistent kernel (avd_gemm_ps.cu) hides the epilogue under
   // the next tile's mainloop (+45 % at M = 32768, tools/kbench.py --M).  AVD_GEMM_V = 3 / 4 forces one of them.
-  static const int gemm_v = env_int("AVD_GEMM_V", 0);
+  const int gemm_v = options().gemm_v;
   {
     int dev = 0, sms = 148;
     if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
@@ -560,10 +550,10 @@ int launch_gemm(const avd_gemm_args& g, cudaStream_t s) {
   if (one16 && g.out_f32 == nullptr && g.resid == nullptr && g.ssq_out == nullptr && g.act == 0) mode = 1;
   else if (one16 && g.out_f32 == nullptr && g.resid == nullptr && g.ssq_out == nullptr && g.act == 2) mode = 2;
   else if (one16 && g.out_f32 != nullptr && g.resid != nullptr && g.ssq_out != nullptr && g.act == 0) mode = 3;
-  if (p.trace != nullptr || bn < 64 || env_int("AVD_GEMM_GENERIC", 0)) mode = 0;
+  if (p.trace != nullptr || bn < 64 || options().gemm_generic) mode = 0;
   // CTA pairs (cta_group::2): each SM stages half of the weight tile.  Needs both pipelines busy in the leader, a
   // specialised epilogue, and the padded grid (an even number of row tiles) still within one wave.
-  const int pair_on = env_int("AVD_GEMM_PAIR", 0);
+  const int pair_on = options().gemm_pair;
   int sms_now = 148;
   {
     int dev = 0;

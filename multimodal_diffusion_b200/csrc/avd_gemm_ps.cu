@@ -469,11 +469,6 @@ if (f16_out) {
   if (threadIdx.x == 0) trace_mark(trace, 7);
 }
 
-static int ps_env_int(const char* name, int dflt) {
-  const char* v = std::getenv(name);
-  return v ? std::atoi(v) : dflt;
-}
-
 int ps_debug_read(unsigned int* out8) {       // host copy of the timeout record; clears it
   for (int i = 0; i < 256; ++i) {
     out8[i] = g_ps_dbg_host != nullptr ? g_ps_dbg_host[i] : 0u;
@@ -498,12 +493,7 @@ static int launch_ps_bn(const CUtensorMap& tmA, const CUtensorMap& tmB, const CU
   using KernelFn = void (*)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const GemmParams, const PsPlan);
   static const KernelFn kernels[4] = {gemm_ps_kernel<BN, 0>, gemm_ps_kernel<BN, 1>, gemm_ps_kernel<BN, 2>,
                                       gemm_ps_kernel<BN, 3>};
-  static bool attr_set = false;
-  if (!attr_set) {
-    for (int m = 0; m < 4; ++m)
-      AVD_CUDA(cudaFuncSetAttribute(kernels[m], cudaFuncAttributeMaxDynamicSharedMemorySize, PS_SMEM_MAX + 1024));
-    attr_set = true;
-  }
+  AVD_TRY(ensure_dyn_smem(reinterpret_cast<const void*>(kernels[mode]), PS_SMEM_MAX + 1024));   // once per device
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(grid);
   cfg.blockDim = dim3(PS_THREADS);
@@ -532,8 +522,8 @@ static bool ps_plan(const avd_gemm_args& g, int out_nseg, int bn, PsPlan* plan, 
   const int fixed = f32_bytes + bf_bytes + PS_TAIL_BYTES;
   int stages = (PS_SMEM_MAX - fixed) / stage;
   if (stages > PS_MAX_STAGES) stages = PS_MAX_STAGES;
-  static const int cap = ps_env_int("AVD_PS_MAX_STAGES", PS_MAX_STAGES);
-  if (stages > cap) stages = cap;
+  const int cap = options().ps_max_stages;
+  if (cap > 0 && stages > cap) stages = cap;
   stages &= ~1;   // even: global iteration `it` then always lands in a ring slot of its own parity, so every slot (and
                   // its two barriers) has ONE producer and ONE issuer, who see its uses in order (parity waits are
                   // only sound when the waiter is never two phases away from the barrier)
@@ -558,7 +548,7 @@ int launch_gemm_ps(const avd_gemm_args& g, GemmParams p, int nseg, int force_bn,
   //   (epilogue constants: 1500 cycles per 64-column round for the generic / residual epilogues, 1100 for the specialised
   //   16-bit-only ones, GELU +10 %: with the old 1500 / +30 % the model kept fc1 on 128-wide tiles, 12 % slower than
   //   256-wide at M = 4256 .. 17024, tools/kbench.py --M with AVD_GEMM_BN=256)
-  static const int c_epi_env = ps_env_int("AVD_PS_EPI_CYCLES", 0);
+  const int c_epi_env = options().ps_epi_cycles;
   const bool fast16 = g.out_bf16 != nullptr && out_nseg == 1 && g.out_f32 == nullptr && g.resid == nullptr &&
                       g.ssq_out == nullptr;
   const int c_epi = c_epi_env > 0 ? c_epi_env : (fast16 ? 1100 : 1500);
@@ -584,7 +574,7 @@ int launch_gemm_ps(const avd_gemm_args& g, GemmParams p, int nseg, int force_bn,
   if (force_bn > 0 && usable(force_bn)) bn = force_bn;
   if (bn == 0) {
     double best = 0.0;
-    for (int i = ps_env_int("AVD_PS_NO256", 0) ? 1 : 0; i < 4; ++i)
+    for (int i = options().ps_no256 ? 1 : 0; i < 4; ++i)
       if (usable(cands[i])) {
         const double c = cost(cands[i]);
         if (bn == 0 || c < best) { bn = cands[i]; best = c; }
@@ -620,7 +610,7 @@ int launch_gemm_ps(const avd_gemm_args& g, GemmParams p, int nseg, int force_bn,
   if (one16 && g.out_f32 == nullptr && g.resid == nullptr && g.ssq_out == nullptr && g.act == 0) mode = 1;
   else if (one16 && g.out_f32 == nullptr && g.resid == nullptr && g.ssq_out == nullptr && g.act == 2) mode = 2;
   else if (one16 && g.out_f32 != nullptr && g.resid != nullptr && g.ssq_out != nullptr && g.act == 0) mode = 3;
-  if (p.trace != nullptr || bn < 64 || ps_env_int("AVD_GEMM_GENERIC", 0)) mode = 0;
+  if (p.trace != nullptr || bn < 64 || options().gemm_generic) mode = 0;
   switch (bn) {
     case 256: return launch_ps_bn<256>(tmA, tmB, tmR, p, plan, smem_bytes, grid, mode, s);
     case 128: return launch_ps_bn<128>(tmA, tmB, tmR, p, plan, smem_bytes, grid, mode, s);

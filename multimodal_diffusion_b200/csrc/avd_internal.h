@@ -111,16 +111,49 @@ struct BuildXArgs {
   int ssq_parts;
   int64_t M;               // n_seq_total * N
 };
+// add_rows: optional [n_tok][d_adapt] rows added after the adapter (positional + modality embeddings); tadd: optional
+// [d_adapt] additive time embedding of this step
 int launch_build_x(const BuildXArgs& a, const float* z, const float* wt, const float* bias, const float* temb,
-                   float* x, void* xa, float* ssq, cudaStream_t s);
+                   float* x, void* xa, float* ssq, cudaStream_t s, const float* add_rows = nullptr,
+                   const float* tadd = nullptr);
+int launch_philox_normal(float* out, uint64_t seed, int64_t clip0, int step, int B, int64_t per_clip, cudaStream_t s);
+int launch_f16_range_scan(const void* buf, int64_t n, unsigned int* counter, cudaStream_t s);
 
 // tcgen05 GEMM (avd_gemm.cu)
 int launch_gemm(const avd_gemm_args& g, cudaStream_t s);
 
-extern int g_skip_kinds;   // debug / measurement: bit k set -> launches of Kind k are skipped (avd_debug_skip_kinds)
-inline bool kind_skipped(int k) { return (g_skip_kinds >> k) & 1; }
-bool pdl_enabled();     // programmatic dependent launch between the kernels of a step (AVD_PDL=0 switches it off)
-extern unsigned long long* g_dbg_trace;   // debug phase trace of the GEMM kernel (avd_debug_trace)
+// Measurement aid scoped to ONE avd_sample_* call (avd_sampler.profile_skip_kinds): bit k set -> launches of Kind k are
+// skipped while that call runs on this thread.  There is no process-wide switch.
+extern thread_local int t_skip_kinds;
+inline bool kind_skipped(int k) { return (t_skip_kinds >> k) & 1; }
+struct SkipKindsScope {
+  explicit SkipKindsScope(int mask) : prev(t_skip_kinds) { t_skip_kinds = mask; }
+  ~SkipKindsScope() { t_skip_kinds = prev; }
+  int prev;
+};
+
+// Tuning / A-B switches.  Every AVD_* environment variable is read ONCE, when the library is first used; afterwards the
+// values only change through avd_set_option (tools and tests), never through the environment.
+struct Options {
+  int pdl;             // AVD_PDL            programmatic dependent launch between the kernels of a step (default 1)
+  int gemm_bn;         // AVD_GEMM_BN        force a tile width (0 = model)
+  int gemm_v;          // AVD_GEMM_V         3 = one-tile kernel, 4 = persistent kernel, 0 = by wave count
+  int gemm_generic;    // AVD_GEMM_GENERIC   1 = generic epilogue instead of the specialised ones
+  int gemm_pair;       // AVD_GEMM_PAIR      cta_group::2 variant of the one-tile kernel (0 off, 1 specialised, 2 all)
+  int ps_max_stages;   // AVD_PS_MAX_STAGES  ring depth cap of the persistent kernel (0 = its maximum)
+  int ps_epi_cycles;   // AVD_PS_EPI_CYCLES  epilogue constant of the tile-width model (0 = built in)
+  int ps_no256;        // AVD_PS_NO256       1 = no 256-wide column-split tiles
+  int attn_poly;       // AVD_ATTN_POLY      polynomial exp2 share of the multi-block attention path
+  int attn_one;        // AVD_ATTN_ONE       0 = multi-block attention kernel even for N <= 192
+  int chains;          // AVD_CHAINS         independent sequence groups of a sampler step run on forked streams (1 = off)
+  int bx_wide;         // AVD_BX_WIDE        -1 = by size, 0 / 1 = never / always the 16-token build_x kernel
+};
+Options& options();
+bool pdl_enabled();
+
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) once per (device, kernel): the attribute is per device
+int ensure_dyn_smem(const void* fn, int bytes);
+extern unsigned long long* g_dbg_trace;   // debug phase trace of the GEMM kernel (avd_debug_trace; needs a build with AVD_DEBUG_HOOKS)
 extern int64_t g_dbg_trace_slots;
 
 // attention (avd_attn.cu)

@@ -39,11 +39,41 @@ def transpose_f32(W: torch.Tensor) -> torch.Tensor:
     return out
 
 
+ACTIVATIONS = {"gelu": 1, "leaky_relu": 2, "relu": 3}     # noise_heads._make_activation's names -> kernel code
+
+
+def activation_code(name: Optional[str]) -> int:
+    key = (name or "gelu").lower()
+    if key not in ACTIVATIONS:
+        raise ValueError(f"Unsupported activation: {name}")          # noise_heads.py:31
+    return ACTIVATIONS[key]
+
+
+def module_hyper(module) -> Dict[str, object]:
+    """Hyper-parameters the packers cannot see in a state_dict, read from a live (reference or mirror) module: norm eps
+    values, head activation, training flag.  Empty for a bare state_dict."""
+    out: Dict[str, object] = {}
+    if isinstance(module, dict) or module is None:
+        return out
+    out["training"] = bool(getattr(module, "training", False))
+    for m in module.modules():
+        cls = type(m).__name__
+        if cls == "RMSNorm" and "rms_eps" not in out:
+            out["rms_eps"] = float(getattr(m, "eps", 1e-6))
+        elif cls == "LayerNorm" and "ln_eps" not in out:
+            out["ln_eps"] = float(m.eps)
+        elif cls in ("GELU", "LeakyReLU", "ReLU") and "activation" not in out:
+            out["activation"] = {"GELU": "gelu", "LeakyReLU": "leaky_relu", "ReLU": "relu"}[cls]
+        elif cls == "Dropout" and float(m.p) > 0.0:
+            out["dropout"] = True
+    return out
+
+
 class PackedCore:
     """MMDiT weights (mmdt.py state_dict keys) packed for avd_mmdt_blocks."""
 
     def __init__(self, sd: Dict[str, torch.Tensor], n_layers: int, n_heads: int, precision, device,
-                 rms_eps: float = 1e-6):
+                 rms_eps: float = 1e-6, ln_eps: float = 1e-5):
         self.precision = _lib.precision_code(precision)
         self.n_layers, self.n_heads = int(n_layers), int(n_heads)
         self.layernorm = "final_norm.scale" not in sd          # build_norm (mmdt.py:45-46): nn.LayerNorm has weight/bias
@@ -80,10 +110,11 @@ class PackedCore:
                 lnp = [_dev_f32(sd[p + k], device) for k in ("norm1.weight", "norm1.bias", "norm2.weight", "norm2.bias")]
                 self.keep += lnp
                 bw.ln1_w, bw.ln1_b, bw.ln2_w, bw.ln2_b = (t.data_ptr() for t in lnp)
-        w.norm_kind, w.ln_eps = (1 if self.layernorm else 0), 1e-5
+        w.norm_kind, w.ln_eps = (1 if self.layernorm else 0), float(ln_eps)
         if self.layernorm:
             self.final_ln_w = _dev_f32(sd["final_norm.weight"], device)
             self.final_ln_b = _dev_f32(sd["final_norm.bias"], device)
+            w.final_ln_w, w.final_ln_b = self.final_ln_w.data_ptr(), self.final_ln_b.data_ptr()
             self.final_scale = torch.ones(d, device=device, dtype=torch.float32)
         else:
             self.final_scale = _dev_f32(sd["final_norm.scale"], device)
@@ -96,39 +127,46 @@ class PackedCore:
 
 
 class PackedHead:
-    """One modality's path of MultiModalNoiseHead (noise_heads.py state_dict keys) for avd_head_forward."""
+    """One modality's path of MultiModalNoiseHead (noise_heads.py state_dict keys) for avd_head_forward:
+    input_proj[m] -> shared[i] ... -> spec[m][j] (or shared_specific_trunk[j]) ... -> out_proj[m]."""
 
     def __init__(self, sd: Dict[str, torch.Tensor], modality: str, precision, device, ln_eps: float = 1e-5,
-                 in_col_scale: Optional[torch.Tensor] = None):
+                 in_col_scale: Optional[torch.Tensor] = None, activation: Optional[str] = "gelu"):
         """in_col_scale: RMSNorm ``scale`` of the layer feeding the head (MMDiT.final_norm); when given it is folded
-        into the columns of input_proj so the fused sampler can apply the norm as a row scale in the GEMM epilogue."""
+        into the columns of input_proj so the fused sampler can apply the norm as a row scale in the GEMM epilogue.
+        activation: the head's `activation` argument ("gelu" / "relu" / "leaky_relu"); it is not part of a state_dict."""
         self.precision = _lib.precision_code(precision)
         self.modality = modality
-        n_shared = 0
-        while f"shared.{n_shared}.0.weight" in sd:
-            n_shared += 1
-        if n_shared > _lib.AVD_MAX_SHARED:
-            raise ValueError(f"at most {_lib.AVD_MAX_SHARED} shared layers")
-        if any(k.startswith(f"spec.{modality}.") or k.startswith("shared_specific_trunk.") for k in sd):
-            raise NotImplementedError("modality-specific trunk layers (num_modality_specific_layers > 1) are not on "
-                                      "the sampler's path (sample_clip.py:99-107)")
+        trunk: List[str] = []                                  # state_dict prefixes of the Linear+LN blocks, in order
+        i = 0
+        while f"shared.{i}.0.weight" in sd:
+            trunk.append(f"shared.{i}")
+            i += 1
+        for prefix in (f"spec.{modality}", "shared_specific_trunk"):     # noise_heads.py:149-172, 213-218
+            j = 0
+            while f"{prefix}.{j}.0.weight" in sd:
+                trunk.append(f"{prefix}.{j}")
+                j += 1
+        if len(trunk) > _lib.AVD_MAX_SHARED:
+            raise ValueError(f"at most {_lib.AVD_MAX_SHARED} trunk layers (shared + modality-specific)")
         self.keep: List[torch.Tensor] = []
         w = _lib.HeadWeights()
         win = _dev_f32(sd[f"input_proj.{modality}.weight"], device)
         wout = _dev_f32(sd[f"out_proj.{modality}.weight"], device)
         w.hidden, w.d_in = int(win.shape[0]), int(win.shape[1])
-        w.d_out, w.n_shared = int(wout.shape[0]), n_shared
+        w.d_out, w.n_shared = int(wout.shape[0]), len(trunk)
         w.precision, w.ln_eps = self.precision, float(ln_eps)
+        w.activation = activation_code(activation)
         cs = None if in_col_scale is None else _dev_f32(in_col_scale, device)
         pin, pout = pack_linear_weight(win, self.precision, cs), pack_linear_weight(wout, self.precision)
         bin_, bout = _dev_f32(sd[f"input_proj.{modality}.bias"], device), _dev_f32(sd[f"out_proj.{modality}.bias"], device)
         self.keep += [pin, pout, bin_, bout]
         w.w_in, w.b_in, w.w_out, w.b_out = pin.data_ptr(), bin_.data_ptr(), pout.data_ptr(), bout.data_ptr()
-        for i in range(n_shared):
-            ws = pack_linear_weight(_dev_f32(sd[f"shared.{i}.0.weight"], device), self.precision)
-            bs = _dev_f32(sd[f"shared.{i}.0.bias"], device)
-            lw = _dev_f32(sd[f"shared.{i}.1.weight"], device)
-            lb = _dev_f32(sd[f"shared.{i}.1.bias"], device)
+        for i, prefix in enumerate(trunk):
+            ws = pack_linear_weight(_dev_f32(sd[f"{prefix}.0.weight"], device), self.precision)
+            bs = _dev_f32(sd[f"{prefix}.0.bias"], device)
+            lw = _dev_f32(sd[f"{prefix}.1.weight"], device)
+            lb = _dev_f32(sd[f"{prefix}.1.bias"], device)
             self.keep += [ws, bs, lw, lb]
             w.w_s[i], w.b_s[i], w.ln_w[i], w.ln_b[i] = ws.data_ptr(), bs.data_ptr(), lw.data_ptr(), lb.data_ptr()
         self.d_in, self.hidden, self.d_out = w.d_in, w.hidden, w.d_out

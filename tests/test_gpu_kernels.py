@@ -212,13 +212,14 @@ def test_gemm_split_precision(dev, M, N, K, precision, tol):
 
 
 @pytest.mark.parametrize("M,N,K", [(2128, 1536, 512), (300, 512, 512), (266, 512, 2048), (2128, 2048, 512)])
-def test_gemm_cta_pair(dev, monkeypatch, M, N, K):
-    """The cta_group::2 variant (two SMs on one 256-row tile, opt-in through AVD_GEMM_PAIR) against the same exact
-    bf16 products, and bit-identical to the single-CTA kernel (same k order per accumulator)."""
-    monkeypatch.setenv("AVD_GEMM_PAIR", "2")
-    got, want, _, _ = _gemm_case(dev, M, N, K, "bf16")
-    monkeypatch.setenv("AVD_GEMM_PAIR", "0")
-    base, _, _, _ = _gemm_case(dev, M, N, K, "bf16")
+def test_gemm_cta_pair(dev, M, N, K):
+    """The cta_group::2 variant (two SMs on one 256-row tile, opt-in through the gemm_pair option) against the same
+    exact bf16 products, and bit-identical to the single-CTA kernel (same k order per accumulator)."""
+    from multimodal_diffusion_b200 import _lib
+    with _lib.option("gemm_pair", 2):
+        got, want, _, _ = _gemm_case(dev, M, N, K, "bf16")
+    with _lib.option("gemm_pair", 0):
+        base, _, _, _ = _gemm_case(dev, M, N, K, "bf16")
     assert rel_l2(got, want) < 2e-6
     assert torch.equal(got, base)
 

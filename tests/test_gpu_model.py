@@ -51,17 +51,18 @@ def test_mmdit_forward_vs_reference(dev, mods, precision, tol):
     assert err_c < tol and err_n < tol
 
 
-def test_mmdit_forward_cta_pair_kernels(dev, mods, monkeypatch):
-    """The specialised epilogues of the cta_group::2 GEMM variant (AVD_GEMM_PAIR=1) through a whole forward."""
+def test_mmdit_forward_cta_pair_kernels(dev, mods):
+    """The specialised epilogues of the cta_group::2 GEMM variant (option gemm_pair = 1) through a whole forward."""
+    from multimodal_diffusion_b200 import _lib
     g = golden("mvp_forward")
     core = mods[2]
     core.precision = "f16"
     X = T(g["X"]).to(dev).repeat(8, 1, 1)        # 16 sequences: the row-tile count the sampling batch has
     with torch.no_grad():
-        monkeypatch.setenv("AVD_GEMM_PAIR", "0")
-        base = core(X)
-        monkeypatch.setenv("AVD_GEMM_PAIR", "1")
-        h = core(X)
+        with _lib.option("gemm_pair", 0):
+            base = core(X)
+        with _lib.option("gemm_pair", 1):
+            h = core(X)
     assert rel_l2(h[:2], g["h_cond"]) < 1.5e-3
     assert torch.equal(h, base)
 

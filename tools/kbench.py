@@ -159,7 +159,7 @@ def main() -> None:
             print(f"   {nm:26s} cycles: median {ck[:, i].median():8.0f} max {ck[:, i].max():8.0f} | ns since kernel start: "
                   f"median {gt[:, i].median():8.0f} max {gt[:, i].max():8.0f}")
         import os
-        v4 = os.environ.get("AVD_GEMM_V", "3") != "3"
+        v4 = _lib.get_option("gemm_v") != 3
         for name, fn in (("qkv", g_qkv), ("oproj", g_o), ("fc1", g_fc1), ("fc2", g_fc2), ("head", g_head)):
             buf = torch.zeros(32 * 512, device=dev, dtype=torch.int64)
             fn()

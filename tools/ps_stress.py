@@ -1,5 +1,5 @@
 """Stress the persistent GEMM inside the fused sampler (development tool): replays the V2A B=8 sampling graph and an
-A2V B=64 call, then prints the barrier-timeout record (run with AVD_PS_NOTRAP=1)."""
+A2V B=64 call, then prints the barrier-timeout record."""
 import ctypes as C
 import sys
 from pathlib import Path

@@ -24,6 +24,10 @@ def main() -> None:
     mods = seeded_modules()
     B = int(sys.argv[1]) if len(sys.argv) > 1 else 8
     target = sys.argv[2] if len(sys.argv) > 2 else "audio"
+    for a in sys.argv:                      # --opt name=value sets a library tuning switch (e.g. --opt chains=2)
+        if a.startswith("--opt="):
+            k, v = a[6:].split("=")
+            _lib.set_option(k, int(v))
     fs = FusedSampler(HotPathConfig(sampler_steps=50, guidance=3.5), mods[0], mods[1], mods[2], mods[3], target, B,
                       device=dev)
     zp = randn(1, *fs.prompt_shape).to(dev)
@@ -35,7 +39,8 @@ def main() -> None:
         _lib.check(lib.avd_sample_step(C.byref(fs.args), 3, z.data_ptr(), None, _lib.stream_ptr()))
 
     us = time_graph(step, 10)
-    print(f"one DDIM+CFG step ({target}, B={B}): {us:9.2f} us  -> {B / (us * 50e-6):8.1f} clips/s")
+    opts = " ".join(a[6:] for a in sys.argv if a.startswith("--opt="))
+    print(f"one DDIM+CFG step ({target}, B={B}) {opts}: {us:9.2f} us  -> {B / (us * 50e-6):8.1f} clips/s")
     if "--kinds" not in sys.argv:
         return
     # per-kind breakdown with the event profiler (eager; includes launch gaps, use for shares only)

@@ -6,7 +6,7 @@ For joint sequence length N in {512 .. 16384} x batch B in {1 .. 64} (cells abov
 runs the mvp.yaml MMDiT (d = 512, L = 8, H = 8, MLP 2048, random init) forward in --precision mode (bf16 / f16) through
 avd_mmdt_blocks on unit-rms activations, times it with CUDA events (warm-up, then the median of `iters` runs), and
 times the GEMM family and the attention family separately by replaying the same call with the other kernels
-dropped (avd_debug_skip_kinds).  FLOPs are SURVEY.md §8(d)'s algorithmic figures: GEMM 24 d^2 per token-layer,
+dropped (avd_core_workspace.profile_skip_kinds).  FLOPs are SURVEY.md §8(d)'s algorithmic figures: GEMM 24 d^2 per token-layer,
 attention 4 N d per token-layer.  Peak = MEASURED_PEAKS.json sustained bf16.  (Correctness of the same call is the
 job of tests/test_gpu_model.py; this tool only measures.)
 """
@@ -85,11 +85,11 @@ def main() -> None:
                                                C.byref(ws), B, N, _lib.stream_ptr()))
 
             us_all = time_call(fwd, args.iters)
-            _lib.check(lib.avd_debug_skip_kinds(all_kinds & ~(1 << KIND_GEMM)))
+            ws.profile_skip_kinds = all_kinds & ~(1 << KIND_GEMM)      # scoped to this workspace's calls
             us_gemm = time_call(fwd, args.iters)
-            _lib.check(lib.avd_debug_skip_kinds(all_kinds & ~(1 << KIND_ATTN_TC)))
+            ws.profile_skip_kinds = all_kinds & ~(1 << KIND_ATTN_TC)
             us_attn = time_call(fwd, args.iters)
-            _lib.check(lib.avd_debug_skip_kinds(0))
+            ws.profile_skip_kinds = 0
             f_gemm = L * M * 24.0 * d * d
             f_attn = L * M * 4.0 * N * d
             row = {
