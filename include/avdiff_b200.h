@@ -56,7 +56,7 @@ int avd_nseg(int precision);                 /* 1 -> 1, 3 -> 2, 6 -> 3, else -1 
 int avd_device_check(void);                  /* 0 iff the current device is sm_100 */
 /* sizeof() of the ABI structs as this library was compiled (binding self-check):
  * 0 avd_cfg_ddim_args, 1 avd_gemm_args, 2 avd_block_weights, 3 avd_core_weights, 4 avd_core_workspace,
- * 5 avd_head_weights, 6 avd_sampler; -1 for any other id */
+ * 5 avd_head_weights, 6 avd_sampler, 7 avd_vae_weights; -1 for any other id */
 int avd_struct_size(int which);
 
 /* Per-launch profiler (CUDA events on `stream` around every kernel this library launches).
@@ -314,6 +314,50 @@ int avd_sample_prepare(const avd_sampler* s, const float* z_prompt, void* stream
 int avd_sample_step(const avd_sampler* s, int step, float* z, float* eps_tap, void* stream);
 /* sample_one_direction's loop (sample_clip.py:317-348 / 359-389) for a batch: prepare + S steps. */
 int avd_sample_loop(const avd_sampler* s, const float* z_prompt, float* z, void* stream);
+
+/* ---------------------------------------------------------------- encoders / decoders
+ * AudioCodec.encode (avdiff/models/encoders/audio_codec.py:184-199): wav[B,1,L] -> z[B,Ca,Fa].
+ *   pre[0][0] Conv1d(1->H,k9)+GELU, pre[1][0] Conv1d(H->H,k9)+GELU, right-pad / crop to Fa*hop, avg_pool1d(hop),
+ *   to_lat 1x1.  (Fa, hop) are what AudioCodec._avgpool_frames derives (:149-176): Fa = frames_per_clip with
+ *   hop = _compute_exact_pool_params(L, Fa), or Fa = ceil(L / hop_samples) with hop = hop_samples.
+ *   Weights in the module's layouts: w_pre0[H,1,9], w_pre1[H,H,9], w_lat[Ca,H,1]; H a multiple of 8, <= 64. */
+int avd_audio_encode(const float* wav, float* z, int B, int L, int H, int Ca, int Fa, int hop, const float* w_pre0,
+                     const float* b_pre0, const float* w_pre1, const float* b_pre1, const float* w_lat,
+                     const float* b_lat, void* stream);
+/* AudioCodec.decode (audio_codec.py:201-214): z[B,Ca,Fa] -> wav[B,1,Fa*hop]: from_lat 1x1, nearest upsample (ATen's
+ * fp32 index rule), smooth[0] / smooth[2] Conv1d(H->H,K)+GELU, smooth[4] Conv1d(H->1,K), tanh.  K in {3,5,7,9,11}.
+ * scratch: >= avd_audio_decode_scratch_bytes() device bytes (one [B,H,Fa*hop] fp32 activation). */
+int64_t avd_audio_decode_scratch_bytes(int B, int H, int Fa, int hop);
+int avd_audio_decode(const float* z, float* wav, float* scratch, int B, int Ca, int Fa, int H, int hop, int K,
+                     const float* w_from, const float* b_from, const float* w_s0, const float* b_s0, const float* w_s2,
+                     const float* b_s2, const float* w_s4, const float* b_s4, void* stream);
+
+#define AVD_VAE_MAX_BLOCKS 8
+/* VideoVAE parameters (avdiff/models/encoders/vae_video3d.py:87-127), fp32 device pointers in the module's layouts:
+ * conv weights [64,Cin,3,3,3], GroupNorm weight / bias [64], 1x1x1 convs [Cout,Cin,1,1,1]. */
+typedef struct {
+  int in_ch, lat_ch, base;           /* 3, Cv, 64 (enc_base = dec_base = 64: the kernels' trunk width) */
+  int t_down, s_down;
+  int enc_blocks, dec_blocks;
+  int out_tanh;                      /* 0 = sigmoid (default), 1 = tanh (out_activation) */
+  float gn_eps;                      /* nn.GroupNorm eps (1e-5) */
+  const float* enc_w[AVD_VAE_MAX_BLOCKS]; const float* enc_b[AVD_VAE_MAX_BLOCKS];        /* enc_net[i][0] */
+  const float* enc_gn_w[AVD_VAE_MAX_BLOCKS]; const float* enc_gn_b[AVD_VAE_MAX_BLOCKS];  /* enc_net[i][2] */
+  const float* to_lat_w; const float* to_lat_b;                                          /* to_lat (or to_mu) */
+  const float* from_lat_w; const float* from_lat_b;
+  const float* dec_w[AVD_VAE_MAX_BLOCKS]; const float* dec_b[AVD_VAE_MAX_BLOCKS];        /* dec_net[i][0] */
+  const float* dec_gn_w[AVD_VAE_MAX_BLOCKS]; const float* dec_gn_b[AVD_VAE_MAX_BLOCKS];  /* dec_net[i][2] */
+  const float* to_img_w; const float* to_img_b;
+} avd_vae_weights;
+/* device scratch for one encode or decode call at full resolution (two [B,64,T,H,W] fp32 activations + statistics) */
+int64_t avd_vae_scratch_bytes(int B, int T, int H, int W);
+/* VideoVAE.encode (vae_video3d.py:164-190, eval: z = mu when variational): x[B,3,T,H,W] -> z[B,Cv,T/td,H/sd,W/sd].
+ * T, H, W must already be multiples of (t_down, s_down, s_down) (the mirror center-crops like :139-162). */
+int avd_video_encode(const avd_vae_weights* w, const float* x, float* z, void* scratch, int B, int T, int H, int W,
+                     void* stream);
+/* VideoVAE.decode (vae_video3d.py:196-214): z[B,Cv,Tl,Hl,Wl] -> x_hat[B,3,T,H,W] (trilinear, align_corners=False). */
+int avd_video_decode(const avd_vae_weights* w, const float* z, float* x, void* scratch, int B, int Tl, int Hl, int Wl, int T,
+                     int H, int W, void* stream);
 
 #ifdef __cplusplus
 }

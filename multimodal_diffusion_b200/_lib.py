@@ -100,6 +100,20 @@ class SamplerArgs(C.Structure):
                 ("profile_skip_kinds", C.c_int), ("f16_sat_count", vp)]
 
 
+AVD_VAE_MAX_BLOCKS = 8
+
+
+class VaeWeights(C.Structure):
+    _fields_ = [("in_ch", C.c_int), ("lat_ch", C.c_int), ("base", C.c_int), ("t_down", C.c_int), ("s_down", C.c_int),
+                ("enc_blocks", C.c_int), ("dec_blocks", C.c_int), ("out_tanh", C.c_int), ("gn_eps", C.c_float),
+                ("enc_w", fp * AVD_VAE_MAX_BLOCKS), ("enc_b", fp * AVD_VAE_MAX_BLOCKS),
+                ("enc_gn_w", fp * AVD_VAE_MAX_BLOCKS), ("enc_gn_b", fp * AVD_VAE_MAX_BLOCKS),
+                ("to_lat_w", fp), ("to_lat_b", fp), ("from_lat_w", fp), ("from_lat_b", fp),
+                ("dec_w", fp * AVD_VAE_MAX_BLOCKS), ("dec_b", fp * AVD_VAE_MAX_BLOCKS),
+                ("dec_gn_w", fp * AVD_VAE_MAX_BLOCKS), ("dec_gn_b", fp * AVD_VAE_MAX_BLOCKS),
+                ("to_img_w", fp), ("to_img_b", fp)]
+
+
 # name -> (restype, argtypes); every symbol include/avdiff_b200.h declares
 _I = C.c_int
 _SIGNATURES = {
@@ -145,9 +159,15 @@ _SIGNATURES = {
     "avd_sample_prepare": (_I, [C.POINTER(SamplerArgs), fp, vp]),
     "avd_sample_step": (_I, [C.POINTER(SamplerArgs), _I, fp, fp, vp]),
     "avd_sample_loop": (_I, [C.POINTER(SamplerArgs), fp, fp, vp]),
+    "avd_audio_encode": (_I, [fp, fp, _I, _I, _I, _I, _I, _I, fp, fp, fp, fp, fp, fp, vp]),
+    "avd_audio_decode_scratch_bytes": (C.c_int64, [_I, _I, _I, _I]),
+    "avd_audio_decode": (_I, [fp, fp, fp, _I, _I, _I, _I, _I, _I, fp, fp, fp, fp, fp, fp, fp, fp, vp]),
+    "avd_vae_scratch_bytes": (C.c_int64, [_I, _I, _I, _I]),
+    "avd_video_encode": (_I, [C.POINTER(VaeWeights), fp, fp, vp, _I, _I, _I, _I, vp]),
+    "avd_video_decode": (_I, [C.POINTER(VaeWeights), fp, fp, vp, _I, _I, _I, _I, _I, _I, _I, vp]),
 }
 EXPORTED_SYMBOLS = tuple(_SIGNATURES)
-ABI_STRUCTS = (CfgDdimArgs, GemmArgs, BlockWeights, CoreWeights, CoreWorkspace, HeadWeights, SamplerArgs)
+ABI_STRUCTS = (CfgDdimArgs, GemmArgs, BlockWeights, CoreWeights, CoreWorkspace, HeadWeights, SamplerArgs, VaeWeights)
 
 _lib: Optional[C.CDLL] = None
 

@@ -2,8 +2,9 @@
 avdiff/models/infer/sample_clip.py's sampling surface; the CLI / file IO of the reference is out of scope).
 
 ``sample_one_direction`` keeps the reference's keyword signature and return value.  The encoders/decoders
-(VideoVAE / AudioCodec) are NOT part of this package: pass any objects with
-``encode`` / ``decode`` (the reference's own modules on CUDA, or stand-ins that inject latents).  The loop
+(VideoVAE / AudioCodec) are the mirror modules of ``avdiff/models/encoders`` (CUDA kernels of
+csrc/avd_codec.cu / avd_vae.cu); any other objects with ``encode`` / ``decode`` work too (stand-ins that inject latents
+in the tests).  The loop
 itself runs as the fused, CUDA-graph-captured kernel sequence of ``FusedSampler`` -- one sequence for the
 cond and null CFG branches together -- instead of the reference's ~400 eager launches per step.
 """
@@ -36,8 +37,15 @@ def add_sinusoidal_timestep(tokens: torch.Tensor, t_scalar: torch.Tensor, dim: i
 
 
 def build_components(cfg: Dict, device: torch.device, vid_vae=None, aud_codec=None):
-    """Reference: sample_clip.py:75-109.  Returns the same 7-tuple; the encoder slots carry whatever the caller
-    supplies (None by default -- the encoders live outside the hot path)."""
+    """Reference: sample_clip.py:75-109.  Returns the same 7-tuple, built in the reference's order (VideoVAE, AudioCodec,
+    adapters, core, head) so a seeded construction draws the same parameters.  vid_vae / aud_codec (extension): use
+    these objects instead of constructing the mirror encoders (anything with ``encode`` / ``decode``)."""
+    from ..encoders.audio_codec import AudioCodec
+    from ..encoders.vae_video3d import VideoVAE
+    if vid_vae is None:
+        vid_vae = VideoVAE.from_config(cfg["video"]).to(device).eval()
+    if aud_codec is None:
+        aud_codec = AudioCodec.from_config(cfg["audio"]).to(device).eval()
     d = int(cfg["tokenizer"]["width"])
     out_v = int(cfg["model"]["heads"]["video"]["out_dim"])
     out_a = int(cfg["model"]["heads"]["audio"]["out_dim"])

@@ -504,6 +504,7 @@ int avd_struct_size(int which) {
     case 4: return (int)sizeof(avd_core_workspace);
     case 5: return (int)sizeof(avd_head_weights);
     case 6: return (int)sizeof(avd_sampler);
+    case 7: return (int)sizeof(avd_vae_weights);
     default: return -1;
   }
 }

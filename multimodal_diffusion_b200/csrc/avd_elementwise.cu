@@ -1046,7 +1046,8 @@ __global__ void __launch_bounds__(BX_THREADS) build_x_kernel(BuildXArgs a, const
 // 393 MB of L2 traffic, 263 us).  Token values sit TRANSPOSED in smem ([k][32 rows]: one k = 8 broadcast 16-byte loads);
 // thread = adapter column(s), k ascending -> the same fp32 summation order as build_x_kernel.
 constexpr int BXW_R = 32;
-constexpr int BXW_J = 2;       // adapter columns per thread (d_adapt <= 512)
+constexpr int BXW_JMAX = 2;    // adapter columns per thread (d_adapt <= 512)
+template <int BXW_J>
 __global__ void __launch_bounds__(BX_THREADS) build_x_wide_kernel(BuildXArgs a, const float* __restrict__ z,
                                                                  const float* __restrict__ wt,
                                                                  const float* __restrict__ bias,
@@ -1095,16 +1096,27 @@ __global__ void __launch_bounds__(BX_THREADS) build_x_wide_kernel(BuildXArgs a, 
   for (int r = 0; r < BXW_R; ++r)
 #pragma unroll
     for (int j = 0; j < BXW_J; ++j) acc[r][j] = 0.0f;
-  constexpr int KU = 4;
-  for (int k0 = 0; k0 < a.d_tok; k0 += KU) {
-    float w[KU][BXW_J];
+  // adapter weights: KU rows per batch, the NEXT batch's loads in flight while this one is consumed (the loads come
+  // from L2, ~600 cycles; without the double buffer every batch would wait them out)
+  constexpr int KU = 8;
+  float wn[KU][BXW_J];
+  auto load_batch = [&](int k0) {
 #pragma unroll
     for (int u = 0; u < KU; ++u)
 #pragma unroll
       for (int j = 0; j < BXW_J; ++j) {
         const int c = tid + j * BX_THREADS;
-        w[u][j] = (j < ncol && c < a.d_adapt && k0 + u < a.d_tok) ? __ldg(wt + (int64_t)(k0 + u) * a.d_adapt + c) : 0.0f;
+        wn[u][j] = (j < ncol && c < a.d_adapt && k0 + u < a.d_tok) ? __ldg(wt + (int64_t)(k0 + u) * a.d_adapt + c) : 0.0f;
       }
+  };
+  load_batch(0);
+  for (int k0 = 0; k0 < a.d_tok; k0 += KU) {
+    float w[KU][BXW_J];
+#pragma unroll
+    for (int u = 0; u < KU; ++u)
+#pragma unroll
+      for (int j = 0; j < BXW_J; ++j) w[u][j] = wn[u][j];
+    if (k0 + KU < a.d_tok) load_batch(k0 + KU);
 #pragma unroll
     for (int u = 0; u < KU; ++u) {
       if (k0 + u < a.d_tok) {
@@ -1182,15 +1194,22 @@ int launch_build_x(const BuildXArgs& a, const float* z, const float* wt, const f
   if (kind_skipped(KIND_BUILD_X)) return 0;
   // many wide tokens (A2V video rows at batch >= 4): 32 tokens per CTA
   const int wide_opt = options().bx_wide;
-  const bool wide = a.d_adapt <= BX_THREADS * BXW_J && a.d_tok * BXW_R * 4 <= 96 * 1024 &&
+  const bool wide = a.d_adapt <= BX_THREADS * BXW_JMAX && a.d_tok * BXW_R * 4 <= 96 * 1024 &&
                     (wide_opt == 1 || (wide_opt != 0 && a.d_tok > 32 && (int64_t)a.B * a.n_tok >= 384));
   if (wide) {
     const int groups = (a.n_tok + BXW_R - 1) / BXW_R;
     const size_t smem = (size_t)BXW_R * a.d_tok * sizeof(float);
-    if (smem > 32 * 1024) AVD_TRY(ensure_dyn_smem(reinterpret_cast<const void*>(build_x_wide_kernel), 96 * 1024));
-    LaunchScope ls(KIND_BUILD_X, s);
-    AVD_CUDA(launch_pdl(build_x_wide_kernel, dim3(a.B * groups), dim3(BX_THREADS), smem, s, a, z, wt, bias, temb, x,
-                        static_cast<__nv_bfloat16*>(xa), ssq, add_rows, tadd));
+    if (a.d_adapt <= BX_THREADS) {
+      if (smem > 32 * 1024) AVD_TRY(ensure_dyn_smem(reinterpret_cast<const void*>(build_x_wide_kernel<1>), 96 * 1024));
+      LaunchScope ls(KIND_BUILD_X, s);
+      AVD_CUDA(launch_pdl(build_x_wide_kernel<1>, dim3(a.B * groups), dim3(BX_THREADS), smem, s, a, z, wt, bias, temb, x,
+                          static_cast<__nv_bfloat16*>(xa), ssq, add_rows, tadd));
+    } else {
+      if (smem > 32 * 1024) AVD_TRY(ensure_dyn_smem(reinterpret_cast<const void*>(build_x_wide_kernel<2>), 96 * 1024));
+      LaunchScope ls(KIND_BUILD_X, s);
+      AVD_CUDA(launch_pdl(build_x_wide_kernel<2>, dim3(a.B * groups), dim3(BX_THREADS), smem, s, a, z, wt, bias, temb, x,
+                          static_cast<__nv_bfloat16*>(xa), ssq, add_rows, tadd));
+    }
     return 0;
   }
   int groups = (a.n_tok + BX_R - 1) / BX_R;

@@ -272,7 +272,8 @@ def test_mirror_build_components(dev):
     from multimodal_diffusion_b200.avdiff.models.infer import sample_clip as sc
     cfg = json.loads((GOLDEN / "cfg_mvp_v2a.json").read_text())
     vae, codec, adapt_v, adapt_a, core, head, tdim = sc.build_components(cfg, dev)
-    assert vae is None and codec is None and tdim == 256
+    assert type(vae).__name__ == "VideoVAE" and type(codec).__name__ == "AudioCodec" and tdim == 256
+    assert codec.cfg.frames_per_clip == 150 and codec.hop == 320 and vae.cfg.t_down == 4 and vae.cfg.s_down == 8
     assert adapt_v.proj.weight.shape == (256, 256) and adapt_a.proj.weight.shape == (256, 32)
     assert len(core.blocks) == 8 and not core.training and not head.training
     ref = seeded_modules()
@@ -365,10 +366,13 @@ def test_fused_loop_eta_positive(dev, mods, w_cpu, target):
     full = _sampler(mods, target, B, "fp32", "fp32", steps=4, eta=eta, seed=seed).sample_eager(zp.to(dev), zi.to(dev))
     part = _sampler(mods, target, 2, "fp32", "fp32", steps=4, eta=eta, seed=seed, clip_index0=2) \
         .sample_eager(zp[2:].to(dev), zi[2:].to(dev))
-    assert rel_l2(part, full[2:]) < 1e-5
+    err_same = rel_l2(part, full[2:])
+    assert err_same < 1e-5
     other = _sampler(mods, target, 2, "fp32", "fp32", steps=4, eta=eta, seed=seed, clip_index0=0) \
         .sample_eager(zp[2:].to(dev), zi[2:].to(dev))
-    assert rel_l2(other, full[2:]) > 1e-3                                 # a different clip index draws different noise
+    # a different clip index draws different noise (sigma * z is small against |z| ~ 1e4 after 4 steps, but far above
+    # the fp32 agreement of the same-index run)
+    assert rel_l2(other, full[2:]) > max(2e-5, 5 * err_same)
 
 
 # ------------------------------------------------------------------------------------------ N4: layernorm core, head variants
@@ -548,3 +552,100 @@ def test_fused_sampler_on_non_current_device(mods):
     assert z1.device.index == 1 and torch.equal(z1, z1e) and torch.equal(z1.cpu(), z0.cpu())
     with pytest.raises(ValueError, match="lives on"):
         fs1.sample_eager(zp.to("cuda:0"), zi.to("cuda:0"))
+
+
+# ------------------------------------------------------------------------------------------ N1: encoders / decoders
+def _golden_codec(seed, **kw):
+    from multimodal_diffusion_b200.avdiff.models.encoders.audio_codec import AudioCodec, AudioCodecConfig
+    torch.manual_seed(seed)
+    return AudioCodec(AudioCodecConfig(lat_ch=8, hidden=64, smooth_kernel=7, **kw)).eval()
+
+
+def _golden_vae():
+    from multimodal_diffusion_b200.avdiff.models.encoders.vae_video3d import VideoVAE, VideoVAEConfig
+    torch.manual_seed(502)
+    vae = VideoVAE(VideoVAEConfig(lat_ch=8, t_down=4, s_down=8, enc_base=64, enc_blocks=2, dec_base=64, dec_blocks=2)).eval()
+    with torch.no_grad():
+        for k, v in vae.state_dict().items():
+            if ".2.weight" in k:
+                v.copy_(1.0 + 0.2 * randn(len(k), *v.shape))
+            elif ".2.bias" in k:
+                v.copy_(0.1 * randn(len(k) + 1, *v.shape))
+    return vae
+
+
+def test_audio_codec_vs_reference(dev):
+    """AudioCodec.encode / decode (audio_codec.py:184-214) against the reference module's outputs: exact-frame pooling
+    with a right pad (L = 3163 -> 10 frames of 317), the hop_samples path (ceil(L / hop) frames), nearest upsample."""
+    g = golden("encoders")
+    codec = _golden_codec(500, hop_samples=320, frames_per_clip=10)
+    sums = np.array([[float(v.double().sum()), float(v.double().abs().sum())] for v in codec.state_dict().values()])
+    assert np.allclose(sums, g["codec_sums"], rtol=1e-12)
+    codec = codec.to(dev)
+    with torch.no_grad():
+        z = codec.encode(T(g["wav"]).to(dev))
+        assert z.shape == (2, 8, 10) and rel_l2(z, g["z_a"]) < TOL_EPS_FP32
+        wav_hat = codec.decode(T(g["z_a"]).to(dev))
+        assert wav_hat.shape == (2, 1, 3200) and rel_l2(wav_hat, g["wav_hat"]) < TOL_EPS_FP32
+        codec2 = _golden_codec(501, hop_samples=160, frames_per_clip=None).to(dev)
+        z2 = codec2.encode(T(g["wav2"]).to(dev))
+        assert z2.shape == (1, 8, 11) and rel_l2(z2, g["z_a2"]) < TOL_EPS_FP32
+        assert rel_l2(codec2.decode(T(g["z_a2"]).to(dev)), g["wav_hat2"]) < TOL_EPS_FP32
+        with pytest.raises(AssertionError):
+            codec.encode(torch.zeros(2, 2, 100, device=dev))                  # audio_codec.py:191
+    from multimodal_diffusion_b200 import _lib
+    with pytest.raises(_lib.AvdError, match="CUDA"), torch.no_grad():
+        codec.encode(torch.zeros(1, 1, 640))                                  # no CPU path
+
+
+def test_video_vae_vs_reference(dev):
+    """VideoVAE.encode / decode (vae_video3d.py:164-214) against the reference module: conv3d + GELU + GroupNorm blocks,
+    AvgPool3d, trilinear upsample; plus the center-crop of a non-divisible clip and a round trip at mvp size."""
+    g = golden("encoders")
+    vae = _golden_vae()
+    sums = np.array([[float(v.double().sum()), float(v.double().abs().sum())] for v in vae.state_dict().values()])
+    assert np.allclose(sums, g["vae_sums"], rtol=1e-12)
+    vae = vae.to(dev)
+    x = T(g["frames"]).to(dev)
+    with torch.no_grad():
+        z = vae.encode(x)
+        err_e = rel_l2(z, g["z_v"])
+        x_hat = vae.decode(T(g["z_v"]).to(dev))
+        err_d = rel_l2(x_hat, g["frames_hat"])
+        print(f"[VideoVAE] encode rel-L2 {err_e:.2e}  decode rel-L2 {err_d:.2e}")
+        assert z.shape == (1, 8, 2, 4, 4) and err_e < TOL_EPS_FP32
+        assert x_hat.shape == (1, 3, 8, 32, 32) and err_d < TOL_EPS_FP32
+        # non-divisible input: center-cropped like the reference (33 -> 32 rows from offset 0, 9 -> 8 frames)
+        xp = torch.nn.functional.pad(x, (0, 0, 0, 1, 0, 1))
+        with pytest.warns(UserWarning):
+            zc = vae.encode(xp)
+        assert torch.equal(zc, z)
+        # full mvp size (3 s, 128 x 128): shapes, finiteness, value range, determinism
+        big = torch.rand(1, 3, 48, 128, 128, device=dev)
+        zb = vae.encode(big)
+        xb = vae.decode(zb)
+        assert zb.shape == (1, 8, 12, 16, 16) and xb.shape == (1, 3, 48, 128, 128)
+        assert torch.isfinite(xb).all() and float(xb.min()) >= 0.0 and float(xb.max()) <= 1.0
+        assert torch.equal(vae.encode(big), zb)
+
+
+def test_sample_one_direction_end_to_end_with_encoders(dev, mods):
+    """wav / frames in -> frames / wav out with NO caller-supplied encoder: build_components' own VideoVAE / AudioCodec
+    (CUDA kernels), the fused loop, the decoders (sample_clip.py:220-394)."""
+    from multimodal_diffusion_b200.avdiff.models.infer import sample_clip as sc
+    cfg = json.loads((GOLDEN / "cfg_mvp_v2a.json").read_text())
+    cfg["diffusion"]["audio"]["sampler_steps"] = 4
+    cfg["diffusion"]["video"]["sampler_steps"] = 4
+    torch.manual_seed(9)
+    vae, codec, _, _, _, _, tdim = sc.build_components(cfg, dev)
+    frames = (torch.rand(48, 128, 128, 3) * 255).to(torch.uint8).numpy()
+    out = sc.sample_one_direction(cfg=cfg, vid_vae=vae, aud_codec=codec, adapt_v=mods[0], adapt_a=mods[1], core=mods[2],
+                                  head=mods[3], tstep_dim=tdim, prompt_modality="video", prompt_video=frames,
+                                  prompt_audio=None, device=dev)
+    assert out["audio"].shape == (48000,) and out["sr"] == 16000 and np.isfinite(out["audio"]).all()
+    assert np.abs(out["audio"]).max() <= 1.0
+    wav = np.tanh(np.random.default_rng(3).standard_normal(48000)).astype(np.float32)
+    out = sc.sample_one_direction(cfg=cfg, vid_vae=vae, aud_codec=codec, adapt_v=mods[0], adapt_a=mods[1], core=mods[2],
+                                  head=mods[3], tstep_dim=tdim, prompt_modality="audio", prompt_video=None,
+                                  prompt_audio=wav, device=dev)
+    assert out["video"].shape == (48, 128, 128, 3) and out["video"].dtype == np.uint8 and out["fps"] == 16
