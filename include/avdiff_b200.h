@@ -304,6 +304,12 @@ typedef struct {
   const float* tadd_steps; const float* tadd_zero;
   int profile_skip_kinds;           /* measurement aid, see avd_core_workspace.profile_skip_kinds */
   unsigned int* f16_sat_count;      /* fp16 range check of every operand buffer after each block / the head; NULL = off */
+  /* adapter weights as split-bf16 GEMM operands [nseg][d - tstep_dim][D] (avd_pack_weight, precision adapt_precision =
+   * AVD_PREC_BF16X3 or AVD_PREC_FP32), or NULL.  When given and the TARGET modality's token width allows a GEMM
+   * (D % 64 == 0: the video tubes) the per-step input builder runs the adapter on tcgen05 (tokenise -> GEMM ->
+   * assemble) instead of CUDA-core FMAs (option bx_wide = 0 / 1 keeps the 4- / 32-token FMA kernels). */
+  const void* wv_pack; const void* wa_pack;
+  int adapt_precision;
 } avd_sampler;
 
 int64_t avd_sampler_workspace_bytes(const avd_sampler* s);

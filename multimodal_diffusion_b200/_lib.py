@@ -97,7 +97,8 @@ class SamplerArgs(C.Structure):
                 ("workspace", vp), ("workspace_bytes", C.c_int64),
                 ("eta", C.c_float), ("seed", C.c_uint64), ("clip_index0", C.c_int64),
                 ("add_v", fp), ("add_a", fp), ("tadd_steps", fp), ("tadd_zero", fp),
-                ("profile_skip_kinds", C.c_int), ("f16_sat_count", vp)]
+                ("profile_skip_kinds", C.c_int), ("f16_sat_count", vp),
+                ("wv_pack", vp), ("wa_pack", vp), ("adapt_precision", C.c_int)]
 
 
 AVD_VAE_MAX_BLOCKS = 8

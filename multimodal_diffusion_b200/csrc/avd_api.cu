@@ -217,7 +217,7 @@ struct SamplerLayout {
   int row_off_v, row_off_a;
   int64_t M;
   // offsets in bytes
-  int64_t x_init, xa_init, ssq_init, x, xa, ssq, qkv, att, hmid, h, act_a, act_b, y, eps, total;
+  int64_t x_init, xa_init, ssq_init, x, xa, ssq, qkv, att, hmid, h, act_a, act_b, y, eps, bx_tok, bx_y, total;
 };
 
 static int sampler_layout(const avd_sampler* s, SamplerLayout* L) {
@@ -271,6 +271,9 @@ static int sampler_layout(const avd_sampler* s, SamplerLayout* L) {
   L->act_b = take((int64_t)L->S_head * M * hid * 2);
   L->y = take(M * hid * 4);
   L->eps = take(M * (int64_t)L->Dt * 4);
+  // tensor-core input builder (target rows): token matrix as up to 3 bf16 segments, adapter output fp32
+  L->bx_tok = take((int64_t)3 * s->B * L->Nt * L->Dt * 2);
+  L->bx_y = take((int64_t)s->B * L->Nt * L->d_adapt * 4);
   (void)Mt;
   L->total = off;
   return 0;
@@ -771,10 +774,20 @@ int avd_sample_step(const avd_sampler* s, int step, float* z, float* eps_tap, vo
   // (1) target rows of the joint sequence, identical in the cond and null sequences
   const int tgt_mod = s->target == AVD_TARGET_VIDEO ? 0 : 1;
   BuildXArgs a = make_build_args(s, L, tgt_mod, true, true);
-  AVD_TRY(launch_build_x(a, z, tgt_mod == 0 ? s->wv_t : s->wa_t, tgt_mod == 0 ? s->bv : s->ba,
-                         s->tstep_dim > 0 ? s->temb_steps + (int64_t)step * s->tstep_dim : nullptr, x_init,
-                         ws + L.xa_init, ssq_init, st, tgt_mod == 0 ? s->add_v : s->add_a,
-                         s->tadd_steps != nullptr ? s->tadd_steps + (int64_t)step * L.d_adapt : nullptr));
+  const float* temb_row = s->tstep_dim > 0 ? s->temb_steps + (int64_t)step * s->tstep_dim : nullptr;
+  const float* tadd_row = s->tadd_steps != nullptr ? s->tadd_steps + (int64_t)step * L.d_adapt : nullptr;
+  const void* w_pack = tgt_mod == 0 ? s->wv_pack : s->wa_pack;
+  const int bx_opt = options().bx_wide;
+  const bool bx_tc = w_pack != nullptr && L.Dt % 64 == 0 && L.d_adapt % 32 == 0 &&
+                     (s->adapt_precision == AVD_PREC_BF16X3 || s->adapt_precision == AVD_PREC_FP32) &&
+                     (bx_opt == 2 || bx_opt < 0);   // measured faster at every batch (B = 1: 289 -> 258 us/step)
+  if (bx_tc)
+    AVD_TRY(launch_build_x_tc(a, z, w_pack, s->adapt_precision, tgt_mod == 0 ? s->bv : s->ba, temb_row, x_init,
+                              ws + L.xa_init, ssq_init, ws + L.bx_tok, reinterpret_cast<float*>(ws + L.bx_y), st,
+                              tgt_mod == 0 ? s->add_v : s->add_a, tadd_row));
+  else
+    AVD_TRY(launch_build_x(a, z, tgt_mod == 0 ? s->wv_t : s->wa_t, tgt_mod == 0 ? s->bv : s->ba, temb_row, x_init,
+                           ws + L.xa_init, ssq_init, st, tgt_mod == 0 ? s->add_v : s->add_a, tadd_row));
   // (2) 2B co-batched sequences through the blocks
   avd_core_workspace cw{};                       // key_mask = NULL: the sampler never pads (sample_clip.py:341)
   cw.x = reinterpret_cast<float*>(ws + L.x);

@@ -1185,6 +1185,95 @@ __global__ void __launch_bounds__(BX_THREADS) build_x_wide_kernel(BuildXArgs a, 
   }
 }
 
+// ---- tensor-core route of the input builder (many wide tokens: the A2V video rows at large batch) ----------------------
+// (1) tokenize_split_kernel: gather the latent into the token matrix as bf16 segments (the GEMM's A operand);
+// (2) launch_gemm: Y = tok W^T + b on tcgen05 (split-bf16 passes: the adapter keeps ~fp32 products);
+// (3) assemble_x_kernel: Y (+ additive rows) and the timestep-embedding columns -> x / xa / ssq rows of the cond and null
+//     sequences.  One warp per token.
+__global__ void __launch_bounds__(256) tokenize_split_kernel(BuildXArgs a, const float* __restrict__ z,
+                                                             __nv_bfloat16* __restrict__ tok, int nseg) {
+  pdl_wait();
+  pdl_launch_dependents();
+  const int64_t total = (int64_t)a.B * a.n_tok * a.d_tok;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int k = (int)(i % a.d_tok);
+    const int64_t r = i / a.d_tok;
+    const int n = (int)(r % a.n_tok), b = (int)(r / a.n_tok);
+    int64_t src;
+    if (a.modality == 0) {
+      const int Hh = a.H / a.th, Ww = a.W / a.tw;
+      const int wk = n % Ww, hj = (n / Ww) % Hh, ti = n / (Ww * Hh);
+      const int dw = k % a.tw, dh = (k / a.tw) % a.th, dt = (k / (a.tw * a.th)) % a.tt, c = k / (a.tw * a.th * a.tt);
+      src = ((((int64_t)b * a.C + c) * a.T + (ti * a.tt + dt)) * a.H + (hj * a.th + dh)) * a.W + (wk * a.tw + dw);
+    } else {
+      const int j = k % a.length, c = k / a.length;
+      src = ((int64_t)b * a.C + c) * a.L + (int64_t)n * a.stride + j;
+    }
+    store_split(tok, total, i, nseg, z[src]);
+  }
+}
+
+__global__ void __launch_bounds__(256) assemble_x_kernel(BuildXArgs a, const float* __restrict__ y,
+                                                         const float* __restrict__ temb, float* __restrict__ x,
+                                                         __nv_bfloat16* __restrict__ xa, float* __restrict__ ssq,
+                                                         const float* __restrict__ add_rows, const float* __restrict__ tadd) {
+  pdl_wait();
+  pdl_launch_dependents();
+  const int row = blockIdx.x * (blockDim.x / 32) + (threadIdx.x >> 5);     // token index over the batch
+  const int lane = threadIdx.x & 31;
+  if (row >= a.B * a.n_tok) return;
+  const int n = row % a.n_tok, b = row / a.n_tok;
+  const int64_t seg_stride = a.M * (int64_t)a.d;
+  const int64_t row_c = ((int64_t)b * a.N + a.row_off + n) * a.d;
+  const int64_t row_n = ((int64_t)(a.B + b) * a.N + a.row_off + n) * a.d;
+  float part = 0.0f;
+  for (int c = lane; c < a.d; c += 32) {
+    float v;
+    if (c < a.d_adapt) {
+      v = y[(int64_t)row * a.d_adapt + c];
+      if (add_rows != nullptr) v += __ldg(add_rows + (int64_t)n * a.d_adapt + c);
+      if (tadd != nullptr) v += __ldg(tadd + c);
+    } else {
+      v = __ldg(temb + c - a.d_adapt);
+    }
+    part = fmaf(v, v, part);
+    if (a.write_cond) { x[row_c + c] = v; store_split(xa, seg_stride, row_c + c, a.nseg, v); }
+    if (a.write_null) { x[row_n + c] = v; store_split(xa, seg_stride, row_n + c, a.nseg, v); }
+  }
+  part = warp_sum(part);
+  for (int p = lane; p < a.ssq_parts; p += 32) {
+    const float v = p == 0 ? part : 0.0f;
+    if (a.write_cond) ssq[((int64_t)b * a.N + a.row_off + n) * a.ssq_parts + p] = v;
+    if (a.write_null) ssq[((int64_t)(a.B + b) * a.N + a.row_off + n) * a.ssq_parts + p] = v;
+  }
+}
+
+int launch_build_x_tc(const BuildXArgs& a, const float* z, const void* w_pack, int w_precision, const float* bias,
+                      const float* temb, float* x, void* xa, float* ssq, void* tok_scratch, float* y_scratch,
+                      cudaStream_t s, const float* add_rows, const float* tadd) {
+  AVD_REQUIRE(a.d_tok % 64 == 0 && a.d_adapt % 32 == 0, "tensor-core input builder needs d_tok % 64 == 0 and d_adapt % 32 == 0");
+  AVD_REQUIRE(a.tstep_dim == 0 || temb != nullptr, "missing timestep-embedding row");
+  if (a.B <= 0 || a.n_tok <= 0) return 0;
+  const int M = a.B * a.n_tok;
+  const int nseg = nseg_of(w_precision);
+  AVD_REQUIRE(nseg == 2 || nseg == 3, "adapter operands are split bf16 (bf16x3 or fp32 mode)");
+  if (!kind_skipped(KIND_BUILD_X)) {
+    LaunchScope ls(KIND_BUILD_X, s);
+    const int64_t total = (int64_t)M * a.d_tok;
+    AVD_CUDA(launch_pdl(tokenize_split_kernel, dim3((unsigned)std::min<int64_t>(cdiv(total, 256), 148 * 8)), dim3(256), 0, s, a,
+                        z, static_cast<__nv_bfloat16*>(tok_scratch), nseg));
+  }
+  avd_gemm_args g{};
+  g.M = M; g.N = a.d_adapt; g.K = a.d_tok; g.precision = w_precision;
+  g.A = tok_scratch; g.W = w_pack; g.bias = bias; g.out_f32 = y_scratch;
+  AVD_TRY(launch_gemm(g, s));
+  if (kind_skipped(KIND_BUILD_X)) return 0;
+  LaunchScope ls(KIND_BUILD_X, s);
+  AVD_CUDA(launch_pdl(assemble_x_kernel, dim3(cdiv(M, 8)), dim3(256), 0, s, a, static_cast<const float*>(y_scratch), temb, x,
+                      static_cast<__nv_bfloat16*>(xa), ssq, add_rows, tadd));
+  return 0;
+}
+
 int launch_build_x(const BuildXArgs& a, const float* z, const float* wt, const float* bias, const float* temb,
                    float* x, void* xa, float* ssq, cudaStream_t s, const float* add_rows, const float* tadd) {
   AVD_REQUIRE(a.d_adapt <= BX_THREADS * BX_J, "adapter width too large for build_x");
@@ -1192,10 +1281,10 @@ int launch_build_x(const BuildXArgs& a, const float* z, const float* wt, const f
   AVD_REQUIRE(a.tstep_dim == 0 || temb != nullptr, "missing timestep-embedding row");
   if (a.B <= 0 || a.n_tok <= 0) return 0;
   if (kind_skipped(KIND_BUILD_X)) return 0;
-  // many wide tokens (A2V video rows at batch >= 4): 32 tokens per CTA
+  // many wide tokens (A2V video rows at batch >= 32) when the tensor-core route is not available: 32 tokens per CTA
   const int wide_opt = options().bx_wide;
   const bool wide = a.d_adapt <= BX_THREADS * BXW_JMAX && a.d_tok * BXW_R * 4 <= 96 * 1024 &&
-                    (wide_opt == 1 || (wide_opt != 0 && a.d_tok > 32 && (int64_t)a.B * a.n_tok >= 384));
+                    (wide_opt == 1 || (wide_opt != 0 && a.d_tok > 32 && (int64_t)a.B * a.n_tok >= 3072));   // measured: wins only at B >= 32
   if (wide) {
     const int groups = (a.n_tok + BXW_R - 1) / BXW_R;
     const size_t smem = (size_t)BXW_R * a.d_tok * sizeof(float);

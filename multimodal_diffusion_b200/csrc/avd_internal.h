@@ -116,6 +116,11 @@ struct BuildXArgs {
 int launch_build_x(const BuildXArgs& a, const float* z, const float* wt, const float* bias, const float* temb,
                    float* x, void* xa, float* ssq, cudaStream_t s, const float* add_rows = nullptr,
                    const float* tadd = nullptr);
+// the same through the tcgen05 GEMM (w_pack: adapter weight as split-bf16 segments [nseg][d_adapt][d_tok], avd_pack_weight);
+// tok_scratch: nseg * B*n_tok*d_tok bf16, y_scratch: B*n_tok*d_adapt fp32
+int launch_build_x_tc(const BuildXArgs& a, const float* z, const void* w_pack, int w_precision, const float* bias,
+                      const float* temb, float* x, void* xa, float* ssq, void* tok_scratch, float* y_scratch,
+                      cudaStream_t s, const float* add_rows = nullptr, const float* tadd = nullptr);
 int launch_philox_normal(float* out, uint64_t seed, int64_t clip0, int step, int B, int64_t per_clip, cudaStream_t s);
 int launch_f16_range_scan(const void* buf, int64_t n, unsigned int* counter, cudaStream_t s);
 
@@ -146,7 +151,8 @@ struct Options {
   int attn_poly;       // AVD_ATTN_POLY      polynomial exp2 share of the multi-block attention path
   int attn_one;        // AVD_ATTN_ONE       0 = multi-block attention kernel even for N <= 192
   int chains;          // AVD_CHAINS         independent sequence groups of a sampler step run on forked streams (1 = off)
-  int bx_wide;         // AVD_BX_WIDE        -1 = by size, 0 / 1 = never / always the 16-token build_x kernel
+  int bx_wide;         // AVD_BX_WIDE        -1 = tensor-core adapter when packed weights are given, else by size; 0 / 1 = the
+                       //                    4- / 32-token FMA build_x kernel; 2 = tensor-core route
 };
 Options& options();
 bool pdl_enabled();

@@ -175,13 +175,17 @@ class PackedHead:
 
 
 class PackedAdapter:
-    """LinearAdapter (proj.weight [d_out,d_in], proj.bias) transposed for the fused input builder."""
+    """LinearAdapter (proj.weight [d_out,d_in], proj.bias): transposed fp32 for the FMA input builder, and (when the
+    shape allows a tcgen05 GEMM: d_in % 64 == 0, d_out % 32 == 0) split-bf16 segments for its tensor-core route."""
 
-    def __init__(self, sd: Dict[str, torch.Tensor], device):
+    def __init__(self, sd: Dict[str, torch.Tensor], device, tc_precision=None):
         W = _dev_f32(sd["proj.weight"], device)
         self.wt = transpose_f32(W)            # [d_in, d_out]
         self.bias = _dev_f32(sd["proj.bias"], device)
         self.d_out, self.d_in = int(W.shape[0]), int(W.shape[1])
+        self.pack = None
+        if tc_precision is not None and self.d_in % 64 == 0 and self.d_out % 32 == 0:
+            self.pack = pack_linear_weight(W, _lib.precision_code(tc_precision))
 
 
 # ---------------------------------------------------------------------------------------------------

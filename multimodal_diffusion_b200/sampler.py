@@ -175,8 +175,10 @@ class FusedSampler:
                                            ln_eps=float(hy_head.get("ln_eps", 1e-5)),
                                            in_col_scale=None if self.core.layernorm else sd_core["final_norm.scale"],
                                            activation=activation or "gelu")
-            self.av = packing.PackedAdapter(_state_dict_of(adapt_v), self.device)
-            self.aa = packing.PackedAdapter(_state_dict_of(adapt_a), self.device)
+            # the adapter's tensor-core route keeps ~fp32 products: 6 split-bf16 passes next to an fp32 core, 3 otherwise
+            self.adapt_precision = "fp32" if _lib.precision_code(core_precision) == _lib.AVD_PREC_FP32 else "bf16x3"
+            self.av = packing.PackedAdapter(_state_dict_of(adapt_v), self.device, tc_precision=self.adapt_precision)
+            self.aa = packing.PackedAdapter(_state_dict_of(adapt_a), self.device, tc_precision=self.adapt_precision)
         d_adapt = cfg.d_model - tdim
         if self.av.d_in != cfg.Dv or self.aa.d_in != cfg.Da or self.av.d_out != d_adapt or self.aa.d_out != d_adapt:
             raise ValueError(f"adapter shapes do not match the config (expected {cfg.Dv}/{cfg.Da} -> {d_adapt}; a trainer "
@@ -217,6 +219,8 @@ class FusedSampler:
         s.wv_t, s.bv = self.av.wt.data_ptr(), self.av.bias.data_ptr()
         s.wa_t, s.ba = self.aa.wt.data_ptr(), self.aa.bias.data_ptr()
         s.add_v, s.add_a = _lib.ptr(self.add_v), _lib.ptr(self.add_a)
+        s.wv_pack, s.wa_pack = _lib.ptr(self.av.pack), _lib.ptr(self.aa.pack)
+        s.adapt_precision = _lib.precision_code(self.adapt_precision)
         s.core, s.head = self.core.struct, self.head.struct
         s.eta, s.seed, s.clip_index0 = float(cfg.eta), int(seed) & (2 ** 64 - 1), int(clip_index0)
         s.workspace, s.workspace_bytes = None, 0

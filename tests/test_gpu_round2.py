@@ -516,6 +516,33 @@ def test_build_x_wide_kernel_bit_identical(dev, mods):
     assert torch.equal(outs[0], outs[1])
 
 
+@pytest.mark.parametrize("core_precision", ["fp32", "f16"])
+def test_build_x_tensor_core_route(dev, mods, w_cpu, core_precision):
+    """Option bx_wide = 2: tokenise -> tcgen05 GEMM (split-bf16, ~fp32 products) -> assemble.  Against the FMA kernel on
+    the same inputs (2-step loop) and, in fp32, against the oracle's first step at the fp32 tolerance."""
+    from multimodal_diffusion_b200 import _lib
+    B = 8
+    zp, zi = randn(61, B, 8, 150), randn(62, B, 8, 12, 16, 16)
+    outs = []
+    for opt in (0, 2):
+        with _lib.option("bx_wide", opt):
+            fs = _sampler(mods, "video", B, core_precision, core_precision, steps=2)
+            outs.append(fs.sample_eager(zp.to(dev), zi.to(dev)))
+    err = rel_l2(outs[1], outs[0])
+    print(f"build_x tc vs fma ({core_precision}): {err:.2e}")
+    # a 2-step schedule multiplies eps differences by ~1/sqrt(alpha_bar_999); in f16 the ~1e-7 input difference flips
+    # fp16 roundings downstream, so the f16 case is held to the oracle tolerance instead
+    if core_precision == "fp32":
+        assert err < 2e-6
+    with _lib.option("bx_wide", 2):
+        fs = _sampler(mods, "video", B, core_precision, core_precision)
+        ocfg = orc.HotPathConfig(sampler_steps=50, guidance=3.5)
+        fs.prepare(zp.to(dev))
+        ec, en, ehat, ez = _step_vs_oracle(fs, ocfg, w_cpu, "video", zi, zp, 0, dev)
+    print(f"build_x tc vs oracle ({core_precision}): eps {max(ec, en):.2e} eps_hat {ehat:.2e}")
+    assert max(ec, en) < (TOL_EPS_FP32 if core_precision == "fp32" else TOL_EPS_16)
+
+
 def test_chains_schedule_matches_single_stream(dev, mods, w_cpu):
     """Option chains = 2: the sequence groups run on forked streams (eager and inside a captured graph); same numbers
     as the single-stream schedule up to the tile shapes the narrower GEMMs pick, and within tolerance of the oracle."""
