@@ -7,13 +7,14 @@ The structures below mirror include/avdiff_b200.h field for field.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from pathlib import Path
 from typing import Optional
 
 import torch
 
 PKG = Path(__file__).resolve().parent
-LIB_PATH = PKG / "libavdiff_b200.so"
+LIB_PATH = Path(os.environ.get("AVD_LIB_PATH") or (PKG / "libavdiff_b200.so"))   # AVD_LIB_PATH: an experimental build (tools/exp_build.sh)
 
 AVD_PREC_BF16 = 1
 AVD_PREC_F16 = 2

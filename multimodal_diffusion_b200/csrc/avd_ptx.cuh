@@ -110,7 +110,11 @@ __device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bu
 // wait: blocks until every grid this launch depends on has completed and its memory is visible (no-op when the
 // kernel was launched without the programmatic-serialization attribute).  launch_dependents: lets the next
 // kernel in the stream begin its prologue once every CTA of this grid has issued it (or exited).
+#ifdef AVD_EXP_NOWAIT   // timing experiment only (tools/exp_build.sh): kernels ignore their dependencies, results are garbage
+__device__ __forceinline__ void pdl_wait() {}
+#else
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+#endif
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 // ---------------------------------------------------------------- clusters
