@@ -171,6 +171,7 @@ static const OptionDesc kOptions[] = {
     {"gemm_bn", "AVD_GEMM_BN", &Options::gemm_bn, 0},
     {"gemm_v", "AVD_GEMM_V", &Options::gemm_v, 0},
     {"gemm_generic", "AVD_GEMM_GENERIC", &Options::gemm_generic, 0},
+    {"gemm_dbg", "AVD_GEMM_DBG", &Options::gemm_dbg, 0},
     {"gemm_pair", "AVD_GEMM_PAIR", &Options::gemm_pair, 0},
     {"ps_max_stages", "AVD_PS_MAX_STAGES", &Options::ps_max_stages, 0},
     {"ps_epi_cycles", "AVD_PS_EPI_CYCLES", &Options::ps_epi_cycles, 0},

@@ -220,6 +220,13 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
     // even 32-column chunk and warp w+4 the odd one.
     const int quad = warp & 3;                 // TMEM lane quadrant this warp may access
     const int hf = warp >> 2;
+#ifdef AVD_DEBUG_HOOKS
+    constexpr bool TRACE_CH = true;            // per-chunk phase stamps in every epilogue mode
+    const int dbg = p.dbg;                     // timing experiments: 1 skip tcgen05.ld, 2 skip global stores, 4 skip staging
+#else
+    constexpr bool TRACE_CH = MODE == 0;
+    constexpr int dbg = 0;
+#endif
     const int row = m0 + quad * 32 + lane;
     const bool live = row < p.M;
     const bool two_acc = iters > 1;
@@ -264,7 +271,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
     const int sw = lane & 7;
     const uint32_t t_row = tmem_acc + ((uint32_t)(quad * 32) << 16);
     uint32_t r[32], r1[32];
-    if (hf < BN / 32) {                        // prefetch this warp's first chunk
+    if (hf < BN / 32 && !(dbg & 1)) {          // prefetch this warp's first chunk
       tmem_ld_32x32(t_row + hf * 32, r);
       if (two_acc) tmem_ld_32x32(t_row + BN + hf * 32, r1);
     }
@@ -279,11 +286,11 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
 #pragma unroll
         for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
       }
-      if (ch + 2 < BN / 32) {                  // next chunk's TMEM loads fly while this one is processed
+      if (ch + 2 < BN / 32 && !(dbg & 1)) {    // next chunk's TMEM loads fly while this one is processed
         tmem_ld_32x32(t_row + (ch + 2) * 32, r);
         if (two_acc) tmem_ld_32x32(t_row + BN + (ch + 2) * 32, r1);
       }
-      if (MODE == 0 && threadIdx.x == 128 && ch == hf) trace_mark(trace, 8);
+      if (TRACE_CH && threadIdx.x == 128 && ch == hf) trace_mark(trace, 8);
 #pragma unroll
       for (int j = 0; j < 32; j += 4) {
         const float4 b4 = *reinterpret_cast<const float4*>(bias_s + ch * 32 + j);
@@ -306,7 +313,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
 #pragma unroll
         for (int j = 0; j < 32; ++j) v[j] = gelu_fast(v[j]);
       }
-      if (MODE == 0 && threadIdx.x == 128 && ch == hf) trace_mark(trace, 9);
+      if (TRACE_CH && threadIdx.x == 128 && ch == hf) trace_mark(trace, 9);
       if (has_f32) {
 #pragma unroll
         for (int c = 0; c < 8; ++c) sts128(fbox + ((c ^ sw) << 4), v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
@@ -363,15 +370,15 @@ if (f16_out) {
             sts128u(bbox + (((c0 + c) ^ sw) << 4), w[4 * c], w[4 * c + 1], w[4 * c + 2], w[4 * c + 3]);
         }
       }
-      if (MODE == 0 && threadIdx.x == 128 && ch == hf) trace_mark(trace, 10);
+      if (TRACE_CH && threadIdx.x == 128 && ch == hf) trace_mark(trace, 10);
       const bool paired = (out_nseg > 0 || has_ssq);   // the two warps of a quadrant share 64-column units
       if (paired) named_bar_sync(2 + quad, 64); else __syncwarp();
-      if (MODE == 0 && threadIdx.x == 128 && ch == hf) trace_mark(trace, 11);
+      if (TRACE_CH && threadIdx.x == 128 && ch == hf) trace_mark(trace, 11);
       if (hf == 0 && has_ssq && live)
         ssq_out[(int64_t)row * (p.N / 64) + ((n0 + ch * 32) >> 6)] = ssq_acc + ssq_x[((ch >> 1) & 1) * 128 + quad * 32 + lane];
       // staged boxes -> global, coalesced: 8 lanes cover one 128-byte row, one warp instruction covers 4 rows
       const int rr = lane >> 3, cc = lane & 7;
-      if (has_f32) {
+      if (has_f32 && !(dbg & 2)) {
         const uint8_t* box = f32_stage + (ch * 4 + quad) * GEMM_BOX;
         float* gp = p.out_f32 + (int64_t)(m0 + quad * 32) * p.N + n0 + ch * 32 + cc * 4;
 #pragma unroll
@@ -381,7 +388,7 @@ if (f16_out) {
           if (m0 + quad * 32 + rw < p.M) *reinterpret_cast<float4*>(gp + (int64_t)rw * p.N) = x4;
         }
       }
-      if (out_nseg > 0) {      // the pair's 64-column bf16 box: this warp stores rows [16 hf, 16 hf + 16)
+      if (out_nseg > 0 && !(dbg & 2)) {      // the pair's 64-column bf16 box: this warp stores rows [16 hf, 16 hf + 16)
         for (int sg = 0; sg < out_nseg; ++sg) {
           const uint8_t* box = bf_stage + ((sg * (BN / 64) + (ch >> 1)) * 4 + quad) * GEMM_BOX;
           __nv_bfloat16* gp = p.out_bf16 + (int64_t)sg * p.M * p.N + (int64_t)(m0 + quad * 32) * p.N + n0 + (ch >> 1) * 64 + cc * 8;
@@ -393,7 +400,7 @@ if (f16_out) {
           }
         }
       }
-      if (MODE == 0 && threadIdx.x == 128 && ch == hf) trace_mark(trace, 12);
+      if (TRACE_CH && threadIdx.x == 128 && ch == hf) trace_mark(trace, 12);
     }
     if (threadIdx.x == 128) trace_mark(trace, 6);
   }
@@ -550,7 +557,12 @@ int launch_gemm(const avd_gemm_args& g, cudaStream_t s) {
   if (one16 && g.out_f32 == nullptr && g.resid == nullptr && g.ssq_out == nullptr && g.act == 0) mode = 1;
   else if (one16 && g.out_f32 == nullptr && g.resid == nullptr && g.ssq_out == nullptr && g.act == 2) mode = 2;
   else if (one16 && g.out_f32 != nullptr && g.resid != nullptr && g.ssq_out != nullptr && g.act == 0) mode = 3;
+#ifdef AVD_DEBUG_HOOKS
+  if (bn < 64 || options().gemm_generic) mode = 0;
+  p.dbg = options().gemm_dbg;
+#else
   if (p.trace != nullptr || bn < 64 || options().gemm_generic) mode = 0;
+#endif
   // CTA pairs (cta_group::2): each SM stages half of the weight tile.  Needs both pipelines busy in the leader, a
   // specialised epilogue, and the padded grid (an even number of row tiles) still within one wave.
   const int pair_on = options().gemm_pair;

@@ -33,6 +33,7 @@ struct GemmParams {
   float a_scale;             // multiplies the accumulator (folded into the row scale)
   float out_scale;           // multiplies the 16-bit output only
   unsigned long long* trace; // debug: per-CTA phase timestamps (avd_debug_trace), nullptr in production
+  int dbg;                   // debug-hooks builds only: epilogue timing experiments (option gemm_dbg)
 };
 
 __device__ __forceinline__ void trace_mark(unsigned long long* trace, int slot) {

@@ -144,6 +144,7 @@ struct Options {
   int gemm_bn;         // AVD_GEMM_BN        force a tile width (0 = model)
   int gemm_v;          // AVD_GEMM_V         3 = one-tile kernel, 4 = persistent kernel, 0 = by wave count
   int gemm_generic;    // AVD_GEMM_GENERIC   1 = generic epilogue instead of the specialised ones
+  int gemm_dbg;        // AVD_GEMM_DBG       debug-hooks builds: epilogue timing experiments (bit 0 no tcgen05.ld, bit 1 no global stores)
   int gemm_pair;       // AVD_GEMM_PAIR      cta_group::2 variant of the one-tile kernel (0 off, 1 specialised, 2 all)
   int ps_max_stages;   // AVD_PS_MAX_STAGES  ring depth cap of the persistent kernel (0 = its maximum)
   int ps_epi_cycles;   // AVD_PS_EPI_CYCLES  epilogue constant of the tile-width model (0 = built in)
