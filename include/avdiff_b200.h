@@ -233,6 +233,8 @@ typedef struct {
   const float* final_ln_b;
 } avd_core_weights;
 
+#define AVD_CHAIN_FLAG_BYTES 2560   /* 4 phases x 160 row groups x u32, see avd_core_workspace.chain_flags */
+
 /* Caller-allocated work buffers for M = n_seq*N rows (S = avd_nseg(precision)):
  *   x fp32 [M,d]; xa bf16 [S][M,d]; ssq fp32 [M, d/64]; qkv bf16 [M,3d] (fp32 in AVD_PREC_FP32 mode);
  *   att bf16 [S][M,d]; hmid bf16 [S][M,d_mlp]. */
@@ -244,6 +246,11 @@ typedef struct {
   /* fp16 mode range check: when not NULL, every 16-bit operand buffer is scanned after each block (avd_f16_range_scan)
    * and saturated / non-finite values are counted here.  NULL (the timed configuration) = no scan kernels. */
   unsigned int* f16_sat_count;
+  /* AVD_CHAIN_FLAG_BYTES of ZERO-INITIALISED device memory, or NULL.  When given (and every GEMM of a block is one wave
+   * of 128-row tiles) out-proj -> fc1 -> fc2 -> the next block's QKV run as ONE persistent launch whose tiles hand their
+   * 128-row groups to the next GEMM through these counters; the launch leaves them zero again.  Zero them once (and
+   * again after a failed launch); never share them between two avd_mmdt_blocks / sampler calls running concurrently. */
+  unsigned int* chain_flags;
   /* measurement aid for THIS call only: bit k set = kernels of profiler kind k are not launched (results meaningless) */
   int profile_skip_kinds;
 } avd_core_workspace;

@@ -25,6 +25,7 @@ AVD_TARGET_VIDEO = 0
 AVD_TARGET_AUDIO = 1
 AVD_MAX_LAYERS = 64
 AVD_MAX_SHARED = 8
+AVD_CHAIN_FLAG_BYTES = 2560
 
 PRECISIONS = {"bf16": AVD_PREC_BF16, "f16": AVD_PREC_F16, "bf16x3": AVD_PREC_BF16X3, "fp32": AVD_PREC_FP32}
 
@@ -74,7 +75,7 @@ class CoreWeights(C.Structure):
 
 class CoreWorkspace(C.Structure):
     _fields_ = [("x", fp), ("xa", vp), ("ssq", fp), ("qkv", vp), ("att", vp), ("hmid", vp), ("key_mask", vp),
-                ("f16_sat_count", vp), ("profile_skip_kinds", C.c_int)]
+                ("f16_sat_count", vp), ("chain_flags", vp), ("profile_skip_kinds", C.c_int)]
 
 
 class HeadWeights(C.Structure):

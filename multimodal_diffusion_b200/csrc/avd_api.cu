@@ -173,6 +173,7 @@ static const OptionDesc kOptions[] = {
     {"gemm_generic", "AVD_GEMM_GENERIC", &Options::gemm_generic, 0},
     {"gemm_dbg", "AVD_GEMM_DBG", &Options::gemm_dbg, 0},
     {"gemm_pair", "AVD_GEMM_PAIR", &Options::gemm_pair, 0},
+    {"gemm_chain", "AVD_GEMM_CHAIN", &Options::gemm_chain, 0},
     {"ps_max_stages", "AVD_PS_MAX_STAGES", &Options::ps_max_stages, 0},
     {"ps_epi_cycles", "AVD_PS_EPI_CYCLES", &Options::ps_epi_cycles, 0},
     {"ps_no256", "AVD_PS_NO256", &Options::ps_no256, 0},
@@ -218,7 +219,7 @@ struct SamplerLayout {
   int row_off_v, row_off_a;
   int64_t M;
   // offsets in bytes
-  int64_t x_init, xa_init, ssq_init, x, xa, ssq, qkv, att, hmid, h, act_a, act_b, y, eps, bx_tok, bx_y, total;
+  int64_t x_init, xa_init, ssq_init, x, xa, ssq, qkv, att, hmid, h, act_a, act_b, y, eps, bx_tok, bx_y, chain_flags, total;
 };
 
 static int sampler_layout(const avd_sampler* s, SamplerLayout* L) {
@@ -275,6 +276,7 @@ static int sampler_layout(const avd_sampler* s, SamplerLayout* L) {
   // tensor-core input builder (target rows): token matrix as up to 3 bf16 segments, adapter output fp32
   L->bx_tok = take((int64_t)3 * s->B * L->Nt * L->Dt * 2);
   L->bx_y = take((int64_t)s->B * L->Nt * L->d_adapt * 4);
+  L->chain_flags = take(GEMM_CHAIN_FLAG_BYTES);   // row-group counters of the chained GEMM launches (zero between launches)
   (void)Mt;
   L->total = off;
   return 0;
@@ -319,67 +321,89 @@ static int core_blocks_rows(const avd_core_weights* w, const float* x_in, const 
   // is its own pass over the fp32 residual stream (layernorm_act_kernel) writing the operand of the QKV / fc1 GEMM
   const bool ln = w->norm_kind == 1;
   const float x_unscale = (f16 && !ln) ? 1.0f / AVD_F16_XSCALE : 0.0f, x_scale = f16 ? AVD_F16_XSCALE : 0.0f;
-  for (int l = 0; l < w->n_layers; ++l) {
+  // the four GEMMs of block l as argument blocks (mmdt.py:96-99); qkv(l) reads the residual stream block l-1 left
+  auto qkv_args = [&](int l) {
     const avd_block_weights& b = w->blocks[l];
-    const void* a_in = (l == 0) ? xa_in : ws->xa;
-    const float* s_in = (l == 0) ? ssq_in : ws->ssq;
-    const float* r_in = (l == 0) ? x_in : ws->x;
-    if (ln) {
-      AVD_REQUIRE(b.ln1_w != nullptr && b.ln1_b != nullptr && b.ln2_w != nullptr && b.ln2_b != nullptr, "missing LayerNorm weights");
-      AVD_TRY(launch_layernorm_act(r_in, b.ln1_w, b.ln1_b, M, d, w->ln_eps, 0, nullptr, ws->xa,
-                                   nseg_arg(w->precision, false), st));
-      a_in = ws->xa;
-      s_in = nullptr;
-    }
-    // qkv = RMS1(x) W_in^T + b_in        (mmdt.py:97 -> :60)
-    avd_gemm_args g{};
+    avd_gemm_args g{};   // qkv = RMS1(x) W_in^T + b_in        (mmdt.py:97 -> :60)
     g.M = M; g.N = 3 * d; g.K = d; g.precision = w->precision;
-    g.A = a_in; g.W = b.w_qkv; g.bias = b.b_qkv;
-    g.ssq_in = s_in; g.ssq_parts = parts; g.rms_dim = d; g.rms_eps = w->rms_eps;
+    g.A = (l == 0 || ln) ? (ln ? ws->xa : xa_in) : ws->xa; g.W = b.w_qkv; g.bias = b.b_qkv;
+    g.ssq_in = ln ? nullptr : ((l == 0) ? ssq_in : ws->ssq); g.ssq_parts = parts; g.rms_dim = d; g.rms_eps = w->rms_eps;
     g.a_scale = x_unscale;
     if (tc_attn) { g.out_bf16 = ws->qkv; g.out_precision = f16 ? AVD_PREC_F16 : AVD_PREC_BF16; }
     else g.out_f32 = static_cast<float*>(ws->qkv);
-    AVD_TRY(launch_gemm(g, st));
-    // a = softmax(q k^T / sqrt(hd)) v
-    if (tc_attn) AVD_TRY(launch_attention_tc(ws->qkv, ws->att, S, n_seq, N, w->n_heads, hd, st, f16, ws->key_mask));
-    else AVD_TRY(launch_attention_f32(static_cast<const float*>(ws->qkv), ws->att, S, n_seq, N, w->n_heads, hd, st,
-                                      ws->key_mask));
-    // x = x + a W_o^T + b_o               (mmdt.py:97)
-    g = avd_gemm_args{};
+    return g;
+  };
+  auto oproj_args = [&](int l) {
+    const avd_block_weights& b = w->blocks[l];
+    avd_gemm_args g{};   // x = x + a W_o^T + b_o               (mmdt.py:97)
     g.M = M; g.N = d; g.K = d; g.precision = w->precision;
-    g.A = ws->att; g.W = b.w_o; g.bias = b.b_o; g.resid = r_in;
+    g.A = ws->att; g.W = b.w_o; g.bias = b.b_o; g.resid = (l == 0) ? x_in : ws->x;
     g.out_f32 = ws->x; g.out_bf16 = ws->xa; g.out_precision = w->precision; g.ssq_out = ws->ssq;
     g.out_scale = x_scale;
-    AVD_TRY(launch_gemm(g, st));
-    // u = gelu(RMS2(x) W_1^T + b_1)       (mmdt.py:98 -> :78-79)
-    g = avd_gemm_args{};
+    return g;
+  };
+  auto fc1_args = [&](int l) {
+    const avd_block_weights& b = w->blocks[l];
+    avd_gemm_args g{};   // u = gelu(RMS2(x) W_1^T + b_1)       (mmdt.py:98 -> :78-79)
     g.M = M; g.N = w->d_mlp; g.K = d; g.precision = w->precision;
-    if (ln) AVD_TRY(launch_layernorm_act(ws->x, b.ln2_w, b.ln2_b, M, d, w->ln_eps, 0, nullptr, ws->xa,
-                                         nseg_arg(w->precision, false), st));
     g.A = ws->xa; g.W = b.w_fc1; g.bias = b.b_fc1;
     g.ssq_in = ln ? nullptr : ws->ssq; g.ssq_parts = parts; g.rms_dim = d; g.rms_eps = w->rms_eps;
     g.a_scale = x_unscale;
     g.act = tc_attn ? 2 : 1;   // bf16 mode: fast erf (|err| < 2e-7, far below the bf16 rounding of the result)
     g.out_bf16 = ws->hmid; g.out_precision = w->precision;
-    AVD_TRY(launch_gemm(g, st));
-    // x = x + u W_2^T + b_2               (mmdt.py:98 -> :81)
-    g = avd_gemm_args{};
+    return g;
+  };
+  auto fc2_args = [&](int l) {
+    const avd_block_weights& b = w->blocks[l];
+    avd_gemm_args g{};   // x = x + u W_2^T + b_2               (mmdt.py:98 -> :81)
     g.M = M; g.N = d; g.K = w->d_mlp; g.precision = w->precision;
     g.A = ws->hmid; g.W = b.w_fc2; g.bias = b.b_fc2; g.resid = ws->x;
     g.out_f32 = ws->x; g.out_bf16 = ws->xa; g.out_precision = w->precision; g.ssq_out = ws->ssq;
     g.out_scale = x_scale;
-    void* xa_out = ws->xa;
     if (l == w->n_layers - 1 && last_out != nullptr) {   // the head's operand: pre-scaled too when the head runs in fp16
       g.out_bf16 = last_out; g.out_precision = last_prec; g.out_scale = is_f16(last_prec) ? AVD_F16_XSCALE : 0.0f;
-      xa_out = last_out;
     }
-    AVD_TRY(launch_gemm(g, st));
+    return g;
+  };
+  // Chained launch (avd_gemm_chain.cu): out-proj -> fc1 -> fc2 -> next block's QKV in ONE persistent kernel with
+  // row-group flags instead of three kernel boundaries, when every one of them is a single wave of tiles.
+  const bool may_chain = options().gemm_chain != 0 && ws->chain_flags != nullptr && !ln && tc_attn &&
+                         ws->f16_sat_count == nullptr;
+  bool qkv_launched = false;                      // block l's QKV already ran as the tail of block l-1's chain
+  for (int l = 0; l < w->n_layers; ++l) {
+    const avd_block_weights& b = w->blocks[l];
+    const float* r_in = (l == 0) ? x_in : ws->x;
+    if (ln) {
+      AVD_REQUIRE(b.ln1_w != nullptr && b.ln1_b != nullptr && b.ln2_w != nullptr && b.ln2_b != nullptr, "missing LayerNorm weights");
+      AVD_TRY(launch_layernorm_act(r_in, b.ln1_w, b.ln1_b, M, d, w->ln_eps, 0, nullptr, ws->xa,
+                                   nseg_arg(w->precision, false), st));
+    }
+    if (!qkv_launched) AVD_TRY(launch_gemm(qkv_args(l), st));
+    qkv_launched = false;
+    // a = softmax(q k^T / sqrt(hd)) v
+    if (tc_attn) AVD_TRY(launch_attention_tc(ws->qkv, ws->att, S, n_seq, N, w->n_heads, hd, st, f16, ws->key_mask));
+    else AVD_TRY(launch_attention_f32(static_cast<const float*>(ws->qkv), ws->att, S, n_seq, N, w->n_heads, hd, st,
+                                      ws->key_mask));
+    if (may_chain) {
+      avd_gemm_args gs[4] = {oproj_args(l), fc1_args(l), fc2_args(l), avd_gemm_args{}};
+      int n = 3;
+      if (l + 1 < w->n_layers) gs[n++] = qkv_args(l + 1);
+      const int rc = launch_gemm_chain(gs, n, ws->chain_flags, GEMM_CHAIN_ROW_TILES, st);
+      if (rc < 0) return rc;
+      if (rc == 1) { qkv_launched = n == 4; continue; }
+    }
+    AVD_TRY(launch_gemm(oproj_args(l), st));
+    if (ln) AVD_TRY(launch_layernorm_act(ws->x, b.ln2_w, b.ln2_b, M, d, w->ln_eps, 0, nullptr, ws->xa,
+                                         nseg_arg(w->precision, false), st));
+    AVD_TRY(launch_gemm(fc1_args(l), st));
+    const avd_gemm_args g2 = fc2_args(l);
+    AVD_TRY(launch_gemm(g2, st));
     if (f16 && ws->f16_sat_count != nullptr) {           // range check of this block's 16-bit operands (not in the timed path)
       AVD_TRY(launch_f16_range_scan(ws->qkv, (int64_t)M * 3 * d, ws->f16_sat_count, st));
       AVD_TRY(launch_f16_range_scan(ws->att, (int64_t)M * d, ws->f16_sat_count, st));
       AVD_TRY(launch_f16_range_scan(ws->hmid, (int64_t)M * w->d_mlp, ws->f16_sat_count, st));
-      if (xa_out != last_out || is_f16(last_prec))
-        AVD_TRY(launch_f16_range_scan(xa_out, (int64_t)M * d, ws->f16_sat_count, st));
+      if (g2.out_bf16 != last_out || is_f16(last_prec))
+        AVD_TRY(launch_f16_range_scan(g2.out_bf16, (int64_t)M * d, ws->f16_sat_count, st));
     }
   }
   return 0;
@@ -418,6 +442,7 @@ static int core_blocks(const avd_core_weights* w, const float* x_in, const void*
     wc.qkv = static_cast<uint8_t*>(ws->qkv) + r0 * 3 * d * 2;
     wc.att = static_cast<uint8_t*>(ws->att) + r0 * d * 2;
     wc.hmid = static_cast<uint8_t*>(ws->hmid) + r0 * w->d_mlp * 2;
+    wc.chain_flags = nullptr;                  // one flag block cannot serve concurrent groups
     void* lo = last_out != nullptr ? static_cast<uint8_t*>(last_out) + r0 * d * 2 : nullptr;
     AVD_TRY(core_blocks_rows(w, x_in + r0 * d, static_cast<const uint8_t*>(xa_in) + r0 * d * 2, ssq_in + r0 * parts, &wc,
                              seq_c, N, lo, last_prec, sc));
@@ -751,6 +776,7 @@ int avd_sample_prepare(const avd_sampler* s, const float* z_prompt, void* stream
   AVD_CUDA(cudaMemsetAsync(ws + L.x_init, 0, (size_t)(L.xa_init - L.x_init), st));
   AVD_CUDA(cudaMemsetAsync(ws + L.xa_init, 0, (size_t)(L.ssq_init - L.xa_init), st));
   AVD_CUDA(cudaMemsetAsync(ws + L.ssq_init, 0, (size_t)(L.x - L.ssq_init), st));
+  AVD_CUDA(cudaMemsetAsync(ws + L.chain_flags, 0, GEMM_CHAIN_FLAG_BYTES, st));   // (also clears what a failed launch left)
   const int prompt_mod = s->target == AVD_TARGET_VIDEO ? 1 : 0;   // A2V: audio prompt; V2A: video prompt
   BuildXArgs a = make_build_args(s, L, prompt_mod, /*cond=*/true, /*null=*/false);
   const float* wt = prompt_mod == 0 ? s->wv_t : s->wa_t;
@@ -798,6 +824,7 @@ int avd_sample_step(const avd_sampler* s, int step, float* z, float* eps_tap, vo
   cw.att = ws + L.att;
   cw.hmid = ws + L.hmid;
   cw.f16_sat_count = s->f16_sat_count;
+  cw.chain_flags = reinterpret_cast<unsigned int*>(ws + L.chain_flags);
   float* eps = reinterpret_cast<float*>(ws + L.eps);
   if (!ln) {
     AVD_TRY(core_blocks(&s->core, x_init, ws + L.xa_init, ssq_init, &cw, L.n_seq, L.N, ws + L.h, s->head.precision, st));

@@ -464,7 +464,8 @@ static int pipe_bytes_of(int bn) {
   }
 }
 
-int launch_gemm(const avd_gemm_args& g, cudaStream_t s) {
+// Validation, kernel parameters, tile width and epilogue mode of one GEMM (shared by launch_gemm and the chained launch).
+int plan_gemm(const avd_gemm_args& g, GemmPlan* plan) {
   const int nseg = nseg_of(g.precision);
   AVD_REQUIRE(nseg > 0, "precision must be 1 (bf16), 2 (f16), 3 or 6");
   AVD_REQUIRE(g.M > 0 && g.N > 0 && g.K > 0, "empty GEMM");
@@ -531,13 +532,34 @@ int launch_gemm(const avd_gemm_args& g, cudaStream_t s) {
   // tiles, every warp on the epilogue); beyond one wave the persistent kernel (avd_gemm_ps.cu) hides the epilogue under
   // the next tile's mainloop (+45 % at M = 32768, tools/kbench.py --M).  AVD_GEMM_V = 3 / 4 forces one of them.
   const int gemm_v = options().gemm_v;
+  plan->p = p;
+  plan->nseg = nseg;
+  plan->force_bn = force_bn;
+  plan->bn = bn;
+  plan->mode = 0;
   {
     int dev = 0, sms = 148;
     if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    const bool persistent = gemm_v == 4 || (gemm_v != 3 && (bn == 0 || (int64_t)mt * (g.N / bn) > sms));
-    if (persistent) return launch_gemm_ps(g, p, nseg, force_bn, s);
+    plan->persistent = gemm_v == 4 || (gemm_v != 3 && (bn == 0 || (int64_t)mt * (g.N / bn) > sms));
+    if (plan->persistent) return 0;
   }
   AVD_REQUIRE(bn > 0, "no tile shape fits this combination of outputs: use fewer outputs per GEMM");
+  // epilogue specialisation (see the kernel's MODE); every other combination uses the generic one
+  const bool one16 = g.out_bf16 != nullptr && out_nseg == 1;
+  if (one16 && g.out_f32 == nullptr && g.resid == nullptr && g.ssq_out == nullptr && g.act == 0) plan->mode = 1;
+  else if (one16 && g.out_f32 == nullptr && g.resid == nullptr && g.ssq_out == nullptr && g.act == 2) plan->mode = 2;
+  else if (one16 && g.out_f32 != nullptr && g.resid != nullptr && g.ssq_out != nullptr && g.act == 0) plan->mode = 3;
+  if (bn < 64 || options().gemm_generic) plan->mode = 0;
+  return 0;
+}
+
+int launch_gemm(const avd_gemm_args& g, cudaStream_t s) {
+  GemmPlan plan;
+  AVD_TRY(plan_gemm(g, &plan));
+  GemmParams p = plan.p;
+  const int nseg = plan.nseg, bn = plan.bn;
+  const int mt = (g.M + GEMM_BM - 1) / GEMM_BM;
+  if (plan.persistent) return launch_gemm_ps(g, p, nseg, plan.force_bn, s);
 
   const int64_t n_ctas = (int64_t)(g.N / bn) * mt;
   p.trace = (g_dbg_trace != nullptr && n_ctas * 32 <= g_dbg_trace_slots) ? g_dbg_trace : nullptr;
@@ -551,17 +573,12 @@ int launch_gemm(const avd_gemm_args& g, cudaStream_t s) {
   tmR = tmA;   // placeholder when unused (never dereferenced)
   if (g.resid != nullptr)
     AVD_TRY(get_tensor_map_3d(g.resid, 4, g.N, g.M, 1, (uint64_t)g.N * 4, (uint64_t)g.M * g.N * 4, 32, 32, &tmR));
-  // epilogue specialisation (see the kernel's MODE); the phase trace and every other combination use the generic one
-  int mode = 0;
-  const bool one16 = g.out_bf16 != nullptr && out_nseg == 1;
-  if (one16 && g.out_f32 == nullptr && g.resid == nullptr && g.ssq_out == nullptr && g.act == 0) mode = 1;
-  else if (one16 && g.out_f32 == nullptr && g.resid == nullptr && g.ssq_out == nullptr && g.act == 2) mode = 2;
-  else if (one16 && g.out_f32 != nullptr && g.resid != nullptr && g.ssq_out != nullptr && g.act == 0) mode = 3;
+  // the phase trace uses the generic epilogue (except in debug-hooks builds, which stamp every mode)
+  int mode = plan.mode;
 #ifdef AVD_DEBUG_HOOKS
-  if (bn < 64 || options().gemm_generic) mode = 0;
   p.dbg = options().gemm_dbg;
 #else
-  if (p.trace != nullptr || bn < 64 || options().gemm_generic) mode = 0;
+  if (p.trace != nullptr) mode = 0;
 #endif
   // CTA pairs (cta_group::2): each SM stages half of the weight tile.  Needs both pipelines busy in the leader, a
   // specialised epilogue, and the padded grid (an even number of row tiles) still within one wave.

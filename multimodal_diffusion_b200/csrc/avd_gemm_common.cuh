@@ -124,6 +124,16 @@ __device__ __forceinline__ uint32_t gelu_pair16(bool f16, float a, float b) {
   return f16 ? gelu_pair_f16x2(a, b) : gelu_pair_bf16x2(a, b);
 }
 
+// what launch_gemm decides before it launches (avd_gemm.cu: plan_gemm); persistent: more than one wave of tiles, the
+// persistent kernel picks its own tile width
+struct GemmPlan {
+  GemmParams p;
+  int nseg, bn, mode, force_bn;
+  bool persistent;
+};
+int plan_gemm(const avd_gemm_args& g, GemmPlan* plan);
+unsigned int* ps_debug_device_ptr();         // host-visible barrier-timeout record shared by the persistent kernels
+
 // persistent kernel (avd_gemm_ps.cu); bn = 0 lets it choose the tile width
 int launch_gemm_ps(const avd_gemm_args& g, GemmParams p, int nseg, int force_bn, cudaStream_t s);
 int ps_debug_read(unsigned int* out8);

@@ -477,6 +477,15 @@ int ps_debug_read(unsigned int* out8) {       // host copy of the timeout record
   return 0;
 }
 
+unsigned int* ps_debug_device_ptr() {
+  if (g_ps_dbg_host == nullptr) {
+    if (cudaHostAlloc(reinterpret_cast<void**>(&g_ps_dbg_host), 1024, cudaHostAllocMapped) != cudaSuccess) return nullptr;
+    for (int i = 0; i < 256; ++i) g_ps_dbg_host[i] = 0u;
+    if (cudaHostGetDevicePointer(reinterpret_cast<void**>(&g_ps_dbg_dev), g_ps_dbg_host, 0) != cudaSuccess) return nullptr;
+  }
+  return g_ps_dbg_dev;
+}
+
 static int ps_num_sms() {
   static int n = 0;
   if (n == 0) {
@@ -524,9 +533,13 @@ static bool ps_plan(const avd_gemm_args& g, int out_nseg, int bn, PsPlan* plan, 
   if (stages > PS_MAX_STAGES) stages = PS_MAX_STAGES;
   const int cap = options().ps_max_stages;
   if (cap > 0 && stages > cap) stages = cap;
-  stages &= ~1;   // even: global iteration `it` then always lands in a ring slot of its own parity, so every slot (and
-                  // its two barriers) has ONE producer and ONE issuer, who see its uses in order (parity waits are
-                  // only sound when the waiter is never two phases away from the barrier)
+  // even: global iteration `it` then always lands in a ring slot of its own parity, so every slot (and its two barriers)
+  // has ONE producer and ONE issuer, who see its uses in order.  The 256-wide column-split tiles do not need that: both
+  // issuers consume every slot in order, and a producer's refill of pass n waits for the consumption of pass n - 1, which
+  // cannot complete before the OTHER producer's fill of pass n - 1 -- no waiter is ever two phases away from its
+  // barrier.  An odd ring is what lets the residual GEMMs (fp32 staging boxes: room for three 48 KB stages, not four)
+  // take the 256-wide tiles: smem port 768 cycles per k-block against 512 of MMA instead of 512 against 256.
+  if (bn != 256) stages &= ~1;
   if (stages < 2) return false;
   plan->stages = stages;
   plan->f32_off = stages * stage;
@@ -585,12 +598,8 @@ int launch_gemm_ps(const avd_gemm_args& g, GemmParams p, int nseg, int force_bn,
   PsPlan plan{};
   int smem_bytes = 0;
   ps_plan(g, out_nseg, bn, &plan, &smem_bytes);
-  if (g_ps_dbg_host == nullptr) {
-    AVD_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&g_ps_dbg_host), 1024, cudaHostAllocMapped));
-    for (int i = 0; i < 256; ++i) g_ps_dbg_host[i] = 0u;
-    AVD_CUDA(cudaHostGetDevicePointer(reinterpret_cast<void**>(&g_ps_dbg_dev), g_ps_dbg_host, 0));
-  }
-  plan.dbg = g_ps_dbg_dev;
+  plan.dbg = ps_debug_device_ptr();
+  AVD_REQUIRE(plan.dbg != nullptr, "cannot allocate the barrier-timeout record");
   plan.tiles_n = g.N / bn;
   plan.tiles_total = mt * plan.tiles_n;
   const int grid = plan.tiles_total < sms ? plan.tiles_total : sms;

@@ -126,6 +126,13 @@ int launch_f16_range_scan(const void* buf, int64_t n, unsigned int* counter, cud
 
 // tcgen05 GEMM (avd_gemm.cu)
 int launch_gemm(const avd_gemm_args& g, cudaStream_t s);
+// chained launch of dependent one-wave GEMMs (avd_gemm_chain.cu): 1 launched, 0 not chainable (launch them one by one),
+// < 0 error.  flags: GEMM_CHAIN_MAX x flags_row_tiles zero-initialised counters (avd_core_workspace.chain_flags).
+int launch_gemm_chain(const avd_gemm_args* gs, int n, unsigned int* flags, int flags_row_tiles, cudaStream_t s);
+constexpr int GEMM_CHAIN_MAX = 4;            // phases per chained launch
+constexpr int GEMM_CHAIN_ROW_TILES = 160;    // row tiles a flag block provides for (>= SM count: one wave)
+constexpr int GEMM_CHAIN_FLAG_BYTES = GEMM_CHAIN_MAX * GEMM_CHAIN_ROW_TILES * 4;
+static_assert(GEMM_CHAIN_FLAG_BYTES == AVD_CHAIN_FLAG_BYTES, "include/avdiff_b200.h states the size of the flag block");
 
 // Measurement aid scoped to ONE avd_sample_* call (avd_sampler.profile_skip_kinds): bit k set -> launches of Kind k are
 // skipped while that call runs on this thread.  There is no process-wide switch.
@@ -145,6 +152,8 @@ struct Options {
   int gemm_v;          // AVD_GEMM_V         3 = one-tile kernel, 4 = persistent kernel, 0 = by wave count
   int gemm_generic;    // AVD_GEMM_GENERIC   1 = generic epilogue instead of the specialised ones
   int gemm_dbg;        // AVD_GEMM_DBG       debug-hooks builds: epilogue timing experiments (bit 0 no tcgen05.ld, bit 1 no global stores)
+  int gemm_chain;      // AVD_GEMM_CHAIN     1 = out-proj -> fc1 -> fc2 -> next QKV as one chained persistent launch (experimental,
+                       //                    measured slower than four PDL-linked launches: DESIGN.md section 5)
   int gemm_pair;       // AVD_GEMM_PAIR      cta_group::2 variant of the one-tile kernel (0 off, 1 specialised, 2 all)
   int ps_max_stages;   // AVD_PS_MAX_STAGES  ring depth cap of the persistent kernel (0 = its maximum)
   int ps_epi_cycles;   // AVD_PS_EPI_CYCLES  epilogue constant of the tile-width model (0 = built in)

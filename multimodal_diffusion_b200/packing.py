@@ -234,6 +234,8 @@ def core_workspace(M: int, d: int, d_mlp: int, precision: int, device):
                            else torch.float32),   # 16-bit storage (bf16 or fp16 bits, per the precision mode)
         "att": torch.empty(S, M, d, device=device, dtype=torch.bfloat16),
         "hmid": torch.empty(S, M, d_mlp, device=device, dtype=torch.bfloat16),
+        # row-group counters of the chained out-proj -> fc1 -> fc2 -> QKV launch (zero between launches)
+        "chain_flags": torch.zeros(_lib.AVD_CHAIN_FLAG_BYTES // 4, device=device, dtype=torch.int32),
     }
     ws = _lib.CoreWorkspace()
     for k, t in bufs.items():

@@ -676,3 +676,32 @@ def test_sample_one_direction_end_to_end_with_encoders(dev, mods):
                                   head=mods[3], tstep_dim=tdim, prompt_modality="audio", prompt_video=None,
                                   prompt_audio=wav, device=dev)
     assert out["video"].shape == (48, 128, 128, 3) and out["video"].dtype == np.uint8 and out["fps"] == 16
+
+
+# ------------------------------------------------------------------------------------------ chained GEMM launch
+def test_chained_block_launch_matches_unchained(dev, lib):
+    """avd_gemm_chain.cu (option gemm_chain, off by default): out-proj -> fc1 -> fc2 -> next QKV of every block as ONE
+    persistent launch with row-group flags.  Same tiles and the same per-tile arithmetic as the four separate launches
+    except fc1's accumulation order (one accumulator in k order instead of two alternating ones), so the results agree to
+    fp16 rounding flips; it is deterministic, graph replay equals eager, and it leaves its flag block zero."""
+    from multimodal_diffusion_b200 import _lib
+    from multimodal_diffusion_b200.sampler import FusedSampler, HotPathConfig
+    mods = seeded_modules()
+    B = 8
+    outs, launches = {}, {}
+    for chain in (0, 1, 1):
+        with _lib.option("gemm_chain", chain):
+            fs = FusedSampler(HotPathConfig(sampler_steps=4, guidance=3.5), mods[0], mods[1], mods[2], mods[3], "audio", B,
+                              device=dev)
+            zp, z0 = randn(1, *fs.prompt_shape).to(dev), randn(2, *fs.latent_shape).to(dev)
+            n0 = lib.avd_launch_count()
+            ze = fs.sample_eager(zp, z0)
+            launches[chain] = lib.avd_launch_count() - n0
+            zg = fs.sample(zp, z0)
+            torch.cuda.synchronize()
+            fs.check_errors()
+            assert torch.equal(ze, zg)
+            outs.setdefault(chain, []).append(ze.clone())
+    assert launches[1] == launches[0] - 4 * 8 * 3            # three launches fewer per block and step
+    assert torch.equal(outs[1][0], outs[1][1])
+    assert rel_l2(outs[1][0].cpu(), outs[0][0].cpu()) < 5e-3
