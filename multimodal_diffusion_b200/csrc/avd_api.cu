@@ -176,6 +176,7 @@ static const OptionDesc kOptions[] = {
     {"gemm_chain", "AVD_GEMM_CHAIN", &Options::gemm_chain, 0},
     {"ps_max_stages", "AVD_PS_MAX_STAGES", &Options::ps_max_stages, 0},
     {"ps_epi_cycles", "AVD_PS_EPI_CYCLES", &Options::ps_epi_cycles, 0},
+    {"ps_pair", "AVD_PS_PAIR", &Options::ps_pair, 1},
     {"ps_no256", "AVD_PS_NO256", &Options::ps_no256, 0},
     {"attn_poly", "AVD_ATTN_POLY", &Options::attn_poly, 0},
     {"attn_one", "AVD_ATTN_ONE", &Options::attn_one, 1},

@@ -136,6 +136,8 @@ unsigned int* ps_debug_device_ptr();         // host-visible barrier-timeout rec
 
 // persistent kernel (avd_gemm_ps.cu); bn = 0 lets it choose the tile width
 int launch_gemm_ps(const avd_gemm_args& g, GemmParams p, int nseg, int force_bn, cudaStream_t s);
+// persistent kernel on CTA pairs (avd_gemm_ps2.cu): 1 launched, 0 does not qualify, < 0 error
+int launch_gemm_ps2(const avd_gemm_args& g, GemmParams p, int nseg, int mode, int sms, cudaStream_t s);
 int ps_debug_read(unsigned int* out8);
 
 }  // namespace avd

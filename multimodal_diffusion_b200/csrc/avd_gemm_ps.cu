@@ -32,8 +32,8 @@ namespace avd {
 
 constexpr int PS_THREADS = 384;
 constexpr int PS_MAX_STAGES = 8;
-constexpr int PS_TAIL_BYTES = 2048;          // barriers + TMEM slot (512 B), ssq exchange (1 KB)
-constexpr int PS_SMEM_MAX = 232448 - 1024;   // 227 KB opt-in limit minus alignment slack
+constexpr int PS_TAIL_BYTES = 3072;          // barriers + TMEM slot (512 B), ssq exchange (512 B), two bias tiles (2 x 1 KB)
+constexpr int PS_SMEM_MAX = 232448;          // the 227 KB opt-in limit (the dynamic region starts 1024-byte aligned)
 
 // Debug records of barrier waits that timed out: {tag, cta, thread, counter, parity, N, K, grid * 1000 + BN}.
 // The record lives in mapped pinned host memory so that it survives a device-side trap.
@@ -53,6 +53,7 @@ template <int BN, int MODE>
 __global__ void __launch_bounds__(PS_THREADS, 1) gemm_ps_kernel(const __grid_constant__ CUtensorMap tmA,
                                                                 const __grid_constant__ CUtensorMap tmB,
                                                                 const __grid_constant__ CUtensorMap tmR,
+                                                                const __grid_constant__ CUtensorMap tmO,
                                                                 const GemmParams p, const PsPlan plan) {
   constexpr int A_BYTES = GEMM_BM * GEMM_BK * 2;
   constexpr int B_BYTES = BN * GEMM_BK * 2;
@@ -238,226 +239,13 @@ __global__ void __launch_bounds__(PS_THREADS, 1) gemm_ps_kernel(const __grid_con
         if (h == 0 && i == my_tiles - 1) trace_mark(trace, 3);
       }
     }
-  } else if (warp >= 4) {
-    // ------------------------------------------------------------------ epilogue
-    const int e = warp - 4;
-    const int quad = warp & 3;                 // TMEM lane quadrant this warp may access
-    const int hf = e >> 2;                     // even / odd 32-column chunks
-    const int act = MODE == 0 ? p.act : (MODE == 2 ? 2 : 0);
-    const int out_nseg = MODE == 0 ? p.out_nseg : 1;
-    const bool f16_out = p.f16_out != 0;
-    const float out_scale = p.out_scale;
-    const bool has_resid = MODE == 0 ? (p.has_resid != 0) : (MODE == 3);
-    const bool has_f32 = MODE == 0 ? (p.out_f32 != nullptr) : (MODE == 3);
-    const bool has_ssq = MODE == 0 ? (p.ssq_out != nullptr) : (MODE == 3);
-    float* const ssq_out = p.ssq_out;
-    const bool paired = (out_nseg > 0 || has_ssq);   // the two warps of a quadrant share 64-column units
-    const bool packed_gelu = (act == 2 && out_nseg == 1 && !has_f32 && !has_ssq);
-    uint8_t* const fbox0 = smem + plan.f32_off + e * 2 * GEMM_BOX;              // this warp's fp32 staging boxes: the
-    // residual chunk q of the warp's chunk sequence lands in box q & 1 (prefetched while chunk q - 1 is processed)
-    // and the fp32 result overwrites it in place; without a residual only box 0 is used
-    constexpr int CPW = NCH >= 2 ? NCH / 2 : 1;                                 // chunks per warp per tile
-    uint8_t* const bf_quad = smem + plan.bf_off + quad * out_nseg * GEMM_BOX;   // [out_nseg] boxes of the pair
-    const int sw = lane & 7;
-    const int rr = lane >> 3, cc = lane & 7;
-    const int tiles_n = plan.tiles_n;
-    const bool warp_has_chunks = hf < NCH;
-    const int n_chunks = warp_has_chunks ? my_tiles * CPW : 0;          // length of this warp's chunk sequence
-    pdl_wait();                                // ssq_in / residual / output buffers belong to earlier kernels until now
-
-    auto issue_resid = [&](int q) {            // residual box of chunk q of this warp's sequence
-      if (!has_resid || q >= n_chunks) return;
-      const int ti = q / CPW;
-      const int ch = hf + 2 * (q - ti * CPW);
-      const int t = (int)blockIdx.x + ti * G;
-      const int mt = t / tiles_n;
-      __syncwarp();
-      if (lane == 0) {
-        fence_async_smem();                    // earlier generic reads of the box are ordered before the async write
-        uint64_t* bar = &res_bar[e * 2 + (q & 1)];
-        mbar_expect_tx(bar, GEMM_BOX);
-        tma_load_3d(fbox0 + (q & 1) * GEMM_BOX, &tmR, bar, (t - mt * tiles_n) * BN + ch * 32, mt * GEMM_BM + quad * 32, 0);
-      }
-    };
-    issue_resid(0);
-    int q = 0;
-
-    for (int i = 0; i < my_tiles; ++i) {
-      const int t = (int)blockIdx.x + i * G;
-      const int mt = t / tiles_n;
-      const int m0 = mt * GEMM_BM, n0 = (t - mt * tiles_n) * BN;
-      const int b = i & 1;
-      const int row = m0 + quad * 32 + lane;
-      const bool live = row < p.M;
-      // lane l keeps bias[n0 + 32 ch + l] of this warp's (at most two) chunks; broadcast by shuffle in the chunk loop
-      float bias_a = 0.0f, bias_b = 0.0f, bias_c = 0.0f, bias_d = 0.0f;
-      if (p.bias != nullptr) {
-        if (hf < NCH) bias_a = __ldg(p.bias + n0 + hf * 32 + lane);
-        if (hf + 2 < NCH) bias_b = __ldg(p.bias + n0 + (hf + 2) * 32 + lane);
-        if (hf + 4 < NCH) bias_c = __ldg(p.bias + n0 + (hf + 4) * 32 + lane);
-        if (hf + 6 < NCH) bias_d = __ldg(p.bias + n0 + (hf + 6) * 32 + lane);
-      }
-      float rinv = 1.0f;
-      if (p.ssq_in != nullptr && live) {
-        float ss = 0.0f;
-        for (int q = 0; q < p.ssq_parts; ++q) ss += p.ssq_in[(int64_t)row * p.ssq_parts + q];
-        rinv = 1.0f / (sqrtf(ss) * p.inv_sqrt_rms_dim + p.rms_eps);
-      }
-      rinv *= p.a_scale;
-      if (warp == 4 && lane == 0 && i == 0) trace_mark(trace, 4);
-      if (lane == 0) {                           // one polling lane per warp, backing off: the issuing threads on the
-        uint32_t spins = 0;                      // same SM sub-partition need the issue slots during the mainloop
-        while (!mbar_try_wait(&acc_full[b], (i >> 1) & 1)) {
-          __nanosleep(64);
-          if (++spins > (1u << 24)) wait(&acc_full[b], (i >> 1) & 1, 4, i);
-        }
-      }
-      __syncwarp();
-      tc_fence_after();
-      if (warp == 4 && lane == 0) trace_mark(trace, i == 0 ? 5 : 8);
-      const bool two_acc = !CS && ipt > 1;   // with a single k-block the tile sits in issuer ((i * ipt) & 1)'s accumulator
-      const uint32_t t_row = tmem_base + (CS ? b * BN : (b * 2 + (two_acc ? 0 : ((i * ipt) & 1))) * BN) +
-                             ((uint32_t)(quad * 32) << 16);
-      uint32_t r[32], r1[32];
-      if (hf < NCH) {
-        tmem_ld_32x32(t_row + hf * 32, r);
-        if (two_acc) tmem_ld_32x32(t_row + BN + hf * 32, r1);
-      } else {                                   // BN = 32: the odd-chunk warps have nothing to read
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&acc_empty[b]);
-      }
-#pragma unroll 1
-      for (int ch = hf; ch < NCH; ch += 2) {
-        float v[32];
-        tmem_ld_wait();
-        if (two_acc) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) + __uint_as_float(r1[j]);
-        } else {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-        }
-        if (ch + 2 < NCH) {                    // next chunk's TMEM loads fly while this one is processed
-          tmem_ld_32x32(t_row + (ch + 2) * 32, r);
-          if (two_acc) tmem_ld_32x32(t_row + BN + (ch + 2) * 32, r1);
-        } else {
-          tc_fence_before();                   // this warp's last read of the accumulator: hand the buffer back
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&acc_empty[b]);
-        }
-        {
-          const int ci = (ch - hf) >> 1;
-          const float bl = ci == 0 ? bias_a : ci == 1 ? bias_b : ci == 2 ? bias_c : bias_d;
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = fmaf(v[j], rinv, __shfl_sync(0xffffffffu, bl, j));
-        }
-        uint8_t* const fbox = fbox0 + (has_resid ? (q & 1) * GEMM_BOX : 0);
-        uint8_t* frow = fbox + lane * 128;
-        if (has_resid) {
-          issue_resid(q + 1);                  // the other box: its last readers (chunk q - 1's stores) are done
-          wait(&res_bar[e * 2 + (q & 1)], (q >> 1) & 1, 5, i);
-#pragma unroll
-          for (int c = 0; c < 8; ++c) {
-            const float4 x4 = lds128(frow + ((c ^ sw) << 4));
-            v[4 * c] += x4.x; v[4 * c + 1] += x4.y; v[4 * c + 2] += x4.z; v[4 * c + 3] += x4.w;
-          }
-        }
-        if (act == 1) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
-        } else if (act == 2 && !packed_gelu) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = gelu_fast(v[j]);
-        }
-        if (has_f32) {
-#pragma unroll
-          for (int c = 0; c < 8; ++c) sts128(frow + ((c ^ sw) << 4), v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
-        }
-        float ssq_acc = 0.0f;
-        if (has_ssq) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) ssq_acc = fmaf(v[j], v[j], ssq_acc);
-          if (hf == 1) ssq_x[quad * 32 + lane] = ssq_acc;
-        }
-        const int c0 = (ch & 1) * 4;
-        if (packed_gelu) {
-          uint8_t* brow = bf_quad + lane * 128;
-if (f16_out) {
-#pragma unroll
-          for (int c = 0; c < 4; ++c)
-            sts128u(brow + (((c0 + c) ^ sw) << 4), gelu_pair_f16x2(v[8 * c], v[8 * c + 1]),
-                    gelu_pair_f16x2(v[8 * c + 2], v[8 * c + 3]), gelu_pair_f16x2(v[8 * c + 4], v[8 * c + 5]),
-                    gelu_pair_f16x2(v[8 * c + 6], v[8 * c + 7]));
-          } else {
-#pragma unroll
-          for (int c = 0; c < 4; ++c)
-            sts128u(brow + (((c0 + c) ^ sw) << 4), gelu_pair_bf16x2(v[8 * c], v[8 * c + 1]),
-                    gelu_pair_bf16x2(v[8 * c + 2], v[8 * c + 3]), gelu_pair_bf16x2(v[8 * c + 4], v[8 * c + 5]),
-                    gelu_pair_bf16x2(v[8 * c + 6], v[8 * c + 7]));
-          }
-        } else if (out_nseg == 1) {
-          uint8_t* brow = bf_quad + lane * 128;
-if (f16_out) {
-#pragma unroll
-          for (int c = 0; c < 4; ++c)
-            sts128u(brow + (((c0 + c) ^ sw) << 4), pack16(true, out_scale, v[8 * c], v[8 * c + 1]), pack16(true, out_scale, v[8 * c + 2], v[8 * c + 3]),
-                    pack16(true, out_scale, v[8 * c + 4], v[8 * c + 5]), pack16(true, out_scale, v[8 * c + 6], v[8 * c + 7]));
-          } else {
-#pragma unroll
-          for (int c = 0; c < 4; ++c)
-            sts128u(brow + (((c0 + c) ^ sw) << 4), pack_bf16x2(v[8 * c], v[8 * c + 1]), pack_bf16x2(v[8 * c + 2], v[8 * c + 3]),
-                    pack_bf16x2(v[8 * c + 4], v[8 * c + 5]), pack_bf16x2(v[8 * c + 6], v[8 * c + 7]));
-          }
-        } else if (out_nseg > 1) {
-          for (int sg = 0; sg < out_nseg; ++sg) {
-            uint32_t w[16];
-#pragma unroll
-            for (int j = 0; j < 16; ++j) {
-              const __nv_bfloat16 h0 = __float2bfloat16_rn(v[2 * j]);
-              const __nv_bfloat16 h1 = __float2bfloat16_rn(v[2 * j + 1]);
-              v[2 * j] -= __bfloat162float(h0);
-              v[2 * j + 1] -= __bfloat162float(h1);
-              w[j] = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
-            }
-            uint8_t* brow = bf_quad + sg * GEMM_BOX + lane * 128;
-#pragma unroll
-            for (int c = 0; c < 4; ++c)
-              sts128u(brow + (((c0 + c) ^ sw) << 4), w[4 * c], w[4 * c + 1], w[4 * c + 2], w[4 * c + 3]);
-          }
-        }
-        if (paired) named_bar_sync(2 + quad, 64); else __syncwarp();
-        if (hf == 0 && has_ssq && live)
-          ssq_out[(int64_t)row * (p.N / 64) + ((n0 + ch * 32) >> 6)] = ssq_acc + ssq_x[quad * 32 + lane];
-        // staged boxes -> global, coalesced: 8 lanes cover one 128-byte row, one warp instruction covers 4 rows
-        if (has_f32) {
-          float* gp = p.out_f32 + (int64_t)(m0 + quad * 32) * p.N + n0 + ch * 32 + cc * 4;
-#pragma unroll
-          for (int it = 0; it < 8; ++it) {
-            const int rw = it * 4 + rr;
-            const float4 x4 = lds128(fbox + rw * 128 + ((cc ^ (rw & 7)) << 4));
-            if (m0 + quad * 32 + rw < p.M) *reinterpret_cast<float4*>(gp + (int64_t)rw * p.N) = x4;
-          }
-        }
-        if (out_nseg > 0) {      // the pair's 64-column bf16 box: this warp stores rows [16 hf, 16 hf + 16)
-          for (int sg = 0; sg < out_nseg; ++sg) {
-            const uint8_t* box = bf_quad + sg * GEMM_BOX;
-            __nv_bfloat16* gp = p.out_bf16 + (int64_t)sg * p.M * p.N + (int64_t)(m0 + quad * 32) * p.N + n0 + (ch >> 1) * 64 + cc * 8;
-#pragma unroll
-            for (int it = 0; it < 4; ++it) {
-              const int rw = hf * 16 + it * 4 + rr;
-              const float4 x4 = lds128(box + rw * 128 + ((cc ^ (rw & 7)) << 4));
-              if (m0 + quad * 32 + rw < p.M) *reinterpret_cast<float4*>(gp + (int64_t)rw * p.N) = x4;
-            }
-          }
-        }
-        ++q;
-        // the pair's shared boxes (bf16, ssq_x) are rewritten by the next chunk / tile: both warps must be done reading
-        if (paired) named_bar_sync(2 + quad, 64); else __syncwarp();
-      }
-      if (warp == 4 && lane == 0) trace_mark(trace, i == 0 ? 6 : 9);
-    }
-  }
+#define PS_EPI_TILE(i) ((int)blockIdx.x + (i) * G)
+#define PS_EPI_ROW0(mt) ((mt) * GEMM_BM)
+#define PS_EPI_ACC_EMPTY(b) mbar_arrive(&acc_empty[b])
+#include "avd_gemm_ps_epilogue.inc"
+#undef PS_EPI_TILE
+#undef PS_EPI_ROW0
+#undef PS_EPI_ACC_EMPTY
 
   __syncwarp();   // lanes 1..31 of the role warps wait here for their lane 0
   tc_fence_before();
@@ -497,12 +285,13 @@ static int ps_num_sms() {
 }
 
 template <int BN>
-static int launch_ps_bn(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmR, const GemmParams& p,
-                        const PsPlan& plan, int smem_bytes, int grid, int mode, cudaStream_t s) {
-  using KernelFn = void (*)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const GemmParams, const PsPlan);
+static int launch_ps_bn(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmR, const CUtensorMap& tmO,
+                        const GemmParams& p, const PsPlan& plan, int smem_bytes, int grid, int mode, cudaStream_t s) {
+  using KernelFn = void (*)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const CUtensorMap, const GemmParams,
+                            const PsPlan);
   static const KernelFn kernels[4] = {gemm_ps_kernel<BN, 0>, gemm_ps_kernel<BN, 1>, gemm_ps_kernel<BN, 2>,
                                       gemm_ps_kernel<BN, 3>};
-  AVD_TRY(ensure_dyn_smem(reinterpret_cast<const void*>(kernels[mode]), PS_SMEM_MAX + 1024));   // once per device
+  AVD_TRY(ensure_dyn_smem(reinterpret_cast<const void*>(kernels[mode]), PS_SMEM_MAX));   // once per device
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(grid);
   cfg.blockDim = dim3(PS_THREADS);
@@ -519,7 +308,7 @@ static int launch_ps_bn(const CUtensorMap& tmA, const CUtensorMap& tmB, const CU
   cfg.numAttrs = na;
   if (kind_skipped(KIND_GEMM)) return 0;
   LaunchScope ls(KIND_GEMM, s);
-  AVD_CUDA(cudaLaunchKernelEx(&cfg, kernels[mode], tmA, tmB, tmR, p, plan));
+  AVD_CUDA(cudaLaunchKernelEx(&cfg, kernels[mode], tmA, tmB, tmR, tmO, p, plan));
   return 0;
 }
 
@@ -527,7 +316,10 @@ static int launch_ps_bn(const CUtensorMap& tmA, const CUtensorMap& tmB, const CU
 static bool ps_plan(const avd_gemm_args& g, int out_nseg, int bn, PsPlan* plan, int* smem_bytes) {
   const int stage = (GEMM_BM + bn) * GEMM_BK * 2;
   const int f32_bytes = (g.out_f32 != nullptr || g.resid != nullptr) ? 16 * GEMM_BOX : 0;
-  const int bf_bytes = out_nseg * 4 * GEMM_BOX;
+  // the 16-bit-only epilogues (MODE 1 / 2) double-buffer their staging boxes for the bulk stores
+  const bool fast16 = g.out_bf16 != nullptr && out_nseg == 1 && g.out_f32 == nullptr && g.resid == nullptr &&
+                      g.ssq_out == nullptr && (g.act == 0 || g.act == 2);
+  const int bf_bytes = out_nseg * 4 * GEMM_BOX * (fast16 ? 2 : 1);
   const int fixed = f32_bytes + bf_bytes + PS_TAIL_BYTES;
   int stages = (PS_SMEM_MAX - fixed) / stage;
   if (stages > PS_MAX_STAGES) stages = PS_MAX_STAGES;
@@ -614,17 +406,33 @@ int launch_gemm_ps(const avd_gemm_args& g, GemmParams p, int nseg, int force_bn,
   tmR = tmA;   // placeholder when unused (never dereferenced)
   if (g.resid != nullptr)
     AVD_TRY(get_tensor_map_3d(g.resid, 4, g.N, g.M, 1, (uint64_t)g.N * 4, (uint64_t)g.M * g.N * 4, 32, 32, &tmR));
+  CUtensorMap tmO = tmA;   // the 16-bit output as {64 columns, 32 rows} boxes (bulk stores of the MODE 1 / 2 epilogues)
+  if (g.out_bf16 != nullptr && out_nseg == 1)
+    AVD_TRY(get_tensor_map_3d(g.out_bf16, 2, g.N, g.M, 1, (uint64_t)g.N * 2, (uint64_t)g.M * g.N * 2, 64, 32, &tmO));
   int mode = 0;
   const bool one16 = g.out_bf16 != nullptr && out_nseg == 1;
   if (one16 && g.out_f32 == nullptr && g.resid == nullptr && g.ssq_out == nullptr && g.act == 0) mode = 1;
   else if (one16 && g.out_f32 == nullptr && g.resid == nullptr && g.ssq_out == nullptr && g.act == 2) mode = 2;
   else if (one16 && g.out_f32 != nullptr && g.resid != nullptr && g.ssq_out != nullptr && g.act == 0) mode = 3;
+#ifdef AVD_DEBUG_HOOKS
+  if (bn < 64 || options().gemm_generic) mode = 0;   // debug-hooks builds stamp every epilogue mode
+#else
   if (p.trace != nullptr || bn < 64 || options().gemm_generic) mode = 0;
+#endif
+  // CTA pairs (avd_gemm_ps2.cu): the 256-wide tiles on two SMs each, half of the weight tile per SM
+  // Measured (tools/kbench.py --M 32768, AVD_PS_PAIR = 0 / 1): the pair wins where the k-loop is long (fc2, K = 2048:
+  // 91.9 -> 83.8 us) and loses a little at K = 512 (QKV 51.7 -> 55.3 us: per tile the leader's one issuing thread also
+  // waits for the peer's epilogue warps and for both CTAs' loads), so by default it takes only GEMMs of >= 16 k-blocks.
+  const int pair_opt = options().ps_pair;
+  if (pair_opt != 0 && g.N % 256 == 0 && (bn == 256 || pair_opt == 2) && (ipt >= 16 || pair_opt == 2)) {
+    const int rc = launch_gemm_ps2(g, p, nseg, mode, sms, s);
+    if (rc != 0) return rc < 0 ? rc : 0;
+  }
   switch (bn) {
-    case 256: return launch_ps_bn<256>(tmA, tmB, tmR, p, plan, smem_bytes, grid, mode, s);
-    case 128: return launch_ps_bn<128>(tmA, tmB, tmR, p, plan, smem_bytes, grid, mode, s);
-    case 64: return launch_ps_bn<64>(tmA, tmB, tmR, p, plan, smem_bytes, grid, mode, s);
-    default: return launch_ps_bn<32>(tmA, tmB, tmR, p, plan, smem_bytes, grid, mode, s);
+    case 256: return launch_ps_bn<256>(tmA, tmB, tmR, tmO, p, plan, smem_bytes, grid, mode, s);
+    case 128: return launch_ps_bn<128>(tmA, tmB, tmR, tmO, p, plan, smem_bytes, grid, mode, s);
+    case 64: return launch_ps_bn<64>(tmA, tmB, tmR, tmO, p, plan, smem_bytes, grid, mode, s);
+    default: return launch_ps_bn<32>(tmA, tmB, tmR, tmO, p, plan, smem_bytes, grid, mode, s);
   }
 }
 
