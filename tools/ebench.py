@@ -112,7 +112,53 @@ def main() -> None:
     report("crossfade_video (48-frame windows, 16-frame hop)", timed(lambda: _lib.check(lib.avd_crossfade_video(vch.data_ptr(), wv.data_ptr(), outv.data_ptr(), nv, Tv, Fv, hopv, st()))), vch.numel() + outv.numel())
     del vch, outv
 
+    # encoders / decoders either side of the sampling loop: CUDA-core fp32 direct convolutions, run once per
+    # clip.  Bound = the fp32 FMA rate (148 SMs x 128 lanes x 2 flop x SM clock), not HBM; the line to read is their time
+    # next to one 50-step sampling call of the same 8 clips (16.3 ms).
+    import numpy as np
+    sys.path.insert(0, str(ROOT / "tests"))
+    from multimodal_diffusion_b200.avdiff.models.infer import sample_clip as sc
+    cfg = json.loads((ROOT / "tests" / "golden" / "cfg_mvp_v2a.json").read_text())
+    torch.manual_seed(0)
+    vae, codec = sc.build_components(cfg, dev)[:2]
+    fp32_peak = 148 * 128 * 2 * float(peaks.get("sm_max_mhz", 1965.0)) * 1e-6     # TFLOP/s
+    Be = 8
+    frames = torch.rand(Be, 3, 48, 128, 128, device=dev)
+    wav = torch.tanh(torch.randn(Be, 1, 48000, device=dev))
+    enc_rows = []
+
+    def conv_flops(mod, voxels_of):
+        tot = 0.0
+        for k, v in mod.state_dict().items():
+            if v.dim() >= 3 and k.endswith("weight"):
+                tot += 2.0 * v.numel() * voxels_of(k)
+        return tot
+
+    with torch.no_grad():
+        zv8 = vae.encode(frames)
+        za8 = codec.encode(wav)
+        vox = 48 * 128 * 128
+        lat = zv8.shape[2] * zv8.shape[3] * zv8.shape[4]
+        cases = [
+            ("VideoVAE.encode (8 clips, 3 s, 128x128)", lambda: vae.encode(frames),
+             Be * conv_flops(vae, lambda k: vox if "enc_net" in k else (lat if "to_lat" in k else 0))),
+            ("VideoVAE.decode", lambda: vae.decode(zv8),
+             Be * conv_flops(vae, lambda k: vox if ("dec_net" in k or "to_img" in k) else (lat if "from_lat" in k else 0))),
+            ("AudioCodec.encode (8 clips, 3 s, 16 kHz)", lambda: codec.encode(wav),
+             Be * conv_flops(codec, lambda k: 48000 if "pre" in k else (za8.shape[-1] if "to_lat" in k else 0))),
+            ("AudioCodec.decode", lambda: codec.decode(za8),
+             Be * conv_flops(codec, lambda k: 48000 if "smooth" in k else (za8.shape[-1] if "from_lat" in k else 0))),
+        ]
+        for name, fn, fl in cases:
+            us = timed(fn, reps=3)
+            enc_rows.append({"kernel": name, "us": round(us, 1), "GFLOP": round(fl / 1e9, 2),
+                             "TFLOPs_fp32": round(fl / us * 1e-6, 2), "frac_of_fp32_fma_peak": round(fl / us * 1e-6 / fp32_peak, 3)})
+            print(json.dumps(enc_rows[-1]), flush=True)
+
     out = {"what": "byte-moving kernels at HBM-streaming sizes on 1 x B200; algorithmic bytes / CUDA-event time",
+           "encoders": {"what": "encode / decode kernels (avd_codec.cu, avd_vae.cu) through the mirror modules, 8 clips; algorithmic "
+                                "conv FLOPs (2 x weights x output positions) / CUDA-event time against the fp32 FMA peak",
+                        "fp32_fma_peak_tflops": round(fp32_peak, 1), "rows": enc_rows},
            "hbm_peak_gbs": peak, "peak_source": "MEASURED_PEAKS.json hbm_gbs (torch copy, read+write bytes)", "rows": rows}
     Path(args.out).parent.mkdir(parents=True, exist_ok=True)
     Path(args.out).write_text(json.dumps(out, indent=1))

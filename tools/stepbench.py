@@ -28,7 +28,8 @@ def main() -> None:
         if a.startswith("--opt="):
             k, v = a[6:].split("=")
             _lib.set_option(k, int(v))
-    fs = FusedSampler(HotPathConfig(sampler_steps=50, guidance=3.5), mods[0], mods[1], mods[2], mods[3], target, B,
+    kw = dict(Fa=500, video_latent=(40, 16, 16)) if "--cfg10" in sys.argv else {}   # the 10 s clip: N = 445 joint tokens
+    fs = FusedSampler(HotPathConfig(sampler_steps=50, guidance=3.5, **kw), mods[0], mods[1], mods[2], mods[3], target, B,
                       device=dev)
     zp = randn(1, *fs.prompt_shape).to(dev)
     z = randn(2, *fs.latent_shape).to(dev)
