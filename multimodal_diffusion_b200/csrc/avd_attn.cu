@@ -532,6 +532,321 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
   }
 }
 
+// =====================================================================================================
+// attn_pipe_kernel: the multi-block case (N > 192 keys) with the three stages of a key block running concurrently.
+//
+// attn_tc_kernel's multi-block path is a serial chain per query tile -- S = Q K^T, row max (first pass over S in TMEM),
+// exp / P (second pass), O_j = P V, O update -- 8400 cycles per 2 x 128 x 192 block against 3072 of MUFU and 1920 of
+// MMA.  Here one CTA owns ONE 128-query tile, which frees TMEM for two S buffers and registers
+// for a whole 96-score half row per thread (one tcgen05.ld pass instead of two):
+//   warp 8 (one lane)  issuer: TMA loads of Q and of the K / V blocks into double buffers; S(j+2) = Q K_{j+2}^T is issued
+//                      as soon as softmax(j) has pulled S(j) out of its TMEM buffer, O_j = P_j V_j as soon as P_j is staged
+//   warps 0..7         softmax of block j -- thread = query row, the two warps of a lane quadrant split the 192 key
+//                      columns -- while the tensor pipe runs S(j+1) / S(j+2) and P(j-1) V(j-1); the read-back of O(j-1)
+//                      is deferred to the start of block j (P V of block j-1 had the whole S wait to finish)
+// Per block the softmax warps then see: wait S (already there), 3 x tcgen05.ld, max, 96 exponentials, P store; the
+// MUFU pipe (16 ex2 per clock per SM) is the floor: 128 x 192 / 16 = 1536 cycles.
+//
+// MEASURED (tools/kbench.py --M 32768, 16 x 2048 tokens): 474 us against 358 us for attn_tc_kernel's multi-block path --
+// 6000 cycles per 128 x 192 block.  With ONE query tile per SM only 8 softmax warps (2 per scheduler) are resident, and
+// each of them walks a dependent chain per block (tcgen05.ld round trip, O read-back, pair exchange, 96 MUFU ops issued
+// from one warp, P stores) with nobody to fill its bubbles; attn_tc_kernel's two tiles x 8 warps hide each other's.  The
+// overlap this kernel adds (S(j+2) and P V under the softmax) is worth less than the second tile's warps.  It is therefore
+// OFF by default (option attn_pipe); a variant of attn_tc_kernel reading S once per 128-key block was measured too
+// (380 us): the multi-block path is not bound by tcgen05.ld volume either.  What is left is an FA4-style split (two
+// softmax warpgroups on two tiles, O kept in TMEM with lazy rescaling, a dedicated correction group), DESIGN.md section 5.
+// =====================================================================================================
+constexpr int AP_THREADS = 288;
+constexpr int AP_XCHG_BYTES = (4 + 2) * 128 * 4;      // row max [2 bufs][2 halves][128], row sum [2 halves][128]
+constexpr int AP_SMEM = ATT_Q_BYTES + 4 * ATT_KV_BYTES + 2 * ATT_P_BYTES + AP_XCHG_BYTES + 256;
+enum { PB_Q = 0, PB_K = 1 /*+b*/, PB_V = 3 /*+b*/, PB_S = 5 /*+b*/, PB_SF = 7 /*+b*/, PB_P = 9 /*+b*/, PB_O = 11, PB_OF = 12,
+       PB_COUNT = 13 };
+
+template <bool F16, bool MASKED>
+__global__ void __launch_bounds__(AP_THREADS, 1) attn_pipe_kernel(const __grid_constant__ CUtensorMap tmQ,
+                                                                  const __grid_constant__ CUtensorMap tmKV,
+                                                                  const AttnParams p) {
+  extern __shared__ __align__(1024) uint8_t ap_smem[];
+  uint8_t* smem = ap_smem;
+  if ((smem_u32(smem) & 1023u) != 0) __trap();
+  uint8_t* sQ = smem;                                  // later: output staging
+  uint8_t* sK = sQ + ATT_Q_BYTES;                      // [2]
+  uint8_t* sV = sK + 2 * ATT_KV_BYTES;                 // [2]
+  uint8_t* sP = sV + 2 * ATT_KV_BYTES;                 // [2] x 3 atoms
+  float* xmax = reinterpret_cast<float*>(sP + 2 * ATT_P_BYTES);
+  float* xsum = xmax + 4 * 128;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 2 * ATT_P_BYTES + AP_XCHG_BYTES);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + PB_COUNT);
+
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5, lane = tid & 31;
+  const int head = blockIdx.y;
+  const int seq = blockIdx.z;
+  const int row_base = seq * p.N;
+  const int q0 = blockIdx.x * ATT_BQ;
+  const int colQ = head * ATT_HD, colK = p.d + head * ATT_HD, colV = 2 * p.d + head * ATT_HD;
+  const int nkv = (p.N + ATT_BKV - 1) / ATT_BKV;
+
+  if (warp == 0) {
+    if (lane < PB_COUNT) {
+      const int i = lane;
+      const bool warps8 = (i >= PB_SF && i < PB_O) || i == PB_OF;      // arrivals: one per softmax warp
+      mbar_init(&bars[i], warps8 ? 8 : 1);
+    }
+    fence_barrier_init();
+  } else if (warp == 1 && lane == 0) {
+    tma_prefetch_desc(&tmQ);
+    tma_prefetch_desc(&tmKV);
+  }
+  if (warp == 8) tmem_alloc<512>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_launch_dependents();
+  const uint32_t tmem_O = tmem_base + 2 * ATT_BKV;     // S buffers at columns [0,192) and [192,384), O at [384,448)
+
+  if (warp == 8) {
+    // ------------------------------------------------------------------ issuer
+    if (lane == 0) {
+      pdl_wait();                                      // qkv comes from the previous kernel
+      mbar_expect_tx(&bars[PB_Q], ATT_Q_BYTES);
+      tma_load_3d(sQ, &tmQ, &bars[PB_Q], colQ, row_base + q0, 0);
+      for (int b = 0; b < 2 && b < nkv; ++b) {
+        mbar_expect_tx(&bars[PB_K + b], ATT_KV_BYTES);
+        tma_load_3d(sK + b * ATT_KV_BYTES, &tmKV, &bars[PB_K + b], colK, row_base + b * ATT_BKV, 0);
+        mbar_expect_tx(&bars[PB_V + b], ATT_KV_BYTES);
+        tma_load_3d(sV + b * ATT_KV_BYTES, &tmKV, &bars[PB_V + b], colV, row_base + b * ATT_BKV, 0);
+      }
+      const uint32_t hi = smem_desc_hi_sw128(1024);
+      const uint32_t q_lo = smem_desc_lo_sw128(smem_u32(sQ), 16);
+      auto issue_S = [&](int j) {                      // S(j) = Q K_j^T into S buffer j & 1
+        const int b = j & 1;
+        const int kv_valid = min(ATT_BKV, p.N - j * ATT_BKV);
+        const int kv_n = (kv_valid + 15) & ~15;
+        const uint32_t idesc_s = make_idesc_bf16(ATT_BQ, kv_n, 0, 0, F16);
+        const uint32_t k_lo = smem_desc_lo_sw128(smem_u32(sK + b * ATT_KV_BYTES), 16);
+#pragma unroll
+        for (int k = 0; k < ATT_HD / 16; ++k)
+          umma_bf16_lh(tmem_base + b * ATT_BKV, q_lo + 2 * k, k_lo + 2 * k, hi, idesc_s, k > 0 ? 1u : 0u);
+        umma_commit(&bars[PB_S + b]);
+      };
+      mbar_wait(&bars[PB_Q], 0);
+      mbar_wait(&bars[PB_K], 0);
+      tc_fence_after();
+      issue_S(0);
+      if (nkv > 1) {
+        mbar_wait(&bars[PB_K + 1], 0);
+        tc_fence_after();
+        issue_S(1);
+      }
+      const uint32_t idesc_o = make_idesc_bf16(ATT_BQ, ATT_HD, 0, 1, F16);    // B = V is MN-major
+      for (int j = 0; j < nkv; ++j) {
+        const int b = j & 1;
+        const uint32_t ph = (j >> 1) & 1;
+        const bool more = j + 2 < nkv;
+        if (more) {                                    // K buffer b is free once the S(j) MMAs have executed
+          mbar_wait(&bars[PB_S + b], ph);
+          mbar_expect_tx(&bars[PB_K + b], ATT_KV_BYTES);
+          tma_load_3d(sK + b * ATT_KV_BYTES, &tmKV, &bars[PB_K + b], colK, row_base + (j + 2) * ATT_BKV, 0);
+        }
+        // O_j = P_j V_j: P staged, V landed, O(j-1) read out of TMEM
+        mbar_wait(&bars[PB_P + b], ph);
+        mbar_wait(&bars[PB_V + b], ph);
+        if (j > 0) mbar_wait(&bars[PB_OF], (j - 1) & 1);
+        tc_fence_after();
+        {
+          const int kv_valid = min(ATT_BKV, p.N - j * ATT_BKV);
+          const int ksteps = ((kv_valid + 15) & ~15) >> 4;
+          const uint32_t p_lo = smem_desc_lo_sw128(smem_u32(sP + b * ATT_P_BYTES), 16);
+          const uint32_t v_lo = smem_desc_lo_sw128(smem_u32(sV + b * ATT_KV_BYTES), 16);
+          for (int ks = 0; ks < ksteps; ++ks) {
+            const uint32_t pa = p_lo + (((ks >> 2) * ATT_Q_BYTES + (ks & 3) * 32) >> 4);
+            const uint32_t va = v_lo + ((ks * 16 * 128) >> 4);                  // 16 keys = 16 rows of 128 B
+            umma_bf16_lh(tmem_O, pa, va, hi, idesc_o, ks > 0 ? 1u : 0u);
+          }
+          umma_commit(&bars[PB_O]);
+        }
+        if (more) {                                    // S(j+2): S buffer b has been read by softmax(j) (it staged P_j after)
+          mbar_wait(&bars[PB_SF + b], ph);
+          mbar_wait(&bars[PB_K + b], ph ^ 1);
+          tc_fence_after();
+          issue_S(j + 2);
+          mbar_wait(&bars[PB_O], j & 1);               // V buffer b is free once the P V MMAs of block j have executed
+          mbar_expect_tx(&bars[PB_V + b], ATT_KV_BYTES);
+          tma_load_3d(sV + b * ATT_KV_BYTES, &tmKV, &bars[PB_V + b], colV, row_base + (j + 2) * ATT_BKV, 0);
+        }
+      }
+    }
+    __syncwarp();
+  } else {
+    // ------------------------------------------------------------------ softmax + output
+    const int sp = warp >> 2, quad = warp & 3;
+    const int r = quad * 32 + lane;                    // row inside the tile == TMEM lane
+    const uint32_t lane_base = (uint32_t)(quad * 32) << 16;
+    const uint32_t pair_bar = 1 + quad;
+    const float sc = p.scale_log2e;
+    float o_acc[32];
+#pragma unroll
+    for (int c = 0; c < 32; ++c) o_acc[c] = 0.0f;
+    float m_run = -INFINITY, l_run = 0.0f, alpha_pend = 0.0f;
+    auto valid_bits = [&](int j, int ch, int lim) -> uint32_t {
+      uint32_t v = lim >= 32 ? 0xffffffffu : (lim > 0 ? ((1u << lim) - 1u) : 0u);
+      if (MASKED && lim > 0) v &= ~p.kmask[(size_t)blockIdx.z * p.kmask_words + j * (ATT_BKV / 32) + ch];
+      return v;
+    };
+    auto drain_O = [&](int j) {                        // o_acc = o_acc * alpha_j + O_j  (this thread's 32 of the 64 columns)
+      mbar_wait(&bars[PB_O], j & 1);
+      tc_fence_after();
+      uint32_t xo[32];
+      tmem_ld_32x32(tmem_O + lane_base + sp * 32, xo);
+      tmem_ld_wait();
+#pragma unroll
+      for (int c = 0; c < 32; ++c) o_acc[c] = fmaf(o_acc[c], alpha_pend, __uint_as_float(xo[c]));
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&bars[PB_OF]);
+    };
+    for (int j = 0; j < nkv; ++j) {
+      const int b = j & 1;
+      const uint32_t ph = (j >> 1) & 1;
+      const int kv_valid = min(ATT_BKV, p.N - j * ATT_BKV);
+      const int nch = (kv_valid + 31) >> 5;
+      const int ch0 = sp * 3;
+      mbar_wait(&bars[PB_S + b], ph);
+      tc_fence_after();
+      uint32_t x[3][32];
+#pragma unroll
+      for (int i = 0; i < 3; ++i)
+        if (i == 0 || ch0 + i < nch) tmem_ld_32x32(tmem_base + b * ATT_BKV + lane_base + (ch0 + i) * 32, x[i]);
+      tmem_ld_wait();
+      tc_fence_before();                               // S buffer b may be overwritten by S(j+2)
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&bars[PB_SF + b]);
+      if (j > 0) drain_O(j - 1);
+      // ---- row max over this thread's valid keys, exchanged with the other half's warp
+      float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+      for (int i = 0; i < 3; ++i) {
+        const uint32_t vb = valid_bits(j, ch0 + i, kv_valid - (ch0 + i) * 32);
+        if (vb == 0xffffffffu) {
+#pragma unroll
+          for (int c = 0; c < 32; ++c) mx[c & 3] = fmaxf(mx[c & 3], __uint_as_float(x[i][c]));
+        } else if (vb != 0u) {
+#pragma unroll
+          for (int c = 0; c < 32; ++c)
+            mx[c & 3] = fmaxf(mx[c & 3], ((vb >> c) & 1u) ? __uint_as_float(x[i][c]) : -INFINITY);
+        }
+      }
+      const float m_part = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
+      float* xm = xmax + (b * 2) * 128;
+      xm[sp * 128 + r] = m_part;
+      named_bar_sync(pair_bar, 64);
+      const float m_new = fmaxf(m_run, fmaxf(m_part, xm[(sp ^ 1) * 128 + r]));
+      const float m_use = m_new == -INFINITY ? 0.0f : m_new;   // every key so far padded: keep the exponents finite
+      const float alpha = ex2_approx((m_run - m_use) * sc);    // m_run = -inf on the first block -> 0
+      const float m_sc = m_use * sc;
+      m_run = m_new;
+      // ---- p = exp2(s*c - m*c), row sum, P -> smem (K-major, 128B swizzle, 64-key atoms)
+      uint8_t* sPb = sP + b * ATT_P_BYTES;
+      float l_blk = 0.0f;
+#pragma unroll
+      for (int i = 0; i < 3; ++i) {
+        const int ch = ch0 + i;
+        const int lim = kv_valid - ch * 32;
+        if (lim > -16) {                               // chunks wholly past round16(keys) are never read by the PV MMA
+          float l0 = 0.0f, l1 = 0.0f;
+          uint32_t w[16];
+          const uint32_t vb = valid_bits(j, ch, lim);
+          float e[32];
+          ex2_chunk(x[i], sc, -m_sc, e);
+          if (vb == 0xffffffffu) {
+#pragma unroll
+            for (int c = 0; c < 32; c += 2) {
+              l0 += e[c];
+              l1 += e[c + 1];
+              w[c >> 1] = F16 ? pack_f16x2(e[c], e[c + 1]) : pack_bf16x2(e[c], e[c + 1]);
+            }
+          } else {
+#pragma unroll
+            for (int c = 0; c < 32; c += 2) {
+              const float p0 = ((vb >> c) & 1u) ? e[c] : 0.0f;
+              const float p1 = ((vb >> (c + 1)) & 1u) ? e[c + 1] : 0.0f;
+              l0 += p0;
+              l1 += p1;
+              w[c >> 1] = F16 ? pack_f16x2(p0, p1) : pack_bf16x2(p0, p1);
+            }
+          }
+          l_blk += l0 + l1;
+          uint8_t* atom = sPb + (ch >> 1) * ATT_Q_BYTES + r * 128;
+          const int q_base = (ch & 1) * 4;
+#pragma unroll
+          for (int q = 0; q < 4; ++q)
+            *reinterpret_cast<uint4*>(atom + (((q_base + q) ^ (r & 7)) << 4)) =
+                make_uint4(w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
+        }
+      }
+      l_run = l_run * alpha + l_blk;
+      alpha_pend = alpha;                              // applied to o_acc when O_j is added
+      fence_async_smem();                              // P (generic-proxy stores) -> visible to the tensor core
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&bars[PB_P + b]);
+    }
+    drain_O(nkv - 1);
+
+    // ---- total row sum = the two halves' partial sums; normalise and store (as attn_tc_kernel)
+    xsum[sp * 128 + r] = l_run;
+    named_bar_sync(pair_bar, 64);
+    const float inv_l = 1.0f / (l_run + xsum[(sp ^ 1) * 128 + r]);
+    const int64_t seg_stride = p.M * (int64_t)p.d;
+    uint8_t* stage = sQ + quad * 32 * 128;             // Q is retired: every S MMA has executed
+    const int q_tile0 = q0 + quad * 32;
+    float rem[32];
+#pragma unroll
+    for (int c = 0; c < 32; ++c) rem[c] = o_acc[c] * inv_l;
+    for (int sg = 0; sg < p.out_nseg; ++sg) {
+#pragma unroll
+      for (int v4 = 0; v4 < 4; ++v4) {
+        uint32_t w[4];
+        if (p.out_nseg == 1) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            w[k] = F16 ? pack_f16x2(rem[v4 * 8 + k * 2], rem[v4 * 8 + k * 2 + 1]) : pack_bf16x2(rem[v4 * 8 + k * 2], rem[v4 * 8 + k * 2 + 1]);
+        } else {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const int c = v4 * 8 + k * 2;
+            const __nv_bfloat16 h0 = __float2bfloat16_rn(rem[c]);
+            const __nv_bfloat16 h1 = __float2bfloat16_rn(rem[c + 1]);
+            rem[c] -= __bfloat162float(h0);
+            rem[c + 1] -= __bfloat162float(h1);
+            w[k] = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
+          }
+        }
+        *reinterpret_cast<uint4*>(stage + lane * 128 + (((sp * 4 + v4) ^ (lane & 7)) << 4)) =
+            make_uint4(w[0], w[1], w[2], w[3]);
+      }
+      named_bar_sync(pair_bar, 64);
+      const int rr = lane >> 3, cc = lane & 7;
+      __nv_bfloat16* gp = p.out + sg * seg_stride + ((int64_t)row_base + q_tile0) * p.d + head * ATT_HD + cc * 8;
+#pragma unroll
+      for (int it = 0; it < 4; ++it) {
+        const int rw = sp * 16 + it * 4 + rr;
+        const uint4 x4 = *reinterpret_cast<const uint4*>(stage + rw * 128 + ((cc ^ (rw & 7)) << 4));
+        if (q_tile0 + rw < p.N) *reinterpret_cast<uint4*>(gp + (int64_t)rw * p.d) = x4;
+      }
+      if (sg + 1 < p.out_nseg) named_bar_sync(pair_bar, 64);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 8) {
+    tc_fence_after();
+    tmem_dealloc<512>(tmem_base);
+  }
+}
+
 int launch_attention_tc(const void* qkv_bf16, void* out, int out_nseg, int n_seq, int N, int n_heads, int hd,
                         cudaStream_t s, bool f16, const uint32_t* kmask) {
   AVD_REQUIRE(hd == ATT_HD, "tcgen05 attention kernel is built for head_dim 64");
@@ -580,6 +895,18 @@ int launch_attention_tc(const void* qkv_bf16, void* out, int out_nseg, int n_seq
   if (kind_skipped(KIND_ATTN_TC)) return 0;
   LaunchScope ls(KIND_ATTN_TC, s);
   AVD_REQUIRE(!f16 || out_nseg == 1, "the fp16 attention output has one segment");
+  if (N > ATT_BKV && options().attn_pipe != 0) {     // multi-block: the pipelined kernel, one 128-query tile per CTA
+    static const AttnFn pipe_kernels[2][2] = {{attn_pipe_kernel<false, false>, attn_pipe_kernel<false, true>},
+                                              {attn_pipe_kernel<true, false>, attn_pipe_kernel<true, true>}};
+    const AttnFn pf = pipe_kernels[f16 ? 1 : 0][kmask != nullptr ? 1 : 0];
+    AVD_TRY(ensure_dyn_smem(reinterpret_cast<const void*>(pf), AP_SMEM));
+    cfg.gridDim = dim3((N + ATT_BQ - 1) / ATT_BQ, n_heads, n_seq);
+    cfg.blockDim = dim3(AP_THREADS);
+    cfg.dynamicSmemBytes = AP_SMEM;
+    p.trace = nullptr;
+    AVD_CUDA(cudaLaunchKernelEx(&cfg, pf, tmQ, tmKV, p));
+    return 0;
+  }
   const AttnFn fn = kernels[(N <= ATT_BKV && options().attn_one) ? 1 : 0][f16 ? 1 : 0][kmask != nullptr ? 1 : 0];
   AVD_TRY(ensure_dyn_smem(reinterpret_cast<const void*>(fn), ATT_SMEM));   // once per device
   AVD_CUDA(cudaLaunchKernelEx(&cfg, fn, tmQ, tmKV, p));

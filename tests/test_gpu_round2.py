@@ -214,6 +214,15 @@ def test_attention_tcgen05_f16_template(dev, lib, n_seq, N):
     _attn_check(dev, lib, n_seq, N, True, 1.5e-3)
 
 
+@pytest.mark.parametrize("n_seq,N,f16", [(3, 445, True), (2, 193, False), (1, 2048, True), (2, 1000, False)])
+def test_attention_pipelined_kernel(dev, lib, n_seq, N, f16):
+    """attn_pipe_kernel (option attn_pipe, off by default: measured slower than attn_tc_kernel's multi-block path, see
+    its header): one query tile per CTA, S double-buffered in TMEM, S(j+2) and P V issued under the softmax of block j."""
+    from multimodal_diffusion_b200 import _lib
+    with _lib.option("attn_pipe", 1):
+        _attn_check(dev, lib, n_seq, N, f16, 1.5e-3 if f16 else 8e-3)
+
+
 @pytest.mark.parametrize("f16", [True, False])
 def test_attention_tcgen05_16k_tokens(dev, lib, f16):
     """configs[4]'s longest sequence: N = 16384 (86 key blocks)."""
