@@ -8,8 +8,8 @@ through the C ABI (avd_mmdt_blocks: tcgen05 GEMMs with fused RMSNorm-prologue / 
 epilogues + the joint-attention kernel).  Eval / no_grad only: this is the sampling path.
 
 ``precision``: "fp32" (6-pass split-bf16 tensor-core GEMMs + fp32 attention; rel-L2 ~1e-6 vs the reference),
-"bf16x3", "bf16" (the timed mode), or "f16" (fp16 operands at the same tensor-core rate: 3 more mantissa bits; the
-residual-stream operand carries a fixed 2^-8 scale so that it cannot overflow).  Default comes from $AVDIFF_B200_PRECISION, else "fp32".
+"bf16x3", "bf16", or "f16" (the mode bench.py times: fp16 operands at the same tensor-core rate as bf16 with 3 more
+mantissa bits; the residual-stream operand carries a fixed 2^-8 scale so that it cannot overflow).  Default comes from $AVDIFF_B200_PRECISION, else "fp32".
 """
 from __future__ import annotations
 
