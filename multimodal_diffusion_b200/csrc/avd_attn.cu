@@ -241,17 +241,17 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
       const int ch1 = min(nch, ch0 + 3);
       float* xm = xmax + ((ph * 2 + t) * 2) * 128;
       const int kv_n = (kv_valid + 15) & ~15;
-      if (leader) {                                 // S_t = Q_t K_j^T (S columns were drained before p_ready of j-1)
-        if (j == 0) mbar_wait(&bars[AB_Q], 0);
+      if (leader && j == 0) {                       // S_t = Q_t K_0^T (later blocks: issued right behind P V of the block before)
+        mbar_wait(&bars[AB_Q], 0);
         mbar_wait(&bars[AB_K], ph);
         tc_fence_after();
-        if (mark && j == 0) att_mark(trace, 2);
+        if (mark) att_mark(trace, 2);
         const uint32_t idesc_s = make_idesc_bf16(ATT_BQ, kv_n, 0, 0, F16);
 #pragma unroll
         for (int k = 0; k < ATT_HD / 16; ++k)
           umma_bf16_lh(tmem_base + t * 256, q_lo + 2 * k, k_lo + 2 * k, hi, idesc_s, k > 0 ? 1u : 0u);
         umma_commit(&bars[AB_S + t]);
-        if (mark && j == 0) att_mark(trace, 3);
+        if (mark) att_mark(trace, 3);
       }
       __syncwarp();
       mbar_wait(&bars[AB_S + t], ph);
@@ -440,6 +440,19 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
         }
         umma_commit(&bars[AB_O + t]);
         if (mark && j == 0) att_mark(trace, 4);
+        if (!ONE_BLOCK && j + 1 < nkv) {
+          // S_t(j+1) = Q_t K_{j+1}^T goes in right behind P V: the S columns were drained when P_j was staged (AB_P), and
+          // K_{j+1} was requested when the S MMAs of block j retired -- the tensor pipe runs it under this tile's O update
+          // instead of after it
+          const int kvn1 = (min(ATT_BKV, p.N - (j + 1) * ATT_BKV) + 15) & ~15;
+          mbar_wait(&bars[AB_K], ph ^ 1);
+          tc_fence_after();
+          const uint32_t idesc_s = make_idesc_bf16(ATT_BQ, kvn1, 0, 0, F16);
+#pragma unroll
+          for (int k = 0; k < ATT_HD / 16; ++k)
+            umma_bf16_lh(tmem_base + t * 256, q_lo + 2 * k, k_lo + 2 * k, hi, idesc_s, k > 0 ? 1u : 0u);
+          umma_commit(&bars[AB_S + t]);
+        }
       }
       __syncwarp();
       mbar_wait(&bars[AB_O + t], ph);
