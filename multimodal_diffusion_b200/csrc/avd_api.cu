@@ -179,6 +179,7 @@ static const OptionDesc kOptions[] = {
     {"ps_pair", "AVD_PS_PAIR", &Options::ps_pair, 1},
     {"ps_no256", "AVD_PS_NO256", &Options::ps_no256, 0},
     {"attn_poly", "AVD_ATTN_POLY", &Options::attn_poly, 0},
+    {"attn_small", "AVD_ATTN_SMALL", &Options::attn_small, 1},
     {"attn_pipe", "AVD_ATTN_PIPE", &Options::attn_pipe, 0},
     {"attn_one", "AVD_ATTN_ONE", &Options::attn_one, 1},
     {"chains", "AVD_CHAINS", &Options::chains, 1},

@@ -860,6 +860,354 @@ __global__ void __launch_bounds__(AP_THREADS, 1) attn_pipe_kernel(const __grid_c
   }
 }
 
+// =====================================================================================================
+// attn_small_kernel: one key block, N <= 136 (the 133-token joint sequence of the mvp configs), TWO CTAs per SM.
+//
+// attn_tc_kernel's single-block path is a latency chain (TMA round trip, S MMA, softmax, P V MMA, store: ~9700 cycles
+// with the tensor pipe active 9 % of the time) and its 182 KB of shared memory, 512 TMEM columns and 512 threads at 128
+// registers allow ONE CTA per SM.  Beyond one wave of (sequence, head) pairs -- A2V batch 64 is 1024 of them -- the SMs
+// then run 6.9 waves of chains back to back.  This kernel fits twice on an SM (111 KB, 256 TMEM columns, 256 threads), so
+// two chains overlap.  What made the footprint is the second query tile, which at N = 133 holds 5 rows: here those rows
+// do not go through the tensor core at all.  Warp w computes row 128 + w on CUDA cores -- q . K^T against the swizzled K
+// tile while the S MMA of the full tile is in flight, the softmax in registers, p . V against the V tile while the P V
+// MMA runs -- 5 x 133 x 64 MACs twice, in fp32.
+//   warps 0..7  softmax / output of the 128-row tile exactly as tile 0 of attn_tc_kernel (thread = row, the two warps of a
+//               TMEM lane quadrant split the key columns); lane 0 of warp 0 issues the TMA loads and the two MMAs
+// =====================================================================================================
+constexpr int AS_THREADS = 256;
+constexpr int AS_KV_ROWS = 144;                        // round16(136)
+constexpr int AS_KV_BYTES = AS_KV_ROWS * ATT_HD * 2;   // 18 KB
+constexpr int AS_MAX_THIN = 8;
+constexpr int AS_XCHG_BYTES = 4 * 128 * 4;             // row max [2 halves][128], row sum [2 halves][128]
+constexpr int AS_THIN_BYTES = AS_MAX_THIN * 160 * 4;   // the thin rows' probabilities [8][160] fp32
+constexpr int AS_SMEM = ATT_Q_BYTES + 2 * AS_KV_BYTES + ATT_P_BYTES + 1024 + AS_XCHG_BYTES + AS_THIN_BYTES + 256;
+enum { SB_Q = 0, SB_K = 1, SB_V = 2, SB_S = 3, SB_P = 4, SB_O = 5, SB_COUNT = 6 };
+
+template <bool F16>
+__device__ __forceinline__ float2 cvt16x2(uint32_t w) {
+  if (F16) return __half22float2(*reinterpret_cast<const __half2*>(&w));
+  return make_float2(__uint_as_float(w << 16), __uint_as_float(w & 0xffff0000u));
+}
+
+template <bool F16, bool MASKED>
+__global__ void __launch_bounds__(AS_THREADS, 2) attn_small_kernel(const __grid_constant__ CUtensorMap tmQ,
+                                                                   const __grid_constant__ CUtensorMap tmQ8,
+                                                                   const __grid_constant__ CUtensorMap tmKV,
+                                                                   const AttnParams p) {
+  extern __shared__ __align__(1024) uint8_t as_smem[];
+  uint8_t* smem = as_smem;
+  if ((smem_u32(smem) & 1023u) != 0) __trap();
+  uint8_t* sQ = smem;                                  // 128 rows (later: output staging)
+  uint8_t* sK = sQ + ATT_Q_BYTES;
+  uint8_t* sV = sK + AS_KV_BYTES;
+  uint8_t* sP = sV + AS_KV_BYTES;                      // 3 atoms of [128 rows][64 keys]
+  uint8_t* sQ1 = sP + ATT_P_BYTES;                     // the thin rows: [8][64] 16-bit, 128B-swizzled
+  float* xmax = reinterpret_cast<float*>(sQ1 + 1024);
+  float* xsum = xmax + 2 * 128;
+  float* thin_p = xsum + 2 * 128;                      // [8][160]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(thin_p) + AS_THIN_BYTES);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + SB_COUNT);
+
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5, lane = tid & 31;
+  const int head = blockIdx.y;
+  const int seq = blockIdx.z;
+  const int row_base = seq * p.N;
+  const int colQ = head * ATT_HD, colK = p.d + head * ATT_HD, colV = 2 * p.d + head * ATT_HD;
+  const int rows1 = p.N > ATT_BQ ? p.N - ATT_BQ : 0;   // thin rows (<= 8)
+  const int kv_valid = p.N;
+  const int kv_n = (kv_valid + 15) & ~15;
+  const int nch = (kv_valid + 31) >> 5;                // <= 5
+  const float sc = p.scale_log2e;
+  const uint32_t* kmask = MASKED ? p.kmask + (size_t)blockIdx.z * p.kmask_words : nullptr;
+
+  if (warp == 1) {
+    if (lane < SB_COUNT) mbar_init(&bars[lane], lane == SB_P ? 8 : 1);
+    fence_barrier_init();
+  } else if (warp == 2 && lane == 0) {
+    tma_prefetch_desc(&tmQ);
+    tma_prefetch_desc(&tmKV);
+    tma_prefetch_desc(&tmQ8);
+  }
+  if (warp == 0) tmem_alloc<256>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_launch_dependents();
+
+  const int sp = warp >> 2, quad = warp & 3;
+  const int r = quad * 32 + lane;
+  const uint32_t tmem_S = tmem_base + ((uint32_t)(quad * 32) << 16);
+  const uint32_t tmem_O = tmem_S + ATT_BKV + sp * 32;
+  const uint32_t pair_bar = 1 + quad;
+  const bool leader = tid == 0;
+  const uint32_t hi = smem_desc_hi_sw128(1024);
+  if (leader) {
+    pdl_wait();
+    mbar_expect_tx(&bars[SB_Q], ATT_Q_BYTES + (rows1 > 0 ? 1024 : 0));
+    tma_load_3d(sQ, &tmQ, &bars[SB_Q], colQ, row_base, 0);
+    if (rows1 > 0) tma_load_3d(sQ1, &tmQ8, &bars[SB_Q], colQ, row_base + ATT_BQ, 0);
+    mbar_expect_tx(&bars[SB_K], AS_KV_BYTES);
+    tma_load_3d(sK, &tmKV, &bars[SB_K], colK, row_base, 0);
+    mbar_expect_tx(&bars[SB_V], AS_KV_BYTES);
+    tma_load_3d(sV, &tmKV, &bars[SB_V], colV, row_base, 0);
+    mbar_wait(&bars[SB_Q], 0);
+    mbar_wait(&bars[SB_K], 0);
+    tc_fence_after();
+    const uint32_t idesc_s = make_idesc_bf16(ATT_BQ, kv_n, 0, 0, F16);
+    const uint32_t q_lo = smem_desc_lo_sw128(smem_u32(sQ), 16);
+    const uint32_t k_lo = smem_desc_lo_sw128(smem_u32(sK), 16);
+#pragma unroll
+    for (int k = 0; k < ATT_HD / 16; ++k)
+      umma_bf16_lh(tmem_base, q_lo + 2 * k, k_lo + 2 * k, hi, idesc_s, k > 0 ? 1u : 0u);
+    umma_commit(&bars[SB_S]);
+  }
+  __syncwarp();
+
+  // ---- thin rows, part 1 (under the S MMA): s = q . K^T on CUDA cores, softmax in registers, p -> smem
+  float thin_inv_l = 0.0f;
+  const bool thin_row = warp < rows1;
+  if (thin_row) {
+    mbar_wait(&bars[SB_Q], 0);
+    mbar_wait(&bars[SB_K], 0);
+    float2 q[32];                                      // the row's 64 query values
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+      const uint4 u = *reinterpret_cast<const uint4*>(sQ1 + warp * 128 + ((c ^ (warp & 7)) << 4));
+      q[4 * c] = cvt16x2<F16>(u.x); q[4 * c + 1] = cvt16x2<F16>(u.y);
+      q[4 * c + 2] = cvt16x2<F16>(u.z); q[4 * c + 3] = cvt16x2<F16>(u.w);
+    }
+    float sv[5];
+    float mx = -INFINITY;
+#pragma unroll
+    for (int i = 0; i < 5; ++i) {
+      const int k = lane + 32 * i;
+      float a0 = 0.0f, a1 = 0.0f, a2 = 0.0f, a3 = 0.0f;   // four independent chains: the dot product is latency, not issue, bound
+      bool ok = k < kv_valid;
+      if (MASKED && ok) ok = !((kmask[k >> 5] >> (k & 31)) & 1u);
+      if (k < kv_n) {
+        const uint8_t* kr = sK + k * 128;
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+          const uint4 u = *reinterpret_cast<const uint4*>(kr + ((c ^ (k & 7)) << 4));
+          const float2 a = cvt16x2<F16>(u.x), b = cvt16x2<F16>(u.y), c2 = cvt16x2<F16>(u.z), d = cvt16x2<F16>(u.w);
+          a0 = fmaf(q[4 * c].x, a.x, a0); a1 = fmaf(q[4 * c].y, a.y, a1);
+          a2 = fmaf(q[4 * c + 1].x, b.x, a2); a3 = fmaf(q[4 * c + 1].y, b.y, a3);
+          a0 = fmaf(q[4 * c + 2].x, c2.x, a0); a1 = fmaf(q[4 * c + 2].y, c2.y, a1);
+          a2 = fmaf(q[4 * c + 3].x, d.x, a2); a3 = fmaf(q[4 * c + 3].y, d.y, a3);
+        }
+      }
+      const float acc = (a0 + a1) + (a2 + a3);
+      sv[i] = ok ? acc : -INFINITY;
+      mx = fmaxf(mx, sv[i]);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    const float m_use = mx == -INFINITY ? 0.0f : mx;
+    float l = 0.0f;
+#pragma unroll
+    for (int i = 0; i < 5; ++i) {
+      const int k = lane + 32 * i;
+      const float pv = sv[i] == -INFINITY ? 0.0f : ex2_approx((sv[i] - m_use) * sc);
+      l += pv;
+      thin_p[warp * 160 + k] = pv;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) l += __shfl_xor_sync(0xffffffffu, l, o);
+    thin_inv_l = 1.0f / l;
+    __syncwarp();
+  }
+
+  // ---- the 128-row tile: single-pass softmax of this thread's chunks (as attn_tc_kernel's one-block path)
+  mbar_wait(&bars[SB_S], 0);
+  tc_fence_after();
+  float l_blk = 0.0f;
+  {
+    const int ch0 = sp * 3;
+    auto valid_bits = [&](int ch, int lim) -> uint32_t {
+      uint32_t v = lim >= 32 ? 0xffffffffu : (lim > 0 ? ((1u << lim) - 1u) : 0u);
+      if (MASKED && lim > 0) v &= ~kmask[ch];
+      return v;
+    };
+    uint32_t x[3][32];
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+      if (i == 0 || ch0 + i < nch) tmem_ld_32x32(tmem_S + (ch0 + i) * 32, x[i]);
+    tmem_ld_wait();
+    float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      const uint32_t vb = valid_bits(ch0 + i, kv_valid - (ch0 + i) * 32);
+      if (vb == 0xffffffffu) {
+#pragma unroll
+        for (int c = 0; c < 32; ++c) mx[c & 3] = fmaxf(mx[c & 3], __uint_as_float(x[i][c]));
+      } else if (vb != 0u) {
+#pragma unroll
+        for (int c = 0; c < 32; ++c)
+          mx[c & 3] = fmaxf(mx[c & 3], ((vb >> c) & 1u) ? __uint_as_float(x[i][c]) : -INFINITY);
+      }
+    }
+    const float m_part = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
+    xmax[sp * 128 + r] = m_part;
+    named_bar_sync(pair_bar, 64);
+    const float m_new = fmaxf(m_part, xmax[(sp ^ 1) * 128 + r]);
+    const float m_sc = (m_new == -INFINITY ? 0.0f : m_new) * sc;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      const int ch = ch0 + i;
+      const int lim = kv_valid - ch * 32;
+      if (lim > -16) {
+        float l0 = 0.0f, l1 = 0.0f;
+        uint32_t w[16];
+        const uint32_t vb = valid_bits(ch, lim);
+        float e[32];
+        ex2_chunk(x[i], sc, -m_sc, e);
+        if (vb == 0xffffffffu) {
+#pragma unroll
+          for (int c = 0; c < 32; c += 2) {
+            l0 += e[c];
+            l1 += e[c + 1];
+            w[c >> 1] = F16 ? pack_f16x2(e[c], e[c + 1]) : pack_bf16x2(e[c], e[c + 1]);
+          }
+        } else {
+#pragma unroll
+          for (int c = 0; c < 32; c += 2) {
+            const float p0 = ((vb >> c) & 1u) ? e[c] : 0.0f;
+            const float p1 = ((vb >> (c + 1)) & 1u) ? e[c + 1] : 0.0f;
+            l0 += p0;
+            l1 += p1;
+            w[c >> 1] = F16 ? pack_f16x2(p0, p1) : pack_bf16x2(p0, p1);
+          }
+        }
+        l_blk += l0 + l1;
+        uint8_t* atom = sP + (ch >> 1) * ATT_Q_BYTES + r * 128;
+        const int q_base = (ch & 1) * 4;
+#pragma unroll
+        for (int q4 = 0; q4 < 4; ++q4)
+          *reinterpret_cast<uint4*>(atom + (((q_base + q4) ^ (r & 7)) << 4)) =
+              make_uint4(w[4 * q4], w[4 * q4 + 1], w[4 * q4 + 2], w[4 * q4 + 3]);
+      }
+    }
+  }
+  fence_async_smem();
+  tc_fence_before();
+  __syncwarp();
+  if (lane == 0) mbar_arrive(&bars[SB_P]);
+  if (leader) {                                        // O = P V
+    mbar_wait(&bars[SB_P], 0);
+    mbar_wait(&bars[SB_V], 0);
+    tc_fence_after();
+    const uint32_t idesc_o = make_idesc_bf16(ATT_BQ, ATT_HD, 0, 1, F16);   // B = V is MN-major
+    const uint32_t p_lo = smem_desc_lo_sw128(smem_u32(sP), 16);
+    const uint32_t v_lo = smem_desc_lo_sw128(smem_u32(sV), 16);
+    const int ksteps = kv_n >> 4;
+    for (int ks = 0; ks < ksteps; ++ks) {
+      const uint32_t pa = p_lo + (((ks >> 2) * ATT_Q_BYTES + (ks & 3) * 32) >> 4);
+      const uint32_t va = v_lo + ((ks * 16 * 128) >> 4);
+      umma_bf16_lh(tmem_base + ATT_BKV, pa, va, hi, idesc_o, ks > 0 ? 1u : 0u);
+    }
+    umma_commit(&bars[SB_O]);
+  }
+  __syncwarp();
+
+  // ---- thin rows, part 2 (under the P V MMA): o = p . V, two output columns per lane, straight to global
+  if (thin_row) {
+    mbar_wait(&bars[SB_V], 0);
+    float oa[4] = {0.0f, 0.0f, 0.0f, 0.0f}, ob[4] = {0.0f, 0.0f, 0.0f, 0.0f};    // four independent chains over the keys
+    const float* pr = thin_p + warp * 160;                 // (entries past kv_valid are zero probabilities)
+    for (int k = 0; k < kv_n; k += 4) {
+#pragma unroll
+      for (int u4 = 0; u4 < 4; ++u4) {
+        const int kk = k + u4;
+        const float pk = pr[kk];
+        const uint32_t u = *reinterpret_cast<const uint32_t*>(sV + kk * 128 + (((lane >> 2) ^ (kk & 7)) << 4) + (lane & 3) * 4);
+        const float2 v2 = cvt16x2<F16>(u);
+        oa[u4] = fmaf(pk, v2.x, oa[u4]);
+        ob[u4] = fmaf(pk, v2.y, ob[u4]);
+      }
+    }
+    float o0 = ((oa[0] + oa[1]) + (oa[2] + oa[3])) * thin_inv_l;
+    float o1 = ((ob[0] + ob[1]) + (ob[2] + ob[3])) * thin_inv_l;
+    const int64_t seg_stride = p.M * (int64_t)p.d;
+    const int64_t off = ((int64_t)row_base + ATT_BQ + warp) * p.d + head * ATT_HD + 2 * lane;
+    for (int sg = 0; sg < p.out_nseg; ++sg) {
+      uint32_t w;
+      if (p.out_nseg == 1) {
+        w = F16 ? pack_f16x2(o0, o1) : pack_bf16x2(o0, o1);
+      } else {
+        const __nv_bfloat16 h0 = __float2bfloat16_rn(o0), h1 = __float2bfloat16_rn(o1);
+        o0 -= __bfloat162float(h0);
+        o1 -= __bfloat162float(h1);
+        w = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
+      }
+      *reinterpret_cast<uint32_t*>(p.out + sg * seg_stride + off) = w;
+    }
+  }
+
+  // ---- O of the 128-row tile: normalise, stage, store
+  mbar_wait(&bars[SB_O], 0);
+  tc_fence_after();
+  float o_acc[32];
+  {
+    uint32_t xo[32];
+    tmem_ld_32x32(tmem_O, xo);
+    tmem_ld_wait();
+#pragma unroll
+    for (int c = 0; c < 32; ++c) o_acc[c] = __uint_as_float(xo[c]);
+  }
+  xsum[sp * 128 + r] = l_blk;
+  named_bar_sync(pair_bar, 64);
+  const float inv_l = 1.0f / (l_blk + xsum[(sp ^ 1) * 128 + r]);
+  {
+    const int64_t seg_stride = p.M * (int64_t)p.d;
+    uint8_t* stage = sQ + quad * 32 * 128;             // Q is retired: the S MMA has executed
+    const int q_tile0 = quad * 32;
+    float rem[32];
+#pragma unroll
+    for (int c = 0; c < 32; ++c) rem[c] = o_acc[c] * inv_l;
+    for (int sg = 0; sg < p.out_nseg; ++sg) {
+#pragma unroll
+      for (int v4 = 0; v4 < 4; ++v4) {
+        uint32_t w[4];
+        if (p.out_nseg == 1) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            w[k] = F16 ? pack_f16x2(rem[v4 * 8 + k * 2], rem[v4 * 8 + k * 2 + 1]) : pack_bf16x2(rem[v4 * 8 + k * 2], rem[v4 * 8 + k * 2 + 1]);
+        } else {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const int c = v4 * 8 + k * 2;
+            const __nv_bfloat16 h0 = __float2bfloat16_rn(rem[c]);
+            const __nv_bfloat16 h1 = __float2bfloat16_rn(rem[c + 1]);
+            rem[c] -= __bfloat162float(h0);
+            rem[c + 1] -= __bfloat162float(h1);
+            w[k] = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
+          }
+        }
+        *reinterpret_cast<uint4*>(stage + lane * 128 + (((sp * 4 + v4) ^ (lane & 7)) << 4)) =
+            make_uint4(w[0], w[1], w[2], w[3]);
+      }
+      named_bar_sync(pair_bar, 64);
+      const int rr = lane >> 3, cc = lane & 7;
+      __nv_bfloat16* gp = p.out + sg * seg_stride + ((int64_t)row_base + q_tile0) * p.d + head * ATT_HD + cc * 8;
+#pragma unroll
+      for (int it = 0; it < 4; ++it) {
+        const int rw = sp * 16 + it * 4 + rr;
+        const uint4 x4 = *reinterpret_cast<const uint4*>(stage + rw * 128 + ((cc ^ (rw & 7)) << 4));
+        if (q_tile0 + rw < p.N) *reinterpret_cast<uint4*>(gp + (int64_t)rw * p.d) = x4;
+      }
+      if (sg + 1 < p.out_nseg) named_bar_sync(pair_bar, 64);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    tmem_dealloc<256>(tmem_base);
+  }
+}
+
 int launch_attention_tc(const void* qkv_bf16, void* out, int out_nseg, int n_seq, int N, int n_heads, int hd,
                         cudaStream_t s, bool f16, const uint32_t* kmask) {
   AVD_REQUIRE(hd == ATT_HD, "tcgen05 attention kernel is built for head_dim 64");
@@ -908,6 +1256,31 @@ int launch_attention_tc(const void* qkv_bf16, void* out, int out_nseg, int n_seq
   if (kind_skipped(KIND_ATTN_TC)) return 0;
   LaunchScope ls(KIND_ATTN_TC, s);
   AVD_REQUIRE(!f16 || out_nseg == 1, "the fp16 attention output has one segment");
+  // single block, at most 8 rows in the second query tile, more (sequence, head) pairs than SMs: two CTAs per SM
+  const int small_opt = options().attn_small;
+  int sms = 148;
+  {
+    int dev = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  }
+  if (small_opt != 0 && N <= ATT_BQ + AS_MAX_THIN && ((int64_t)n_heads * n_seq > sms || small_opt == 2)) {
+    using SmallFn = void (*)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const AttnParams);
+    static const SmallFn small_kernels[2][2] = {{attn_small_kernel<false, false>, attn_small_kernel<false, true>},
+                                                {attn_small_kernel<true, false>, attn_small_kernel<true, true>}};
+    const SmallFn sf = small_kernels[f16 ? 1 : 0][kmask != nullptr ? 1 : 0];
+    CUtensorMap tmQ8, tmKVs;
+    AVD_TRY(get_tensor_map_3d(qkv_bf16, 2, (uint64_t)3 * d, (uint64_t)M, 1, (uint64_t)3 * d * 2, (uint64_t)M * 3 * d * 2,
+                              ATT_HD, AS_MAX_THIN, &tmQ8));
+    AVD_TRY(get_tensor_map_3d(qkv_bf16, 2, (uint64_t)3 * d, (uint64_t)M, 1, (uint64_t)3 * d * 2, (uint64_t)M * 3 * d * 2,
+                              ATT_HD, AS_KV_ROWS, &tmKVs));
+    AVD_TRY(ensure_dyn_smem(reinterpret_cast<const void*>(sf), AS_SMEM));
+    cfg.gridDim = dim3(1, n_heads, n_seq);
+    cfg.blockDim = dim3(AS_THREADS);
+    cfg.dynamicSmemBytes = AS_SMEM;
+    p.trace = nullptr;
+    AVD_CUDA(cudaLaunchKernelEx(&cfg, sf, tmQ, tmQ8, tmKVs, p));
+    return 0;
+  }
   if (N > ATT_BKV && options().attn_pipe != 0) {     // multi-block: the pipelined kernel, one 128-query tile per CTA
     static const AttnFn pipe_kernels[2][2] = {{attn_pipe_kernel<false, false>, attn_pipe_kernel<false, true>},
                                               {attn_pipe_kernel<true, false>, attn_pipe_kernel<true, true>}};

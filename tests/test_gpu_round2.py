@@ -223,6 +223,39 @@ def test_attention_pipelined_kernel(dev, lib, n_seq, N, f16):
         _attn_check(dev, lib, n_seq, N, f16, 1.5e-3 if f16 else 8e-3)
 
 
+@pytest.mark.parametrize("n_seq,N,f16", [(2, 133, True), (3, 133, False), (2, 136, True), (1, 128, False), (2, 100, True),
+                                         (20, 133, True)])
+def test_attention_small_kernel(dev, lib, n_seq, N, f16):
+    """attn_small_kernel (two CTAs per SM, N <= 136: the rows past 128 run on CUDA cores), forced with attn_small = 2; the
+    last case (160 (sequence, head) pairs > SM count) takes it by the default rule."""
+    from multimodal_diffusion_b200 import _lib
+    with _lib.option("attn_small", 2 if n_seq < 20 else 1):
+        _attn_check(dev, lib, n_seq, N, f16, 1.5e-3 if f16 else 8e-3)
+
+
+def test_attention_small_kernel_with_key_mask(dev, lib):
+    """key_padding_mask through attn_small_kernel: the tile rows (TMEM path) and the thin rows (CUDA-core path) must ignore
+    the same keys as the two-tile kernel."""
+    from multimodal_diffusion_b200 import _lib, packing
+    H, hd, n_seq, N = 8, 64, 3, 133
+    qkv = (randn(5, n_seq * N, 3 * H * hd) * 1.5).to(torch.float16).to(dev)
+    mask = torch.zeros(n_seq, N, dtype=torch.bool)
+    mask[0, 100:] = True
+    mask[1, 5:40] = True
+    mask[2, ::3] = True
+    bits = packing.pack_key_padding_mask(mask.to(dev))
+    outs = []
+    for opt in (0, 2):
+        out = torch.zeros(1, n_seq * N, H * hd, device=dev, dtype=torch.float16)
+        with _lib.option("attn_small", opt):
+            _lib.check(lib.avd_attention_masked(qkv.data_ptr(), 0, out.data_ptr(), _lib.AVD_PREC_F16, n_seq, N, H, hd,
+                                                bits.data_ptr(), _lib.stream_ptr()))
+        torch.cuda.synchronize()
+        outs.append(out.float().cpu())
+    assert torch.isfinite(outs[1]).all()
+    assert rel_l2(outs[1], outs[0]) < 1.5e-3
+
+
 @pytest.mark.parametrize("f16", [True, False])
 def test_attention_tcgen05_16k_tokens(dev, lib, f16):
     """configs[4]'s longest sequence: N = 16384 (86 key blocks)."""
