@@ -59,24 +59,6 @@ __device__ __forceinline__ void sts128u(uint8_t* p, uint32_t a, uint32_t b, uint
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(smem_u32(p)), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
 
-// GELU with erf from Abramowitz-Stegun 7.1.26 (|erf error| <= 1.5e-7): 2 MUFU + ~12 FMA-pipe instructions instead
-// of erff's ~40.  Used in bf16 mode only, where the result is rounded to bf16 (2^-9) anyway.
-__device__ __forceinline__ float gelu_fast(float x) {
-  const float y = fabsf(x) * 0.70710678118654752440f;
-  float t;
-  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, y, 1.0f)));
-  float pl = fmaf(t, 1.061405429f, -1.453152027f);
-  pl = fmaf(pl, t, 1.421413741f);
-  pl = fmaf(pl, t, -0.284496736f);
-  pl = fmaf(pl, t, 0.254829592f);
-  pl *= t;
-  float e;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(-y * y * 1.4426950408889634f));
-  const float erf_abs = fmaf(-pl, e, 1.0f);
-  const float h = 0.5f * x;
-  return fmaf(fabsf(h), erf_abs, h);          // 0.5 x (1 + sign(x) erf|.|) = h + |h| erf_abs
-}
-
 // GELU of two values in f16x2 arithmetic, tanh form with the hardware tanh.approx.f16x2, packed as bf16x2.  Used only
 // where the result is stored as ONE bf16 segment (fc1 of the bf16 mode): |tanh form - erf form| <= 4.8e-4 and the
 // f16 arithmetic (2^-11) are both below the bf16 quantum (2^-9) of the stored value; rms over N(0,1) inputs 3e-4 vs
