@@ -17,10 +17,10 @@
 //   warps 2,3   MMA issuers of pipeline 0 / 1 (warp 2 also owns the TMEM allocation): one lane issues
 //               tcgen05.mma.cta_group::1.kind::f16 (M=128, N=BN, K=16) x 4 per 64-wide k-block; tcgen05.commit
 //               releases the smem stage / signals the epilogue
-//   warps 4..7  epilogue: tcgen05.ld 32 lanes x 32 columns of both accumulators -> registers; thread == output row
+//   all 8 warps epilogue: tcgen05.ld 32 lanes x 32 columns of both accumulators -> registers; thread == output row
 //               v = (acc0+acc1) * rinv(row) + bias (+ resid) [gelu]; results are staged in 128B-swizzled smem boxes
-//               and leave through TMA stores (fp32 and/or bf16 segments); per-row partial sums of squares feed the
-//               NEXT GEMM's RMSNorm row scale.
+//               and leave with 16-byte coalesced stores (fp32 and/or bf16 segments; bulk tensor stores were measured
+//               equal here); per-row partial sums of squares feed the NEXT GEMM's RMSNorm row scale.
 //
 // Precision modes are realised by the k-loop: for mode p the operands are stored as hi/(mid/)lo bf16
 // segments and the loop runs over a list of (A segment, W segment) pairs, smallest products first, all
