@@ -420,11 +420,12 @@ int launch_gemm_ps(const avd_gemm_args& g, GemmParams p, int nseg, int force_bn,
   if (p.trace != nullptr || bn < 64 || options().gemm_generic) mode = 0;
 #endif
   // CTA pairs (avd_gemm_ps2.cu): the 256-wide tiles on two SMs each, half of the weight tile per SM
-  // Measured (tools/kbench.py --M 32768, AVD_PS_PAIR = 0 / 1): the pair wins where the k-loop is long (fc2, K = 2048:
-  // 91.9 -> 83.8 us) and loses a little at K = 512 (QKV 51.7 -> 55.3 us: per tile the leader's one issuing thread also
-  // waits for the peer's epilogue warps and for both CTAs' loads), so by default it takes only GEMMs of >= 16 k-blocks.
+  // Measured (tools/kbench.py --M 32768, AVD_PS_PAIR = 0 / 1): QKV 51.7 -> 47.2 us (1092 TFLOP/s), fc1 83.1 -> 77.5,
+  // fc2 91.9 -> 83.9, out-proj 41.2 -> 40.6.  (With a RELEASE at cluster scope on the peer's buffer hand-back the pair
+  // was 7 % slower than the single-CTA kernel at K = 512: every epilogue warp then waited for its outstanding global
+  // stores once per tile; the arrival is relaxed now, avd_gemm_ps2.cu.)
   const int pair_opt = options().ps_pair;
-  if (pair_opt != 0 && g.N % 256 == 0 && (bn == 256 || pair_opt == 2) && (ipt >= 16 || pair_opt == 2)) {
+  if (pair_opt != 0 && g.N % 256 == 0 && (bn == 256 || pair_opt == 2)) {
     const int rc = launch_gemm_ps2(g, p, nseg, mode, sms, s);
     if (rc != 0) return rc < 0 ? rc : 0;
   }

@@ -36,8 +36,10 @@ struct P2Plan {
   int f32_off, bf_off, tail_off;
 };
 
+// (relaxed: the arrival hands back a TMEM buffer whose reads were ordered by tcgen05.wait::ld + tcgen05.fence; a
+// release at cluster scope makes the warp wait for its outstanding global stores first, once per tile and warp)
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+  asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 
 template <int MODE>

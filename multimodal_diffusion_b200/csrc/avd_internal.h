@@ -157,8 +157,8 @@ struct Options {
   int gemm_pair;       // AVD_GEMM_PAIR      cta_group::2 variant of the one-tile kernel (0 off, 1 specialised, 2 all)
   int ps_max_stages;   // AVD_PS_MAX_STAGES  ring depth cap of the persistent kernel (0 = its maximum)
   int ps_epi_cycles;   // AVD_PS_EPI_CYCLES  epilogue constant of the tile-width model (0 = built in)
-  int ps_pair;         // AVD_PS_PAIR        persistent kernel on CTA pairs (cta_group::2, avd_gemm_ps2.cu): 0 off, 1 (default) for
-                       //                    256-wide tiles with >= 16 k-blocks, 2 for every GEMM whose N is a multiple of 256
+  int ps_pair;         // AVD_PS_PAIR        persistent kernel on CTA pairs (cta_group::2, avd_gemm_ps2.cu): 0 off, 1 (default) wherever
+                       //                    the tile-width model picks 256-wide tiles, 2 for every GEMM whose N is a multiple of 256
   int ps_no256;        // AVD_PS_NO256       1 = no 256-wide column-split tiles
   int attn_poly;       // AVD_ATTN_POLY      polynomial exp2 share of the multi-block attention path
   int attn_small;      // AVD_ATTN_SMALL     1 (default) = two-CTAs-per-SM kernel (attn_small_kernel) for N <= 136 when there are more
