@@ -406,7 +406,7 @@ if (f16_out) {
   }
 
   tc_fence_before();
-  if (PAIR) cluster_sync_all(); else __syncthreads();   // neither CTA of a pair may retire while the other still drains
+  if (PAIR) cluster_sync_relaxed(); else __syncthreads();   // neither CTA of a pair may retire while the other still drains
   if (warp == 2) {
     tc_fence_after();
     if (PAIR) tmem_dealloc_2cta<TMEM_COLS>(tmem_acc); else tmem_dealloc<TMEM_COLS>(tmem_acc);

@@ -210,7 +210,7 @@ __global__ void __launch_bounds__(P2_THREADS, 1) gemm_ps2_kernel(const __grid_co
 
   __syncwarp();   // lanes 1..31 of the role warps wait here for their lane 0
   tc_fence_before();
-  cluster_sync_all();   // neither CTA of a pair may retire while the other still signals its barriers or runs MMAs on its smem
+  cluster_sync_relaxed();   // neither CTA of a pair may retire while the other still signals its barriers or runs MMAs on its smem
   if (warp == 2) {
     tc_fence_after();
     tmem_dealloc_2cta<TMEM_COLS>(tmem_base);
