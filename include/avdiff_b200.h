@@ -345,6 +345,18 @@ int avd_audio_decode(const float* z, float* wav, float* scratch, int B, int Ca, 
                      const float* w_from, const float* b_from, const float* w_s0, const float* b_s0, const float* w_s2,
                      const float* b_s2, const float* w_s4, const float* b_s4, void* stream);
 
+/* avd_audio_decode without caller scratch and without any allocation: the intermediate activation lives in a
+ * file-scope device array of AVD_AUDIO_DECODE_STATIC_MAX_BYTES that every GPU loading the library holds until exit.
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call
+ * cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  Calls no cudaMalloc / cudaFree /
+ * allocating library routine.  Returns -1 with a message when B*H*Fa*hop*4 exceeds the limit.  All calls on a device
+ * share the one array: calls that overlap on the GPU (different streams) race -- serialise them.  The array keeps the
+ * previous call's contents; nothing in it has to start at zero (the first kernel writes all that the second reads). */
+#define AVD_AUDIO_DECODE_STATIC_MAX_BYTES (16 * 1024 * 1024)
+int avd_audio_decode_static(const float* z, float* wav, int B, int Ca, int Fa, int H, int hop, int K,
+                            const float* w_from, const float* b_from, const float* w_s0, const float* b_s0,
+                            const float* w_s2, const float* b_s2, const float* w_s4, const float* b_s4, void* stream);
+
 #define AVD_VAE_MAX_BLOCKS 8
 /* VideoVAE parameters (avdiff/models/encoders/vae_video3d.py:87-127), fp32 device pointers in the module's layouts:
  * conv weights [64,Cin,3,3,3], GroupNorm weight / bias [64], 1x1x1 convs [Cout,Cin,1,1,1]. */

@@ -26,6 +26,7 @@ AVD_TARGET_AUDIO = 1
 AVD_MAX_LAYERS = 64
 AVD_MAX_SHARED = 8
 AVD_CHAIN_FLAG_BYTES = 2560
+AVD_AUDIO_DECODE_STATIC_MAX_BYTES = 16 * 1024 * 1024   # include/avdiff_b200.h
 
 PRECISIONS = {"bf16": AVD_PREC_BF16, "f16": AVD_PREC_F16, "bf16x3": AVD_PREC_BF16X3, "fp32": AVD_PREC_FP32}
 
@@ -165,6 +166,7 @@ _SIGNATURES = {
     "avd_audio_encode": (_I, [fp, fp, _I, _I, _I, _I, _I, _I, fp, fp, fp, fp, fp, fp, vp]),
     "avd_audio_decode_scratch_bytes": (C.c_int64, [_I, _I, _I, _I]),
     "avd_audio_decode": (_I, [fp, fp, fp, _I, _I, _I, _I, _I, _I, fp, fp, fp, fp, fp, fp, fp, fp, vp]),
+    "avd_audio_decode_static": (_I, [fp, fp, _I, _I, _I, _I, _I, _I, fp, fp, fp, fp, fp, fp, fp, fp, vp]),
     "avd_vae_scratch_bytes": (C.c_int64, [_I, _I, _I, _I]),
     "avd_video_encode": (_I, [C.POINTER(VaeWeights), fp, fp, vp, _I, _I, _I, _I, vp]),
     "avd_video_decode": (_I, [C.POINTER(VaeWeights), fp, fp, vp, _I, _I, _I, _I, _I, _I, _I, vp]),

@@ -16,6 +16,9 @@
 #include "avd_internal.h"
 #include "avd_ptx.cuh"
 
+#include <mutex>
+#include <string>
+
 namespace avd {
 
 constexpr int AC_THREADS = 256;
@@ -297,3 +300,44 @@ int avd_audio_decode(const float* z, float* wav, float* scratch, int B, int Ca, 
 }
 
 }  // extern "C"
+
+// ---- allocation-free variant of the audio decoder -----------------------------------------------------------------
+// The one intermediate of avd_audio_decode (the [B,H,Fa*hop] fp32 activation between its two kernels) lives in a
+// file-scope device array instead of caller memory.  Every GPU that loads the library holds these 16 MiB until exit.
+// In HOST code the name below is only a stand-in for the symbol: the device address comes from cudaGetSymbolAddress,
+// looked up once per device (with that device current) and cached.
+static __device__ __align__(256) float g_audio_decode_static_scratch[AVD_AUDIO_DECODE_STATIC_MAX_BYTES / 4];
+
+static int audio_decode_static_ptr(float** out) {
+  constexpr int MAX_DEV = 64;
+  static std::mutex mu;
+  static float* ptrs[MAX_DEV] = {};
+  int dev = 0;
+  AVD_CUDA(cudaGetDevice(&dev));
+  AVD_REQUIRE(dev >= 0 && dev < MAX_DEV, "device ordinal beyond the static-scratch table");
+  std::lock_guard<std::mutex> lk(mu);
+  if (ptrs[dev] == nullptr) {
+    void* p = nullptr;
+    AVD_CUDA(cudaGetSymbolAddress(&p, g_audio_decode_static_scratch));
+    AVD_REQUIRE(p != nullptr, "cudaGetSymbolAddress returned a null scratch address");
+    ptrs[dev] = static_cast<float*>(p);
+  }
+  *out = ptrs[dev];
+  return 0;
+}
+
+extern "C" int avd_audio_decode_static(const float* z, float* wav, int B, int Ca, int Fa, int H, int hop, int K,
+                                       const float* w_from, const float* b_from, const float* w_s0, const float* b_s0,
+                                       const float* w_s2, const float* b_s2, const float* w_s4, const float* b_s4,
+                                       void* stream) {
+  AVD_REQUIRE(B > 0 && Fa > 0 && hop > 0 && H > 0, "bad shape");
+  const int64_t need = (int64_t)B * H * Fa * hop * 4;
+  if (need > (int64_t)AVD_AUDIO_DECODE_STATIC_MAX_BYTES)
+    AVD_FAIL("avd_audio_decode_static: B*H*Fa*hop*4 = " + std::to_string(need) + " bytes of scratch exceed the built-in " +
+             std::to_string((int64_t)AVD_AUDIO_DECODE_STATIC_MAX_BYTES) + " (use avd_audio_decode with caller scratch)");
+  float* scratch = nullptr;
+  AVD_TRY(audio_decode_static_ptr(&scratch));
+  // kernel A writes every element of [B,H,L] that kernel B reads, so nothing in the shared array has to start at zero
+  return avd_audio_decode(z, wav, scratch, B, Ca, Fa, H, hop, K, w_from, b_from, w_s0, b_s0, w_s2, b_s2, w_s4, b_s4,
+                          stream);
+}
