@@ -134,6 +134,12 @@ __device__ __forceinline__ void thin_row_softmax(const float* srow, uint8_t* sPt
 // barrier slots
 enum { AB_Q = 0, AB_K = 1, AB_V = 2, AB_S = 3 /*+t*/, AB_P = 5 /*+t*/, AB_O = 7 /*+t*/, AB_R = 9 /*+t*/, AB_COUNT = 11 };
 
+#ifndef AVD_ATT_STAGGER
+#define AVD_ATT_STAGGER 0
+#endif
+#ifndef AVD_LAZY_MAX
+#define AVD_LAZY_MAX 1   // multi-block softmax: one pass against the carried max (0: always max pass + exp pass; 16 x 2048 keys 348 -> 318 us)
+#endif
 template <bool ONE_BLOCK, bool F16, bool MASKED>   // MASKED: key_padding_mask bits present (its own instantiation: the single-block kernel sits at its 128-register limit). F16: q/k/v, P and the output are fp16 (AVD_PREC_F16) instead of bf16.  ONE_BLOCK: N <= 192 keys, the whole score row stays in registers (single softmax pass)
 __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ,
                                                                  const __grid_constant__ CUtensorMap tmKV,
@@ -217,6 +223,8 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
     const float sc = p.scale_log2e;
     const bool mark = (tid == 0);
     const bool leader = (warp & 7) == 0 && lane == 0;      // issues this tile's MMAs
+    // requests K_{j+1} / V_{j+1}: the leader of the tile whose MMAs retire last (staggered tiles: the second one)
+    const bool loader = leader && t == ((!ONE_BLOCK && AVD_ATT_STAGGER != 0) ? n_tiles - 1 : 0);
     const uint32_t hi = smem_desc_hi_sw128(1024);
     const uint32_t q_lo = smem_desc_lo_sw128(smem_u32(sQ + t * ATT_Q_BYTES), 16);
     const uint32_t k_lo = smem_desc_lo_sw128(smem_u32(sK), 16);
@@ -256,12 +264,20 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
       __syncwarp();
       mbar_wait(&bars[AB_S + t], ph);
       tc_fence_after();
-      if (tid == 0 && j + 1 < nkv) {                // K_{j+1} may land as soon as every tile's S MMAs have read K_j
-        for (int tt = 1; tt < n_tiles; ++tt) mbar_wait(&bars[AB_S + tt], ph);
+      if (loader && j + 1 < nkv) {                  // K_{j+1} may land as soon as every tile's S MMAs have read K_j
+        for (int tt = 0; tt < n_tiles; ++tt)
+          if (tt != t) mbar_wait(&bars[AB_S + tt], ph);
         mbar_expect_tx(&bars[AB_K], ATT_KV_BYTES);
         tma_load_3d(sK, &tmKV, &bars[AB_K], colK, row_base + (j + 1) * ATT_BKV, 0);
       }
       if (mark && j == 0) att_mark(trace, 5);
+      if constexpr (!ONE_BLOCK && AVD_ATT_STAGGER != 0) {
+        // the second tile's softmax of block j starts when the first tile's is over: while one tile is in its exponentials
+        // (MUFU-bound) the tensor pipe runs the other's P V and next S, instead of both tiles idling through both tiles'
+        // MMAs.  Tile 0 cannot be two P phases ahead of a tile-1 warp here: K_{j+1} is requested by tile 1's leader in ITS
+        // block j, a whole TMA + MMA + softmax pass before tile 0 completes P_{j+1}.
+        if (t == 1 && (AVD_ATT_STAGGER == 2 || j == 0)) mbar_wait(&bars[AB_P + 0], ph);
+      }
       float l_blk = 0.0f, alpha;
       if constexpr (ONE_BLOCK) {
         // ---- single pass: up to 3 chunks (96 scores) of this row live in registers
@@ -353,6 +369,72 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
           }
         }
         }   // !thin
+      } else if (AVD_LAZY_MAX && j > 0) {
+        // ---- lazy reference max: exponentials against the carried m_run in ONE pass over the S columns while the block's
+        // own max is tracked; the pass is repeated with the new max only when some row of the warp moved up by more than
+        // 2^8 (P must stay inside fp16 / the row sum well conditioned).  Both warps of a pair hold the same 32 rows and
+        // see the same exchanged max, so they take the same branch.
+        auto pass = [&](float m_sc, float& m_part) {
+          float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+          l_blk = 0.0f;
+          for (int ch = ch0; ch < ch1; ++ch) {
+            uint32_t x[32];
+            tmem_ld_32x32(tmem_S + ch * 32, x);
+            tmem_ld_wait();
+            const uint32_t vm = valid_bits(j, ch, kv_valid - ch * 32);
+            float l0 = 0.0f, l1 = 0.0f;
+            uint32_t w[16];
+            if (vm == 0xffffffffu) {
+              float e[32];
+              ex2_chunk(x, sc, -m_sc, e);
+#pragma unroll
+              for (int c = 0; c < 32; c += 2) {
+                mx[c & 3] = fmaxf(mx[c & 3], __uint_as_float(x[c]));
+                mx[(c + 1) & 3] = fmaxf(mx[(c + 1) & 3], __uint_as_float(x[c + 1]));
+                l0 += e[c];
+                l1 += e[c + 1];
+                w[c >> 1] = F16 ? pack_f16x2(e[c], e[c + 1]) : pack_bf16x2(e[c], e[c + 1]);
+              }
+            } else {
+#pragma unroll
+              for (int c = 0; c < 32; c += 2) {
+                const bool v0 = (vm >> c) & 1u, v1 = (vm >> (c + 1)) & 1u;
+                const float s0 = __uint_as_float(x[c]), s1 = __uint_as_float(x[c + 1]);
+                mx[c & 3] = fmaxf(mx[c & 3], v0 ? s0 : -INFINITY);
+                mx[(c + 1) & 3] = fmaxf(mx[(c + 1) & 3], v1 ? s1 : -INFINITY);
+                const float p0 = v0 ? ex2_approx(fmaf(s0, sc, -m_sc)) : 0.0f;
+                const float p1 = v1 ? ex2_approx(fmaf(s1, sc, -m_sc)) : 0.0f;
+                l0 += p0;
+                l1 += p1;
+                w[c >> 1] = F16 ? pack_f16x2(p0, p1) : pack_bf16x2(p0, p1);
+              }
+            }
+            l_blk += l0 + l1;
+            uint8_t* atom = sPt + (ch >> 1) * ATT_Q_BYTES + r * 128;
+            const int q_base = (ch & 1) * 4;
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+              *reinterpret_cast<uint4*>(atom + (((q_base + q) ^ (r & 7)) << 4)) =
+                  make_uint4(w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
+          }
+          m_part = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
+        };
+        const float m_ref = m_run == -INFINITY ? 0.0f : m_run;
+        float m_part;
+        pass(m_ref * sc, m_part);
+        xm[sp * 128 + r] = m_part;
+        named_bar_sync(pair_bar, 64);
+        const float m_row = fmaxf(m_part, xm[(sp ^ 1) * 128 + r]);
+        const bool need = m_row != -INFINITY && (m_run == -INFINITY || (m_row - m_run) * sc > 8.0f);
+        alpha = 1.0f;
+        if (__any_sync(0xffffffffu, need)) {
+          const float m_new = fmaxf(m_run, m_row);
+          const float m_use = m_new == -INFINITY ? 0.0f : m_new;
+          alpha = ex2_approx((m_run - m_use) * sc);
+          m_run = m_new;
+          float dummy;
+          pass(m_use * sc, dummy);
+        }
       } else {
         // ---- pass 1: row max over this thread's valid keys
         float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
@@ -471,8 +553,9 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
       if (j + 1 < nkv) {
         tc_fence_before();
         mbar_arrive(&bars[AB_R + t]);
-        if (tid == 0) {                             // V_{j+1} once every tile's PV MMAs have read V_j
-          for (int tt = 1; tt < n_tiles; ++tt) mbar_wait(&bars[AB_O + tt], ph);
+        if (loader) {                               // V_{j+1} once every tile's PV MMAs have read V_j
+          for (int tt = 0; tt < n_tiles; ++tt)
+            if (tt != t) mbar_wait(&bars[AB_O + tt], ph);
           mbar_expect_tx(&bars[AB_V], ATT_KV_BYTES);
           tma_load_3d(sV, &tmKV, &bars[AB_V], colV, row_base + (j + 1) * ATT_BKV, 0);
         }

@@ -187,11 +187,16 @@ def test_long_context_f16_batch2_vs_oracle(dev, mods, w_cpu):
     assert max(ec, en) < TOL_EPS_16 and ehat < TOL_EPS_16
 
 
-def _attn_check(dev, lib, n_seq, N, f16, tol):
+def _attn_check(dev, lib, n_seq, N, f16, tol, key_ramp=0.0):
     from multimodal_diffusion_b200 import _lib
     H, hd = 8, 64
     dt = torch.float16 if f16 else torch.bfloat16
-    qkv = (randn(3, n_seq * N, 3 * H * hd) * 1.5).to(dt).to(dev)
+    qkv = randn(3, n_seq * N, 3 * H * hd) * 1.5
+    if key_ramp:          # scores rise with the key index by key_ramp / 2 nats over the sequence (every head's dim 0)
+        v5 = qkv.view(n_seq, N, 3, H, hd)
+        v5[:, :, 0, :, 0] = 4.0
+        v5[:, :, 1, :, 0] = torch.linspace(-key_ramp, key_ramp, N).view(1, N, 1)
+    qkv = qkv.to(dt).to(dev)
     out = torch.zeros(1, n_seq * N, H * hd, device=dev, dtype=dt)
     _lib.check(lib.avd_attention(qkv.data_ptr(), 0, out.data_ptr(), _lib.AVD_PREC_F16 if f16 else _lib.AVD_PREC_BF16,
                                  n_seq, N, H, hd, _lib.stream_ptr()))
@@ -212,6 +217,15 @@ def _attn_check(dev, lib, n_seq, N, f16, tol):
 def test_attention_tcgen05_f16_template(dev, lib, n_seq, N):
     """The F16 instantiations of attn_tc_kernel (single-block N <= 192 and multi-block) at kernel level."""
     _attn_check(dev, lib, n_seq, N, True, 1.5e-3)
+
+
+@pytest.mark.parametrize("f16", [True, False])
+@pytest.mark.parametrize("N,ramp", [(1000, 10.0), (1000, 60.0), (2048, 25.0), (445, 30.0)])
+def test_attention_multiblock_rising_max(dev, lib, N, ramp, f16):
+    """The multi-block softmax takes its exponentials against the CARRIED row max and repeats a block only when the max
+    rose by more than 2^8: scores that climb with the key index exercise both branches (ramp 10: ~2.7 log2 units per
+    192-key block, repeats now and then; ramp 60: ~17 per block, repeats every block)."""
+    _attn_check(dev, lib, 2, N, f16, 1.5e-3 if f16 else 8e-3, key_ramp=ramp)
 
 
 @pytest.mark.parametrize("n_seq,N,f16", [(3, 445, True), (2, 193, False), (1, 2048, True), (2, 1000, False)])
