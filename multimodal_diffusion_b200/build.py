@@ -20,9 +20,9 @@ CSRC = PKG / "csrc"
 ROOT = PKG.parent
 LIB = PKG / "libavdiff_b200.so"
 OBJ_DIR = ROOT / "build" / "obj"
-SOURCES = ["avd_elementwise.cu", "avd_gemm.cu", "avd_gemm_ps.cu", "avd_gemm_chain.cu", "avd_gemm_ps2.cu", "avd_attn.cu", "avd_stream.cu", "avd_codec.cu",
+SOURCES = ["avd_elementwise.cu", "avd_gemm.cu", "avd_gemm_ps.cu", "avd_gemm_chain.cu", "avd_gemm_ps2.cu", "avd_attn.cu", "avd_attn_fa.cu", "avd_stream.cu", "avd_codec.cu",
            "avd_vae.cu", "avd_api.cu"]
-HEADERS = [CSRC / "avd_internal.h", CSRC / "avd_ptx.cuh", CSRC / "avd_gemm_common.cuh", CSRC / "avd_gemm_ps_epilogue.inc", ROOT / "include" / "avdiff_b200.h"]
+HEADERS = [CSRC / "avd_internal.h", CSRC / "avd_ptx.cuh", CSRC / "avd_gemm_common.cuh", CSRC / "avd_gemm_ps_epilogue.inc", CSRC / "avd_attn_common.cuh", ROOT / "include" / "avdiff_b200.h"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-std=c++17", "-lineinfo",

@@ -20,18 +20,14 @@
 // the next sequence (or are zero fill) and never reach the result.
 //
 // attn_f32_kernel (fp32-parity mode): CUDA-core fp32, one warp per query row, scores staged in smem.
-#include "avd_internal.h"
-#include "avd_ptx.cuh"
+#include "avd_attn_common.cuh"
 
 #include <cstdlib>
 
 namespace avd {
 
-constexpr int ATT_BQ = 128;
 constexpr int ATT_BKV = 192;                         // key block: S_t needs ATT_BKV TMEM columns per query tile
-constexpr int ATT_HD = 64;
 constexpr int ATT_THREADS = 512;
-constexpr int ATT_Q_BYTES = ATT_BQ * ATT_HD * 2;     // 16 KB: [128 rows][64 bf16], 128B swizzle
 constexpr int ATT_KV_BYTES = ATT_BKV * ATT_HD * 2;   // 24 KB
 constexpr int ATT_P_BYTES = 3 * ATT_Q_BYTES;         // three 64-key swizzle atoms of [128 rows][128 B]
 constexpr int ATT_XCHG_BYTES = (8 + 4) * 128 * 4;    // row-max exchange [2 bufs][2 tiles][2 halves][128], row-sum [2][2][128]
@@ -40,57 +36,10 @@ constexpr int ATT_THIN_BYTES = ATT_THIN_ROWS * ATT_BKV * 4 + 64;   // its raw sc
 constexpr int ATT_SMEM = 2 * ATT_Q_BYTES + 2 * ATT_KV_BYTES + 2 * ATT_P_BYTES + ATT_XCHG_BYTES + 256 + ATT_THIN_BYTES;
 constexpr uint32_t ATT_TMEM_COLS = 512;
 
-struct AttnParams {
-  int N;            // tokens per sequence
-  int d;            // model width (row stride of out)
-  int n_heads;
-  int64_t M;        // total rows (n_seq * N)
-  __nv_bfloat16* out;
-  int out_nseg;
-  float scale_log2e;  // (1/sqrt(hd)) * log2(e)
-  unsigned long long* trace;   // debug phase stamps (avd_debug_trace)
-  int poly_exp;     // multi-block path: every second exponential on the FMA pipe (ex2_poly)
-  const uint32_t* kmask;   // key_padding_mask as bits [n_seq][kmask_words] (bit = 1: key ignored) or NULL
-  int kmask_words;         // ceil(N / 32)
-};
-
-__device__ __forceinline__ float ex2_approx(float x) {
-  float y;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
-// The exponentials of a 32-score chunk, issued back to back.  Left to itself the compiler interleaves each MUFU.EX2 with
-// the FADD / F2FP that consumes the previous one, and with two softmax warps per scheduler every such pair then waits out
-// the MUFU latency (the SASS showed MUFU, FADD, MUFU, FADD ...).  The volatile asm keeps the 32 independent MUFUs together;
-// sums and packs follow.  What remains is the pipe itself: 16 exponentials per cycle per SM, i.e. 8 cycles per warp
-// instruction on each scheduler -- 128 rows x 160 key columns = 1280 cycles per CTA, which is what the phase trace shows.
-__device__ __forceinline__ void ex2_chunk(const uint32_t (&x)[32], float sc, float neg_m_sc, float (&e)[32]) {
-#pragma unroll
-  for (int c = 0; c < 32; ++c) {
-    const float a = fmaf(__uint_as_float(x[c]), sc, neg_m_sc);
-    asm volatile("ex2.approx.ftz.f32 %0, %1;" : "=f"(e[c]) : "f"(a));
-  }
-}
-
-// 2^x for x <= 0 on the FMA / ALU pipes: round-to-integer through the 1.5 * 2^23 constant, a degree-4 near-minimax
-// polynomial for 2^f on [-0.5, 0.5] (max relative error 2.9e-6 in fp32, below the 16-bit rounding P gets), and the integer
-// part added into the exponent field.  Used for every second exponential of the MULTI-BLOCK path only: with 16 softmax
-// warps per SM and 49 152 exponentials per 192-key block that path is bound by the 16-lane MUFU pipe (the split
-// FlashAttention-4 describes); in the single-block kernel (8 warps, latency bound) the same change cost 24 %.
-__device__ __forceinline__ float ex2_poly(float x) {
-  x = fmaxf(x, -125.0f);                       // keeps the result a normal number (scores this far down round to 0 in P)
-  const float xf = x + 12582912.0f;
-  const float n = xf - 12582912.0f;
-  const float f = x - n;
-  float q = 0.009582850150763988f;
-  q = fmaf(q, f, 0.055906426161527634f);
-  q = fmaf(q, f, 0.24024099111557007f);
-  q = fmaf(q, f, 0.6931241750717163f);
-  q = fmaf(q, f, 1.0f);
-  return __int_as_float(__float_as_int(q) + (__float_as_int(xf) << 23));
-}
-
 __device__ __forceinline__ void att_mark(unsigned long long* trace, int slot) {
+#ifdef AVD_ATT_WTRACE
+  return;                                  // the per-warp stamps below own the buffer
+#endif
   if (trace != nullptr) {
     const int cta = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
     unsigned long long g, c;
@@ -100,6 +49,21 @@ __device__ __forceinline__ void att_mark(unsigned long long* trace, int slot) {
     trace[(cta * 16 + slot) * 2 + 1] = c;
   }
 }
+
+// Per-warp timeline of one CTA (experimental builds with -DAVD_ATT_WTRACE; tools/attn_wtrace.py): lane 0 of every warp of
+// CTA 0 stamps clock64 at slot `slot` of key blocks 3..5 into the avd_debug_trace buffer (which must hold 32 u64 per CTA).
+#ifdef AVD_ATT_WTRACE
+#define ATT_WMARK(slot)                                                                                         \
+  do {                                                                                                          \
+    if (trace != nullptr && lane == 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && j >= 3 && j < 6) { \
+      unsigned long long c_;                                                                                    \
+      asm volatile("mov.u64 %0, %%clock64;" : "=l"(c_));                                                        \
+      trace[(warp * 3 + (j - 3)) * 12 + (slot)] = c_;                                                           \
+    }                                                                                                           \
+  } while (0)
+#else
+#define ATT_WMARK(slot) do { } while (0)
+#endif
 
 // Softmax of ONE row of a thin query tile by one whole warp (lane = key column mod 32), from the raw scores the tile's
 // TMEM-reading warps dumped to smem.  A thin tile (the 5 rows 128..132 of the 133-token joint sequence) would otherwise
@@ -249,6 +213,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
       const int ch1 = min(nch, ch0 + 3);
       float* xm = xmax + ((ph * 2 + t) * 2) * 128;
       const int kv_n = (kv_valid + 15) & ~15;
+      ATT_WMARK(0);
       if (leader && j == 0) {                       // S_t = Q_t K_0^T (later blocks: issued right behind P V of the block before)
         mbar_wait(&bars[AB_Q], 0);
         mbar_wait(&bars[AB_K], ph);
@@ -264,6 +229,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
       __syncwarp();
       mbar_wait(&bars[AB_S + t], ph);
       tc_fence_after();
+      ATT_WMARK(1);
       if (loader && j + 1 < nkv) {                  // K_{j+1} may land as soon as every tile's S MMAs have read K_j
         for (int tt = 0; tt < n_tiles; ++tt)
           if (tt != t) mbar_wait(&bars[AB_S + tt], ph);
@@ -422,9 +388,11 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
         const float m_ref = m_run == -INFINITY ? 0.0f : m_run;
         float m_part;
         pass(m_ref * sc, m_part);
+        ATT_WMARK(2);
         xm[sp * 128 + r] = m_part;
         named_bar_sync(pair_bar, 64);
         const float m_row = fmaxf(m_part, xm[(sp ^ 1) * 128 + r]);
+        ATT_WMARK(3);
         const bool need = m_row != -INFINITY && (m_run == -INFINITY || (m_row - m_run) * sc > 8.0f);
         alpha = 1.0f;
         if (__any_sync(0xffffffffu, need)) {
@@ -434,6 +402,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
           m_run = m_new;
           float dummy;
           pass(m_use * sc, dummy);
+          ATT_WMARK(4);
         }
       } else {
         // ---- pass 1: row max over this thread's valid keys
@@ -507,12 +476,14 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
       fence_async_smem();   // P (generic-proxy stores) -> visible to the tensor core's async-proxy reads
       tc_fence_before();    // the S columns have been read: the next S MMA may overwrite them
       mbar_arrive(&bars[AB_P + t]);
+      ATT_WMARK(5);
       if (mark && j == 0) att_mark(trace, 7);
       if (leader) {                                 // O_t,j = P_t V_j
         mbar_wait(&bars[AB_P + t], ph);
         mbar_wait(&bars[AB_V], ph);
         if (j > 0) mbar_wait(&bars[AB_R + t], ph ^ 1);     // O_t,j-1 has been read out of TMEM
         tc_fence_after();
+        ATT_WMARK(9);
         const uint32_t idesc_o = make_idesc_bf16(ATT_BQ, ATT_HD, 0, 1, F16);   // B = V is MN-major
         const int ksteps = kv_n >> 4;
         for (int ks = 0; ks < ksteps; ++ks) {
@@ -522,6 +493,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
         }
         umma_commit(&bars[AB_O + t]);
         if (mark && j == 0) att_mark(trace, 4);
+        ATT_WMARK(10);
         if (!ONE_BLOCK && j + 1 < nkv) {
           // S_t(j+1) = Q_t K_{j+1}^T goes in right behind P V: the S columns were drained when P_j was staged (AB_P), and
           // K_{j+1} was requested when the S MMAs of block j retired -- the tensor pipe runs it under this tile's O update
@@ -529,6 +501,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
           const int kvn1 = (min(ATT_BKV, p.N - (j + 1) * ATT_BKV) + 15) & ~15;
           mbar_wait(&bars[AB_K], ph ^ 1);
           tc_fence_after();
+          ATT_WMARK(11);
           const uint32_t idesc_s = make_idesc_bf16(ATT_BQ, kvn1, 0, 0, F16);
 #pragma unroll
           for (int k = 0; k < ATT_HD / 16; ++k)
@@ -537,8 +510,10 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
         }
       }
       __syncwarp();
+      ATT_WMARK(6);
       mbar_wait(&bars[AB_O + t], ph);
       tc_fence_after();
+      ATT_WMARK(7);
       if (mark && j == 0) att_mark(trace, 8);
       {   // ---- O = O * alpha + O_j on this thread's 32 output columns
         uint32_t x[32];
@@ -550,6 +525,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
           else o_acc[c] = fmaf(o_acc[c], alpha, __uint_as_float(x[c]));
         }
       }
+      ATT_WMARK(8);
       if (j + 1 < nkv) {
         tc_fence_before();
         mbar_arrive(&bars[AB_R + t]);
@@ -1363,6 +1339,10 @@ int launch_attention_tc(const void* qkv_bf16, void* out, int out_nseg, int n_seq
     p.trace = nullptr;
     AVD_CUDA(cudaLaunchKernelEx(&cfg, sf, tmQ, tmQ8, tmKVs, p));
     return 0;
+  }
+  if (N > ATT_BKV && options().attn_fa != 0) {       // multi-block: P and O resident in tensor memory (avd_attn_fa.cu)
+    const int rc = launch_attention_fa(qkv_bf16, p, n_seq, f16, s);
+    if (rc != 0) return rc < 0 ? rc : 0;
   }
   if (N > ATT_BKV && options().attn_pipe != 0) {     // multi-block: the pipelined kernel, one 128-query tile per CTA
     static const AttnFn pipe_kernels[2][2] = {{attn_pipe_kernel<false, false>, attn_pipe_kernel<false, true>},

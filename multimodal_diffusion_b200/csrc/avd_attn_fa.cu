@@ -1,0 +1,345 @@
+// avd_attn_fa.cu -- K5, multi-block case (N > 192 keys): attention with P and O resident in TENSOR MEMORY.
+//
+// What the per-warp timeline of attn_tc_kernel's multi-block path showed (tools/attn_wtrace.py, 16 x 2048 keys): a key
+// block of 2 x 128 x 192 scores costs 6900 cycles against 3072 of MUFU; the 12 P V MMAs (N = 64) take ~96 cycles each
+// instead of 32 because both operands come through the shared-memory port (P was staged there with 48 KB of STS per tile
+// and block, next to the S MMAs' operands and the TMA writes), the tile's issuer lane sits in a softmax warp and makes it
+// late, and every block reads O back (tcgen05.ld + 32 FMA per thread) after waiting for P V.  Here (the split
+// FlashAttention-4 describes, sized for head_dim 64):
+//
+//   * P never touches shared memory: the softmax threads write it with tcgen05.st into TMEM columns next to S, and
+//     O += P V is a tcgen05.mma with the A operand IN TMEM (32 cycles per K = 16 step, only V's 2 KB from smem);
+//   * O stays in TMEM across the key blocks (the MMA accumulates).  A row's reference max only moves when the block's max
+//     exceeds it by more than 2^8; then -- rarely after the first blocks -- the two warps that own the row rescale their
+//     32 + 32 O columns in place (tcgen05.ld / st).  No per-block O read-out, no wait for P V in the softmax loop;
+//   * 128-key blocks: a thread's 64 scores live in registers, so the block max is known before any exponential (one
+//     tcgen05.ld pass, no speculative pass);
+//   * one control lane (warp 16) issues every TMA load (4-stage K / V ring, two blocks ahead) and every MMA, in the fixed
+//     order  P V_0(j), S_0(j+1), P V_1(j), S_1(j+1): while one tile's softmax runs, the tensor pipe works for the other.
+//
+// TMEM per query tile t (256 columns): S [0, 128) fp32 | P [128, 192) 16-bit pairs | O [192, 256) fp32.
+// One CTA = one (sequence, head, PAIR of 128-query tiles); warps 0..7 softmax of tile 0, 8..15 of tile 1 (warp w: TMEM lanes
+// 32 (w % 4).., the two warps of a lane quadrant split the key columns and the output columns in halves).
+#include "avd_attn_common.cuh"
+
+#include <type_traits>
+
+namespace avd {
+
+constexpr int FA_BKV = 128;
+constexpr int FA_STAGES = 4;
+constexpr int FA_KV_BYTES = FA_BKV * ATT_HD * 2;            // 16 KB: [128 keys][64] 16-bit, 128B swizzle
+constexpr int FA_THREADS = 17 * 32;
+constexpr int FA_XCHG_BYTES = (8 + 4) * 128 * 4;            // row max [2 bufs][2 tiles][2 halves][128], row sum [2][2][128]
+constexpr int FA_SMEM = 2 * ATT_Q_BYTES + FA_STAGES * 2 * FA_KV_BYTES + FA_XCHG_BYTES + 256;
+constexpr float FA_RESCALE_LOG2 = 8.0f;                     // a row's reference max moves when the block max is 2^8 above it
+enum { FB_Q = 0, FB_KF = 1 /*+stage*/, FB_VF = 5 /*+stage*/, FB_KVE = 9 /*+stage*/, FB_S = 13 /*+tile*/, FB_P = 15 /*+tile*/,
+       FB_O = 17 /*+tile*/, FB_COUNT = 19 };
+
+template <bool F16, bool MASKED>
+__global__ void __launch_bounds__(FA_THREADS, 1) attn_fa_kernel(const __grid_constant__ CUtensorMap tmQKV,
+                                                                const AttnParams p) {
+  extern __shared__ __align__(1024) uint8_t fa_smem[];
+  uint8_t* smem = fa_smem;
+  if ((smem_u32(smem) & 1023u) != 0) __trap();   // 128B-swizzle tiles need 1024-B aligned bases
+  uint8_t* sQ = smem;                                       // 2 query tiles (later: output staging)
+  uint8_t* sKV = sQ + 2 * ATT_Q_BYTES;                      // [stage]{K, V}
+  float* xmax = reinterpret_cast<float*>(sKV + FA_STAGES * 2 * FA_KV_BYTES);
+  float* xsum = xmax + 8 * 128;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(xmax) + FA_XCHG_BYTES);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + FB_COUNT);
+
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5, lane = tid & 31;
+  const int head = blockIdx.y, seq = blockIdx.z;
+  const int row_base = seq * p.N;
+  const int q_first = blockIdx.x * 2 * ATT_BQ;
+  const int n_tiles = (p.N - q_first > ATT_BQ) ? 2 : 1;
+  const int colQ = head * ATT_HD, colK = p.d + head * ATT_HD, colV = 2 * p.d + head * ATT_HD;
+  const int nkv = (p.N + FA_BKV - 1) / FA_BKV;
+
+  if (warp == 1) {
+    if (lane < FB_COUNT) {
+      uint32_t count = 1;
+      if (lane >= FB_P && lane < FB_O) {                    // arrivals: the warp pairs of the tile that own valid query rows
+        const int rows = min(ATT_BQ, p.N - q_first - (lane - FB_P) * ATT_BQ);
+        count = rows > 0 ? 64 * ((rows + 31) >> 5) : 1;
+      }
+      mbar_init(&bars[lane], count);
+    }
+    fence_barrier_init();
+  } else if (warp == 2 && lane == 0) {
+    tma_prefetch_desc(&tmQKV);
+  }
+  if (warp == 0) tmem_alloc<512>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_launch_dependents();
+
+  if (warp == 16) {
+    // ------------------------------------------------------------------ control lane: TMA loads and every MMA
+    if (lane == 0) {
+      auto load_kv = [&](int b) {
+        const int s = b & (FA_STAGES - 1);
+        uint8_t* k = sKV + s * 2 * FA_KV_BYTES;
+        mbar_expect_tx(&bars[FB_KF + s], FA_KV_BYTES);
+        tma_load_3d(k, &tmQKV, &bars[FB_KF + s], colK, row_base + b * FA_BKV, 0);
+        mbar_expect_tx(&bars[FB_VF + s], FA_KV_BYTES);
+        tma_load_3d(k + FA_KV_BYTES, &tmQKV, &bars[FB_VF + s], colV, row_base + b * FA_BKV, 0);
+      };
+      pdl_wait();                                           // qkv comes from the previous kernel
+      mbar_expect_tx(&bars[FB_Q], n_tiles * ATT_Q_BYTES);
+      for (int t = 0; t < n_tiles; ++t)
+        tma_load_3d(sQ + t * ATT_Q_BYTES, &tmQKV, &bars[FB_Q], colQ, row_base + q_first + t * ATT_BQ, 0);
+      for (int b = 0; b < min(2, nkv); ++b) load_kv(b);
+
+      const uint32_t hi = smem_desc_hi_sw128(1024);
+      const uint32_t idesc_o = make_idesc_bf16(ATT_BQ, ATT_HD, 0, 1, F16);       // B = V is MN-major
+      auto issue_s = [&](int t, int b) {                    // S_t(b) = Q_t K_b^T -> TMEM columns [256 t, 256 t + 128)
+        const int kvn = (min(FA_BKV, p.N - b * FA_BKV) + 15) & ~15;
+        const uint32_t idesc_s = make_idesc_bf16(ATT_BQ, kvn, 0, 0, F16);
+        const uint32_t q_lo = smem_desc_lo_sw128(smem_u32(sQ + t * ATT_Q_BYTES), 16);
+        const uint32_t k_lo = smem_desc_lo_sw128(smem_u32(sKV + (b & (FA_STAGES - 1)) * 2 * FA_KV_BYTES), 16);
+#pragma unroll
+        for (int k = 0; k < ATT_HD / 16; ++k)
+          umma_bf16_lh(tmem_base + t * 256, q_lo + 2 * k, k_lo + 2 * k, hi, idesc_s, k > 0 ? 1u : 0u);
+        umma_commit(&bars[FB_S + t]);
+      };
+      mbar_wait(&bars[FB_Q], 0);
+      mbar_wait(&bars[FB_KF + 0], 0);
+      tc_fence_after();
+      for (int t = 0; t < n_tiles; ++t) issue_s(t, 0);
+
+      for (int j = 0; j < nkv; ++j) {
+        const int s = j & (FA_STAGES - 1);
+        if (j + 2 < nkv) {                                  // the stage of block j - 2 was handed back two blocks ago
+          const int b = j + 2;
+          if (b >= FA_STAGES) mbar_wait(&bars[FB_KVE + (b & (FA_STAGES - 1))], ((b / FA_STAGES) - 1) & 1);
+          load_kv(b);
+        }
+        const int kvn = (min(FA_BKV, p.N - j * FA_BKV) + 15) & ~15;
+        const uint32_t v_lo = smem_desc_lo_sw128(smem_u32(sKV + s * 2 * FA_KV_BYTES + FA_KV_BYTES), 16);
+        for (int t = 0; t < n_tiles; ++t) {
+          mbar_wait(&bars[FB_P + t], j & 1);                // P_t(j) is in TMEM (and O_t rescaled where a row's max moved)
+          if (t == 0) mbar_wait(&bars[FB_VF + s], (j / FA_STAGES) & 1);
+          tc_fence_after();
+          const uint32_t d_o = tmem_base + t * 256 + 192, a_p = tmem_base + t * 256 + 128;
+          for (int ks = 0; ks < (kvn >> 4); ++ks)           // O_t += P_t(j) V_j: A from TMEM, 8 columns per 16 keys
+            umma_bf16_ts(d_o, a_p + ks * 8, v_lo + ks * 128, hi, idesc_o, (j > 0 || ks > 0) ? 1u : 0u);
+          if (t == n_tiles - 1) umma_commit(&bars[FB_KVE + s]);   // K_j / V_j have been read by every tile
+          if (j + 1 < nkv) {
+            if (t == 0) {
+              mbar_wait(&bars[FB_KF + ((j + 1) & (FA_STAGES - 1))], ((j + 1) / FA_STAGES) & 1);
+              tc_fence_after();
+            }
+            issue_s(t, j + 1);                              // in order behind P V_t(j): S_t(j+1) complete => O_t current
+          } else {
+            umma_commit(&bars[FB_O + t]);
+          }
+        }
+      }
+    }
+  } else if ((warp >> 3) < n_tiles && q_first + (warp >> 3) * ATT_BQ + (warp & 3) * 32 < p.N) {
+    // ------------------------------------------------------------------ softmax + output of query tile t
+    const int t = warp >> 3, sp = (warp >> 2) & 1, quad = warp & 3;
+    const int r = quad * 32 + lane;                         // row inside the tile == TMEM lane
+    const uint32_t tmem_T = tmem_base + t * 256 + ((uint32_t)(quad * 32) << 16);
+    const uint32_t tmem_S = tmem_T + sp * 64;               // this thread's 64 score columns
+    const uint32_t tmem_P = tmem_T + 128 + sp * 32;         // ... their 32 columns of 16-bit pairs
+    const uint32_t tmem_O = tmem_T + 192 + sp * 32;         // this thread's 32 of the 64 output columns
+    const uint32_t pair_bar = 1 + t * 4 + quad;             // named barrier of the two warps that share these rows
+    const float sc = p.scale_log2e;
+    float m_run = -INFINITY, l_run = 0.0f;
+    auto valid_bits = [&](int j, int ch, int lim) -> uint32_t {
+      uint32_t v = lim >= 32 ? 0xffffffffu : (lim > 0 ? ((1u << lim) - 1u) : 0u);
+      if (MASKED && lim > 0) v &= ~p.kmask[(size_t)blockIdx.z * p.kmask_words + j * (FA_BKV / 32) + ch];
+      return v;
+    };
+    for (int j = 0; j < nkv; ++j) {
+      const uint32_t ph = j & 1;
+      const int kv_valid = min(FA_BKV, p.N - j * FA_BKV);
+      float* xm = xmax + ((ph * 2 + t) * 2) * 128;
+      // one pass over this thread's (up to) two 32-score chunks: block max over the valid keys and, with EXP, the
+      // exponentials against the reference max `neg_m_sc` -> P columns (tcgen05.st) and the partial row sum
+      auto pass = [&](auto exp_tag, float neg_m_sc, float& l_blk) -> float {
+        constexpr bool EXP = decltype(exp_tag)::value;
+        float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+        l_blk = 0.0f;
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+          const int lim = kv_valid - (sp * 2 + i) * 32;
+          if (lim > 0) {
+            uint32_t x[32];
+            tmem_ld_32x32(tmem_S + i * 32, x);
+            tmem_ld_wait();
+            const uint32_t vb = valid_bits(j, sp * 2 + i, lim);
+            float e[32];
+            if (EXP) ex2_chunk(x, sc, neg_m_sc, e);
+            if (vb == 0xffffffffu) {
+#pragma unroll
+              for (int c = 0; c < 32; ++c) mx[c & 3] = fmaxf(mx[c & 3], __uint_as_float(x[c]));
+            } else {
+#pragma unroll
+              for (int c = 0; c < 32; ++c) {
+                const bool v = (vb >> c) & 1u;
+                mx[c & 3] = fmaxf(mx[c & 3], v ? __uint_as_float(x[c]) : -INFINITY);
+                if (EXP) e[c] = v ? e[c] : 0.0f;
+              }
+            }
+            if (EXP) {
+              float l0 = 0.0f, l1 = 0.0f;
+              uint32_t w[16];
+#pragma unroll
+              for (int c = 0; c < 32; c += 2) {
+                l0 += e[c];
+                l1 += e[c + 1];
+                w[c >> 1] = F16 ? pack_f16x2(e[c], e[c + 1]) : pack_bf16x2(e[c], e[c + 1]);
+              }
+              l_blk += l0 + l1;
+              tmem_st_32x16(tmem_P + i * 16, w);
+            }
+          }
+        }
+        return fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
+      };
+      mbar_wait(&bars[FB_S + t], ph);
+      tc_fence_after();
+      // Speculate that the reference max stays: exponentials against the carried m_run in the same pass that finds the
+      // block max (no pair exchange between the TMEM load and the MUFU work).  A warp with a row that has no reference yet
+      // (first block, or only padded keys so far) finds the max first.  Both warps of a pair hold the same rows and the same
+      // m_run, so they take the same branches.
+      const bool spec = !__any_sync(0xffffffffu, m_run == -INFINITY);
+      float l_blk = 0.0f, m_part;
+      if (spec) m_part = pass(std::true_type{}, -m_run * sc, l_blk);
+      else m_part = pass(std::false_type{}, 0.0f, l_blk);
+      xm[sp * 128 + r] = m_part;
+      named_bar_sync(pair_bar, 64);
+      const float m_row = fmaxf(m_part, xm[(sp ^ 1) * 128 + r]);
+      // the reference max moves only when it must: first live block of the row, or the block max is 2^8 above it (P stays
+      // inside fp16, the row sum well conditioned)
+      const bool need = m_row != -INFINITY && (m_run == -INFINITY || (m_row - m_run) * sc > FA_RESCALE_LOG2);
+      bool have_p = spec;
+      if (__any_sync(0xffffffffu, need)) {
+        float alpha = 1.0f;
+        if (need) {
+          alpha = ex2_approx((m_run - m_row) * sc);         // m_run = -inf on the first live block -> 0
+          m_run = m_row;
+          l_run *= alpha;
+        }
+        if (j > 0) {                                        // S_t(j) complete => P V_t(j-1) complete: O_t is current
+          uint32_t o[32];
+          tmem_ld_32x32(tmem_O, o);
+          tmem_ld_wait();
+#pragma unroll
+          for (int c = 0; c < 32; ++c) o[c] = __float_as_uint(__uint_as_float(o[c]) * alpha);
+          tmem_st_32x32(tmem_O, o);
+        }
+        have_p = false;
+      }
+      if (!have_p) {
+        const float neg_m_sc = m_run == -INFINITY ? 0.0f : -m_run * sc;   // every key so far padded: exponents stay finite
+        (void)pass(std::true_type{}, neg_m_sc, l_blk);
+      }
+      l_run += l_blk;
+      tmem_st_wait();
+      tc_fence_before();    // S has been read, P (and a rescaled O) written: the tile's next MMAs may go
+      mbar_arrive(&bars[FB_P + t]);
+    }
+
+    // ---- O_t complete; total row sum = the two halves' partial sums; normalise this thread's 32 output columns
+    mbar_wait(&bars[FB_O + t], 0);
+    tc_fence_after();
+    float rem[32];
+    {
+      uint32_t o[32];
+      tmem_ld_32x32(tmem_O, o);
+      tmem_ld_wait();
+      float* xs = xsum + (t * 2) * 128;
+      xs[sp * 128 + r] = l_run;
+      named_bar_sync(pair_bar, 64);
+      const float inv_l = 1.0f / (l_run + xs[(sp ^ 1) * 128 + r]);
+#pragma unroll
+      for (int c = 0; c < 32; ++c) rem[c] = __uint_as_float(o[c]) * inv_l;
+    }
+    // ---- stage the 32 rows x 128 B of this warp pair in the retired Q tile; coalesced 128-byte row stores
+    const int64_t seg_stride = p.M * (int64_t)p.d;
+    uint8_t* stage = sQ + t * ATT_Q_BYTES + quad * 32 * 128;
+    const int q_tile0 = q_first + t * ATT_BQ + quad * 32;          // first query row of this warp pair
+    for (int sg = 0; sg < p.out_nseg; ++sg) {
+#pragma unroll
+      for (int v4 = 0; v4 < 4; ++v4) {
+        uint32_t w[4];
+        if (p.out_nseg == 1) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            w[k] = F16 ? pack_f16x2(rem[v4 * 8 + k * 2], rem[v4 * 8 + k * 2 + 1])
+                       : pack_bf16x2(rem[v4 * 8 + k * 2], rem[v4 * 8 + k * 2 + 1]);
+        } else {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const int c = v4 * 8 + k * 2;
+            const __nv_bfloat16 h0 = __float2bfloat16_rn(rem[c]);
+            const __nv_bfloat16 h1 = __float2bfloat16_rn(rem[c + 1]);
+            rem[c] -= __bfloat162float(h0);
+            rem[c + 1] -= __bfloat162float(h1);
+            w[k] = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
+          }
+        }
+        *reinterpret_cast<uint4*>(stage + lane * 128 + (((sp * 4 + v4) ^ (lane & 7)) << 4)) =
+            make_uint4(w[0], w[1], w[2], w[3]);
+      }
+      named_bar_sync(pair_bar, 64);
+      const int rr = lane >> 3, cc = lane & 7;
+      __nv_bfloat16* gp = p.out + sg * seg_stride + ((int64_t)row_base + q_tile0) * p.d + head * ATT_HD + cc * 8;
+#pragma unroll
+      for (int it = 0; it < 4; ++it) {                       // this warp stores rows [16 sp, 16 sp + 16) of the pair's 32
+        const int rw = sp * 16 + it * 4 + rr;
+        const uint4 x4 = *reinterpret_cast<const uint4*>(stage + rw * 128 + ((cc ^ (rw & 7)) << 4));
+        if (q_tile0 + rw < p.N) *reinterpret_cast<uint4*>(gp + (int64_t)rw * p.d) = x4;
+      }
+      if (sg + 1 < p.out_nseg) named_bar_sync(pair_bar, 64);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    tmem_dealloc<512>(tmem_base);
+  }
+}
+
+int launch_attention_fa(const void* qkv16, const AttnParams& p, int n_seq, bool f16, cudaStream_t s) {
+  if (p.N <= FA_BKV) return 0;
+  const int d = p.d;
+  CUtensorMap tm;
+  AVD_TRY(get_tensor_map_3d(qkv16, 2, (uint64_t)3 * d, (uint64_t)p.M, 1, (uint64_t)3 * d * 2, (uint64_t)p.M * 3 * d * 2,
+                            ATT_HD, ATT_BQ, &tm));
+  using Fn = void (*)(const CUtensorMap, const AttnParams);
+  static const Fn kernels[2][2] = {{attn_fa_kernel<false, false>, attn_fa_kernel<false, true>},
+                                   {attn_fa_kernel<true, false>, attn_fa_kernel<true, true>}};
+  const Fn fn = kernels[f16 ? 1 : 0][p.kmask != nullptr ? 1 : 0];
+  AVD_TRY(ensure_dyn_smem(reinterpret_cast<const void*>(fn), FA_SMEM));
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3((p.N + 2 * ATT_BQ - 1) / (2 * ATT_BQ), p.n_heads, n_seq);
+  cfg.blockDim = dim3(FA_THREADS);
+  cfg.dynamicSmemBytes = FA_SMEM;
+  cfg.stream = s;
+  cudaLaunchAttribute attrs[1];
+  int na = 0;
+  if (pdl_enabled()) {
+    attrs[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attrs[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  cfg.attrs = attrs;
+  cfg.numAttrs = na;
+  AttnParams q = p;
+  q.trace = nullptr;
+  AVD_CUDA(cudaLaunchKernelEx(&cfg, fn, tm, q));
+  return 1;
+}
+
+}  // namespace avd

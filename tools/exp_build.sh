@@ -7,7 +7,7 @@ root=$(cd "$(dirname "$0")/.." && pwd)
 out=$root/build/exp/$tag; mkdir -p $out
 cs=$root/multimodal_diffusion_b200/csrc
 pids=()
-for f in avd_elementwise avd_gemm avd_gemm_ps avd_gemm_chain avd_gemm_ps2 avd_attn avd_stream avd_codec avd_vae avd_api; do
+for f in avd_elementwise avd_gemm avd_gemm_ps avd_gemm_chain avd_gemm_ps2 avd_attn avd_attn_fa avd_stream avd_codec avd_vae avd_api; do
   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo -Xcompiler -fPIC "$@" -c $cs/$f.cu -o $out/$f.o &
   pids+=($!)
 done
