@@ -50,21 +50,6 @@ __device__ __forceinline__ void att_mark(unsigned long long* trace, int slot) {
   }
 }
 
-// Per-warp timeline of one CTA (experimental builds with -DAVD_ATT_WTRACE; tools/attn_wtrace.py): lane 0 of every warp of
-// CTA 0 stamps clock64 at slot `slot` of key blocks 3..5 into the avd_debug_trace buffer (which must hold 32 u64 per CTA).
-#ifdef AVD_ATT_WTRACE
-#define ATT_WMARK(slot)                                                                                         \
-  do {                                                                                                          \
-    if (trace != nullptr && lane == 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && j >= 3 && j < 6) { \
-      unsigned long long c_;                                                                                    \
-      asm volatile("mov.u64 %0, %%clock64;" : "=l"(c_));                                                        \
-      trace[(warp * 3 + (j - 3)) * 12 + (slot)] = c_;                                                           \
-    }                                                                                                           \
-  } while (0)
-#else
-#define ATT_WMARK(slot) do { } while (0)
-#endif
-
 // Softmax of ONE row of a thin query tile by one whole warp (lane = key column mod 32), from the raw scores the tile's
 // TMEM-reading warps dumped to smem.  A thin tile (the 5 rows 128..132 of the 133-token joint sequence) would otherwise
 // cost its two TMEM-lane-bound warps a full 160 MUFU instructions for 5 live lanes, all on scheduler 0: the longest

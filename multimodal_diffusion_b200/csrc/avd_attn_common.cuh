@@ -60,6 +60,31 @@ __device__ __forceinline__ float ex2_poly(float x) {
   return __int_as_float(__float_as_int(q) + (__float_as_int(xf) << 23));
 }
 
+// Per-warp timeline of one CTA (experimental builds with -DAVD_ATT_WTRACE; tools/attn_wtrace.py): lane 0 of every warp of
+// CTA 0 stamps clock64 at slot `slot` of key blocks 3..5 into the avd_debug_trace buffer (which must hold 32 u64 per CTA).
+#ifdef AVD_ATT_WTRACE
+#define ATT_WMARK(slot)                                                                                         \
+  do {                                                                                                          \
+    if (trace != nullptr && lane == 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && j >= 3 && j < 6) { \
+      unsigned long long c_;                                                                                    \
+      asm volatile("mov.u64 %0, %%clock64;" : "=l"(c_));                                                        \
+      trace[(warp * 3 + (j - 3)) * 12 + (slot)] = c_;                                                           \
+    }                                                                                                           \
+  } while (0)
+// the same, issued only once `dep` (a float) is available: a stamp after the instruction that produces it
+#define ATT_WMARK_DEP(slot, dep)                                                                                \
+  do {                                                                                                          \
+    if (trace != nullptr && lane == 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && j >= 3 && j < 6) { \
+      unsigned long long c_;                                                                                    \
+      asm volatile("{\n\t.reg .f32 t_;\n\tmov.f32 t_, %1;\n\tmov.u64 %0, %%clock64;\n\t}" : "=l"(c_) : "f"(dep));      \
+      trace[(warp * 3 + (j - 3)) * 12 + (slot)] = c_;                                                           \
+    }                                                                                                           \
+  } while (0)
+#else
+#define ATT_WMARK(slot) do { } while (0)
+#define ATT_WMARK_DEP(slot, dep) do { } while (0)
+#endif
+
 // multi-block attention with P / O in tensor memory (avd_attn_fa.cu): 1 launched, 0 not applicable, < 0 error
 int launch_attention_fa(const void* qkv16, const AttnParams& p, int n_seq, bool f16, cudaStream_t s);
 

@@ -32,6 +32,10 @@ constexpr int FA_KV_BYTES = FA_BKV * ATT_HD * 2;            // 16 KB: [128 keys]
 constexpr int FA_THREADS = 17 * 32;
 constexpr int FA_XCHG_BYTES = (8 + 4) * 128 * 4;            // row max [2 bufs][2 tiles][2 halves][128], row sum [2][2][128]
 constexpr int FA_SMEM = 2 * ATT_Q_BYTES + FA_STAGES * 2 * FA_KV_BYTES + FA_XCHG_BYTES + 256;
+#ifndef AVD_FA_PINGPONG
+#define AVD_FA_PINGPONG 0
+#endif
+constexpr bool FA_PINGPONG = AVD_FA_PINGPONG != 0;
 constexpr float FA_RESCALE_LOG2 = 8.0f;                     // a row's reference max moves when the block max is 2^8 above it
 enum { FB_Q = 0, FB_KF = 1 /*+stage*/, FB_VF = 5 /*+stage*/, FB_KVE = 9 /*+stage*/, FB_S = 13 /*+tile*/, FB_P = 15 /*+tile*/,
        FB_O = 17 /*+tile*/, FB_COUNT = 19 };
@@ -57,6 +61,8 @@ __global__ void __launch_bounds__(FA_THREADS, 1) attn_fa_kernel(const __grid_con
   const int n_tiles = (p.N - q_first > ATT_BQ) ? 2 : 1;
   const int colQ = head * ATT_HD, colK = p.d + head * ATT_HD, colV = 2 * p.d + head * ATT_HD;
   const int nkv = (p.N + FA_BKV - 1) / FA_BKV;
+  unsigned long long* const trace = p.trace;   // per-warp stamps of -DAVD_ATT_WTRACE builds (ATT_WMARK), else unused
+  (void)trace;
 
   if (warp == 1) {
     if (lane < FB_COUNT) {
@@ -75,70 +81,86 @@ __global__ void __launch_bounds__(FA_THREADS, 1) attn_fa_kernel(const __grid_con
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);   // warp-uniform for the compiler too
   pdl_launch_dependents();
 
   if (warp == 16) {
-    // ------------------------------------------------------------------ control lane: TMA loads and every MMA
-    if (lane == 0) {
-      auto load_kv = [&](int b) {
+    // ------------------------------------------------------------------ control warp: TMA loads and every MMA
+    // The whole warp runs this code converged (all lanes wait on the barriers); one elected lane issues the tcgen05
+    // instructions (umma_*_elect), lane 0 the TMA loads.
+    auto load_kv = [&](int b) {
+      if (lane == 0) {
         const int s = b & (FA_STAGES - 1);
         uint8_t* k = sKV + s * 2 * FA_KV_BYTES;
         mbar_expect_tx(&bars[FB_KF + s], FA_KV_BYTES);
         tma_load_3d(k, &tmQKV, &bars[FB_KF + s], colK, row_base + b * FA_BKV, 0);
         mbar_expect_tx(&bars[FB_VF + s], FA_KV_BYTES);
         tma_load_3d(k + FA_KV_BYTES, &tmQKV, &bars[FB_VF + s], colV, row_base + b * FA_BKV, 0);
-      };
+      }
+      __syncwarp();
+    };
+    if (lane == 0) {
       pdl_wait();                                           // qkv comes from the previous kernel
       mbar_expect_tx(&bars[FB_Q], n_tiles * ATT_Q_BYTES);
       for (int t = 0; t < n_tiles; ++t)
         tma_load_3d(sQ + t * ATT_Q_BYTES, &tmQKV, &bars[FB_Q], colQ, row_base + q_first + t * ATT_BQ, 0);
-      for (int b = 0; b < min(2, nkv); ++b) load_kv(b);
+    }
+    __syncwarp();
+    for (int b = 0; b < min(2, nkv); ++b) load_kv(b);
 
-      const uint32_t hi = smem_desc_hi_sw128(1024);
-      const uint32_t idesc_o = make_idesc_bf16(ATT_BQ, ATT_HD, 0, 1, F16);       // B = V is MN-major
-      auto issue_s = [&](int t, int b) {                    // S_t(b) = Q_t K_b^T -> TMEM columns [256 t, 256 t + 128)
-        const int kvn = (min(FA_BKV, p.N - b * FA_BKV) + 15) & ~15;
-        const uint32_t idesc_s = make_idesc_bf16(ATT_BQ, kvn, 0, 0, F16);
-        const uint32_t q_lo = smem_desc_lo_sw128(smem_u32(sQ + t * ATT_Q_BYTES), 16);
-        const uint32_t k_lo = smem_desc_lo_sw128(smem_u32(sKV + (b & (FA_STAGES - 1)) * 2 * FA_KV_BYTES), 16);
+    const uint32_t hi = smem_desc_hi_sw128(1024);
+    const uint32_t idesc_o = make_idesc_bf16(ATT_BQ, ATT_HD, 0, 1, F16);         // B = V is MN-major
+    const uint32_t q_lo0 = smem_desc_lo_sw128(smem_u32(sQ), 16);
+    const uint32_t kv_lo0 = smem_desc_lo_sw128(smem_u32(sKV), 16);
+    auto issue_s = [&](int t, int b) {                      // S_t(b) = Q_t K_b^T -> TMEM columns [256 t, 256 t + 128)
+      const int kvn = (min(FA_BKV, p.N - b * FA_BKV) + 15) & ~15;
+      const uint32_t idesc_s = make_idesc_bf16(ATT_BQ, kvn, 0, 0, F16);
+      const uint32_t q_lo = q_lo0 + t * (ATT_Q_BYTES >> 4);
+      const uint32_t k_lo = kv_lo0 + (b & (FA_STAGES - 1)) * (2 * FA_KV_BYTES >> 4);
 #pragma unroll
-        for (int k = 0; k < ATT_HD / 16; ++k)
-          umma_bf16_lh(tmem_base + t * 256, q_lo + 2 * k, k_lo + 2 * k, hi, idesc_s, k > 0 ? 1u : 0u);
-        umma_commit(&bars[FB_S + t]);
-      };
-      mbar_wait(&bars[FB_Q], 0);
-      mbar_wait(&bars[FB_KF + 0], 0);
-      tc_fence_after();
-      for (int t = 0; t < n_tiles; ++t) issue_s(t, 0);
+      for (int k = 0; k < ATT_HD / 16; ++k)
+        umma_bf16_lh_elect(tmem_base + t * 256, q_lo + 2 * k, k_lo + 2 * k, hi, idesc_s, k > 0 ? 1u : 0u);
+      umma_commit_elect(&bars[FB_S + t]);
+    };
+    mbar_wait(&bars[FB_Q], 0);
+    mbar_wait(&bars[FB_KF + 0], 0);
+    tc_fence_after();
+    for (int t = 0; t < n_tiles; ++t) issue_s(t, 0);
 
-      for (int j = 0; j < nkv; ++j) {
-        const int s = j & (FA_STAGES - 1);
-        if (j + 2 < nkv) {                                  // the stage of block j - 2 was handed back two blocks ago
-          const int b = j + 2;
-          if (b >= FA_STAGES) mbar_wait(&bars[FB_KVE + (b & (FA_STAGES - 1))], ((b / FA_STAGES) - 1) & 1);
-          load_kv(b);
-        }
-        const int kvn = (min(FA_BKV, p.N - j * FA_BKV) + 15) & ~15;
-        const uint32_t v_lo = smem_desc_lo_sw128(smem_u32(sKV + s * 2 * FA_KV_BYTES + FA_KV_BYTES), 16);
-        for (int t = 0; t < n_tiles; ++t) {
-          mbar_wait(&bars[FB_P + t], j & 1);                // P_t(j) is in TMEM (and O_t rescaled where a row's max moved)
-          if (t == 0) mbar_wait(&bars[FB_VF + s], (j / FA_STAGES) & 1);
-          tc_fence_after();
-          const uint32_t d_o = tmem_base + t * 256 + 192, a_p = tmem_base + t * 256 + 128;
-          for (int ks = 0; ks < (kvn >> 4); ++ks)           // O_t += P_t(j) V_j: A from TMEM, 8 columns per 16 keys
-            umma_bf16_ts(d_o, a_p + ks * 8, v_lo + ks * 128, hi, idesc_o, (j > 0 || ks > 0) ? 1u : 0u);
-          if (t == n_tiles - 1) umma_commit(&bars[FB_KVE + s]);   // K_j / V_j have been read by every tile
-          if (j + 1 < nkv) {
-            if (t == 0) {
-              mbar_wait(&bars[FB_KF + ((j + 1) & (FA_STAGES - 1))], ((j + 1) / FA_STAGES) & 1);
-              tc_fence_after();
-            }
-            issue_s(t, j + 1);                              // in order behind P V_t(j): S_t(j+1) complete => O_t current
-          } else {
-            umma_commit(&bars[FB_O + t]);
+    for (int j = 0; j < nkv; ++j) {
+      const int s = j & (FA_STAGES - 1);
+      if (j + 2 < nkv) {                                    // the stage of block j - 2 was handed back two blocks ago
+        const int b = j + 2;
+        if (b >= FA_STAGES) mbar_wait(&bars[FB_KVE + (b & (FA_STAGES - 1))], ((b / FA_STAGES) - 1) & 1);
+        load_kv(b);
+      }
+      const int kvn = (min(FA_BKV, p.N - j * FA_BKV) + 15) & ~15;
+      const uint32_t v_lo = kv_lo0 + ((s * 2 * FA_KV_BYTES + FA_KV_BYTES) >> 4);
+      for (int t = 0; t < n_tiles; ++t) {
+        mbar_wait(&bars[FB_P + t], j & 1);                  // P_t(j) is in TMEM (and O_t rescaled where a row's max moved)
+        if (t == 0) mbar_wait(&bars[FB_VF + s], (j / FA_STAGES) & 1);
+        tc_fence_after();
+        ATT_WMARK(t * 3);
+        if (j + 1 < nkv) {                                  // S_t(j+1) first: the tile's next softmax pass waits for it
+          if (t == 0) {
+            mbar_wait(&bars[FB_KF + ((j + 1) & (FA_STAGES - 1))], ((j + 1) / FA_STAGES) & 1);
+            tc_fence_after();
           }
+          issue_s(t, j + 1);
+          ATT_WMARK(t * 3 + 1);
         }
+        const uint32_t d_o = tmem_base + t * 256 + 192, a_p = tmem_base + t * 256 + 128;
+        if (kvn == FA_BKV) {
+#pragma unroll
+          for (int ks = 0; ks < FA_BKV / 16; ++ks)          // O_t += P_t(j) V_j: A from TMEM, 8 columns per 16 keys
+            umma_bf16_ts_elect(d_o, a_p + ks * 8, v_lo + ks * 128, hi, idesc_o, (j > 0 || ks > 0) ? 1u : 0u);
+        } else {
+          for (int ks = 0; ks < (kvn >> 4); ++ks)
+            umma_bf16_ts_elect(d_o, a_p + ks * 8, v_lo + ks * 128, hi, idesc_o, (j > 0 || ks > 0) ? 1u : 0u);
+        }
+        umma_commit_elect(&bars[FB_O + t]);                 // P_t(j) has been read, O_t is current (phase j)
+        if (t == n_tiles - 1) umma_commit_elect(&bars[FB_KVE + s]);   // K_j / V_j have been read by every tile
+        ATT_WMARK(t * 3 + 2);
       }
     }
   } else if ((warp >> 3) < n_tiles && q_first + (warp >> 3) * ATT_BQ + (warp & 3) * 32 < p.N) {
@@ -163,6 +185,16 @@ __global__ void __launch_bounds__(FA_THREADS, 1) attn_fa_kernel(const __grid_con
       float* xm = xmax + ((ph * 2 + t) * 2) * 128;
       // one pass over this thread's (up to) two 32-score chunks: block max over the valid keys and, with EXP, the
       // exponentials against the reference max `neg_m_sc` -> P columns (tcgen05.st) and the partial row sum
+      // P V_t(j-1) reads the P columns and updates O_t behind S_t(j) on the tensor pipe: before this block's first P store
+      // (or O rescale) it must have completed -- by then it normally has
+      bool pv_seen = (j == 0);
+      auto pv_done = [&]() {
+        if (!pv_seen) {
+          mbar_wait(&bars[FB_O + t], ph ^ 1);
+          tc_fence_after();
+          pv_seen = true;
+        }
+      };
       auto pass = [&](auto exp_tag, float neg_m_sc, float& l_blk) -> float {
         constexpr bool EXP = decltype(exp_tag)::value;
         float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
@@ -174,20 +206,18 @@ __global__ void __launch_bounds__(FA_THREADS, 1) attn_fa_kernel(const __grid_con
             uint32_t x[32];
             tmem_ld_32x32(tmem_S + i * 32, x);
             tmem_ld_wait();
+            if (EXP) ATT_WMARK(6 + 3 * i);
             const uint32_t vb = valid_bits(j, sp * 2 + i, lim);
+            if (vb != 0xffffffffu) {                        // padded / out-of-sequence keys: score -inf, probability 0
+#pragma unroll
+              for (int c = 0; c < 32; ++c)
+                if (!((vb >> c) & 1u)) x[c] = 0xff800000u;
+            }
             float e[32];
             if (EXP) ex2_chunk(x, sc, neg_m_sc, e);
-            if (vb == 0xffffffffu) {
+            if (EXP) ATT_WMARK_DEP(7 + 3 * i, e[31]);
 #pragma unroll
-              for (int c = 0; c < 32; ++c) mx[c & 3] = fmaxf(mx[c & 3], __uint_as_float(x[c]));
-            } else {
-#pragma unroll
-              for (int c = 0; c < 32; ++c) {
-                const bool v = (vb >> c) & 1u;
-                mx[c & 3] = fmaxf(mx[c & 3], v ? __uint_as_float(x[c]) : -INFINITY);
-                if (EXP) e[c] = v ? e[c] : 0.0f;
-              }
-            }
+            for (int c = 0; c < 32; ++c) mx[c & 3] = fmaxf(mx[c & 3], __uint_as_float(x[c]));
             if (EXP) {
               float l0 = 0.0f, l1 = 0.0f;
               uint32_t w[16];
@@ -198,14 +228,25 @@ __global__ void __launch_bounds__(FA_THREADS, 1) attn_fa_kernel(const __grid_con
                 w[c >> 1] = F16 ? pack_f16x2(e[c], e[c + 1]) : pack_bf16x2(e[c], e[c + 1]);
               }
               l_blk += l0 + l1;
+              pv_done();
               tmem_st_32x16(tmem_P + i * 16, w);
+              ATT_WMARK_DEP(8 + 3 * i, l_blk);
             }
           }
         }
         return fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
       };
+      ATT_WMARK(0);
       mbar_wait(&bars[FB_S + t], ph);
       tc_fence_after();
+      ATT_WMARK(1);
+      if (FA_PINGPONG && n_tiles == 2) {
+        // The two tiles' softmax passes ALTERNATE: tile 1 starts block j when tile 0 has staged P(j), tile 0 starts block
+        // j + 1 when tile 1 has staged P(j).  Free-running, both tiles sit in their MUFU-bound passes at the same time and
+        // then both wait for their MMAs; alternating, one tile's P V / S MMAs run under the other's exponentials.
+        if (t == 1) mbar_wait(&bars[FB_P + 0], ph);
+        else if (j > 0) mbar_wait(&bars[FB_P + 1], ph ^ 1);
+      }
       // Speculate that the reference max stays: exponentials against the carried m_run in the same pass that finds the
       // block max (no pair exchange between the TMEM load and the MUFU work).  A warp with a row that has no reference yet
       // (first block, or only padded keys so far) finds the max first.  Both warps of a pair hold the same rows and the same
@@ -214,8 +255,10 @@ __global__ void __launch_bounds__(FA_THREADS, 1) attn_fa_kernel(const __grid_con
       float l_blk = 0.0f, m_part;
       if (spec) m_part = pass(std::true_type{}, -m_run * sc, l_blk);
       else m_part = pass(std::false_type{}, 0.0f, l_blk);
+      ATT_WMARK(2);
       xm[sp * 128 + r] = m_part;
       named_bar_sync(pair_bar, 64);
+      ATT_WMARK(3);
       const float m_row = fmaxf(m_part, xm[(sp ^ 1) * 128 + r]);
       // the reference max moves only when it must: first live block of the row, or the block max is 2^8 above it (P stays
       // inside fp16, the row sum well conditioned)
@@ -228,7 +271,8 @@ __global__ void __launch_bounds__(FA_THREADS, 1) attn_fa_kernel(const __grid_con
           m_run = m_row;
           l_run *= alpha;
         }
-        if (j > 0) {                                        // S_t(j) complete => P V_t(j-1) complete: O_t is current
+        if (j > 0) {
+          pv_done();                                        // O_t is current
           uint32_t o[32];
           tmem_ld_32x32(tmem_O, o);
           tmem_ld_wait();
@@ -242,14 +286,16 @@ __global__ void __launch_bounds__(FA_THREADS, 1) attn_fa_kernel(const __grid_con
         const float neg_m_sc = m_run == -INFINITY ? 0.0f : -m_run * sc;   // every key so far padded: exponents stay finite
         (void)pass(std::true_type{}, neg_m_sc, l_blk);
       }
+      ATT_WMARK(4);
       l_run += l_blk;
       tmem_st_wait();
       tc_fence_before();    // S has been read, P (and a rescaled O) written: the tile's next MMAs may go
       mbar_arrive(&bars[FB_P + t]);
+      ATT_WMARK(5);
     }
 
     // ---- O_t complete; total row sum = the two halves' partial sums; normalise this thread's 32 output columns
-    mbar_wait(&bars[FB_O + t], 0);
+    mbar_wait(&bars[FB_O + t], (nkv - 1) & 1);
     tc_fence_after();
     float rem[32];
     {
@@ -337,7 +383,9 @@ int launch_attention_fa(const void* qkv16, const AttnParams& p, int n_seq, bool 
   cfg.attrs = attrs;
   cfg.numAttrs = na;
   AttnParams q = p;
+#ifndef AVD_ATT_WTRACE
   q.trace = nullptr;
+#endif
   AVD_CUDA(cudaLaunchKernelEx(&cfg, fn, tm, q));
   return 1;
 }

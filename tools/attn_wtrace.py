@@ -26,6 +26,7 @@ def main() -> None:
     ap.add_argument("--N", type=int, default=2048)
     ap.add_argument("--seq", type=int, default=16)
     ap.add_argument("--bf16", action="store_true")
+    ap.add_argument("--blk", type=int, default=1, help="0..2: which of the key blocks 3, 4, 5 to print")
     args = ap.parse_args()
     lib = _lib.load()
     dev = torch.device("cuda:0")
@@ -46,25 +47,44 @@ def main() -> None:
     _lib.check(lib.avd_debug_trace(buf.data_ptr(), buf.numel()))
     run()
     _lib.check(lib.avd_debug_trace(None, 0))
-    t = buf[:16 * 3 * 12].view(16, 3, 12).cpu()
+    t = buf[:17 * 3 * 12].view(17, 3, 12).cpu()
     if int(t.max()) == 0:
         print("no stamps: library not built with -DAVD_ATT_WTRACE, or the single-block kernel ran")
         return
-    t0 = int(t[:, 1, 0][t[:, 1, 0] > 0].min())
+    B = args.blk
+    t0 = int(t[:, B, 0][t[:, B, 0] > 0].min())
     print(f"attention {args.seq} seq x {args.N} keys x {H} heads, CTA 0, key block 4; cycles since the first warp's block top")
     print("warp tile half quad | " + " ".join(f"{n:>13s}" for n in NAMES) + " |  period(3->4) period(4->5)")
+    if _lib.get_option("attn_fa") != 0:
+        names = ["top", "S ready", "pass done", "max exchanged", "rescale/repeat", "P arrived"]
+        print("warp tile half quad | " + " ".join(f"{n:>14s}" for n in names) + " |  period(3->4) period(4->5)")
+        for w in range(16):
+            if int(t[w, B, 0]) == 0:
+                continue
+            row = " ".join(f"{int(t[w, B, sl]) - t0:14d}" for sl in range(6))
+            print(f"{w:4d} {w >> 3:4d} {(w >> 2) & 1:4d} {w & 3:4d} | {row} | {int(t[w, B, 0] - t[w, 0, 0]):13d} "
+                  f"{int(t[w, 2, 0] - t[w, B, 0]):12d}")
+        print("inside the pass:    chunk 0: ld done, exps done, P stored | chunk 1: ld done, exps done, P stored")
+        for w in range(16):
+            if int(t[w, B, 0]) == 0:
+                continue
+            print(f"{w:4d}                | " + " ".join(f"{int(t[w, B, sl]) - t0:10d}" for sl in range(6, 12)))
+        c = [int(t[16, B, sl]) - t0 for sl in range(6)]
+        print(f"control lane: tile 0: P/V there {c[0]}, S(j+1) issued {c[1]}, PV issued {c[2]} | tile 1: P there {c[3]}, "
+              f"S(j+1) issued {c[4]}, PV issued {c[5]} | period {int(t[16, 2, 0] - t[16, 1, 0])}")
+        return
     for w in range(16):
-        if int(t[w, 1, 0]) == 0:
+        if int(t[w, B, 0]) == 0:
             continue
         row = []
         for sl in range(9):
-            v = int(t[w, 1, sl])
+            v = int(t[w, B, sl])
             row.append(f"{v - t0:13d}" if v > 0 else f"{'-':>13s}")
-        p34 = int(t[w, 1, 0] - t[w, 0, 0])
-        p45 = int(t[w, 2, 0] - t[w, 1, 0])
+        p34 = int(t[w, B, 0] - t[w, 0, 0])
+        p45 = int(t[w, 2, 0] - t[w, B, 0])
         print(f"{w:4d} {w >> 3:4d} {(w >> 2) & 1:4d} {w & 3:4d} | " + " ".join(row) + f" | {p34:13d} {p45:12d}")
         if (w & 7) == 0:                      # the tile's MMA issuer
-            a, b, c, d = (int(t[w, 1, sl]) - t0 for sl in (9, 10, 11, 6))
+            a, b, c, d = (int(t[w, B, sl]) - t0 for sl in (9, 10, 11, 6))
             print(f"      issuer: P/V/R waits over {a}, PV issued+committed {b}, K(j+1) there {c}, S(j+1) issued+committed {d}")
 
 
