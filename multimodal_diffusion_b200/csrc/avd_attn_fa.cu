@@ -29,19 +29,28 @@ namespace avd {
 constexpr int FA_BKV = 128;
 constexpr int FA_STAGES = 4;
 constexpr int FA_KV_BYTES = FA_BKV * ATT_HD * 2;            // 16 KB: [128 keys][64] 16-bit, 128B swizzle
-constexpr int FA_THREADS = 17 * 32;
+constexpr int FA_THREADS = 17 * 32;                          // SW = 8: two softmax warps per TMEM lane quadrant and tile
+constexpr int FA_THREADS_ROW = 9 * 32;                       // SW = 4: one softmax thread per query row
 constexpr int FA_XCHG_BYTES = (8 + 4) * 128 * 4;            // row max [2 bufs][2 tiles][2 halves][128], row sum [2][2][128]
 constexpr int FA_SMEM = 2 * ATT_Q_BYTES + FA_STAGES * 2 * FA_KV_BYTES + FA_XCHG_BYTES + 256;
 #ifndef AVD_FA_PINGPONG
 #define AVD_FA_PINGPONG 0
 #endif
 constexpr bool FA_PINGPONG = AVD_FA_PINGPONG != 0;
+#ifndef AVD_FA_INTERLEAVE
+#define AVD_FA_INTERLEAVE 0
+#endif
+constexpr bool FA_INTERLEAVE = AVD_FA_INTERLEAVE != 0;
+#ifndef AVD_FA_POLY
+#define AVD_FA_POLY 0
+#endif
+constexpr int FA_POLY = AVD_FA_POLY;
 constexpr float FA_RESCALE_LOG2 = 8.0f;                     // a row's reference max moves when the block max is 2^8 above it
 enum { FB_Q = 0, FB_KF = 1 /*+stage*/, FB_VF = 5 /*+stage*/, FB_KVE = 9 /*+stage*/, FB_S = 13 /*+tile*/, FB_P = 15 /*+tile*/,
        FB_O = 17 /*+tile*/, FB_COUNT = 19 };
 
-template <bool F16, bool MASKED>
-__global__ void __launch_bounds__(FA_THREADS, 1) attn_fa_kernel(const __grid_constant__ CUtensorMap tmQKV,
+template <bool F16, bool MASKED, int SW>
+__global__ void __launch_bounds__((2 * SW + 1) * 32, 1) attn_fa_kernel(const __grid_constant__ CUtensorMap tmQKV,
                                                                 const AttnParams p) {
   extern __shared__ __align__(1024) uint8_t fa_smem[];
   uint8_t* smem = fa_smem;
@@ -69,7 +78,7 @@ __global__ void __launch_bounds__(FA_THREADS, 1) attn_fa_kernel(const __grid_con
       uint32_t count = 1;
       if (lane >= FB_P && lane < FB_O) {                    // arrivals: the warp pairs of the tile that own valid query rows
         const int rows = min(ATT_BQ, p.N - q_first - (lane - FB_P) * ATT_BQ);
-        count = rows > 0 ? 64 * ((rows + 31) >> 5) : 1;
+        count = rows > 0 ? (SW * 8) * ((rows + 31) >> 5) : 1;
       }
       mbar_init(&bars[lane], count);
     }
@@ -84,7 +93,7 @@ __global__ void __launch_bounds__(FA_THREADS, 1) attn_fa_kernel(const __grid_con
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);   // warp-uniform for the compiler too
   pdl_launch_dependents();
 
-  if (warp == 16) {
+  if (warp == 2 * SW) {
     // ------------------------------------------------------------------ control warp: TMA loads and every MMA
     // The whole warp runs this code converged (all lanes wait on the barriers); one elected lane issues the tcgen05
     // instructions (umma_*_elect), lane 0 the TMA loads.
@@ -163,8 +172,200 @@ __global__ void __launch_bounds__(FA_THREADS, 1) attn_fa_kernel(const __grid_con
         ATT_WMARK(t * 3 + 2);
       }
     }
-  } else if ((warp >> 3) < n_tiles && q_first + (warp >> 3) * ATT_BQ + (warp & 3) * 32 < p.N) {
-    // ------------------------------------------------------------------ softmax + output of query tile t
+  } else if (SW == 4 && (warp >> 2) < n_tiles && q_first + (warp >> 2) * ATT_BQ + (warp & 3) * 32 < p.N) {
+    // ------------------------------------------------------------------ softmax + output of query tile t, one THREAD per row
+    // 128 scores of a block live in this thread's registers: the row max needs no exchange, the exponentials run as one
+    // interleaved stream (MUFU c, sum / pack of c - 8), and with two warps per scheduler the two tiles alternate between
+    // their MUFU-bound pass and the wait for their MMAs.
+    const int t = warp >> 2, quad = warp & 3;
+    const uint32_t tmem_T = tmem_base + t * 256 + ((uint32_t)(quad * 32) << 16);
+    const float sc = p.scale_log2e;
+    float m_run = -INFINITY, l_run = 0.0f;
+    for (int j = 0; j < nkv; ++j) {
+      const uint32_t ph = j & 1;
+      const int kv_valid = min(FA_BKV, p.N - j * FA_BKV);
+      ATT_WMARK(0);
+      mbar_wait(&bars[FB_S + t], ph);
+      tc_fence_after();
+      ATT_WMARK(1);
+      bool pv_seen = (j == 0);
+      auto pv_done = [&]() {                                // P V_t(j-1) has read P and updated O (see the SW = 8 branch)
+        if (!pv_seen) {
+          mbar_wait(&bars[FB_O + t], ph ^ 1);
+          tc_fence_after();
+          pv_seen = true;
+        }
+      };
+      // one pass over the row's (up to) four 32-score chunks, the next chunk's tcgen05.ld in flight under the current one's
+      // arithmetic: block max over the valid keys and, with EXP, the exponentials against `neg_m_sc` as ONE interleaved
+      // stream (MUFU c, max of score c, sum / pack of exponential c - 8) -> P columns, partial row sum
+      auto pass = [&](auto exp_tag, float neg_m_sc, float& l_blk) -> float {
+        constexpr bool EXP = decltype(exp_tag)::value;
+        float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+        float l0 = 0.0f, l1 = 0.0f;
+        uint32_t x0[32], x1[32], x2[32];                     // chunk i lives in x{i % 3}: exponentials / raw scores / in flight
+        auto mask = [&](int i, uint32_t (&x)[32]) {          // padded / out-of-sequence keys: score -inf, probability 0
+          const int lim = kv_valid - i * 32;                 // (<= 0: a chunk past the keys of a ragged last block -- stale TMEM)
+          uint32_t vb = lim >= 32 ? 0xffffffffu : (lim > 0 ? ((1u << lim) - 1u) : 0u);
+          if (MASKED && lim > 0) vb &= ~p.kmask[(size_t)blockIdx.z * p.kmask_words + j * (FA_BKV / 32) + i];
+          if (vb != 0xffffffffu) {
+#pragma unroll
+            for (int c = 0; c < 32; ++c)
+              if (!((vb >> c) & 1u)) x[c] = 0xff800000u;
+          }
+        };
+        // max of raw score c and its exponential (in place)
+        auto expo = [&](uint32_t (&x)[32], int c) {
+          mx[c & 3] = fmaxf(mx[c & 3], __uint_as_float(x[c]));
+          if (EXP) {
+            const float a = fmaf(__uint_as_float(x[c]), sc, neg_m_sc);
+            float e;
+            asm volatile("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(a));
+            x[c] = __float_as_uint(e);
+          }
+        };
+        // row sum and 16-bit pack of exponentials c, c + 1 of a chunk whose MUFU work finished a chunk ago
+        auto post = [&](const uint32_t (&e)[32], int c, uint32_t (&w)[16]) {
+          l0 += __uint_as_float(e[c]);
+          l1 += __uint_as_float(e[c + 1]);
+          w[c >> 1] = F16 ? pack_f16x2(__uint_as_float(e[c]), __uint_as_float(e[c + 1]))
+                          : pack_bf16x2(__uint_as_float(e[c]), __uint_as_float(e[c + 1]));
+        };
+        // chunk i (exponentials in `cur`): its sums / packs run between the exponentials of chunk i + 1 (raw scores landing
+        // in `nxt`) while chunk i + 2 is fetched into `pre` -- nothing in the stream waits for a MUFU result less than a
+        // chunk old
+        // All four chunks are always processed (straight-line code keeps the three buffers in registers): in a ragged last
+        // block the chunks past the keys read stale TMEM, are masked to -inf and store zeros that P V (K = round16(keys)) never reads.
+        auto step = [&](int i, uint32_t (&cur)[32], uint32_t (&nxt)[32], uint32_t (&pre)[32]) {
+          uint32_t w[16];
+          if (i + 1 < 4) {
+            tmem_ld_wait();                                  // chunk i + 1 has landed
+            if (i + 2 < 4) tmem_ld_32x32(tmem_T + (i + 2) * 32, pre);
+            mask(i + 1, nxt);
+#pragma unroll
+            for (int c = 0; c < 32; c += 2) {
+              expo(nxt, c);
+              expo(nxt, c + 1);
+              if (EXP) post(cur, c, w);
+            }
+          } else if (EXP) {
+#pragma unroll
+            for (int c = 0; c < 32; c += 2) post(cur, c, w);
+          }
+          if (EXP) {
+            if (i == 0) pv_done();
+            tmem_st_32x16(tmem_T + 128 + i * 16, w);
+          }
+        };
+        tmem_ld_32x32(tmem_T, x0);
+        tmem_ld_wait();
+        tmem_ld_32x32(tmem_T + 32, x1);
+        mask(0, x0);
+#pragma unroll
+        for (int c = 0; c < 32; ++c) expo(x0, c);
+        step(0, x0, x1, x2);
+        step(1, x1, x2, x0);
+        step(2, x2, x0, x1);
+        step(3, x0, x1, x2);
+        l_blk = l0 + l1;
+        return fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
+      };
+      // speculate that the reference max stays (exponentials in the same pass that finds the block max); a warp with a
+      // row that has no reference yet finds the max first
+      const bool spec = !__any_sync(0xffffffffu, m_run == -INFINITY);
+      float l_blk = 0.0f;
+      const float m_row = spec ? pass(std::true_type{}, -m_run * sc, l_blk) : pass(std::false_type{}, 0.0f, l_blk);
+      ATT_WMARK(2);
+      // the reference max moves only when it must: first live block of the row, or the block max is 2^8 above it
+      const bool need = m_row != -INFINITY && (m_run == -INFINITY || (m_row - m_run) * sc > FA_RESCALE_LOG2);
+      bool have_p = spec;
+      if (__any_sync(0xffffffffu, need)) {
+        float alpha = 1.0f;
+        if (need) {
+          alpha = ex2_approx((m_run - m_row) * sc);
+          m_run = m_row;
+          l_run *= alpha;
+        }
+        if (j > 0) {
+          pv_done();
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            uint32_t o[32];
+            tmem_ld_32x32(tmem_T + 192 + h * 32, o);
+            tmem_ld_wait();
+#pragma unroll
+            for (int c = 0; c < 32; ++c) o[c] = __float_as_uint(__uint_as_float(o[c]) * alpha);
+            tmem_st_32x32(tmem_T + 192 + h * 32, o);
+          }
+        }
+        have_p = false;
+      }
+      ATT_WMARK(3);
+      if (!have_p) {
+        const float neg_m_sc = m_run == -INFINITY ? 0.0f : -m_run * sc;
+        (void)pass(std::true_type{}, neg_m_sc, l_blk);
+      }
+      l_run += l_blk;
+      ATT_WMARK(4);
+      tmem_st_wait();
+      tc_fence_before();    // S has been read, P (and a rescaled O) written: the tile's next MMAs may go
+      mbar_arrive(&bars[FB_P + t]);
+      ATT_WMARK(5);
+    }
+
+    // ---- O_t complete: normalise this thread's row, stage the warp's 32 rows x 128 B in the retired Q tile, coalesced stores
+    mbar_wait(&bars[FB_O + t], (nkv - 1) & 1);
+    tc_fence_after();
+    float rem[64];
+    {
+      const float inv_l = 1.0f / l_run;
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        uint32_t o[32];
+        tmem_ld_32x32(tmem_T + 192 + h * 32, o);
+        tmem_ld_wait();
+#pragma unroll
+        for (int c = 0; c < 32; ++c) rem[h * 32 + c] = __uint_as_float(o[c]) * inv_l;
+      }
+    }
+    const int64_t seg_stride = p.M * (int64_t)p.d;
+    uint8_t* stage = sQ + t * ATT_Q_BYTES + quad * 32 * 128;
+    const int q_tile0 = q_first + t * ATT_BQ + quad * 32;          // first query row of this warp
+    for (int sg = 0; sg < p.out_nseg; ++sg) {
+#pragma unroll
+      for (int v8 = 0; v8 < 8; ++v8) {
+        uint32_t w[4];
+        if (p.out_nseg == 1) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            w[k] = F16 ? pack_f16x2(rem[v8 * 8 + k * 2], rem[v8 * 8 + k * 2 + 1])
+                       : pack_bf16x2(rem[v8 * 8 + k * 2], rem[v8 * 8 + k * 2 + 1]);
+        } else {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const int c = v8 * 8 + k * 2;
+            const __nv_bfloat16 h0 = __float2bfloat16_rn(rem[c]);
+            const __nv_bfloat16 h1 = __float2bfloat16_rn(rem[c + 1]);
+            rem[c] -= __bfloat162float(h0);
+            rem[c + 1] -= __bfloat162float(h1);
+            w[k] = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
+          }
+        }
+        *reinterpret_cast<uint4*>(stage + lane * 128 + ((v8 ^ (lane & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+      }
+      __syncwarp();
+      const int rr = lane >> 3, cc = lane & 7;
+      __nv_bfloat16* gp = p.out + sg * seg_stride + ((int64_t)row_base + q_tile0) * p.d + head * ATT_HD + cc * 8;
+#pragma unroll
+      for (int it = 0; it < 8; ++it) {
+        const int rw = it * 4 + rr;
+        const uint4 x4 = *reinterpret_cast<const uint4*>(stage + rw * 128 + ((cc ^ (rw & 7)) << 4));
+        if (q_tile0 + rw < p.N) *reinterpret_cast<uint4*>(gp + (int64_t)rw * p.d) = x4;
+      }
+      if (sg + 1 < p.out_nseg) __syncwarp();
+    }
+  } else if (SW == 8 && (warp >> 3) < n_tiles && q_first + (warp >> 3) * ATT_BQ + (warp & 3) * 32 < p.N) {
+    // ------------------------------------------------------------------ softmax + output of query tile t, two warps per row group
     const int t = warp >> 3, sp = (warp >> 2) & 1, quad = warp & 3;
     const int r = quad * 32 + lane;                         // row inside the tile == TMEM lane
     const uint32_t tmem_T = tmem_base + t * 256 + ((uint32_t)(quad * 32) << 16);
@@ -214,18 +415,57 @@ __global__ void __launch_bounds__(FA_THREADS, 1) attn_fa_kernel(const __grid_con
                 if (!((vb >> c) & 1u)) x[c] = 0xff800000u;
             }
             float e[32];
-            if (EXP) ex2_chunk(x, sc, neg_m_sc, e);
-            if (EXP) ATT_WMARK_DEP(7 + 3 * i, e[31]);
+            if (!EXP || !FA_INTERLEAVE) {
+              if (EXP) {
+                if (FA_POLY == 0) {
+                  ex2_chunk(x, sc, neg_m_sc, e);
+                } else {                                    // every FA_POLY-th exponential on the FMA pipe (ex2_poly)
 #pragma unroll
-            for (int c = 0; c < 32; ++c) mx[c & 3] = fmaxf(mx[c & 3], __uint_as_float(x[c]));
+                  for (int c = 0; c < 32; ++c) {
+                    const float a = fmaf(__uint_as_float(x[c]), sc, neg_m_sc);
+                    if (c % FA_POLY == FA_POLY - 1) e[c] = ex2_poly(a);
+                    else asm volatile("ex2.approx.ftz.f32 %0, %1;" : "=f"(e[c]) : "f"(a));
+                  }
+                }
+                ATT_WMARK_DEP(7 + 3 * i, e[31]);
+              }
+#pragma unroll
+              for (int c = 0; c < 32; ++c) mx[c & 3] = fmaxf(mx[c & 3], __uint_as_float(x[c]));
+            }
             if (EXP) {
               float l0 = 0.0f, l1 = 0.0f;
               uint32_t w[16];
+              if (FA_INTERLEAVE) {
+                // one instruction stream with the MUFU work spread through it: exponential c, the max of score c, and the
+                // sum / pack of exponential c - 8 (whose MUFU result has landed) -- the warp's ALU work runs under its own
+                // MUFU occupancy instead of after it
+                constexpr int D = 8;
 #pragma unroll
-              for (int c = 0; c < 32; c += 2) {
-                l0 += e[c];
-                l1 += e[c + 1];
-                w[c >> 1] = F16 ? pack_f16x2(e[c], e[c + 1]) : pack_bf16x2(e[c], e[c + 1]);
+                for (int c = 0; c < 32 + D; ++c) {
+                  if (c < 32) {
+                    const float a = fmaf(__uint_as_float(x[c]), sc, neg_m_sc);
+                    asm volatile("ex2.approx.ftz.f32 %0, %1;" : "=f"(e[c]) : "f"(a));
+                    asm volatile("max.f32 %0, %0, %1;" : "+f"(mx[c & 3]) : "f"(__uint_as_float(x[c])));
+                  }
+                  if (c >= D) {
+                    const int k = c - D;
+                    if (k & 1) {
+                      asm volatile("add.f32 %0, %0, %1;" : "+f"(l1) : "f"(e[k]));
+                      if (F16) asm volatile("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(w[k >> 1]) : "f"(e[k]), "f"(e[k - 1]));
+                      else asm volatile("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(w[k >> 1]) : "f"(e[k]), "f"(e[k - 1]));
+                    } else {
+                      asm volatile("add.f32 %0, %0, %1;" : "+f"(l0) : "f"(e[k]));
+                    }
+                  }
+                }
+                ATT_WMARK_DEP(7 + 3 * i, l1);
+              } else {
+#pragma unroll
+                for (int c = 0; c < 32; c += 2) {
+                  l0 += e[c];
+                  l1 += e[c + 1];
+                  w[c >> 1] = F16 ? pack_f16x2(e[c], e[c + 1]) : pack_bf16x2(e[c], e[c + 1]);
+                }
               }
               l_blk += l0 + l1;
               pv_done();
@@ -364,13 +604,17 @@ int launch_attention_fa(const void* qkv16, const AttnParams& p, int n_seq, bool 
   AVD_TRY(get_tensor_map_3d(qkv16, 2, (uint64_t)3 * d, (uint64_t)p.M, 1, (uint64_t)3 * d * 2, (uint64_t)p.M * 3 * d * 2,
                             ATT_HD, ATT_BQ, &tm));
   using Fn = void (*)(const CUtensorMap, const AttnParams);
-  static const Fn kernels[2][2] = {{attn_fa_kernel<false, false>, attn_fa_kernel<false, true>},
-                                   {attn_fa_kernel<true, false>, attn_fa_kernel<true, true>}};
-  const Fn fn = kernels[f16 ? 1 : 0][p.kmask != nullptr ? 1 : 0];
+  static const Fn kernels[2][2][2] = {
+      {{attn_fa_kernel<false, false, 8>, attn_fa_kernel<false, true, 8>},
+       {attn_fa_kernel<true, false, 8>, attn_fa_kernel<true, true, 8>}},
+      {{attn_fa_kernel<false, false, 4>, attn_fa_kernel<false, true, 4>},
+       {attn_fa_kernel<true, false, 4>, attn_fa_kernel<true, true, 4>}}};
+  const bool row = options().attn_fa == 2;                  // one softmax thread per query row
+  const Fn fn = kernels[row ? 1 : 0][f16 ? 1 : 0][p.kmask != nullptr ? 1 : 0];
   AVD_TRY(ensure_dyn_smem(reinterpret_cast<const void*>(fn), FA_SMEM));
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3((p.N + 2 * ATT_BQ - 1) / (2 * ATT_BQ), p.n_heads, n_seq);
-  cfg.blockDim = dim3(FA_THREADS);
+  cfg.blockDim = dim3(row ? FA_THREADS_ROW : FA_THREADS);
   cfg.dynamicSmemBytes = FA_SMEM;
   cfg.stream = s;
   cudaLaunchAttribute attrs[1];

@@ -232,18 +232,20 @@ def test_attention_multiblock_rising_max(dev, lib, N, ramp, f16):
                                               (2, 1000, False, 0.0), (1, 257, True, 0.0), (2, 384, False, 0.0),
                                               (1, 640, True, 0.0), (2, 1000, True, 10.0), (2, 1000, False, 60.0),
                                               (1, 2048, True, 25.0), (1, 16384, True, 0.0)])
-def test_attention_tmem_resident_kernel(dev, lib, n_seq, N, f16, ramp):
+@pytest.mark.parametrize("fa", [1, 2])
+def test_attention_tmem_resident_kernel(dev, lib, n_seq, N, f16, ramp, fa):
     """attn_fa_kernel (option attn_fa; N > 192): P written to tensor memory and used as the A operand of P V, O accumulated
     in tensor memory and rescaled in place only when a row's max rises by more than 2^8, 128-key blocks through a 4-stage
     K / V ring.  Ragged last blocks (445 = 3 x 128 + 61, 193, 257: a one-row second query tile), scores that climb along
     the keys (in-place rescales in every block), 128 key blocks."""
     from multimodal_diffusion_b200 import _lib
-    with _lib.option("attn_fa", 1):
+    with _lib.option("attn_fa", fa):          # 1: two softmax warps per row group, 2: one softmax thread per query row
         _attn_check(dev, lib, n_seq, N, f16, 1.5e-3 if f16 else 8e-3, key_ramp=ramp)
 
 
+@pytest.mark.parametrize("fa", [1, 2])
 @pytest.mark.parametrize("N", [445, 1000])
-def test_attention_tmem_resident_kernel_with_key_mask(dev, lib, N):
+def test_attention_tmem_resident_kernel_with_key_mask(dev, lib, N, fa):
     """key_padding_mask through attn_fa_kernel against the two-pass multi-block kernel: ragged tails, scattered padded keys,
     a fully padded 32-key chunk and a fully padded 128-key block."""
     from multimodal_diffusion_b200 import _lib, packing
@@ -259,7 +261,7 @@ def test_attention_tmem_resident_kernel_with_key_mask(dev, lib, N):
     for dt, prec, tol in ((torch.float16, _lib.AVD_PREC_F16, 1.5e-3), (torch.bfloat16, _lib.AVD_PREC_BF16, 8e-3)):
         qkv = (randn(6, n_seq * N, 3 * H * hd) * 1.5).to(dt).to(dev)
         outs = []
-        for opt in (0, 1):
+        for opt in (0, fa):
             out = torch.zeros(1, n_seq * N, H * hd, device=dev, dtype=dt)
             with _lib.option("attn_fa", opt):
                 _lib.check(lib.avd_attention_masked(qkv.data_ptr(), 0, out.data_ptr(), prec, n_seq, N, H, hd,
