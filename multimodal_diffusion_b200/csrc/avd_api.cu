@@ -181,7 +181,7 @@ static const OptionDesc kOptions[] = {
     {"attn_poly", "AVD_ATTN_POLY", &Options::attn_poly, 0},
     {"attn_small", "AVD_ATTN_SMALL", &Options::attn_small, 1},
     {"attn_pipe", "AVD_ATTN_PIPE", &Options::attn_pipe, 0},
-    {"attn_fa", "AVD_ATTN_FA", &Options::attn_fa, 0},
+    {"attn_fa", "AVD_ATTN_FA", &Options::attn_fa, 1},
     {"attn_one", "AVD_ATTN_ONE", &Options::attn_one, 1},
     {"chains", "AVD_CHAINS", &Options::chains, 1},
     {"bx_wide", "AVD_BX_WIDE", &Options::bx_wide, -1},

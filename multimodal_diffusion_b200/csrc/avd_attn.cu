@@ -1325,7 +1325,7 @@ int launch_attention_tc(const void* qkv_bf16, void* out, int out_nseg, int n_seq
     AVD_CUDA(cudaLaunchKernelEx(&cfg, sf, tmQ, tmQ8, tmKVs, p));
     return 0;
   }
-  if (N > ATT_BKV && options().attn_fa != 0) {       // multi-block: P and O resident in tensor memory (avd_attn_fa.cu)
+  if (N > ATT_BKV && options().attn_fa != 0 && options().attn_pipe == 0) {   // multi-block: P and O resident in tensor memory (avd_attn_fa.cu)
     const int rc = launch_attention_fa(qkv_bf16, p, n_seq, f16, s);
     if (rc != 0) return rc < 0 ? rc : 0;
   }

@@ -597,12 +597,379 @@ __global__ void __launch_bounds__((2 * SW + 1) * 32, 1) attn_fa_kernel(const __g
   }
 }
 
+// =====================================================================================================
+// attn_fa2_kernel: the same data path with S DOUBLE-BUFFERED in tensor memory -- the softmax threads never wait for an MMA.
+//
+// What is left in attn_fa_kernel's block period (3460 cycles per 2 x 128 x 128 scores against 2048 of MUFU) is the serial
+// hand-over  P(j) staged -> control warp sees it -> S(j+1) issued -> S(j+1) complete -> next pass: ~1000 cycles in which the
+// tile's softmax warps idle.  With 96-key blocks a tile's TMEM quarter holds two S buffers and O (96 + 96 + 64 = 256 columns)
+// when P(j) is written IN PLACE over the first 48 columns of S(j): one thread owns a whole row (its 96 scores are in registers
+// before any P column is stored, so the row max is exact and nothing is speculative).  S(j+1) was issued a block ago; the
+// control warp answers P(j) with P V(j) and then S(j+2) into the buffer P V(j) is reading, in order on the tensor pipe.
+//   TMEM per query tile t: S / P buffer 0 [0, 96) | buffer 1 [96, 192) | O [192, 256)
+//   warps 0..3 softmax of tile 0 (thread = query row), 4..7 tile 1, warp 8 control (TMA ring of four 96-key K / V stages,
+//   three blocks ahead; every MMA, elected lane)
+// =====================================================================================================
+#ifndef AVD_F2_BKV
+#define AVD_F2_BKV 96
+#endif
+constexpr int F2_BKV = AVD_F2_BKV;                          // 64 or 96
+constexpr int F2_NCH = F2_BKV / 32;
+#ifndef AVD_F2_STAGGER_NS
+#define AVD_F2_STAGGER_NS 0
+#endif
+constexpr unsigned F2_STAGGER_NS = AVD_F2_STAGGER_NS;
+constexpr int F2_STAGES = 4;
+constexpr int F2_KV_BYTES = F2_BKV * ATT_HD * 2;            // 12 KB
+constexpr int F2_THREADS = 9 * 32;
+constexpr int F2_SMEM = 2 * ATT_Q_BYTES + F2_STAGES * 2 * F2_KV_BYTES + 512;
+enum { GB_Q = 0, GB_KF = 1 /*+stage*/, GB_VF = 5 /*+stage*/, GB_KVE = 9 /*+stage*/, GB_S = 13 /*+2 tile + buffer*/,
+       GB_P = 17 /*+tile*/, GB_O = 19 /*+tile*/, GB_COUNT = 21 };
+
+template <bool F16, bool MASKED>
+__global__ void __launch_bounds__(F2_THREADS, 1) attn_fa2_kernel(const __grid_constant__ CUtensorMap tmQ,
+                                                                 const __grid_constant__ CUtensorMap tmKV,
+                                                                 const AttnParams p) {
+  extern __shared__ __align__(1024) uint8_t fa_smem[];
+  uint8_t* smem = fa_smem;
+  if ((smem_u32(smem) & 1023u) != 0) __trap();
+  uint8_t* sQ = smem;                                       // 2 query tiles (later: output staging)
+  uint8_t* sKV = sQ + 2 * ATT_Q_BYTES;                      // [stage]{K, V}
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sKV + F2_STAGES * 2 * F2_KV_BYTES);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + GB_COUNT);
+
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5, lane = tid & 31;
+  const int head = blockIdx.y, seq = blockIdx.z;
+  const int row_base = seq * p.N;
+  const int q_first = blockIdx.x * 2 * ATT_BQ;
+  const int n_tiles = (p.N - q_first > ATT_BQ) ? 2 : 1;
+  const int colQ = head * ATT_HD, colK = p.d + head * ATT_HD, colV = 2 * p.d + head * ATT_HD;
+  const int nkv = (p.N + F2_BKV - 1) / F2_BKV;
+  unsigned long long* const trace = p.trace;
+  (void)trace;
+
+  if (warp == 1) {
+    if (lane < GB_COUNT) {
+      uint32_t count = 1;
+      if (lane >= GB_P && lane < GB_O) {                    // arrivals: the warps of the tile that own valid query rows
+        const int rows = min(ATT_BQ, p.N - q_first - (lane - GB_P) * ATT_BQ);
+        count = rows > 0 ? 32 * ((rows + 31) >> 5) : 1;
+      }
+      mbar_init(&bars[lane], count);
+    }
+    fence_barrier_init();
+  } else if (warp == 2 && lane == 0) {
+    tma_prefetch_desc(&tmQ);
+    tma_prefetch_desc(&tmKV);
+  }
+  if (warp == 0) tmem_alloc<512>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
+  pdl_launch_dependents();
+
+  if (warp == 8) {
+    // ------------------------------------------------------------------ control warp (converged; elected lane issues)
+    auto load_kv = [&](int b) {
+      if (lane == 0) {
+        const int s = b & (F2_STAGES - 1);
+        uint8_t* k = sKV + s * 2 * F2_KV_BYTES;
+        mbar_expect_tx(&bars[GB_KF + s], F2_KV_BYTES);
+        tma_load_3d(k, &tmKV, &bars[GB_KF + s], colK, row_base + b * F2_BKV, 0);
+        mbar_expect_tx(&bars[GB_VF + s], F2_KV_BYTES);
+        tma_load_3d(k + F2_KV_BYTES, &tmKV, &bars[GB_VF + s], colV, row_base + b * F2_BKV, 0);
+      }
+      __syncwarp();
+    };
+    if (lane == 0) {
+      pdl_wait();
+      mbar_expect_tx(&bars[GB_Q], n_tiles * ATT_Q_BYTES);
+      for (int t = 0; t < n_tiles; ++t)
+        tma_load_3d(sQ + t * ATT_Q_BYTES, &tmQ, &bars[GB_Q], colQ, row_base + q_first + t * ATT_BQ, 0);
+    }
+    __syncwarp();
+    for (int b = 0; b < min(3, nkv); ++b) load_kv(b);
+
+    const uint32_t hi = smem_desc_hi_sw128(1024);
+    const uint32_t idesc_o = make_idesc_bf16(ATT_BQ, ATT_HD, 0, 1, F16);         // B = V is MN-major
+    const uint32_t q_lo0 = smem_desc_lo_sw128(smem_u32(sQ), 16);
+    const uint32_t kv_lo0 = smem_desc_lo_sw128(smem_u32(sKV), 16);
+    auto issue_s = [&](int t, int b) {                      // S_t(b) = Q_t K_b^T -> the tile's buffer b & 1
+      const int kvn = (min(F2_BKV, p.N - b * F2_BKV) + 15) & ~15;
+      const uint32_t idesc_s = make_idesc_bf16(ATT_BQ, kvn, 0, 0, F16);
+      const uint32_t q_lo = q_lo0 + t * (ATT_Q_BYTES >> 4);
+      const uint32_t k_lo = kv_lo0 + (b & (F2_STAGES - 1)) * (2 * F2_KV_BYTES >> 4);
+#pragma unroll
+      for (int k = 0; k < ATT_HD / 16; ++k)
+        umma_bf16_lh_elect(tmem_base + t * 256 + (b & 1) * F2_BKV, q_lo + 2 * k, k_lo + 2 * k, hi, idesc_s, k > 0 ? 1u : 0u);
+      umma_commit_elect(&bars[GB_S + t * 2 + (b & 1)]);
+    };
+    mbar_wait(&bars[GB_Q], 0);
+    for (int b = 0; b < min(2, nkv); ++b) {
+      mbar_wait(&bars[GB_KF + b], 0);
+      tc_fence_after();
+      for (int t = 0; t < n_tiles; ++t) issue_s(t, b);
+    }
+    for (int j = 0; j < nkv; ++j) {
+      const int s = j & (F2_STAGES - 1);
+      const int kvn = (min(F2_BKV, p.N - j * F2_BKV) + 15) & ~15;
+      const uint32_t v_lo = kv_lo0 + ((s * 2 * F2_KV_BYTES + F2_KV_BYTES) >> 4);
+      for (int t = 0; t < n_tiles; ++t) {
+        mbar_wait(&bars[GB_P + t], j & 1);                  // P_t(j) is in its buffer (and O_t rescaled where a row's max moved)
+        if (t == 0) mbar_wait(&bars[GB_VF + s], (j / F2_STAGES) & 1);
+        tc_fence_after();
+        ATT_WMARK(t * 3);
+        const uint32_t d_o = tmem_base + t * 256 + 192, a_p = tmem_base + t * 256 + (j & 1) * F2_BKV;
+        if (kvn == F2_BKV) {
+#pragma unroll
+          for (int ks = 0; ks < F2_BKV / 16; ++ks)          // O_t += P_t(j) V_j: A from TMEM, 8 columns per 16 keys
+            umma_bf16_ts_elect(d_o, a_p + ks * 8, v_lo + ks * 128, hi, idesc_o, (j > 0 || ks > 0) ? 1u : 0u);
+        } else {
+          for (int ks = 0; ks < (kvn >> 4); ++ks)
+            umma_bf16_ts_elect(d_o, a_p + ks * 8, v_lo + ks * 128, hi, idesc_o, (j > 0 || ks > 0) ? 1u : 0u);
+        }
+        umma_commit_elect(&bars[GB_O + t]);                 // O_t is current through block j (phase j)
+        if (t == n_tiles - 1) umma_commit_elect(&bars[GB_KVE + s]);   // K_j / V_j have been read by every tile
+        ATT_WMARK(t * 3 + 1);
+        if (j + 2 < nkv) {                                  // S_t(j+2) into the buffer P V_t(j) is reading: in order behind it
+          if (t == 0) {
+            mbar_wait(&bars[GB_KF + ((j + 2) & (F2_STAGES - 1))], ((j + 2) / F2_STAGES) & 1);
+            tc_fence_after();
+          }
+          issue_s(t, j + 2);
+          ATT_WMARK(t * 3 + 2);
+        }
+      }
+      if (j + 3 < nkv) {                                    // the stage of block j - 1 was handed back a block ago
+        const int b = j + 3;
+        if (b >= F2_STAGES) mbar_wait(&bars[GB_KVE + (b & (F2_STAGES - 1))], ((b / F2_STAGES) - 1) & 1);
+        load_kv(b);
+      }
+    }
+  } else if ((warp >> 2) < n_tiles && q_first + (warp >> 2) * ATT_BQ + (warp & 3) * 32 < p.N) {
+    // ------------------------------------------------------------------ softmax + output of query tile t, one thread per row
+    const int t = warp >> 2, quad = warp & 3;
+    const uint32_t tmem_T = tmem_base + t * 256 + ((uint32_t)(quad * 32) << 16);
+    const float sc = p.scale_log2e;
+    float m_run = -INFINITY, l_run = 0.0f;
+    // Nothing couples the two tiles any more, and started together they stay in step: both in their MUFU-bound exponentials,
+    // then both in the MUFU-free part of a block.  The second tile starts half a block late.
+    if (F2_STAGGER_NS > 0 && t == 1) __nanosleep(F2_STAGGER_NS);
+    for (int j = 0; j < nkv; ++j) {
+      const int kv_valid = min(F2_BKV, p.N - j * F2_BKV);
+      const uint32_t tmem_S = tmem_T + (j & 1) * F2_BKV;
+      ATT_WMARK(0);
+      mbar_wait(&bars[GB_S + t * 2 + (j & 1)], (j >> 1) & 1);
+      tc_fence_after();
+      ATT_WMARK(1);
+      // The whole block body exists twice: RAGGED (a key_padding_mask, or the last block of a sequence that is not a
+      // multiple of the block) carries the per-score selects, the common form has none (if-converted, they cost 96 SEL +
+      // predicate set-up per block on every block).
+      float l0 = 0.0f, l1 = 0.0f;
+      bool o_seen = false;
+      auto block = [&](auto ragged_tag) {
+        constexpr bool RAGGED = decltype(ragged_tag)::value;
+        // all chunks, always (straight-line code keeps them in registers): in a ragged last block the chunks past the
+        // keys read stale TMEM, are masked to -inf and store zeros that P V (K = round16(keys)) never reads
+        uint32_t x[F2_NCH][32];
+#pragma unroll
+        for (int i = 0; i < F2_NCH; ++i) tmem_ld_32x32(tmem_S + i * 32, x[i]);
+        tmem_ld_wait();
+        ATT_WMARK(2);
+        float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+        auto mask_max = [&](int i, uint32_t (&x)[32]) {       // padded / out-of-sequence keys: score -inf, probability 0
+          const int lim = kv_valid - i * 32;
+          uint32_t vb = lim >= 32 ? 0xffffffffu : (lim > 0 ? ((1u << lim) - 1u) : 0u);
+          if (MASKED && lim > 0) vb &= ~p.kmask[(size_t)blockIdx.z * p.kmask_words + j * (F2_BKV / 32) + i];
+          if (RAGGED && vb != 0xffffffffu) {
+#pragma unroll
+            for (int c = 0; c < 32; ++c)
+              if (!((vb >> c) & 1u)) x[c] = 0xff800000u;
+          }
+#pragma unroll
+          for (int c = 0; c < 32; ++c) mx[c & 3] = fmaxf(mx[c & 3], __uint_as_float(x[c]));
+        };
+#pragma unroll
+        for (int i = 0; i < F2_NCH; ++i) mask_max(i, x[i]);
+        const float m_row = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
+        // the reference max moves only when it must: first live block of the row, or the block max is 2^8 above it (P stays
+        // inside fp16, the row sum well conditioned)
+        const bool need = m_row != -INFINITY && (m_run == -INFINITY || (m_row - m_run) * sc > FA_RESCALE_LOG2);
+        if (__any_sync(0xffffffffu, need)) {
+          float alpha = 1.0f;
+          if (need) {
+            alpha = ex2_approx((m_run - m_row) * sc);         // m_run = -inf on the first live block -> 0
+            m_run = m_row;
+            l_run *= alpha;
+          }
+          if (j > 0) {
+            mbar_wait(&bars[GB_O + t], (j - 1) & 1);          // P V_t(j-1) complete: O_t is current
+            tc_fence_after();
+            o_seen = true;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              uint32_t o[32];
+              tmem_ld_32x32(tmem_T + 192 + h * 32, o);
+              tmem_ld_wait();
+#pragma unroll
+              for (int c = 0; c < 32; ++c) o[c] = __float_as_uint(__uint_as_float(o[c]) * alpha);
+              tmem_st_32x32(tmem_T + 192 + h * 32, o);
+            }
+          }
+        }
+        ATT_WMARK(3);
+        const float neg_m_sc = m_run == -INFINITY ? 0.0f : -m_run * sc;   // every key so far padded: exponents stay finite
+        auto expo = [&](uint32_t (&x)[32], int c) {
+          const float a = fmaf(__uint_as_float(x[c]), sc, neg_m_sc);
+          float e;
+          asm volatile("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(a));
+          x[c] = __float_as_uint(e);
+        };
+        auto post = [&](const uint32_t (&e)[32], int c, uint32_t (&w)[16]) {
+          l0 += __uint_as_float(e[c]);
+          l1 += __uint_as_float(e[c + 1]);
+          w[c >> 1] = F16 ? pack_f16x2(__uint_as_float(e[c]), __uint_as_float(e[c + 1]))
+                          : pack_bf16x2(__uint_as_float(e[c]), __uint_as_float(e[c + 1]));
+        };
+        // the exponentials of chunk i + 1 between the sums / packs of chunk i: nothing waits for a MUFU result less than a
+        // chunk old.  P(j) goes IN PLACE over the first 48 columns of S(j) -- every score of the row is in registers.
+        {
+          uint32_t w[16];
+#pragma unroll
+          for (int c = 0; c < 32; ++c) expo(x[0], c);
+#pragma unroll
+          for (int i = 0; i < F2_NCH; ++i) {
+            if (i + 1 < F2_NCH) {
+#pragma unroll
+              for (int c = 0; c < 32; c += 2) {
+                expo(x[i + 1], c);
+                expo(x[i + 1], c + 1);
+                post(x[i], c, w);
+              }
+            } else {
+#pragma unroll
+              for (int c = 0; c < 32; c += 2) post(x[i], c, w);
+            }
+            tmem_st_32x16(tmem_S + i * 16, w);
+          }
+        }
+      };
+      if (MASKED || kv_valid < F2_BKV) block(std::true_type{});
+      else block(std::false_type{});
+      l_run += l0 + l1;
+      ATT_WMARK(4);
+      // S(j+1) was issued a block ago, so nothing else keeps this warp from running a block ahead of the control warp:
+      // P(j) is only announced once P V(j-1) has completed, i.e. the control warp has consumed P(j-1) -- the P barrier is
+      // never two phases ahead of its waiter (every block consumes one phase of the O barrier, in order)
+      if (j > 0 && !o_seen) {
+        mbar_wait(&bars[GB_O + t], (j - 1) & 1);
+        tc_fence_after();
+      }
+      tmem_st_wait();
+      tc_fence_before();    // S has been read, P (and a rescaled O) written: the tile's next MMAs may go
+      mbar_arrive(&bars[GB_P + t]);
+      ATT_WMARK(5);
+    }
+
+    // ---- O_t complete: normalise this thread's row, stage the warp's 32 rows x 128 B in the retired Q tile, coalesced stores
+    mbar_wait(&bars[GB_O + t], (nkv - 1) & 1);
+    tc_fence_after();
+    float rem[64];
+    {
+      const float inv_l = 1.0f / l_run;
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        uint32_t o[32];
+        tmem_ld_32x32(tmem_T + 192 + h * 32, o);
+        tmem_ld_wait();
+#pragma unroll
+        for (int c = 0; c < 32; ++c) rem[h * 32 + c] = __uint_as_float(o[c]) * inv_l;
+      }
+    }
+    const int64_t seg_stride = p.M * (int64_t)p.d;
+    uint8_t* stage = sQ + t * ATT_Q_BYTES + quad * 32 * 128;
+    const int q_tile0 = q_first + t * ATT_BQ + quad * 32;          // first query row of this warp
+    for (int sg = 0; sg < p.out_nseg; ++sg) {
+#pragma unroll
+      for (int v8 = 0; v8 < 8; ++v8) {
+        uint32_t w[4];
+        if (p.out_nseg == 1) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            w[k] = F16 ? pack_f16x2(rem[v8 * 8 + k * 2], rem[v8 * 8 + k * 2 + 1])
+                       : pack_bf16x2(rem[v8 * 8 + k * 2], rem[v8 * 8 + k * 2 + 1]);
+        } else {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const int c = v8 * 8 + k * 2;
+            const __nv_bfloat16 h0 = __float2bfloat16_rn(rem[c]);
+            const __nv_bfloat16 h1 = __float2bfloat16_rn(rem[c + 1]);
+            rem[c] -= __bfloat162float(h0);
+            rem[c + 1] -= __bfloat162float(h1);
+            w[k] = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
+          }
+        }
+        *reinterpret_cast<uint4*>(stage + lane * 128 + ((v8 ^ (lane & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+      }
+      __syncwarp();
+      const int rr = lane >> 3, cc = lane & 7;
+      __nv_bfloat16* gp = p.out + sg * seg_stride + ((int64_t)row_base + q_tile0) * p.d + head * ATT_HD + cc * 8;
+#pragma unroll
+      for (int it = 0; it < 8; ++it) {
+        const int rw = it * 4 + rr;
+        const uint4 x4 = *reinterpret_cast<const uint4*>(stage + rw * 128 + ((cc ^ (rw & 7)) << 4));
+        if (q_tile0 + rw < p.N) *reinterpret_cast<uint4*>(gp + (int64_t)rw * p.d) = x4;
+      }
+      if (sg + 1 < p.out_nseg) __syncwarp();
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    tmem_dealloc<512>(tmem_base);
+  }
+}
+
 int launch_attention_fa(const void* qkv16, const AttnParams& p, int n_seq, bool f16, cudaStream_t s) {
   if (p.N <= FA_BKV) return 0;
   const int d = p.d;
   CUtensorMap tm;
   AVD_TRY(get_tensor_map_3d(qkv16, 2, (uint64_t)3 * d, (uint64_t)p.M, 1, (uint64_t)3 * d * 2, (uint64_t)p.M * 3 * d * 2,
                             ATT_HD, ATT_BQ, &tm));
+  if (options().attn_fa == 3) {                             // S double-buffered, 96-key blocks (attn_fa2_kernel)
+    CUtensorMap tmkv;
+    AVD_TRY(get_tensor_map_3d(qkv16, 2, (uint64_t)3 * d, (uint64_t)p.M, 1, (uint64_t)3 * d * 2, (uint64_t)p.M * 3 * d * 2,
+                              ATT_HD, F2_BKV, &tmkv));
+    using Fn2 = void (*)(const CUtensorMap, const CUtensorMap, const AttnParams);
+    static const Fn2 k2[2][2] = {{attn_fa2_kernel<false, false>, attn_fa2_kernel<false, true>},
+                                 {attn_fa2_kernel<true, false>, attn_fa2_kernel<true, true>}};
+    const Fn2 f2 = k2[f16 ? 1 : 0][p.kmask != nullptr ? 1 : 0];
+    AVD_TRY(ensure_dyn_smem(reinterpret_cast<const void*>(f2), F2_SMEM));
+    cudaLaunchConfig_t c2{};
+    c2.gridDim = dim3((p.N + 2 * ATT_BQ - 1) / (2 * ATT_BQ), p.n_heads, n_seq);
+    c2.blockDim = dim3(F2_THREADS);
+    c2.dynamicSmemBytes = F2_SMEM;
+    c2.stream = s;
+    cudaLaunchAttribute a2[1];
+    int n2 = 0;
+    if (pdl_enabled()) {
+      a2[n2].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+      a2[n2].val.programmaticStreamSerializationAllowed = 1;
+      ++n2;
+    }
+    c2.attrs = a2;
+    c2.numAttrs = n2;
+    AttnParams q2 = p;
+#ifndef AVD_ATT_WTRACE
+    q2.trace = nullptr;
+#endif
+    AVD_CUDA(cudaLaunchKernelEx(&c2, f2, tm, tmkv, q2));
+    return 1;
+  }
   using Fn = void (*)(const CUtensorMap, const AttnParams);
   static const Fn kernels[2][2][2] = {
       {{attn_fa_kernel<false, false, 8>, attn_fa_kernel<false, true, 8>},

@@ -225,25 +225,27 @@ def test_attention_multiblock_rising_max(dev, lib, N, ramp, f16):
     """The multi-block softmax takes its exponentials against the CARRIED row max and repeats a block only when the max
     rose by more than 2^8: scores that climb with the key index exercise both branches (ramp 10: ~2.7 log2 units per
     192-key block, repeats now and then; ramp 60: ~17 per block, repeats every block)."""
-    _attn_check(dev, lib, 2, N, f16, 1.5e-3 if f16 else 8e-3, key_ramp=ramp)
+    from multimodal_diffusion_b200 import _lib
+    with _lib.option("attn_fa", 0):           # attn_tc_kernel's two-tile multi-block path (the default is attn_fa_kernel)
+        _attn_check(dev, lib, 2, N, f16, 1.5e-3 if f16 else 8e-3, key_ramp=ramp)
 
 
 @pytest.mark.parametrize("n_seq,N,f16,ramp", [(3, 445, True, 0.0), (2, 193, False, 0.0), (1, 2048, True, 0.0),
                                               (2, 1000, False, 0.0), (1, 257, True, 0.0), (2, 384, False, 0.0),
                                               (1, 640, True, 0.0), (2, 1000, True, 10.0), (2, 1000, False, 60.0),
                                               (1, 2048, True, 25.0), (1, 16384, True, 0.0)])
-@pytest.mark.parametrize("fa", [1, 2])
+@pytest.mark.parametrize("fa", [1, 2, 3])
 def test_attention_tmem_resident_kernel(dev, lib, n_seq, N, f16, ramp, fa):
     """attn_fa_kernel (option attn_fa; N > 192): P written to tensor memory and used as the A operand of P V, O accumulated
     in tensor memory and rescaled in place only when a row's max rises by more than 2^8, 128-key blocks through a 4-stage
     K / V ring.  Ragged last blocks (445 = 3 x 128 + 61, 193, 257: a one-row second query tile), scores that climb along
     the keys (in-place rescales in every block), 128 key blocks."""
     from multimodal_diffusion_b200 import _lib
-    with _lib.option("attn_fa", fa):          # 1: two softmax warps per row group, 2: one softmax thread per query row
+    with _lib.option("attn_fa", fa):          # 1: two softmax warps per row group, 2: one thread per query row, 3: S double-buffered
         _attn_check(dev, lib, n_seq, N, f16, 1.5e-3 if f16 else 8e-3, key_ramp=ramp)
 
 
-@pytest.mark.parametrize("fa", [1, 2])
+@pytest.mark.parametrize("fa", [1, 2, 3])
 @pytest.mark.parametrize("N", [445, 1000])
 def test_attention_tmem_resident_kernel_with_key_mask(dev, lib, N, fa):
     """key_padding_mask through attn_fa_kernel against the two-pass multi-block kernel: ragged tails, scattered padded keys,

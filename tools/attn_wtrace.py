@@ -58,18 +58,18 @@ def main() -> None:
     if _lib.get_option("attn_fa") != 0:
         names = ["top", "S ready", "pass done", "max exchanged", "rescale/repeat", "P arrived"]
         print("warp tile half quad | " + " ".join(f"{n:>14s}" for n in names) + " |  period(3->4) period(4->5)")
-        for w in range(8 if _lib.get_option("attn_fa") == 2 else 16):
+        for w in range(8 if _lib.get_option("attn_fa") >= 2 else 16):
             if int(t[w, B, 0]) == 0:
                 continue
             row = " ".join(f"{int(t[w, B, sl]) - t0:14d}" for sl in range(6))
             print(f"{w:4d} {w >> 3:4d} {(w >> 2) & 1:4d} {w & 3:4d} | {row} | {int(t[w, B, 0] - t[w, 0, 0]):13d} "
                   f"{int(t[w, 2, 0] - t[w, B, 0]):12d}")
         print("inside the pass:    chunk 0: ld done, exps done, P stored | chunk 1: ld done, exps done, P stored")
-        for w in range(0 if _lib.get_option("attn_fa") == 2 else 16):
+        for w in range(0 if _lib.get_option("attn_fa") >= 2 else 16):
             if int(t[w, B, 0]) == 0:
                 continue
             print(f"{w:4d}                | " + " ".join(f"{int(t[w, B, sl]) - t0:10d}" for sl in range(6, 12)))
-        cw = 8 if _lib.get_option("attn_fa") == 2 else 16
+        cw = 8 if _lib.get_option("attn_fa") >= 2 else 16
         c = [int(t[cw, B, sl]) - t0 for sl in range(6)]
         print(f"control lane: tile 0: P/V there {c[0]}, S(j+1) issued {c[1]}, PV issued {c[2]} | tile 1: P there {c[3]}, "
               f"S(j+1) issued {c[4]}, PV issued {c[5]} | period {int(t[cw, 2, 0] - t[cw, 1, 0])}")

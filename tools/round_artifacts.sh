@@ -12,11 +12,14 @@ timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --c
 timeout 600 ncu --set full --import-source on --clock-control none -k regex:gemm -s 8 -c 4 -f -o $o/${tag}_gemm_mvp python tools/kbench.py --once > $o/ncu_a.log 2>&1
 timeout 600 ncu --set full --import-source on --clock-control none -k regex:gemm -s 8 -c 4 -f -o $o/${tag}_gemm_m32768 python tools/kbench.py --once --M 32768 > $o/ncu_b.log 2>&1
 timeout 600 ncu --set full --import-source on --clock-control none -k regex:attn_tc -s 2 -c 1 -f -o $o/${tag}_attn_mvp python tools/kbench.py --once > $o/ncu_c.log 2>&1
-for n in gemm_mvp gemm_m32768 attn_mvp; do python tools/ncu_summary.py $o/${tag}_${n}.ncu-rep $o/${tag}_${n}_ncu_full_summary.csv; done
+timeout 600 ncu --set full --import-source on --clock-control none -k regex:attn_fa -s 2 -c 1 -f -o $o/${tag}_attn_m32768 python tools/kbench.py --once --M 32768 > $o/ncu_d.log 2>&1
+for n in gemm_mvp gemm_m32768 attn_mvp attn_m32768; do python tools/ncu_summary.py $o/${tag}_${n}.ncu-rep $o/${tag}_${n}_ncu_full_summary.csv; done
 timeout 200 python tools/stepbench.py 8 audio --kinds > $o/${tag}_stepbench.txt 2>&1
 timeout 200 python tools/stepbench.py 64 video --kinds >> $o/${tag}_stepbench.txt 2>&1
 timeout 200 python tools/stepbench.py 8 video --cfg10 --kinds >> $o/${tag}_stepbench.txt 2>&1
 timeout 200 python tools/kbench.py --M 32768 >> $o/${tag}_stepbench.txt 2>&1
 timeout 200 python tools/kbench.py --M 17024 >> $o/${tag}_stepbench.txt 2>&1
+timeout 200 python tools/kbench.py --M 7120 >> $o/${tag}_stepbench.txt 2>&1
+for v in 0 2 3; do echo "== AVD_ATTN_FA=$v" >> $o/${tag}_stepbench.txt; AVD_ATTN_FA=$v timeout 200 python tools/kbench.py --M 32768 2>&1 | grep "^attn" >> $o/${tag}_stepbench.txt; done
 timeout 900 python tools/sweep.py --precision f16 --out $o/${tag}_sweep_mmdt_forward.json > $o/sweep.log 2>&1; tail -3 $o/sweep.log
 timeout 300 python tools/ebench.py --out $o/${tag}_elementwise_hbm.json > $o/ebench.log 2>&1; tail -3 $o/ebench.log
