@@ -47,7 +47,7 @@ constexpr bool FA_INTERLEAVE = AVD_FA_INTERLEAVE != 0;
 constexpr int FA_POLY = AVD_FA_POLY;
 constexpr float FA_RESCALE_LOG2 = 8.0f;                     // a row's reference max moves when the block max is 2^8 above it
 enum { FB_Q = 0, FB_KF = 1 /*+stage*/, FB_VF = 5 /*+stage*/, FB_KVE = 9 /*+stage*/, FB_S = 13 /*+tile*/, FB_P = 15 /*+tile*/,
-       FB_O = 17 /*+tile*/, FB_COUNT = 19 };
+       FB_O = 17 /*+tile*/, FB_R = 19 /*+tile*/, FB_COUNT = 21 };
 
 template <bool F16, bool MASKED, int SW>
 __global__ void __launch_bounds__((2 * SW + 1) * 32, 1) attn_fa_kernel(const __grid_constant__ CUtensorMap tmQKV,
@@ -76,8 +76,8 @@ __global__ void __launch_bounds__((2 * SW + 1) * 32, 1) attn_fa_kernel(const __g
   if (warp == 1) {
     if (lane < FB_COUNT) {
       uint32_t count = 1;
-      if (lane >= FB_P && lane < FB_O) {                    // arrivals: the warp pairs of the tile that own valid query rows
-        const int rows = min(ATT_BQ, p.N - q_first - (lane - FB_P) * ATT_BQ);
+      if ((lane >= FB_P && lane < FB_O) || lane >= FB_R) {  // arrivals: the warps of the tile that own valid query rows
+        const int rows = min(ATT_BQ, p.N - q_first - ((lane - FB_P) & 1) * ATT_BQ);
         count = rows > 0 ? (SW * 8) * ((rows + 31) >> 5) : 1;
       }
       mbar_init(&bars[lane], count);
@@ -146,18 +146,17 @@ __global__ void __launch_bounds__((2 * SW + 1) * 32, 1) attn_fa_kernel(const __g
       const int kvn = (min(FA_BKV, p.N - j * FA_BKV) + 15) & ~15;
       const uint32_t v_lo = kv_lo0 + ((s * 2 * FA_KV_BYTES + FA_KV_BYTES) >> 4);
       for (int t = 0; t < n_tiles; ++t) {
-        mbar_wait(&bars[FB_P + t], j & 1);                  // P_t(j) is in TMEM (and O_t rescaled where a row's max moved)
-        if (t == 0) mbar_wait(&bars[FB_VF + s], (j / FA_STAGES) & 1);
-        tc_fence_after();
-        ATT_WMARK(t * 3);
-        if (j + 1 < nkv) {                                  // S_t(j+1) first: the tile's next softmax pass waits for it
-          if (t == 0) {
-            mbar_wait(&bars[FB_KF + ((j + 1) & (FA_STAGES - 1))], ((j + 1) / FA_STAGES) & 1);
-            tc_fence_after();
-          }
+        if (j + 1 < nkv) {                                  // S_t(j+1) first: the tile's next softmax pass waits for it,
+          mbar_wait(&bars[FB_R + t], j & 1);                // and it only needs S_t(j) READ (P stores may still be in flight)
+          if (t == 0) mbar_wait(&bars[FB_KF + ((j + 1) & (FA_STAGES - 1))], ((j + 1) / FA_STAGES) & 1);
+          tc_fence_after();
+          ATT_WMARK(t * 3);
           issue_s(t, j + 1);
           ATT_WMARK(t * 3 + 1);
         }
+        mbar_wait(&bars[FB_P + t], j & 1);                  // P_t(j) is in TMEM (and O_t rescaled where a row's max moved)
+        if (t == 0) mbar_wait(&bars[FB_VF + s], (j / FA_STAGES) & 1);
+        tc_fence_after();
         const uint32_t d_o = tmem_base + t * 256 + 192, a_p = tmem_base + t * 256 + 128;
         if (kvn == FA_BKV) {
 #pragma unroll
@@ -305,6 +304,8 @@ __global__ void __launch_bounds__((2 * SW + 1) * 32, 1) attn_fa_kernel(const __g
         const float neg_m_sc = m_run == -INFINITY ? 0.0f : -m_run * sc;
         (void)pass(std::true_type{}, neg_m_sc, l_blk);
       }
+      tc_fence_before();
+      mbar_arrive(&bars[FB_R + t]);                         // S_t(j) will not be read again: S_t(j+1) may overwrite it
       l_run += l_blk;
       ATT_WMARK(4);
       tmem_st_wait();
@@ -526,6 +527,8 @@ __global__ void __launch_bounds__((2 * SW + 1) * 32, 1) attn_fa_kernel(const __g
         const float neg_m_sc = m_run == -INFINITY ? 0.0f : -m_run * sc;   // every key so far padded: exponents stay finite
         (void)pass(std::true_type{}, neg_m_sc, l_blk);
       }
+      tc_fence_before();
+      mbar_arrive(&bars[FB_R + t]);                         // S_t(j) will not be read again: S_t(j+1) may overwrite it
       ATT_WMARK(4);
       l_run += l_blk;
       tmem_st_wait();
