@@ -45,7 +45,13 @@ constexpr bool FA_INTERLEAVE = AVD_FA_INTERLEAVE != 0;
 #define AVD_FA_POLY 0
 #endif
 constexpr int FA_POLY = AVD_FA_POLY;
-constexpr float FA_RESCALE_LOG2 = 8.0f;                     // a row's reference max moves when the block max is 2^8 above it
+// A row's reference max moves when the block max is 2^FA_RESCALE_LOG2 above it; until then P = exp2(s - ref) may reach
+// 2^8 (fp16 keeps its full mantissa there; the row sum and O are fp32).  2^12 was measured too: no difference (235 vs 232 us),
+// a repeated pass is rare enough at 2^8.
+#ifndef AVD_FA_RESCALE_LOG2
+#define AVD_FA_RESCALE_LOG2 8
+#endif
+constexpr float FA_RESCALE_LOG2 = (float)AVD_FA_RESCALE_LOG2;
 enum { FB_Q = 0, FB_KF = 1 /*+stage*/, FB_VF = 5 /*+stage*/, FB_KVE = 9 /*+stage*/, FB_S = 13 /*+tile*/, FB_P = 15 /*+tile*/,
        FB_O = 17 /*+tile*/, FB_R = 19 /*+tile*/, FB_COUNT = 21 };
 
@@ -275,7 +281,7 @@ __global__ void __launch_bounds__((2 * SW + 1) * 32, 1) attn_fa_kernel(const __g
       float l_blk = 0.0f;
       const float m_row = spec ? pass(std::true_type{}, -m_run * sc, l_blk) : pass(std::false_type{}, 0.0f, l_blk);
       ATT_WMARK(2);
-      // the reference max moves only when it must: first live block of the row, or the block max is 2^8 above it
+      // the reference max moves only when it must: first live block of the row, or the block max is 2^FA_RESCALE_LOG2 above it
       const bool need = m_row != -INFINITY && (m_run == -INFINITY || (m_row - m_run) * sc > FA_RESCALE_LOG2);
       bool have_p = spec;
       if (__any_sync(0xffffffffu, need)) {
@@ -501,7 +507,7 @@ __global__ void __launch_bounds__((2 * SW + 1) * 32, 1) attn_fa_kernel(const __g
       named_bar_sync(pair_bar, 64);
       ATT_WMARK(3);
       const float m_row = fmaxf(m_part, xm[(sp ^ 1) * 128 + r]);
-      // the reference max moves only when it must: first live block of the row, or the block max is 2^8 above it (P stays
+      // the reference max moves only when it must: first live block of the row, or the block max is 2^FA_RESCALE_LOG2 above it (P stays
       // inside fp16, the row sum well conditioned)
       const bool need = m_row != -INFINITY && (m_run == -INFINITY || (m_row - m_run) * sc > FA_RESCALE_LOG2);
       bool have_p = spec;
@@ -797,7 +803,7 @@ __global__ void __launch_bounds__(F2_THREADS, 1) attn_fa2_kernel(const __grid_co
 #pragma unroll
         for (int i = 0; i < F2_NCH; ++i) mask_max(i, x[i]);
         const float m_row = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
-        // the reference max moves only when it must: first live block of the row, or the block max is 2^8 above it (P stays
+        // the reference max moves only when it must: first live block of the row, or the block max is 2^FA_RESCALE_LOG2 above it (P stays
         // inside fp16, the row sum well conditioned)
         const bool need = m_row != -INFINITY && (m_run == -INFINITY || (m_row - m_run) * sc > FA_RESCALE_LOG2);
         if (__any_sync(0xffffffffu, need)) {
