@@ -246,6 +246,26 @@ def test_attention_tmem_resident_kernel(dev, lib, n_seq, N, f16, ramp, fa):
 
 
 @pytest.mark.parametrize("fa", [1, 2, 3])
+def test_attention_tmem_resident_kernel_split_output(dev, lib, fa):
+    """bf16x3 mode: bf16 q / k / v in, the attention output written as TWO bf16 segments (value + residual); the multi-block
+    kernels' multi-segment epilogue against fp64, tighter than one bf16 segment allows."""
+    from multimodal_diffusion_b200 import _lib
+    H, hd, n_seq, N = 8, 64, 2, 445
+    qkv = (randn(8, n_seq * N, 3 * H * hd) * 1.5).bfloat16().to(dev)
+    out = torch.zeros(2, n_seq * N, H * hd, device=dev, dtype=torch.bfloat16)
+    with _lib.option("attn_fa", fa):
+        _lib.check(lib.avd_attention(qkv.data_ptr(), 0, out.data_ptr(), _lib.AVD_PREC_BF16X3, n_seq, N, H, hd,
+                                     _lib.stream_ptr()))
+    torch.cuda.synchronize()
+    q, k, v = qkv.double().view(n_seq, N, 3, H, hd).permute(2, 0, 3, 1, 4)
+    want = (torch.softmax(q @ k.transpose(-1, -2) / math.sqrt(hd), dim=-1) @ v).permute(0, 2, 1, 3).reshape(n_seq * N, H * hd)
+    one = rel_l2(out[0].float(), want)
+    both = rel_l2(out.float().sum(0), want)
+    print(f"[attention bf16x3 fa={fa}] rel-L2 one segment {one:.2e}, two segments {both:.2e}")
+    assert both < 4e-3 and both < one                        # P is bf16: the second segment removes the output rounding only
+
+
+@pytest.mark.parametrize("fa", [1, 2, 3])
 @pytest.mark.parametrize("N", [445, 1000])
 def test_attention_tmem_resident_kernel_with_key_mask(dev, lib, N, fa):
     """key_padding_mask through attn_fa_kernel against the two-pass multi-block kernel: ragged tails, scattered padded keys,
