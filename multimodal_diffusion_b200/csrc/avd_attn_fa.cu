@@ -630,13 +630,14 @@ constexpr int F2_NCH = F2_BKV / 32;
 constexpr unsigned F2_STAGGER_NS = AVD_F2_STAGGER_NS;
 constexpr int F2_STAGES = 4;
 constexpr int F2_KV_BYTES = F2_BKV * ATT_HD * 2;            // 12 KB
-constexpr int F2_THREADS = 9 * 32;
-constexpr int F2_SMEM = 2 * ATT_Q_BYTES + F2_STAGES * 2 * F2_KV_BYTES + 512;
+constexpr int F2_XCHG_BYTES = (8 + 4) * 128 * 4;            // SW = 8: row max [2 bufs][2 tiles][2 halves][128], row sum [2][2][128]
+constexpr int F2_SMEM = 2 * ATT_Q_BYTES + F2_STAGES * 2 * F2_KV_BYTES + F2_XCHG_BYTES + 512;
 enum { GB_Q = 0, GB_KF = 1 /*+stage*/, GB_VF = 5 /*+stage*/, GB_KVE = 9 /*+stage*/, GB_S = 13 /*+2 tile + buffer*/,
        GB_P = 17 /*+tile*/, GB_O = 19 /*+tile*/, GB_COUNT = 21 };
 
-template <bool F16, bool MASKED>
-__global__ void __launch_bounds__(F2_THREADS, 1) attn_fa2_kernel(const __grid_constant__ CUtensorMap tmQ,
+template <bool F16, bool MASKED, int SW>   // SW = 4: one softmax thread per query row; SW = 8 (96-key blocks only): two warps per
+                                           // row group, each with 48 of the block's scores in registers
+__global__ void __launch_bounds__((2 * SW + 1) * 32, 1) attn_fa2_kernel(const __grid_constant__ CUtensorMap tmQ,
                                                                  const __grid_constant__ CUtensorMap tmKV,
                                                                  const AttnParams p) {
   extern __shared__ __align__(1024) uint8_t fa_smem[];
@@ -644,8 +645,11 @@ __global__ void __launch_bounds__(F2_THREADS, 1) attn_fa2_kernel(const __grid_co
   if ((smem_u32(smem) & 1023u) != 0) __trap();
   uint8_t* sQ = smem;                                       // 2 query tiles (later: output staging)
   uint8_t* sKV = sQ + 2 * ATT_Q_BYTES;                      // [stage]{K, V}
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sKV + F2_STAGES * 2 * F2_KV_BYTES);
+  float* xmax = reinterpret_cast<float*>(sKV + F2_STAGES * 2 * F2_KV_BYTES);
+  float* xsum = xmax + 8 * 128;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(xmax) + F2_XCHG_BYTES);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + GB_COUNT);
+  static_assert(SW == 4 || (SW == 8 && F2_BKV == 96), "the two-warps-per-row-group form splits a 96-key block 48 / 48");
 
   const int tid = threadIdx.x;
   const int warp = tid >> 5, lane = tid & 31;
@@ -663,7 +667,7 @@ __global__ void __launch_bounds__(F2_THREADS, 1) attn_fa2_kernel(const __grid_co
       uint32_t count = 1;
       if (lane >= GB_P && lane < GB_O) {                    // arrivals: the warps of the tile that own valid query rows
         const int rows = min(ATT_BQ, p.N - q_first - (lane - GB_P) * ATT_BQ);
-        count = rows > 0 ? 32 * ((rows + 31) >> 5) : 1;
+        count = rows > 0 ? (SW * 8) * ((rows + 31) >> 5) : 1;
       }
       mbar_init(&bars[lane], count);
     }
@@ -679,7 +683,7 @@ __global__ void __launch_bounds__(F2_THREADS, 1) attn_fa2_kernel(const __grid_co
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
   pdl_launch_dependents();
 
-  if (warp == 8) {
+  if (warp == 2 * SW) {
     // ------------------------------------------------------------------ control warp (converged; elected lane issues)
     auto load_kv = [&](int b) {
       if (lane == 0) {
@@ -731,13 +735,16 @@ __global__ void __launch_bounds__(F2_THREADS, 1) attn_fa2_kernel(const __grid_co
         tc_fence_after();
         ATT_WMARK(t * 3);
         const uint32_t d_o = tmem_base + t * 256 + 192, a_p = tmem_base + t * 256 + (j & 1) * F2_BKV;
+        // O_t += P_t(j) V_j: A from TMEM, 8 columns per 16 keys.  SW = 8: the two warps of a row group each wrote the P of
+        // their 48 keys over the start of their own 48 score columns -- k-steps 3.. read from column 48 on.
+        auto p_col = [&](int ks) { return (SW == 8 && ks >= 3) ? ks * 8 + 24 : ks * 8; };
         if (kvn == F2_BKV) {
 #pragma unroll
-          for (int ks = 0; ks < F2_BKV / 16; ++ks)          // O_t += P_t(j) V_j: A from TMEM, 8 columns per 16 keys
-            umma_bf16_ts_elect(d_o, a_p + ks * 8, v_lo + ks * 128, hi, idesc_o, (j > 0 || ks > 0) ? 1u : 0u);
+          for (int ks = 0; ks < F2_BKV / 16; ++ks)
+            umma_bf16_ts_elect(d_o, a_p + p_col(ks), v_lo + ks * 128, hi, idesc_o, (j > 0 || ks > 0) ? 1u : 0u);
         } else {
           for (int ks = 0; ks < (kvn >> 4); ++ks)
-            umma_bf16_ts_elect(d_o, a_p + ks * 8, v_lo + ks * 128, hi, idesc_o, (j > 0 || ks > 0) ? 1u : 0u);
+            umma_bf16_ts_elect(d_o, a_p + p_col(ks), v_lo + ks * 128, hi, idesc_o, (j > 0 || ks > 0) ? 1u : 0u);
         }
         umma_commit_elect(&bars[GB_O + t]);                 // O_t is current through block j (phase j)
         if (t == n_tiles - 1) umma_commit_elect(&bars[GB_KVE + s]);   // K_j / V_j have been read by every tile
@@ -757,7 +764,7 @@ __global__ void __launch_bounds__(F2_THREADS, 1) attn_fa2_kernel(const __grid_co
         load_kv(b);
       }
     }
-  } else if ((warp >> 2) < n_tiles && q_first + (warp >> 2) * ATT_BQ + (warp & 3) * 32 < p.N) {
+  } else if (SW == 4 && (warp >> 2) < n_tiles && q_first + (warp >> 2) * ATT_BQ + (warp & 3) * 32 < p.N) {
     // ------------------------------------------------------------------ softmax + output of query tile t, one thread per row
     const int t = warp >> 2, quad = warp & 3;
     const uint32_t tmem_T = tmem_base + t * 256 + ((uint32_t)(quad * 32) << 16);
@@ -934,6 +941,179 @@ __global__ void __launch_bounds__(F2_THREADS, 1) attn_fa2_kernel(const __grid_co
       if (sg + 1 < p.out_nseg) __syncwarp();
     }
   }
+  else if (SW == 8 && warp < 16 && (warp >> 3) < n_tiles && q_first + (warp >> 3) * ATT_BQ + (warp & 3) * 32 < p.N) {
+    // ------------------------------------------------------------------ softmax + output of query tile t, two warps per row group
+    // Each warp keeps 48 of the block's 96 scores of its rows in registers (exact block max after one exchange with its
+    // partner, nothing speculative) and writes their P over the first 24 of its own 48 score columns.
+    const int t = warp >> 3, sp = (warp >> 2) & 1, quad = warp & 3;
+    const int r = quad * 32 + lane;
+    const uint32_t tmem_T = tmem_base + t * 256 + ((uint32_t)(quad * 32) << 16);
+    const uint32_t tmem_O = tmem_T + 192 + sp * 32;
+    const uint32_t pair_bar = 1 + t * 4 + quad;
+    const float sc = p.scale_log2e;
+    float m_run = -INFINITY, l_run = 0.0f;
+    if (F2_STAGGER_NS > 0 && t == 1) __nanosleep(F2_STAGGER_NS);   // the second tile half a block behind the first
+    for (int j = 0; j < nkv; ++j) {
+      const int kv_valid = min(F2_BKV, p.N - j * F2_BKV);
+      const uint32_t tmem_S = tmem_T + (j & 1) * F2_BKV + sp * 48;
+      float* xm = xmax + (((j & 1) * 2 + t) * 2) * 128;
+      ATT_WMARK(0);
+      mbar_wait(&bars[GB_S + t * 2 + (j & 1)], (j >> 1) & 1);
+      tc_fence_after();
+      ATT_WMARK(1);
+      float l0 = 0.0f, l1 = 0.0f;
+      bool o_seen = false;
+      auto block = [&](auto ragged_tag) {
+        constexpr bool RAGGED = decltype(ragged_tag)::value;
+        uint32_t xa[32], xb[16];
+        tmem_ld_32x32(tmem_S, xa);
+        tmem_ld_32x16(tmem_S + 32, xb);
+        tmem_ld_wait();
+        ATT_WMARK(2);
+        if (RAGGED) {                                       // padded / out-of-sequence keys: score -inf, probability 0
+          const int lim = kv_valid - sp * 48;               // my key k (0..47) is inside the sequence iff k < lim
+          uint64_t vb = lim >= 48 ? 0xFFFFFFFFFFFFull : (lim > 0 ? ((1ull << lim) - 1ull) : 0ull);
+          if (MASKED) {
+            const uint32_t* km = p.kmask + (size_t)blockIdx.z * p.kmask_words;
+            const int w0 = j * 3;
+            const uint32_t m0 = w0 < p.kmask_words ? km[w0] : 0u, m1 = w0 + 1 < p.kmask_words ? km[w0 + 1] : 0u,
+                           m2 = w0 + 2 < p.kmask_words ? km[w0 + 2] : 0u;
+            const uint64_t pad = sp == 0 ? ((uint64_t)m0 | ((uint64_t)(m1 & 0xffffu) << 32))
+                                         : ((uint64_t)(m1 >> 16) | ((uint64_t)m2 << 16));
+            vb &= ~pad;
+          }
+#pragma unroll
+          for (int c = 0; c < 32; ++c)
+            if (!((vb >> c) & 1ull)) xa[c] = 0xff800000u;
+#pragma unroll
+          for (int c = 0; c < 16; ++c)
+            if (!((vb >> (32 + c)) & 1ull)) xb[c] = 0xff800000u;
+        }
+        float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+        for (int c = 0; c < 32; ++c) mx[c & 3] = fmaxf(mx[c & 3], __uint_as_float(xa[c]));
+#pragma unroll
+        for (int c = 0; c < 16; ++c) mx[c & 3] = fmaxf(mx[c & 3], __uint_as_float(xb[c]));
+        const float m_part = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
+        xm[sp * 128 + r] = m_part;
+        named_bar_sync(pair_bar, 64);
+        const float m_row = fmaxf(m_part, xm[(sp ^ 1) * 128 + r]);
+        const bool need = m_row != -INFINITY && (m_run == -INFINITY || (m_row - m_run) * sc > FA_RESCALE_LOG2);
+        if (__any_sync(0xffffffffu, need)) {
+          float alpha = 1.0f;
+          if (need) {
+            alpha = ex2_approx((m_run - m_row) * sc);       // m_run = -inf on the first live block -> 0
+            m_run = m_row;
+            l_run *= alpha;
+          }
+          if (j > 0) {
+            mbar_wait(&bars[GB_O + t], (j - 1) & 1);        // P V_t(j-1) complete: O_t is current
+            tc_fence_after();
+            o_seen = true;
+            uint32_t o[32];
+            tmem_ld_32x32(tmem_O, o);
+            tmem_ld_wait();
+#pragma unroll
+            for (int c = 0; c < 32; ++c) o[c] = __float_as_uint(__uint_as_float(o[c]) * alpha);
+            tmem_st_32x32(tmem_O, o);
+          }
+        }
+        ATT_WMARK(3);
+        const float neg_m_sc = m_run == -INFINITY ? 0.0f : -m_run * sc;
+        auto expo = [&](uint32_t& x) {
+          const float a = fmaf(__uint_as_float(x), sc, neg_m_sc);
+          float e;
+          asm volatile("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(a));
+          x = __float_as_uint(e);
+        };
+        auto post = [&](uint32_t e0, uint32_t e1) -> uint32_t {
+          l0 += __uint_as_float(e0);
+          l1 += __uint_as_float(e1);
+          return F16 ? pack_f16x2(__uint_as_float(e0), __uint_as_float(e1))
+                     : pack_bf16x2(__uint_as_float(e0), __uint_as_float(e1));
+        };
+        uint32_t w[16], w2[8];
+#pragma unroll
+        for (int c = 0; c < 32; ++c) expo(xa[c]);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {                       // the last 16 exponentials between the sums / packs of the first 32
+          expo(xb[2 * i]);
+          expo(xb[2 * i + 1]);
+          w[2 * i] = post(xa[4 * i], xa[4 * i + 1]);
+          w[2 * i + 1] = post(xa[4 * i + 2], xa[4 * i + 3]);
+        }
+        tmem_st_32x16(tmem_S, w);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) w2[i] = post(xb[2 * i], xb[2 * i + 1]);
+        tmem_st_32x8(tmem_S + 16, w2);
+      };
+      if (MASKED || kv_valid < F2_BKV) block(std::true_type{});
+      else block(std::false_type{});
+      l_run += l0 + l1;
+      ATT_WMARK(4);
+      if (j > 0 && !o_seen) {                               // the P barrier is never two phases ahead of the control warp
+        mbar_wait(&bars[GB_O + t], (j - 1) & 1);
+        tc_fence_after();
+      }
+      tmem_st_wait();
+      tc_fence_before();
+      mbar_arrive(&bars[GB_P + t]);
+      ATT_WMARK(5);
+    }
+
+    // ---- O_t complete; total row sum = the two halves' partial sums; normalise this thread's 32 output columns
+    mbar_wait(&bars[GB_O + t], (nkv - 1) & 1);
+    tc_fence_after();
+    float rem[32];
+    {
+      uint32_t o[32];
+      tmem_ld_32x32(tmem_O, o);
+      tmem_ld_wait();
+      float* xs = xsum + (t * 2) * 128;
+      xs[sp * 128 + r] = l_run;
+      named_bar_sync(pair_bar, 64);
+      const float inv_l = 1.0f / (l_run + xs[(sp ^ 1) * 128 + r]);
+#pragma unroll
+      for (int c = 0; c < 32; ++c) rem[c] = __uint_as_float(o[c]) * inv_l;
+    }
+    const int64_t seg_stride = p.M * (int64_t)p.d;
+    uint8_t* stage = sQ + t * ATT_Q_BYTES + quad * 32 * 128;
+    const int q_tile0 = q_first + t * ATT_BQ + quad * 32;
+    for (int sg = 0; sg < p.out_nseg; ++sg) {
+#pragma unroll
+      for (int v4 = 0; v4 < 4; ++v4) {
+        uint32_t w[4];
+        if (p.out_nseg == 1) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            w[k] = F16 ? pack_f16x2(rem[v4 * 8 + k * 2], rem[v4 * 8 + k * 2 + 1])
+                       : pack_bf16x2(rem[v4 * 8 + k * 2], rem[v4 * 8 + k * 2 + 1]);
+        } else {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const int c = v4 * 8 + k * 2;
+            const __nv_bfloat16 h0 = __float2bfloat16_rn(rem[c]);
+            const __nv_bfloat16 h1 = __float2bfloat16_rn(rem[c + 1]);
+            rem[c] -= __bfloat162float(h0);
+            rem[c + 1] -= __bfloat162float(h1);
+            w[k] = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
+          }
+        }
+        *reinterpret_cast<uint4*>(stage + lane * 128 + (((sp * 4 + v4) ^ (lane & 7)) << 4)) =
+            make_uint4(w[0], w[1], w[2], w[3]);
+      }
+      named_bar_sync(pair_bar, 64);
+      const int rr = lane >> 3, cc = lane & 7;
+      __nv_bfloat16* gp = p.out + sg * seg_stride + ((int64_t)row_base + q_tile0) * p.d + head * ATT_HD + cc * 8;
+#pragma unroll
+      for (int it = 0; it < 4; ++it) {
+        const int rw = sp * 16 + it * 4 + rr;
+        const uint4 x4 = *reinterpret_cast<const uint4*>(stage + rw * 128 + ((cc ^ (rw & 7)) << 4));
+        if (q_tile0 + rw < p.N) *reinterpret_cast<uint4*>(gp + (int64_t)rw * p.d) = x4;
+      }
+      if (sg + 1 < p.out_nseg) named_bar_sync(pair_bar, 64);
+    }
+  }
 
   tc_fence_before();
   __syncthreads();
@@ -949,18 +1129,27 @@ int launch_attention_fa(const void* qkv16, const AttnParams& p, int n_seq, bool 
   CUtensorMap tm;
   AVD_TRY(get_tensor_map_3d(qkv16, 2, (uint64_t)3 * d, (uint64_t)p.M, 1, (uint64_t)3 * d * 2, (uint64_t)p.M * 3 * d * 2,
                             ATT_HD, ATT_BQ, &tm));
-  if (options().attn_fa == 3) {                             // S double-buffered, 96-key blocks (attn_fa2_kernel)
+  if (options().attn_fa >= 3) {                             // S double-buffered, 96-key blocks (attn_fa2_kernel)
     CUtensorMap tmkv;
     AVD_TRY(get_tensor_map_3d(qkv16, 2, (uint64_t)3 * d, (uint64_t)p.M, 1, (uint64_t)3 * d * 2, (uint64_t)p.M * 3 * d * 2,
                               ATT_HD, F2_BKV, &tmkv));
     using Fn2 = void (*)(const CUtensorMap, const CUtensorMap, const AttnParams);
-    static const Fn2 k2[2][2] = {{attn_fa2_kernel<false, false>, attn_fa2_kernel<false, true>},
-                                 {attn_fa2_kernel<true, false>, attn_fa2_kernel<true, true>}};
-    const Fn2 f2 = k2[f16 ? 1 : 0][p.kmask != nullptr ? 1 : 0];
+    static const Fn2 k2[2][2][2] = {
+        {{attn_fa2_kernel<false, false, 4>, attn_fa2_kernel<false, true, 4>},
+         {attn_fa2_kernel<true, false, 4>, attn_fa2_kernel<true, true, 4>}},
+#if AVD_F2_BKV == 96
+        {{attn_fa2_kernel<false, false, 8>, attn_fa2_kernel<false, true, 8>},
+         {attn_fa2_kernel<true, false, 8>, attn_fa2_kernel<true, true, 8>}}};
+#else
+        {{attn_fa2_kernel<false, false, 4>, attn_fa2_kernel<false, true, 4>},
+         {attn_fa2_kernel<true, false, 4>, attn_fa2_kernel<true, true, 4>}}};
+#endif
+    const bool two = options().attn_fa == 4 && F2_BKV == 96;   // two softmax warps per row group
+    const Fn2 f2 = k2[two ? 1 : 0][f16 ? 1 : 0][p.kmask != nullptr ? 1 : 0];
     AVD_TRY(ensure_dyn_smem(reinterpret_cast<const void*>(f2), F2_SMEM));
     cudaLaunchConfig_t c2{};
     c2.gridDim = dim3((p.N + 2 * ATT_BQ - 1) / (2 * ATT_BQ), p.n_heads, n_seq);
-    c2.blockDim = dim3(F2_THREADS);
+    c2.blockDim = dim3(two ? 17 * 32 : 9 * 32);
     c2.dynamicSmemBytes = F2_SMEM;
     c2.stream = s;
     cudaLaunchAttribute a2[1];

@@ -164,8 +164,9 @@ struct Options {
   int attn_small;      // AVD_ATTN_SMALL     1 (default) = two-CTAs-per-SM kernel (attn_small_kernel) for N <= 136 when there are more
                        //                    (sequence, head) pairs than SMs; 2 = always when N <= 136; 0 = never
   int attn_fa;         // AVD_ATTN_FA        multi-block attention (N > 192) with P / O in tensor memory (avd_attn_fa.cu): 1 (default)
-                       //                    two softmax warps per row group, 2 one thread per row, 3 S double-buffered (96-key
-                       //                    blocks; both measured slower), 0 = attn_tc_kernel's two-tile path
+                       //                    two softmax warps per row group, 2 one thread per row, 3 / 4 S double-buffered (96-key
+                       //                    blocks; thread per row / two warps per row group) -- all measured slower than 1;
+                       //                    0 = attn_tc_kernel's two-tile path
   int attn_pipe;       // AVD_ATTN_PIPE      1 (default) = pipelined multi-block attention kernel (attn_pipe_kernel) for N > 192
   int attn_one;        // AVD_ATTN_ONE       0 = multi-block attention kernel even for N <= 192
   int chains;          // AVD_CHAINS         independent sequence groups of a sampler step run on forked streams (1 = off)

@@ -234,7 +234,7 @@ def test_attention_multiblock_rising_max(dev, lib, N, ramp, f16):
                                               (2, 1000, False, 0.0), (1, 257, True, 0.0), (2, 384, False, 0.0),
                                               (1, 640, True, 0.0), (2, 1000, True, 10.0), (2, 1000, False, 60.0),
                                               (1, 2048, True, 25.0), (1, 16384, True, 0.0)])
-@pytest.mark.parametrize("fa", [1, 2, 3])
+@pytest.mark.parametrize("fa", [1, 2, 3, 4])
 def test_attention_tmem_resident_kernel(dev, lib, n_seq, N, f16, ramp, fa):
     """attn_fa_kernel (option attn_fa; N > 192): P written to tensor memory and used as the A operand of P V, O accumulated
     in tensor memory and rescaled in place only when a row's max rises by more than 2^8, 128-key blocks through a 4-stage
@@ -245,7 +245,7 @@ def test_attention_tmem_resident_kernel(dev, lib, n_seq, N, f16, ramp, fa):
         _attn_check(dev, lib, n_seq, N, f16, 1.5e-3 if f16 else 8e-3, key_ramp=ramp)
 
 
-@pytest.mark.parametrize("fa", [1, 2, 3])
+@pytest.mark.parametrize("fa", [1, 2, 3, 4])
 def test_attention_tmem_resident_kernel_split_output(dev, lib, fa):
     """bf16x3 mode: bf16 q / k / v in, the attention output written as TWO bf16 segments (value + residual); the multi-block
     kernels' multi-segment epilogue against fp64, tighter than one bf16 segment allows."""
@@ -265,7 +265,7 @@ def test_attention_tmem_resident_kernel_split_output(dev, lib, fa):
     assert both < 4e-3 and both < one                        # P is bf16: the second segment removes the output rounding only
 
 
-@pytest.mark.parametrize("fa", [1, 2, 3])
+@pytest.mark.parametrize("fa", [1, 2, 3, 4])
 @pytest.mark.parametrize("N", [445, 1000])
 def test_attention_tmem_resident_kernel_with_key_mask(dev, lib, N, fa):
     """key_padding_mask through attn_fa_kernel against the two-pass multi-block kernel: ragged tails, scattered padded keys,

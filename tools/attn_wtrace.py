@@ -58,7 +58,7 @@ def main() -> None:
     if _lib.get_option("attn_fa") != 0:
         names = ["top", "S ready", "pass done", "max exchanged", "rescale/repeat", "P arrived"]
         print("warp tile half quad | " + " ".join(f"{n:>14s}" for n in names) + " |  period(3->4) period(4->5)")
-        for w in range(8 if _lib.get_option("attn_fa") >= 2 else 16):
+        for w in range(8 if _lib.get_option("attn_fa") in (2, 3) else 16):
             if int(t[w, B, 0]) == 0:
                 continue
             row = " ".join(f"{int(t[w, B, sl]) - t0:14d}" for sl in range(6))
@@ -69,7 +69,7 @@ def main() -> None:
             if int(t[w, B, 0]) == 0:
                 continue
             print(f"{w:4d}                | " + " ".join(f"{int(t[w, B, sl]) - t0:10d}" for sl in range(6, 12)))
-        cw = 8 if _lib.get_option("attn_fa") >= 2 else 16
+        cw = 8 if _lib.get_option("attn_fa") in (2, 3) else 16
         c = [int(t[cw, B, sl]) - t0 for sl in range(6)]
         print(f"control lane: tile 0: P/V there {c[0]}, S(j+1) issued {c[1]}, PV issued {c[2]} | tile 1: P there {c[3]}, "
               f"S(j+1) issued {c[4]}, PV issued {c[5]} | period {int(t[cw, 2, 0] - t[cw, 1, 0])}")
