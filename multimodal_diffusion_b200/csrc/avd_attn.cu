@@ -83,9 +83,6 @@ __device__ __forceinline__ void thin_row_softmax(const float* srow, uint8_t* sPt
 // barrier slots
 enum { AB_Q = 0, AB_K = 1, AB_V = 2, AB_S = 3 /*+t*/, AB_P = 5 /*+t*/, AB_O = 7 /*+t*/, AB_R = 9 /*+t*/, AB_COUNT = 11 };
 
-#ifndef AVD_ATT_STAGGER
-#define AVD_ATT_STAGGER 0
-#endif
 #ifndef AVD_LAZY_MAX
 #define AVD_LAZY_MAX 1   // multi-block softmax: one pass against the carried max (0: always max pass + exp pass; 16 x 2048 keys 348 -> 318 us)
 #endif
@@ -172,8 +169,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
     const float sc = p.scale_log2e;
     const bool mark = (tid == 0);
     const bool leader = (warp & 7) == 0 && lane == 0;      // issues this tile's MMAs
-    // requests K_{j+1} / V_{j+1}: the leader of the tile whose MMAs retire last (staggered tiles: the second one)
-    const bool loader = leader && t == ((!ONE_BLOCK && AVD_ATT_STAGGER != 0) ? n_tiles - 1 : 0);
+    const bool loader = leader && t == 0;                  // requests K_{j+1} / V_{j+1}
     const uint32_t hi = smem_desc_hi_sw128(1024);
     const uint32_t q_lo = smem_desc_lo_sw128(smem_u32(sQ + t * ATT_Q_BYTES), 16);
     const uint32_t k_lo = smem_desc_lo_sw128(smem_u32(sK), 16);
@@ -222,13 +218,6 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
         tma_load_3d(sK, &tmKV, &bars[AB_K], colK, row_base + (j + 1) * ATT_BKV, 0);
       }
       if (mark && j == 0) att_mark(trace, 5);
-      if constexpr (!ONE_BLOCK && AVD_ATT_STAGGER != 0) {
-        // the second tile's softmax of block j starts when the first tile's is over: while one tile is in its exponentials
-        // (MUFU-bound) the tensor pipe runs the other's P V and next S, instead of both tiles idling through both tiles'
-        // MMAs.  Tile 0 cannot be two P phases ahead of a tile-1 warp here: K_{j+1} is requested by tile 1's leader in ITS
-        // block j, a whole TMA + MMA + softmax pass before tile 0 completes P_{j+1}.
-        if (t == 1 && (AVD_ATT_STAGGER == 2 || j == 0)) mbar_wait(&bars[AB_P + 0], ph);
-      }
       float l_blk = 0.0f, alpha;
       if constexpr (ONE_BLOCK) {
         // ---- single pass: up to 3 chunks (96 scores) of this row live in registers

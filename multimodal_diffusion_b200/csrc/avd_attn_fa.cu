@@ -12,10 +12,13 @@
 //   * O stays in TMEM across the key blocks (the MMA accumulates).  A row's reference max only moves when the block's max
 //     exceeds it by more than 2^8; then -- rarely after the first blocks -- the two warps that own the row rescale their
 //     32 + 32 O columns in place (tcgen05.ld / st).  No per-block O read-out, no wait for P V in the softmax loop;
-//   * 128-key blocks: a thread's 64 scores live in registers, so the block max is known before any exponential (one
-//     tcgen05.ld pass, no speculative pass);
-//   * one control lane (warp 16) issues every TMA load (4-stage K / V ring, two blocks ahead) and every MMA, in the fixed
-//     order  P V_0(j), S_0(j+1), P V_1(j), S_1(j+1): while one tile's softmax runs, the tensor pipe works for the other.
+//   * 128-key blocks, ONE pass over S per block: the exponentials are taken against the row's carried reference max in
+//     the same pass that finds the block max (no pair exchange between the tcgen05.ld and the MUFU work); the pass is
+//     repeated only when the reference has to move;
+//   * one control WARP (warp 16, converged; an elected lane issues -- umma_*_elect) issues every TMA load (4-stage K / V
+//     ring, two blocks ahead) and every MMA, in the fixed order  S_0(j+1), P V_0(j), S_1(j+1), P V_1(j): S(j+1) goes as soon
+//     as S(j) has been read (its own barrier), P V(j) once P(j) is stored; while one tile's softmax runs, the tensor pipe
+//     works for the other.
 //
 // TMEM per query tile t (256 columns): S [0, 128) fp32 | P [128, 192) 16-bit pairs | O [192, 256) fp32.
 // One CTA = one (sequence, head, PAIR of 128-query tiles); warps 0..7 softmax of tile 0, 8..15 of tile 1 (warp w: TMEM lanes
@@ -33,18 +36,6 @@ constexpr int FA_THREADS = 17 * 32;                          // SW = 8: two soft
 constexpr int FA_THREADS_ROW = 9 * 32;                       // SW = 4: one softmax thread per query row
 constexpr int FA_XCHG_BYTES = (8 + 4) * 128 * 4;            // row max [2 bufs][2 tiles][2 halves][128], row sum [2][2][128]
 constexpr int FA_SMEM = 2 * ATT_Q_BYTES + FA_STAGES * 2 * FA_KV_BYTES + FA_XCHG_BYTES + 256;
-#ifndef AVD_FA_PINGPONG
-#define AVD_FA_PINGPONG 0
-#endif
-constexpr bool FA_PINGPONG = AVD_FA_PINGPONG != 0;
-#ifndef AVD_FA_INTERLEAVE
-#define AVD_FA_INTERLEAVE 0
-#endif
-constexpr bool FA_INTERLEAVE = AVD_FA_INTERLEAVE != 0;
-#ifndef AVD_FA_POLY
-#define AVD_FA_POLY 0
-#endif
-constexpr int FA_POLY = AVD_FA_POLY;
 // A row's reference max moves when the block max is 2^FA_RESCALE_LOG2 above it; until then P = exp2(s - ref) may reach
 // 2^8 (fp16 keeps its full mantissa there; the row sum and O are fp32).  2^12 was measured too: no difference (235 vs 232 us),
 // a repeated pass is rare enough at 2^8.
@@ -422,57 +413,20 @@ __global__ void __launch_bounds__((2 * SW + 1) * 32, 1) attn_fa_kernel(const __g
                 if (!((vb >> c) & 1u)) x[c] = 0xff800000u;
             }
             float e[32];
-            if (!EXP || !FA_INTERLEAVE) {
-              if (EXP) {
-                if (FA_POLY == 0) {
-                  ex2_chunk(x, sc, neg_m_sc, e);
-                } else {                                    // every FA_POLY-th exponential on the FMA pipe (ex2_poly)
-#pragma unroll
-                  for (int c = 0; c < 32; ++c) {
-                    const float a = fmaf(__uint_as_float(x[c]), sc, neg_m_sc);
-                    if (c % FA_POLY == FA_POLY - 1) e[c] = ex2_poly(a);
-                    else asm volatile("ex2.approx.ftz.f32 %0, %1;" : "=f"(e[c]) : "f"(a));
-                  }
-                }
-                ATT_WMARK_DEP(7 + 3 * i, e[31]);
-              }
-#pragma unroll
-              for (int c = 0; c < 32; ++c) mx[c & 3] = fmaxf(mx[c & 3], __uint_as_float(x[c]));
+            if (EXP) {
+              ex2_chunk(x, sc, neg_m_sc, e);
+              ATT_WMARK_DEP(7 + 3 * i, e[31]);
             }
+#pragma unroll
+            for (int c = 0; c < 32; ++c) mx[c & 3] = fmaxf(mx[c & 3], __uint_as_float(x[c]));
             if (EXP) {
               float l0 = 0.0f, l1 = 0.0f;
               uint32_t w[16];
-              if (FA_INTERLEAVE) {
-                // one instruction stream with the MUFU work spread through it: exponential c, the max of score c, and the
-                // sum / pack of exponential c - 8 (whose MUFU result has landed) -- the warp's ALU work runs under its own
-                // MUFU occupancy instead of after it
-                constexpr int D = 8;
 #pragma unroll
-                for (int c = 0; c < 32 + D; ++c) {
-                  if (c < 32) {
-                    const float a = fmaf(__uint_as_float(x[c]), sc, neg_m_sc);
-                    asm volatile("ex2.approx.ftz.f32 %0, %1;" : "=f"(e[c]) : "f"(a));
-                    asm volatile("max.f32 %0, %0, %1;" : "+f"(mx[c & 3]) : "f"(__uint_as_float(x[c])));
-                  }
-                  if (c >= D) {
-                    const int k = c - D;
-                    if (k & 1) {
-                      asm volatile("add.f32 %0, %0, %1;" : "+f"(l1) : "f"(e[k]));
-                      if (F16) asm volatile("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(w[k >> 1]) : "f"(e[k]), "f"(e[k - 1]));
-                      else asm volatile("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(w[k >> 1]) : "f"(e[k]), "f"(e[k - 1]));
-                    } else {
-                      asm volatile("add.f32 %0, %0, %1;" : "+f"(l0) : "f"(e[k]));
-                    }
-                  }
-                }
-                ATT_WMARK_DEP(7 + 3 * i, l1);
-              } else {
-#pragma unroll
-                for (int c = 0; c < 32; c += 2) {
-                  l0 += e[c];
-                  l1 += e[c + 1];
-                  w[c >> 1] = F16 ? pack_f16x2(e[c], e[c + 1]) : pack_bf16x2(e[c], e[c + 1]);
-                }
+              for (int c = 0; c < 32; c += 2) {
+                l0 += e[c];
+                l1 += e[c + 1];
+                w[c >> 1] = F16 ? pack_f16x2(e[c], e[c + 1]) : pack_bf16x2(e[c], e[c + 1]);
               }
               l_blk += l0 + l1;
               pv_done();
@@ -487,13 +441,6 @@ __global__ void __launch_bounds__((2 * SW + 1) * 32, 1) attn_fa_kernel(const __g
       mbar_wait(&bars[FB_S + t], ph);
       tc_fence_after();
       ATT_WMARK(1);
-      if (FA_PINGPONG && n_tiles == 2) {
-        // The two tiles' softmax passes ALTERNATE: tile 1 starts block j when tile 0 has staged P(j), tile 0 starts block
-        // j + 1 when tile 1 has staged P(j).  Free-running, both tiles sit in their MUFU-bound passes at the same time and
-        // then both wait for their MMAs; alternating, one tile's P V / S MMAs run under the other's exponentials.
-        if (t == 1) mbar_wait(&bars[FB_P + 0], ph);
-        else if (j > 0) mbar_wait(&bars[FB_P + 1], ph ^ 1);
-      }
       // Speculate that the reference max stays: exponentials against the carried m_run in the same pass that finds the
       // block max (no pair exchange between the TMEM load and the MUFU work).  A warp with a row that has no reference yet
       // (first block, or only padded keys so far) finds the max first.  Both warps of a pair hold the same rows and the same

@@ -20,6 +20,6 @@ timeout 200 python tools/stepbench.py 8 video --cfg10 --kinds >> $o/${tag}_stepb
 timeout 200 python tools/kbench.py --M 32768 >> $o/${tag}_stepbench.txt 2>&1
 timeout 200 python tools/kbench.py --M 17024 >> $o/${tag}_stepbench.txt 2>&1
 timeout 200 python tools/kbench.py --M 7120 >> $o/${tag}_stepbench.txt 2>&1
-for v in 0 2 3; do echo "== AVD_ATTN_FA=$v" >> $o/${tag}_stepbench.txt; AVD_ATTN_FA=$v timeout 200 python tools/kbench.py --M 32768 2>&1 | grep "^attn" >> $o/${tag}_stepbench.txt; done
+for v in 0 2 3 4; do echo "== AVD_ATTN_FA=$v" >> $o/${tag}_stepbench.txt; AVD_ATTN_FA=$v timeout 200 python tools/kbench.py --M 32768 2>&1 | grep "^attn" >> $o/${tag}_stepbench.txt; done
 timeout 900 python tools/sweep.py --precision f16 --out $o/${tag}_sweep_mmdt_forward.json > $o/sweep.log 2>&1; tail -3 $o/sweep.log
 timeout 300 python tools/ebench.py --out $o/${tag}_elementwise_hbm.json > $o/ebench.log 2>&1; tail -3 $o/ebench.log
