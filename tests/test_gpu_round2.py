@@ -197,10 +197,15 @@ def _attn_check(dev, lib, n_seq, N, f16, tol, key_ramp=0.0):
         v5[:, :, 0, :, 0] = 4.0
         v5[:, :, 1, :, 0] = torch.linspace(-key_ramp, key_ramp, N).view(1, N, 1)
     qkv = qkv.to(dt).to(dev)
-    out = torch.zeros(1, n_seq * N, H * hd, device=dev, dtype=dt)
+    # guard bands of 32 rows either side of the output (compute-sanitizer is closed on the pool): a store past the last
+    # query row of a ragged tile, or before the first, would change them
+    G = 32
+    buf = torch.full((n_seq * N + 2 * G, H * hd), 7.0, device=dev, dtype=dt)
+    out = buf[G:G + n_seq * N].unsqueeze(0)
     _lib.check(lib.avd_attention(qkv.data_ptr(), 0, out.data_ptr(), _lib.AVD_PREC_F16 if f16 else _lib.AVD_PREC_BF16,
                                  n_seq, N, H, hd, _lib.stream_ptr()))
     torch.cuda.synchronize()
+    assert bool((buf[:G] == 7.0).all()) and bool((buf[G + n_seq * N:] == 7.0).all()), "attention wrote outside its output"
     # checker: fp32 softmax(q k^T / 8) v with torch on the GPU, one (sequence, head) at a time
     q, k, v = qkv.float().view(n_seq, N, 3, H, hd).permute(2, 0, 3, 1, 4)
     worst = 0.0
