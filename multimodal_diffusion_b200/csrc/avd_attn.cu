@@ -168,7 +168,10 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
     float m_run = -INFINITY, l_run = 0.0f;
     const float sc = p.scale_log2e;
     const bool mark = (tid == 0);
-    const bool leader = (warp & 7) == 0 && lane == 0;      // issues this tile's MMAs
+    const bool leader = (warp & 7) == 0 && lane == 0;      // first lane of the tile's issuing warp
+    // The tile's first warp issues its MMAs CONVERGED: all lanes wait on the barriers, an elected lane issues
+    // (umma_*_elect).  Under a divergent `if (leader)` every tcgen05 instruction sits in an R2UR / vote / branch loop.
+    const bool lead_warp = (warp & 7) == 0;
     const bool loader = leader && t == 0;                  // requests K_{j+1} / V_{j+1}
     const uint32_t hi = smem_desc_hi_sw128(1024);
     const uint32_t q_lo = smem_desc_lo_sw128(smem_u32(sQ + t * ATT_Q_BYTES), 16);
@@ -195,7 +198,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
       float* xm = xmax + ((ph * 2 + t) * 2) * 128;
       const int kv_n = (kv_valid + 15) & ~15;
       ATT_WMARK(0);
-      if (leader && j == 0) {                       // S_t = Q_t K_0^T (later blocks: issued right behind P V of the block before)
+      if (lead_warp && j == 0) {                    // S_t = Q_t K_0^T (later blocks: issued right behind P V of the block before)
         mbar_wait(&bars[AB_Q], 0);
         mbar_wait(&bars[AB_K], ph);
         tc_fence_after();
@@ -203,8 +206,8 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
         const uint32_t idesc_s = make_idesc_bf16(ATT_BQ, kv_n, 0, 0, F16);
 #pragma unroll
         for (int k = 0; k < ATT_HD / 16; ++k)
-          umma_bf16_lh(tmem_base + t * 256, q_lo + 2 * k, k_lo + 2 * k, hi, idesc_s, k > 0 ? 1u : 0u);
-        umma_commit(&bars[AB_S + t]);
+          umma_bf16_lh_elect(tmem_base + t * 256, q_lo + 2 * k, k_lo + 2 * k, hi, idesc_s, k > 0 ? 1u : 0u);
+        umma_commit_elect(&bars[AB_S + t]);
         if (mark) att_mark(trace, 3);
       }
       __syncwarp();
@@ -452,7 +455,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
       mbar_arrive(&bars[AB_P + t]);
       ATT_WMARK(5);
       if (mark && j == 0) att_mark(trace, 7);
-      if (leader) {                                 // O_t,j = P_t V_j
+      if (lead_warp) {                              // O_t,j = P_t V_j
         mbar_wait(&bars[AB_P + t], ph);
         mbar_wait(&bars[AB_V], ph);
         if (j > 0) mbar_wait(&bars[AB_R + t], ph ^ 1);     // O_t,j-1 has been read out of TMEM
@@ -463,9 +466,9 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
         for (int ks = 0; ks < ksteps; ++ks) {
           const uint32_t pa = p_lo + (((ks >> 2) * ATT_Q_BYTES + (ks & 3) * 32) >> 4);
           const uint32_t va = v_lo + ((ks * 16 * 128) >> 4);            // 16 keys = 16 rows of 128 B
-          umma_bf16_lh(tmem_base + t * 256 + ATT_BKV, pa, va, hi, idesc_o, ks > 0 ? 1u : 0u);
+          umma_bf16_lh_elect(tmem_base + t * 256 + ATT_BKV, pa, va, hi, idesc_o, ks > 0 ? 1u : 0u);
         }
-        umma_commit(&bars[AB_O + t]);
+        umma_commit_elect(&bars[AB_O + t]);
         if (mark && j == 0) att_mark(trace, 4);
         ATT_WMARK(10);
         if (!ONE_BLOCK && j + 1 < nkv) {
@@ -479,8 +482,8 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attn_tc_kernel(const __grid_co
           const uint32_t idesc_s = make_idesc_bf16(ATT_BQ, kvn1, 0, 0, F16);
 #pragma unroll
           for (int k = 0; k < ATT_HD / 16; ++k)
-            umma_bf16_lh(tmem_base + t * 256, q_lo + 2 * k, k_lo + 2 * k, hi, idesc_s, k > 0 ? 1u : 0u);
-          umma_commit(&bars[AB_S + t]);
+            umma_bf16_lh_elect(tmem_base + t * 256, q_lo + 2 * k, k_lo + 2 * k, hi, idesc_s, k > 0 ? 1u : 0u);
+          umma_commit_elect(&bars[AB_S + t]);
         }
       }
       __syncwarp();
@@ -985,6 +988,9 @@ __global__ void __launch_bounds__(AS_THREADS, 2) attn_small_kernel(const __grid_
     tma_load_3d(sK, &tmKV, &bars[SB_K], colK, row_base, 0);
     mbar_expect_tx(&bars[SB_V], AS_KV_BYTES);
     tma_load_3d(sV, &tmKV, &bars[SB_V], colV, row_base, 0);
+  }
+  __syncwarp();
+  if (warp == 0) {                                     // the MMAs are issued by the converged warp (elected lane)
     mbar_wait(&bars[SB_Q], 0);
     mbar_wait(&bars[SB_K], 0);
     tc_fence_after();
@@ -993,10 +999,9 @@ __global__ void __launch_bounds__(AS_THREADS, 2) attn_small_kernel(const __grid_
     const uint32_t k_lo = smem_desc_lo_sw128(smem_u32(sK), 16);
 #pragma unroll
     for (int k = 0; k < ATT_HD / 16; ++k)
-      umma_bf16_lh(tmem_base, q_lo + 2 * k, k_lo + 2 * k, hi, idesc_s, k > 0 ? 1u : 0u);
-    umma_commit(&bars[SB_S]);
+      umma_bf16_lh_elect(tmem_base, q_lo + 2 * k, k_lo + 2 * k, hi, idesc_s, k > 0 ? 1u : 0u);
+    umma_commit_elect(&bars[SB_S]);
   }
-  __syncwarp();
 
   // ---- thin rows, part 1 (under the S MMA): s = q . K^T on CUDA cores, softmax in registers, p -> smem
   float thin_inv_l = 0.0f;
@@ -1127,7 +1132,7 @@ __global__ void __launch_bounds__(AS_THREADS, 2) attn_small_kernel(const __grid_
   tc_fence_before();
   __syncwarp();
   if (lane == 0) mbar_arrive(&bars[SB_P]);
-  if (leader) {                                        // O = P V
+  if (warp == 0) {                                     // O = P V
     mbar_wait(&bars[SB_P], 0);
     mbar_wait(&bars[SB_V], 0);
     tc_fence_after();
@@ -1138,9 +1143,9 @@ __global__ void __launch_bounds__(AS_THREADS, 2) attn_small_kernel(const __grid_
     for (int ks = 0; ks < ksteps; ++ks) {
       const uint32_t pa = p_lo + (((ks >> 2) * ATT_Q_BYTES + (ks & 3) * 32) >> 4);
       const uint32_t va = v_lo + ((ks * 16 * 128) >> 4);
-      umma_bf16_lh(tmem_base + ATT_BKV, pa, va, hi, idesc_o, ks > 0 ? 1u : 0u);
+      umma_bf16_lh_elect(tmem_base + ATT_BKV, pa, va, hi, idesc_o, ks > 0 ? 1u : 0u);
     }
-    umma_commit(&bars[SB_O]);
+    umma_commit_elect(&bars[SB_O]);
   }
   __syncwarp();
 
