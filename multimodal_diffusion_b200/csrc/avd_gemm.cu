@@ -179,7 +179,9 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
     }
   } else if (warp < 4) {
     // ------------------------------------------------------------------ MMA issuer of pipeline h
-    if (lane == 0 && rank == 0) {
+    // !PAIR: the whole warp runs the loop converged and an elected lane issues (umma_*_elect) -- under a divergent
+    // `lane == 0` every tcgen05 instruction sits in an R2UR / vote / branch loop.  PAIR: lane 0 of the leader CTA.
+    if ((PAIR ? lane == 0 : true) && rank == 0) {
       const int h = warp - 2;
       const int count = (iters - h + 1) >> 1;
       uint64_t* full = bars + h * STAGES;
@@ -198,18 +200,18 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
 #pragma unroll
         for (int k = 0; k < GEMM_BK / 16; ++k) {   // +32 bytes (2 x 16-byte units) per 16-wide k step
           if (PAIR) umma_2cta_lh(acc, a_lo + 2 * k, b_lo + 2 * k, desc_hi, idesc, (j > 0 || k > 0) ? 1u : 0u);
-          else umma_bf16_lh(acc, a_lo + 2 * k, b_lo + 2 * k, desc_hi, idesc, (j > 0 || k > 0) ? 1u : 0u);
+          else umma_bf16_lh_elect(acc, a_lo + 2 * k, b_lo + 2 * k, desc_hi, idesc, (j > 0 || k > 0) ? 1u : 0u);
         }
         if (j + STAGES < count) {                  // stage reusable (in both CTAs) once these MMAs have read it
-          if (PAIR) umma_commit_2cta(&empty[st]); else umma_commit(&empty[st]);
+          if (PAIR) umma_commit_2cta(&empty[st]); else umma_commit_elect(&empty[st]);
         }
         a_lo += S::STAGE_BYTES >> 4;
         if (++st == STAGES) { st = 0; ph ^= 1; a_lo = a_lo0; }
       }
       if (PAIR) umma_commit_2cta(&acc_bar[h]);     // (the host only pairs CTAs when both pipelines have work)
-      else if (count > 0) umma_commit(&acc_bar[h]);   // accumulator h complete
-      else mbar_arrive(&acc_bar[h]);               // nothing to do for this pipeline (a single k-block)
-      if (h == 0) trace_mark(trace, 3);
+      else if (count > 0) umma_commit_elect(&acc_bar[h]);   // accumulator h complete
+      else if (lane == 0) mbar_arrive(&acc_bar[h]);   // nothing to do for this pipeline (a single k-block)
+      if (h == 0 && lane == 0) trace_mark(trace, 3);
     }
   }
   __syncwarp();   // lanes 1..31 of the role warps sleep here (no polling next to the issuing lane) until lane 0 is done
