@@ -124,7 +124,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
 
   if (warp < 2) {
     // ------------------------------------------------------------------ TMA producer of pipeline h
-    if (lane == 0) {
+    // (!PAIR: the warp runs converged, an elected lane issues the expect_tx / TMA instructions; PAIR: lane 0)
+    if (PAIR ? lane == 0 : true) {
       const int h = warp;
       const int count = (iters - h + 1) >> 1;            // iterations h, h+2, ...
       uint64_t* full = bars + h * STAGES;
@@ -138,12 +139,12 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
       // PAIR: both CTAs' boxes complete on the leader's barrier, which expects the bytes of both
       const uint32_t full0 = PAIR ? mapa_u32(smem_u32(full), 0) : 0u;
       auto expect = [&](int j) {
-        if (!PAIR) mbar_expect_tx(&full[j], S::STAGE_BYTES);
+        if (!PAIR) mbar_expect_tx_elect(&full[j], S::STAGE_BYTES);
         else if (rank == 0) mbar_expect_tx(&full[j], 2 * S::STAGE_BYTES);
       };
       auto load = [&](void* dst, const CUtensorMap* tm, int j, int c0, int c1, int c2) {
         if (PAIR) tma_load_3d_2sm(dst, tm, full0 + 8u * j, c0, c1, c2);
-        else tma_load_3d(dst, tm, &full[j], c0, c1, c2);
+        else tma_load_3d_elect(dst, tm, &full[j], c0, c1, c2);
       };
       for (int j = 0; j < pre; ++j) {
         expect(j);
@@ -158,10 +159,17 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_tc_kernel(const __grid_c
         while (kb >= kblocks) { kb -= kblocks; ++pi; }
       }
       if (h == 0 && k_resid) {
-        mbar_expect_tx(res_bar, S::F32_TILE);
-        for (int ch = 0; ch < BN / 32; ++ch)
-          for (int q = 0; q < 4; ++q)
-            tma_load_3d(res_tile + (ch * 4 + q) * GEMM_BOX, &tmR, res_bar, n0 + ch * 32, m0 + q * 32, 0);
+        if (PAIR) {
+          mbar_expect_tx(res_bar, S::F32_TILE);
+          for (int ch = 0; ch < BN / 32; ++ch)
+            for (int q = 0; q < 4; ++q)
+              tma_load_3d(res_tile + (ch * 4 + q) * GEMM_BOX, &tmR, res_bar, n0 + ch * 32, m0 + q * 32, 0);
+        } else {
+          mbar_expect_tx_elect(res_bar, S::F32_TILE);
+          for (int ch = 0; ch < BN / 32; ++ch)
+            for (int q = 0; q < 4; ++q)
+              tma_load_3d_elect(res_tile + (ch * 4 + q) * GEMM_BOX, &tmR, res_bar, n0 + ch * 32, m0 + q * 32, 0);
+        }
       }
       int st = 0;
       uint32_t ph = 0;                                   // parity of the ring pass being REFILLED
