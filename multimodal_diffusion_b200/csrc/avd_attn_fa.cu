@@ -93,17 +93,14 @@ __global__ void __launch_bounds__((2 * SW + 1) * 32, 1) attn_fa_kernel(const __g
   if (warp == 2 * SW) {
     // ------------------------------------------------------------------ control warp: TMA loads and every MMA
     // The whole warp runs this code converged (all lanes wait on the barriers); one elected lane issues the tcgen05
-    // instructions (umma_*_elect), lane 0 the TMA loads.
+    // instructions and the K / V TMA loads (*_elect); lane 0 only the one-off Q load.
     auto load_kv = [&](int b) {
-      if (lane == 0) {
-        const int s = b & (FA_STAGES - 1);
-        uint8_t* k = sKV + s * 2 * FA_KV_BYTES;
-        mbar_expect_tx(&bars[FB_KF + s], FA_KV_BYTES);
-        tma_load_3d(k, &tmQKV, &bars[FB_KF + s], colK, row_base + b * FA_BKV, 0);
-        mbar_expect_tx(&bars[FB_VF + s], FA_KV_BYTES);
-        tma_load_3d(k + FA_KV_BYTES, &tmQKV, &bars[FB_VF + s], colV, row_base + b * FA_BKV, 0);
-      }
-      __syncwarp();
+      const int s = b & (FA_STAGES - 1);
+      uint8_t* k = sKV + s * 2 * FA_KV_BYTES;
+      mbar_expect_tx_elect(&bars[FB_KF + s], FA_KV_BYTES);
+      tma_load_3d_elect(k, &tmQKV, &bars[FB_KF + s], colK, row_base + b * FA_BKV, 0);
+      mbar_expect_tx_elect(&bars[FB_VF + s], FA_KV_BYTES);
+      tma_load_3d_elect(k + FA_KV_BYTES, &tmQKV, &bars[FB_VF + s], colV, row_base + b * FA_BKV, 0);
     };
     if (lane == 0) {
       pdl_wait();                                           // qkv comes from the previous kernel
@@ -633,15 +630,12 @@ __global__ void __launch_bounds__((2 * SW + 1) * 32, 1) attn_fa2_kernel(const __
   if (warp == 2 * SW) {
     // ------------------------------------------------------------------ control warp (converged; elected lane issues)
     auto load_kv = [&](int b) {
-      if (lane == 0) {
-        const int s = b & (F2_STAGES - 1);
-        uint8_t* k = sKV + s * 2 * F2_KV_BYTES;
-        mbar_expect_tx(&bars[GB_KF + s], F2_KV_BYTES);
-        tma_load_3d(k, &tmKV, &bars[GB_KF + s], colK, row_base + b * F2_BKV, 0);
-        mbar_expect_tx(&bars[GB_VF + s], F2_KV_BYTES);
-        tma_load_3d(k + F2_KV_BYTES, &tmKV, &bars[GB_VF + s], colV, row_base + b * F2_BKV, 0);
-      }
-      __syncwarp();
+      const int s = b & (F2_STAGES - 1);
+      uint8_t* k = sKV + s * 2 * F2_KV_BYTES;
+      mbar_expect_tx_elect(&bars[GB_KF + s], F2_KV_BYTES);
+      tma_load_3d_elect(k, &tmKV, &bars[GB_KF + s], colK, row_base + b * F2_BKV, 0);
+      mbar_expect_tx_elect(&bars[GB_VF + s], F2_KV_BYTES);
+      tma_load_3d_elect(k + F2_KV_BYTES, &tmKV, &bars[GB_VF + s], colV, row_base + b * F2_BKV, 0);
     };
     if (lane == 0) {
       pdl_wait();
