@@ -71,8 +71,8 @@ def main() -> None:
             print(f"{w:4d}                | " + " ".join(f"{int(t[w, B, sl]) - t0:10d}" for sl in range(6, 12)))
         cw = 8 if _lib.get_option("attn_fa") in (2, 3) else 16
         c = [int(t[cw, B, sl]) - t0 for sl in range(6)]
-        print(f"control lane: tile 0: P/V there {c[0]}, S(j+1) issued {c[1]}, PV issued {c[2]} | tile 1: P there {c[3]}, "
-              f"S(j+1) issued {c[4]}, PV issued {c[5]} | period {int(t[cw, 2, 0] - t[cw, 1, 0])}")
+        print(f"control warp: tile 0: S read seen {c[0]}, S(j+1) issued {c[1]}, P V(j) issued {c[2]} | tile 1: S read seen {c[3]}, "
+              f"S(j+1) issued {c[4]}, P V(j) issued {c[5]} | period {int(t[cw, 2, 0] - t[cw, 1, 0])}")
         return
     for w in range(16):
         if int(t[w, B, 0]) == 0:
